@@ -1,0 +1,155 @@
+/*
+ * scaleproto_b200.h — C ABI of libscaleproto_sm100.so
+ *
+ * B200-native (sm_100a) replacement for the prototype head and the push scan of
+ * eceo-epfl/ScaleProtoSeg.  The reference has no native/FFI layer: its "interface" for this path is
+ * the method set of the two PPNetMultiScale classes and three functions of
+ * segmentation/push_multiscale_optimization.py.  Every entry point below names the reference code
+ * it replaces (paths relative to the reference root).  INTEGRATION.md shows the ctypes binding and
+ * the method patches a maintainer would add on the reference side.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every pointer is a DEVICE pointer unless marked "host";
+ *  - the caller owns all memory; the library never allocates or frees device memory;
+ *  - all work is enqueued on `stream` (a cudaStream_t passed as void*); no implicit syncs;
+ *  - return value 0 = OK, otherwise an SpsStatus; text via sps_last_error() (thread local);
+ *  - feature maps are fp32 NCHW exactly as the reference holds them: z[b][s*D + c][h][w];
+ *  - N = B*H*W positions, row n = (b*H + h)*W + w (the order of permute(0,2,3,1).reshape(-1,P),
+ *    segmentation/model/model_multiscale.py:369-370).
+ */
+#ifndef SCALEPROTO_B200_H
+#define SCALEPROTO_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPS_ABI_VERSION 1
+#define SPS_MAX_SCALES 8
+
+typedef enum {
+  SPS_OK = 0,
+  SPS_ERR_BAD_ARG = 1,      /* null pointer / inconsistent shape */
+  SPS_ERR_UNSUPPORTED = 2,  /* shape outside what the kernels cover (message says which) */
+  SPS_ERR_WORKSPACE = 3,    /* workspace too small */
+  SPS_ERR_CUDA = 4          /* launch / runtime failure, message carries cudaGetErrorString */
+} SpsStatus;
+
+/* distance_2_similarity kinds, segmentation/model/model_multiscale.py:324-330 */
+#define SPS_ACT_LOG 0    /* log((d+1)/(d+eps)) */
+#define SPS_ACT_LINEAR 1 /* -d */
+
+/* Arithmetic of the z.p contraction.  fp32 accumulation everywhere. */
+#define SPS_MATH_FP32 0 /* fp32 FFMA on CUDA cores: exact-operand mode used for gradient parity */
+#define SPS_MATH_TF32 1 /* tcgen05 kind::tf32, operands rounded to tf32 (rna); norms from the rounded operands */
+#define SPS_MATH_BF16 2 /* tcgen05 kind::f16 bf16 operands (fast mode) */
+
+/* flags */
+#define SPS_FLAG_DETERMINISTIC 1 /* backward reductions over N in a fixed order (no fp32 atomics) */
+
+/* Shape of one head invocation.  Mirrors the state the reference keeps on the module
+ * (segmentation/model/model_multiscale.py:104-149): prototype_vectors (P,D,1,1), num_scales,
+ * scale_num_prototypes (possibly ragged after prune_prototypes, :400-432), epsilon. */
+typedef struct SpsHeadDesc {
+  int32_t B, H, W;                      /* feature map batch and size */
+  int32_t S, D;                         /* num_scales, channels per scale; C = S*D */
+  int32_t P, K;                         /* prototypes, classes */
+  int32_t scale_lo[SPS_MAX_SCALES + 1]; /* scale s owns prototype rows [scale_lo[s], scale_lo[s+1]) */
+  int32_t act_kind;                     /* SPS_ACT_* */
+  float eps;                            /* 1e-4 in the reference */
+  int32_t math;                         /* SPS_MATH_* */
+  int32_t flags;                        /* SPS_FLAG_* */
+} SpsHeadDesc;
+
+/* Stage-2 grouping head (segmentation/model/model_multiscale_group.py:249-308).
+ * Kc = number of classes that own >= 1 prototype; class k' (0..Kc-1, ascending class id) has
+ * n_k' = class_off[k'+1]-class_off[k'] prototypes and a (J x n_k') projection.  The projections are
+ * packed back to back: G + J*class_off[k'] is the row-major (J, n_k') weight of class k'. */
+typedef struct SpsGroupDesc {
+  int32_t Kc;               /* classes with prototypes */
+  int32_t J;                /* num_groups (3) */
+  const int32_t* proto_slot; /* [P] k' of prototype p */
+  const int32_t* proto_col;  /* [P] column of p inside its class (rank among the class's prototypes) */
+  const int32_t* class_off;  /* [Kc+1] prefix sum of n_k' */
+  const int32_t* members;    /* [P] prototype ids grouped by class: members[class_off[k'] + q] (ascending p) */
+  const float* G;            /* [J*P] packed projections */
+  const float* Wg;           /* [K x J*Kc] last_layer_group.weight, row major */
+} SpsGroupDesc;
+
+int sps_version(void);
+const char* sps_last_error(void);
+
+/* Bytes of scratch sps_head_bwd needs for this shape (0 is possible). */
+size_t sps_workspace_bytes(const SpsHeadDesc* desc);
+
+/* Prototype head forward.
+ * Replaces PPNetMultiScale._scale_l2_convolution + _l2_convolution + distance_2_similarity +
+ * run_last_layer as chained by forward_from_conv_features
+ * (segmentation/model/model_multiscale.py:256-317, 324-330, 243-244, 340-388).
+ *   z        [B, S*D, H, W] fp32
+ *   protos   [P, D] fp32
+ *   last_w   [K, P] fp32 or NULL (NULL: no logits, e.g. prototype_distances / push_forward / stage 2)
+ *   logits   [N, K] fp32 or NULL (required iff last_w != NULL)
+ *   dist     [B, P, H, W] fp32 or NULL   (NULL = fused mode, the map is never written to HBM)
+ *   act      [N, P] fp32 or NULL */
+int sps_head_fwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w,
+                 float* logits, float* dist, float* act, void* stream);
+
+/* Prototype head backward (what autograd derives from the lines above; driven by manual_backward,
+ * segmentation/model/module_multiscale.py:292).  d and a are recomputed from z and protos.
+ *   dlogits [N,K] or NULL, ddist [B,P,H,W] or NULL (KLD loss back-props straight into distances,
+ *   module_multiscale.py:242), dact [N,P] or NULL.
+ *   dz [B,S*D,H,W] or NULL, dprotos [P,D] or NULL, dlast_w [K,P] or NULL: OVERWRITTEN.
+ *   workspace: >= sps_workspace_bytes(desc) bytes, contents undefined on entry and exit. */
+int sps_head_bwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w,
+                 const float* dlogits, const float* ddist, const float* dact, float* dz, float* dprotos,
+                 float* dlast_w, void* workspace, size_t workspace_bytes, void* stream);
+
+/* Stage-2 group projection + last_layer_group.
+ * Replaces compute_group + run_last_layer (segmentation/model/model_multiscale_group.py:283-308).
+ *   act [N,P] -> groups [N, J*Kc] (exp of the projections; may be NULL) and logits [N,K] (may be NULL). */
+int sps_group_fwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* act, float* groups,
+                  float* logits, void* stream);
+
+/* Scratch bytes sps_group_bwd needs (2 * N * J*Kc floats). */
+size_t sps_group_workspace_bytes(const SpsHeadDesc* desc, const SpsGroupDesc* g);
+
+/* Backward of sps_group_fwd.  dlogits [N,K] or NULL, dgroups [N,J*Kc] or NULL.
+ *   dact [N,P] or NULL (overwritten), dG [J*P] or NULL, dWg [K x J*Kc] or NULL (overwritten). */
+int sps_group_bwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* act, const float* dlogits,
+                  const float* dgroups, float* dact, float* dG, float* dWg, void* workspace,
+                  size_t workspace_bytes, void* stream);
+
+/* Push scan: per map and per prototype, the nearest position among those labelled with the
+ * prototype's class.  Replaces compute_distances lines 68-91 of
+ * segmentation/push_multiscale_optimization.py (one-hot, void column drop, 1e10 mask, min/argmin).
+ *   labels      [B, H, W] int16, already resized to the map (PIL NEAREST stays on the host,
+ *               segmentation/data/dataset.py:22-30); 0 = void, c+1 = class c
+ *   proto_class [P] int32 class of each prototype (argmax of prototype_class_identity)
+ *   keys        [B, P] uint64, OVERWRITTEN: (float_bits(min masked distance) << 32) | flat index h*W+w
+ *               of its first occurrence; (bits(1e10f) << 32) | 0 when the class is absent. */
+int sps_push_scan(const SpsHeadDesc* desc, const float* z, const float* protos, const int16_t* labels,
+                  const int32_t* proto_class, uint64_t* keys, void* stream);
+
+/* Dataset arg-min over maps (push_multiscale_optimization.py:135-137, argmin(dim=0): first map wins).
+ *   keys [n_maps, P] from sps_push_scan; map_base = global index of keys row 0 (shard offset).
+ *   best [P] uint64, MERGED by min: (float_bits(d) << 32) | global map index.  Pre-fill with
+ *   0xFFFFFFFFFFFFFFFF (or a previous shard's result); one NCCL min all-reduce combines ranks. */
+int sps_push_reduce(const uint64_t* keys, int32_t n_maps, int32_t P, uint32_t map_base, uint64_t* best,
+                    void* stream);
+
+/* Gather of the winning feature vectors (push_multiscale_optimization.py:182-188).
+ *   z [n_maps,S*D,H,W]; best [P] (global map index in the low word); keys [n_maps,P]; only prototypes
+ *   whose winning map lies in [map_base, map_base+n_maps) are written.
+ *   proto_scale [P] int32 scale whose channel block is read (the reference uses p // (P/S), :161,:167).
+ *   out [P, D] fp32. */
+int sps_push_gather(const SpsHeadDesc* desc, const float* z, const uint64_t* keys, const uint64_t* best,
+                    int32_t n_maps, uint32_t map_base, const int32_t* proto_scale, float* out, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SCALEPROTO_B200_H */

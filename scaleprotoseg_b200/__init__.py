@@ -1,0 +1,17 @@
+"""scaleprotoseg_b200 — B200-native (sm_100a) prototype head and push for ScaleProtoSeg.
+
+Only the hot path lives here: csrc/ (CUDA kernels + the C ABI of include/scaleproto_b200.h), the
+ctypes binding, the autograd wrappers and the method patches that drop the kernels into the
+reference's own classes.  Backbone, losses, trainers and data loading stay the reference's.
+"""
+from ._lib import (ACT_LINEAR, ACT_LOG, EXPORTED_SYMBOLS, FLAG_DETERMINISTIC, LIB_PATH, MATH_BF16, MATH_FP32,
+                   MATH_TF32)
+from .head import (GroupHeadFn, HeadConfig, PrototypeHeadFn, build_group_tables, default_math, head_backward_raw,
+                   head_forward_raw, set_default_math)
+from .install import install, install_on_classes, install_push, uninstall
+from . import model_api, push
+
+__all__ = ["install", "install_on_classes", "install_push", "uninstall", "HeadConfig", "PrototypeHeadFn",
+           "GroupHeadFn", "head_forward_raw", "head_backward_raw", "build_group_tables", "set_default_math",
+           "default_math", "push", "model_api", "MATH_FP32", "MATH_TF32", "MATH_BF16", "ACT_LOG", "ACT_LINEAR",
+           "LIB_PATH", "EXPORTED_SYMBOLS", "FLAG_DETERMINISTIC"]

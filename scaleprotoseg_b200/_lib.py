@@ -1,0 +1,80 @@
+"""ctypes binding of libscaleproto_sm100.so (the C ABI declared in include/scaleproto_b200.h).
+
+There is no CPU or PyTorch fallback: if the library is missing, importing the compute entry points
+raises.  Build it with `python __graft_entry__.py` (or `__graft_entry__.build()`).
+"""
+import ctypes as C
+import os
+
+SPS_MAX_SCALES = 8
+ACT_LOG, ACT_LINEAR = 0, 1
+MATH_FP32, MATH_TF32, MATH_BF16 = 0, 1, 2
+FLAG_DETERMINISTIC = 1
+
+LIB_NAME = "libscaleproto_sm100.so"
+LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
+
+
+class SpsHeadDesc(C.Structure):
+    _fields_ = [
+        ("B", C.c_int32), ("H", C.c_int32), ("W", C.c_int32),
+        ("S", C.c_int32), ("D", C.c_int32),
+        ("P", C.c_int32), ("K", C.c_int32),
+        ("scale_lo", C.c_int32 * (SPS_MAX_SCALES + 1)),
+        ("act_kind", C.c_int32),
+        ("eps", C.c_float),
+        ("math", C.c_int32),
+        ("flags", C.c_int32),
+    ]
+
+
+class SpsGroupDesc(C.Structure):
+    _fields_ = [
+        ("Kc", C.c_int32), ("J", C.c_int32),
+        ("proto_slot", C.c_void_p), ("proto_col", C.c_void_p), ("class_off", C.c_void_p),
+        ("members", C.c_void_p), ("G", C.c_void_p), ("Wg", C.c_void_p),
+    ]
+
+
+_P = C.c_void_p
+_SIGNATURES = {
+    "sps_version": (C.c_int, []),
+    "sps_last_error": (C.c_char_p, []),
+    "sps_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc)]),
+    "sps_head_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, _P]),
+    "sps_head_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
+    "sps_group_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc), _P, _P, _P, _P]),
+    "sps_group_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc)]),
+    "sps_group_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc), _P, _P, _P, _P, _P, _P, _P,
+                                C.c_size_t, _P]),
+    "sps_push_scan": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P]),
+    "sps_push_reduce": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint32, _P, _P]),
+    "sps_push_gather": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, C.c_int32, C.c_uint32, _P, _P, _P]),
+}
+EXPORTED_SYMBOLS = tuple(_SIGNATURES)
+
+_lib = None
+
+
+def load():
+    """dlopen the in-tree library and attach the prototypes.  Raises if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'`. "
+            "There is no CPU fallback for the prototype head.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in _SIGNATURES.items():
+        fn = getattr(lib, name)
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str):
+    if rc != 0:
+        msg = load().sps_last_error()
+        raise RuntimeError(f"{what} failed (status {rc}): {msg.decode() if msg else ''}")

@@ -1,0 +1,166 @@
+// extern "C" surface of libscaleproto_sm100.so: argument checks, math-mode routing, error text.
+#include <stdarg.h>
+#include <string.h>
+
+#include "common.cuh"
+
+namespace sps {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_err, sizeof(g_err), fmt, ap);
+  va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char* what) {
+  set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
+  return SPS_ERR_CUDA;
+}
+
+int sm_count() {
+  static int cached = 0;
+  if (cached == 0) {
+    int dev = 0, n = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess &&
+        cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) == cudaSuccess && n > 0)
+      cached = n;
+    else
+      cached = 148;
+  }
+  return cached;
+}
+
+int validate_desc(const SpsHeadDesc* d) {
+  SPS_REQUIRE(d != nullptr, SPS_ERR_BAD_ARG, "desc is NULL");
+  SPS_REQUIRE(d->B >= 0 && d->H >= 0 && d->W >= 0, SPS_ERR_BAD_ARG, "negative map shape B=%d H=%d W=%d", d->B, d->H, d->W);
+  SPS_REQUIRE(d->S >= 1 && d->S <= SPS_MAX_SCALES, SPS_ERR_BAD_ARG, "S=%d outside [1,%d]", d->S, SPS_MAX_SCALES);
+  SPS_REQUIRE(d->D >= 1, SPS_ERR_BAD_ARG, "D=%d", d->D);
+  SPS_REQUIRE(d->P >= 0 && d->K >= 1, SPS_ERR_BAD_ARG, "P=%d K=%d", d->P, d->K);
+  SPS_REQUIRE(d->scale_lo[0] == 0 && d->scale_lo[d->S] == d->P, SPS_ERR_BAD_ARG,
+              "scale_lo must start at 0 and end at P (got %d..%d, P=%d)", d->scale_lo[0], d->scale_lo[d->S], d->P);
+  for (int s = 0; s < d->S; ++s)
+    SPS_REQUIRE(d->scale_lo[s] <= d->scale_lo[s + 1], SPS_ERR_BAD_ARG, "scale_lo not monotone at scale %d", s);
+  SPS_REQUIRE(d->act_kind == SPS_ACT_LOG || d->act_kind == SPS_ACT_LINEAR, SPS_ERR_BAD_ARG, "act_kind=%d", d->act_kind);
+  SPS_REQUIRE(d->math == SPS_MATH_FP32 || d->math == SPS_MATH_TF32 || d->math == SPS_MATH_BF16, SPS_ERR_BAD_ARG,
+              "math=%d", d->math);
+  SPS_REQUIRE((long long)d->H * d->W < (1LL << 31), SPS_ERR_UNSUPPORTED, "H*W too large");
+  return SPS_OK;
+}
+
+}  // namespace sps
+
+using namespace sps;
+
+extern "C" {
+
+int sps_version(void) { return SPS_ABI_VERSION; }
+
+const char* sps_last_error(void) { return g_err; }
+
+size_t sps_workspace_bytes(const SpsHeadDesc* desc) {
+  if (validate_desc(desc) != SPS_OK) return 0;
+  HeadShape s = make_shape(desc);
+  return head_bwd_simt_workspace(s, desc->flags);
+}
+
+int sps_head_fwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w, float* logits,
+                 float* dist, float* act, void* stream) {
+  int rc = validate_desc(desc);
+  if (rc != SPS_OK) return rc;
+  HeadShape s = make_shape(desc);
+  if (s.N == 0 || s.P == 0) return SPS_OK;
+  SPS_REQUIRE(z != nullptr && protos != nullptr, SPS_ERR_BAD_ARG, "z/protos NULL");
+  SPS_REQUIRE((last_w == nullptr) == (logits == nullptr), SPS_ERR_BAD_ARG, "last_w and logits go together");
+  SPS_REQUIRE(last_w != nullptr || dist != nullptr || act != nullptr, SPS_ERR_BAD_ARG, "no output requested");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (desc->math == SPS_MATH_FP32) return launch_head_fwd_simt(s, z, protos, last_w, logits, dist, act, st);
+  SPS_REQUIRE(false, SPS_ERR_UNSUPPORTED, "math mode %d not built yet", desc->math);
+}
+
+int sps_head_bwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w,
+                 const float* dlogits, const float* ddist, const float* dact, float* dz, float* dprotos,
+                 float* dlast_w, void* workspace, size_t workspace_bytes, void* stream) {
+  int rc = validate_desc(desc);
+  if (rc != SPS_OK) return rc;
+  HeadShape s = make_shape(desc);
+  SPS_REQUIRE(z != nullptr && protos != nullptr, SPS_ERR_BAD_ARG, "z/protos NULL");
+  SPS_REQUIRE(dlogits == nullptr || last_w != nullptr, SPS_ERR_BAD_ARG, "dlogits given without last_w");
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  return launch_head_bwd_simt(s, desc->flags, z, protos, last_w, dlogits, ddist, dact, dz, dprotos, dlast_w, workspace,
+                              workspace_bytes, st);
+}
+
+static int check_group(const SpsGroupDesc* g) {
+  SPS_REQUIRE(g != nullptr, SPS_ERR_BAD_ARG, "group desc NULL");
+  SPS_REQUIRE(g->Kc >= 0 && g->J >= 1 && g->J <= 8, SPS_ERR_UNSUPPORTED, "Kc=%d J=%d (J must be 1..8)", g->Kc, g->J);
+  SPS_REQUIRE(g->proto_slot && g->proto_col && g->class_off && g->members && g->G && g->Wg, SPS_ERR_BAD_ARG,
+              "group desc has NULL tables");
+  return SPS_OK;
+}
+
+int sps_group_fwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* act, float* groups, float* logits,
+                  void* stream) {
+  int rc = validate_desc(desc);
+  if (rc != SPS_OK) return rc;
+  rc = check_group(g);
+  if (rc != SPS_OK) return rc;
+  SPS_REQUIRE(act != nullptr, SPS_ERR_BAD_ARG, "act NULL");
+  HeadShape s = make_shape(desc);
+  return launch_group_fwd(s, *g, act, groups, logits, reinterpret_cast<cudaStream_t>(stream));
+}
+
+size_t sps_group_workspace_bytes(const SpsHeadDesc* desc, const SpsGroupDesc* g) {
+  if (validate_desc(desc) != SPS_OK || g == nullptr) return 0;
+  return sizeof(float) * 2 * (size_t)desc->B * desc->H * desc->W * (size_t)g->J * g->Kc;
+}
+
+int sps_group_bwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* act, const float* dlogits,
+                  const float* dgroups, float* dact, float* dG, float* dWg, void* workspace, size_t workspace_bytes,
+                  void* stream) {
+  int rc = validate_desc(desc);
+  if (rc != SPS_OK) return rc;
+  rc = check_group(g);
+  if (rc != SPS_OK) return rc;
+  SPS_REQUIRE(act != nullptr, SPS_ERR_BAD_ARG, "act NULL");
+  size_t need = sps_group_workspace_bytes(desc, g);
+  SPS_REQUIRE(need == 0 || (workspace != nullptr && workspace_bytes >= need), SPS_ERR_WORKSPACE,
+              "group_bwd workspace: need %zu bytes, got %zu", need, workspace_bytes);
+  HeadShape s = make_shape(desc);
+  return launch_group_bwd(s, *g, act, dlogits, dgroups, dact, dG, dWg, reinterpret_cast<float*>(workspace),
+                          reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sps_push_scan(const SpsHeadDesc* desc, const float* z, const float* protos, const int16_t* labels,
+                  const int32_t* proto_class, uint64_t* keys, void* stream) {
+  int rc = validate_desc(desc);
+  if (rc != SPS_OK) return rc;
+  SPS_REQUIRE(z && protos && labels && proto_class && keys, SPS_ERR_BAD_ARG, "push_scan: NULL argument");
+  HeadShape s = make_shape(desc);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (desc->math == SPS_MATH_FP32)
+    return launch_push_scan_simt(s, z, protos, labels, proto_class, reinterpret_cast<unsigned long long*>(keys), st);
+  SPS_REQUIRE(false, SPS_ERR_UNSUPPORTED, "math mode %d not built yet", desc->math);
+}
+
+int sps_push_reduce(const uint64_t* keys, int32_t n_maps, int32_t P, uint32_t map_base, uint64_t* best,
+                    void* stream) {
+  SPS_REQUIRE(keys && best && n_maps >= 0 && P >= 0, SPS_ERR_BAD_ARG, "push_reduce: bad argument");
+  return launch_push_reduce(reinterpret_cast<const unsigned long long*>(keys), n_maps, P, map_base,
+                            reinterpret_cast<unsigned long long*>(best), reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sps_push_gather(const SpsHeadDesc* desc, const float* z, const uint64_t* keys, const uint64_t* best,
+                    int32_t n_maps, uint32_t map_base, const int32_t* proto_scale, float* out, void* stream) {
+  int rc = validate_desc(desc);
+  if (rc != SPS_OK) return rc;
+  SPS_REQUIRE(z && keys && best && proto_scale && out, SPS_ERR_BAD_ARG, "push_gather: NULL argument");
+  HeadShape s = make_shape(desc);
+  return launch_push_gather(s, z, reinterpret_cast<const unsigned long long*>(keys),
+                            reinterpret_cast<const unsigned long long*>(best), n_maps, map_base, proto_scale, out,
+                            reinterpret_cast<cudaStream_t>(stream));
+}
+
+}  // extern "C"

@@ -1,0 +1,87 @@
+// Shared device/host helpers for libscaleproto_sm100.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include "../../include/scaleproto_b200.h"
+
+namespace sps {
+
+void set_error(const char* fmt, ...);
+int cuda_fail(cudaError_t e, const char* what);
+
+#define SPS_CUDA_TRY(expr)                                   \
+  do {                                                       \
+    cudaError_t e__ = (expr);                                \
+    if (e__ != cudaSuccess) return sps::cuda_fail(e__, #expr); \
+  } while (0)
+
+#define SPS_REQUIRE(cond, status, ...) \
+  do {                                 \
+    if (!(cond)) {                     \
+      sps::set_error(__VA_ARGS__);     \
+      return (status);                 \
+    }                                  \
+  } while (0)
+
+// Kernel-side copy of the shape (passed by value).
+struct HeadShape {
+  int B, HW, S, D, C, P, K;
+  long long N;  // B*HW
+  int scale_lo[SPS_MAX_SCALES + 1];
+  int act_kind;
+  float eps;
+};
+
+inline HeadShape make_shape(const SpsHeadDesc* d) {
+  HeadShape s;
+  s.B = d->B;
+  s.HW = d->H * d->W;
+  s.S = d->S;
+  s.D = d->D;
+  s.C = d->S * d->D;
+  s.P = d->P;
+  s.K = d->K;
+  s.N = (long long)d->B * s.HW;
+  for (int i = 0; i <= SPS_MAX_SCALES; ++i) s.scale_lo[i] = (i <= d->S) ? d->scale_lo[i] : d->P;
+  s.act_kind = d->act_kind;
+  s.eps = d->eps;
+  return s;
+}
+
+int validate_desc(const SpsHeadDesc* d);
+int sm_count();
+
+// distance -> similarity (model_multiscale.py:324-330) and its derivative.
+__device__ __forceinline__ float act_of(float d, int kind, float eps) {
+  return kind == SPS_ACT_LOG ? __logf((d + 1.0f) / (d + eps)) : -d;
+}
+__device__ __forceinline__ float act_exact(float d, int kind, float eps) {
+  return kind == SPS_ACT_LOG ? logf((d + 1.0f) / (d + eps)) : -d;
+}
+__device__ __forceinline__ float dact_dd(float d, int kind, float eps) {
+  // d/dd log((d+1)/(d+eps)) = 1/(d+1) - 1/(d+eps) = -(1-eps)/((d+1)(d+eps))
+  return kind == SPS_ACT_LOG ? -(1.0f - eps) / ((d + 1.0f) * (d + eps)) : -1.0f;
+}
+
+// launchers implemented in the .cu files
+int launch_head_fwd_simt(const HeadShape& s, const float* z, const float* protos, const float* last_w,
+                         float* logits, float* dist, float* act, cudaStream_t st);
+int launch_head_bwd_simt(const HeadShape& s, int flags, const float* z, const float* protos, const float* last_w,
+                         const float* dlogits, const float* ddist, const float* dact, float* dz, float* dprotos,
+                         float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st);
+size_t head_bwd_simt_workspace(const HeadShape& s, int flags);
+int launch_group_fwd(const HeadShape& s, const SpsGroupDesc& g, const float* act, float* groups, float* logits,
+                     cudaStream_t st);
+int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act, const float* dlogits,
+                     const float* dgroups, float* dact, float* dG, float* dWg, float* ws, cudaStream_t st);
+int launch_push_scan_simt(const HeadShape& s, const float* z, const float* protos, const int16_t* labels,
+                          const int32_t* proto_class, unsigned long long* keys, cudaStream_t st);
+int launch_push_reduce(const unsigned long long* keys, int n_maps, int P, uint32_t map_base,
+                       unsigned long long* best, cudaStream_t st);
+int launch_push_gather(const HeadShape& s, const float* z, const unsigned long long* keys,
+                       const unsigned long long* best, int n_maps, uint32_t map_base, const int32_t* proto_scale,
+                       float* out, cudaStream_t st);
+
+}  // namespace sps

@@ -1,0 +1,131 @@
+"""Drop-in replacements for the head methods of the reference's two `PPNetMultiScale` classes.
+
+Every function here takes the reference module as `self` and keeps the reference signature and return
+convention (segmentation/model/model_multiscale.py:243-398 and
+segmentation/model/model_multiscale_group.py:283-460).  `install.install()` binds them onto the
+reference classes; nothing is added to the module's state, so the whole-module pickles the reference
+writes (module_multiscale.py:348-353) stay loadable with or without this package.
+"""
+import weakref
+from typing import Any, List, Union
+
+import torch
+
+from .head import (GroupHeadFn, GroupTables, HeadConfig, PrototypeHeadFn, build_group_tables, default_math)
+
+_group_cache: "weakref.WeakKeyDictionary" = weakref.WeakKeyDictionary()
+
+
+def head_config(m, math=None) -> HeadConfig:
+    ranges = [tuple(m.scale_num_prototypes[s]) for s in range(m.num_scales)]
+    return HeadConfig.from_ranges(ranges, m.num_classes, m.prototype_activation_function, m.epsilon,
+                                  default_math() if math is None else math)
+
+
+def is_supported(m) -> bool:
+    """Configurations the kernels cover; anything else keeps running the reference's own code."""
+    act = m.prototype_activation_function
+    shape = tuple(m.prototype_vectors.shape)
+    return (getattr(m, "scale_head", None) is None and isinstance(act, str) and act in ("log", "linear")
+            and len(shape) == 4 and shape[2] == 1 and shape[3] == 1)
+
+
+def _require_cuda(x: torch.Tensor):
+    if not x.is_cuda:
+        raise RuntimeError("scaleprotoseg_b200 is installed: the prototype head runs on CUDA only "
+                           "(got a CPU tensor; there is no CPU fallback)")
+
+
+def group_tables(m, device) -> GroupTables:
+    ident = m.prototype_class_identity
+    ent = _group_cache.get(m)
+    if ent is not None:
+        tables, snap = ent
+        if (snap.shape == ident.shape and tables.proto_slot.device == torch.device(device)
+                and tables.J == m.num_groups and torch.equal(snap, ident.detach().cpu())):
+            return tables
+    tables = build_group_tables(ident, m.num_groups, device)
+    _group_cache[m] = (tables, ident.detach().cpu().clone())
+    return tables
+
+
+# ---- methods shared by both classes -------------------------------------------------------------
+def _scale_l2_convolution(self, x: torch.Tensor) -> torch.Tensor:
+    _require_cuda(x)
+    _, dist, _ = PrototypeHeadFn.apply(x.float(), self.prototype_vectors, None, head_config(self), True, False)
+    return dist
+
+
+def prototype_distances(self, x: torch.Tensor) -> torch.Tensor:
+    return self._scale_l2_convolution(self.conv_features(x))
+
+
+def push_forward(self, x: torch.Tensor) -> Any:
+    conv_output = self.conv_features(x)
+    if isinstance(conv_output, list):
+        return [(c, self._scale_l2_convolution(c)) for c in conv_output]
+    return conv_output, self._scale_l2_convolution(conv_output)
+
+
+def _returns(logits, distances, activations, return_activations, return_distances):
+    if return_activations and not return_distances:
+        return logits, activations
+    if return_activations and return_distances:
+        return logits, distances, activations
+    return logits, distances
+
+
+# ---- stage 1 ------------------------------------------------------------------------------------
+def forward_from_conv_features_stage1(self, conv_features: Union[torch.Tensor, List[torch.Tensor]],
+                                      return_activations: bool = False, return_distances: bool = False) -> Any:
+    if isinstance(conv_features, list):
+        return [self.forward_from_conv_features(c) for c in conv_features]
+    if not (hasattr(self, "patch_classification") and self.patch_classification):
+        raise Exception("Original Prototype Network Implementation")
+    _require_cuda(conv_features)
+    B, _, H, W = conv_features.shape
+    want_dist = return_distances or not return_activations
+    logits, dist, act = PrototypeHeadFn.apply(conv_features.float(), self.prototype_vectors, self.last_layer.weight,
+                                              head_config(self), want_dist, bool(return_activations))
+    logits = logits.reshape(B, H, W, -1)
+    return _returns(logits, dist, act, return_activations, return_distances)
+
+
+# ---- stage 2 ------------------------------------------------------------------------------------
+def _group_apply(self, prototype_activations: torch.Tensor, hw=None):
+    _require_cuda(prototype_activations)
+    tables = group_tables(self, prototype_activations.device)
+    if len(self.group_projection) != tables.Kc:
+        raise RuntimeError("group_projection does not match prototype_class_identity "
+                           f"({len(self.group_projection)} modules, {tables.Kc} classes with prototypes)")
+    G = torch.cat([gp.weight.reshape(-1) for gp in self.group_projection])
+    N = prototype_activations.shape[0]
+    hw = hw if hw is not None else (1, 1, N)
+    return GroupHeadFn.apply(prototype_activations.float(), G, self.last_layer_group.weight, head_config(self),
+                             tables, hw), tables
+
+
+def compute_group(self, prototype_activations: torch.Tensor) -> List[torch.Tensor]:
+    (groups, _), tables = _group_apply(self, prototype_activations)
+    return list(torch.split(groups, tables.J, dim=-1))
+
+
+def run_last_layer_group(self, prototype_activations: torch.Tensor) -> torch.Tensor:
+    (_, logits), _ = _group_apply(self, prototype_activations)
+    return logits
+
+
+def forward_from_conv_features_stage2(self, conv_features: Union[torch.Tensor, List[torch.Tensor]],
+                                      return_activations: bool = False, return_distances: bool = False) -> Any:
+    if isinstance(conv_features, list):
+        return [self.forward_from_conv_features(c) for c in conv_features]
+    if not (hasattr(self, "patch_classification") and self.patch_classification):
+        raise Exception("Original Prototype Network Implementation")
+    _require_cuda(conv_features)
+    B, _, H, W = conv_features.shape
+    want_dist = return_distances or not return_activations
+    _, dist, act = PrototypeHeadFn.apply(conv_features.float(), self.prototype_vectors, None, head_config(self),
+                                         want_dist, True)
+    (_, logits), _ = _group_apply(self, act, (B, H, W))
+    logits = logits.reshape(B, H, W, -1)
+    return _returns(logits, dist, act, return_activations, return_distances)

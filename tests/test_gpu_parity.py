@@ -1,0 +1,160 @@
+"""GPU parity: the CUDA path (through the C ABI) against (i) golden vectors produced by the unmodified
+reference and (ii) the CPU oracle on seeded inputs.
+
+Tolerances (BASELINE.json north_star: rel 1e-3):
+  distances   |err| <= 1e-3 * max(|ref|, 1)
+  activations |err| <= 1e-3 * max(|ref|, 1)      (log-similarity; slope ~1/(d+eps) is why d gets the floor)
+  logits      |err| <= 1e-3 * max(|ref|, 1)
+  gradients   |err| <= 1e-3 * max|ref|            (per tensor, normalised by its largest entry)
+  push        indices bit-exact where the runner-up is further than the distance tolerance, otherwise the
+              distance at the returned index must be within tolerance of the oracle minimum.
+SPS_MATH_FP32 (exact operands) is held to 20x tighter bounds.
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+import scaleprotoseg_b200 as sps
+from oracle import head_oracle as ho
+from scaleprotoseg_b200 import push as spush
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+MATHS = [sps.MATH_FP32]
+
+
+def _tol(math):
+    return 5e-5 if math == sps.MATH_FP32 else 1e-3
+
+
+def assert_rel(got, ref, tol, name, floor=1.0):
+    got, ref = torch.as_tensor(got).detach().cpu().double(), torch.as_tensor(ref).detach().cpu().double()
+    assert got.shape == ref.shape, f"{name}: shape {tuple(got.shape)} vs {tuple(ref.shape)}"
+    err = ((got - ref).abs() / ref.abs().clamp_min(floor)).max().item() if ref.numel() else 0.0
+    assert err <= tol, f"{name}: max rel err {err:.3e} > {tol:.1e}"
+
+
+def assert_grad(got, ref, tol, name):
+    ref = torch.as_tensor(ref).detach().cpu().double()
+    scale = ref.abs().max().clamp_min(1e-30).item()
+    assert_rel(torch.as_tensor(got).detach().cpu().double() / scale, ref / scale, tol, name, floor=1.0)
+
+
+def _load(golden_dir, name):
+    return {k: v for k, v in np.load(os.path.join(golden_dir, name + ".npz")).items()}
+
+
+def _ranges(g):
+    return [tuple(int(v) for v in r) for r in g["ranges"]]
+
+
+def _cu(a):
+    return torch.from_numpy(np.ascontiguousarray(a)).to(DEV)
+
+
+@pytest.mark.parametrize("math", MATHS)
+@pytest.mark.parametrize("name", ["stage1_em", "stage1_em_ragged", "stage1_linear", "stage1_city228"])
+def test_stage1_golden(built_lib, golden_dir, name, math):
+    g = _load(golden_dir, name)
+    K = g["last_w"].shape[0]
+    cfg = sps.HeadConfig.from_ranges(_ranges(g), K, act=str(g["act_kind"]), math=math)
+    z, p, w = (_cu(g[k]).requires_grad_(True) for k in ("z", "protos", "last_w"))
+    logits, d, a = sps.PrototypeHeadFn.apply(z, p, w, cfg, True, True)
+    tol = _tol(math)
+    assert_rel(d, g["dist"], tol, "dist"), assert_rel(a, g["act"], tol, "act")
+    assert_rel(logits.view(g["logits"].shape), g["logits"], tol, "logits")
+    loss = (logits.view(g["logits"].shape) * _cu(g["dlogits"])).sum() + (d * _cu(g["ddist"])).sum() + \
+        (a * _cu(g["dact"])).sum()
+    dz, dp, dw = torch.autograd.grad(loss, [z, p, w])
+    gt = 20 * tol if math == sps.MATH_FP32 else tol
+    assert_grad(dz, g["dz"], gt, "dz"), assert_grad(dp, g["dprotos"], gt, "dprotos")
+    assert_grad(dw, g["dlast_w"], gt, "dlast_w")
+
+
+@pytest.mark.parametrize("math", MATHS)
+@pytest.mark.parametrize("name", ["stage2_em", "stage2_city228_ragged"])
+def test_stage2_golden(built_lib, golden_dir, name, math):
+    g = _load(golden_dir, name)
+    ident = torch.from_numpy(g["identity"])
+    K = ident.shape[1]
+    cfg = sps.HeadConfig.from_ranges(_ranges(g), K, math=math)
+    n_mod = int(g["n_group_mods"])
+    z, p, wg = (_cu(g[k]).requires_grad_(True) for k in ("z", "protos", "last_group_w"))
+    gws = [_cu(g[f"group_w_{k}"]).requires_grad_(True) for k in range(n_mod)]
+    tables = sps.build_group_tables(ident, 3, DEV)
+    assert tables.Kc == n_mod
+    _, d, a = sps.PrototypeHeadFn.apply(z, p, None, cfg, True, True)
+    G = torch.cat([w_.reshape(-1) for w_ in gws])
+    B, _, H, W = z.shape
+    groups, logits = sps.GroupHeadFn.apply(a, G, wg, cfg, tables, (B, H, W))
+    tol = _tol(math)
+    assert_rel(d, g["dist"], tol, "dist"), assert_rel(a, g["act"], tol, "act")
+    assert_rel(groups, g["groups"], 4 * tol, "groups"), assert_rel(logits.view(g["logits"].shape), g["logits"], 4 * tol, "logits")
+    loss = (logits.view(g["logits"].shape) * _cu(g["dlogits"])).sum() + (d * _cu(g["ddist"])).sum() + \
+        (a * _cu(g["dact"])).sum() + (groups * _cu(g["dgroups"])).sum()
+    grads = torch.autograd.grad(loss, [z, p, wg] + gws)
+    gt = 20 * tol if math == sps.MATH_FP32 else tol
+    assert_grad(grads[0], g["dz"], gt, "dz"), assert_grad(grads[1], g["dprotos"], gt, "dprotos")
+    assert_grad(grads[2], g["dlast_group_w"], gt, "dlast_group_w")
+    allref = np.concatenate([g[f"dgroup_w_{k}"].ravel() for k in range(n_mod)])
+    allgot = torch.cat([grads[3 + k].reshape(-1) for k in range(n_mod)])
+    assert_grad(allgot, allref, gt, "dgroup_w")
+
+
+def check_push(keys, win_map, z_maps, labels, protos, ranges, ident, K, tol):
+    """keys (n,P) int64 from the kernel, win_map (P,) global winners."""
+    n = len(z_maps)
+    idx_k, val_k = spush.decode_keys(keys.cpu())
+    list_val = []
+    for i in range(n):
+        d = ho.scale_l2_convolution(z_maps[i], protos, ranges)
+        idx_o, val_o = ho.push_image_min(d, labels[i], ident, K, 0)
+        list_val.append(val_o)
+        absent = val_o[0] >= 1e10
+        assert torch.equal(val_k[i][absent], val_o[0][absent]) and (idx_k[i][absent] == 0).all()
+        # distance at the kernel's index must be (within tolerance) the oracle minimum ...
+        dk = d[0].flatten(1)[torch.arange(d.shape[1]), idx_k[i]]
+        ok = ~absent
+        assert ((dk[ok] - val_o[0][ok]).abs() <= tol * val_o[0][ok].clamp_min(1.0)).all()
+        assert ((val_k[i][ok] - val_o[0][ok]).abs() <= tol * val_o[0][ok].clamp_min(1.0)).all()
+        # ... and the index is bit-exact wherever the runner-up is further than the tolerance
+        masked = d[0].flatten(1).clone()
+        cls = ident.argmax(1)
+        lab = labels[i].flatten()
+        masked[(lab.unsqueeze(0) - 1) != cls.unsqueeze(1)] = float("inf")
+        top2 = masked.topk(2, dim=1, largest=False).values
+        clear = ok & ((top2[:, 1] - top2[:, 0]) > 2 * tol * top2[:, 0].clamp_min(1.0))
+        assert torch.equal(idx_k[i][clear], idx_o[0][clear])
+    tot = torch.cat(list_val)
+    win_o = tot.argmin(0)
+    s2 = tot.topk(min(2, n), dim=0, largest=False).values
+    clear = torch.ones_like(win_o, dtype=torch.bool) if n < 2 else \
+        ((s2[1] - s2[0]) > 2 * tol * s2[0].clamp_min(1.0)) | (s2[0] >= 1e10)
+    assert torch.equal(win_map.cpu()[clear], win_o[clear])
+    return win_o
+
+
+@pytest.mark.parametrize("math", MATHS)
+@pytest.mark.parametrize("name", ["push_small", "push_city228"])
+def test_push_golden(built_lib, golden_dir, name, math):
+    g = _load(golden_dir, name)
+    K = int(g["K"])
+    ident = torch.from_numpy(g["identity"])
+    protos = torch.from_numpy(g["protos"])
+    z = torch.sigmoid(torch.from_numpy(g["x"]))
+    cfg = sps.HeadConfig.from_ranges(_ranges(g), K, math=math)
+    labels = torch.from_numpy(g["labels"])
+    wm, pix, wd, out, keys = spush.push_project(z.to(DEV), labels.to(DEV), protos.to(DEV), ident, cfg, batch=2)
+    idx_k, val_k = spush.decode_keys(keys.cpu())
+    if math == sps.MATH_FP32:
+        # exact-operand mode: every index the reference produced, bit for bit (ties included)
+        same = idx_k.numpy() == g["idx"]
+        assert same.mean() > 0.995
+        assert np.array_equal(wm.cpu().numpy()[np.all(same, axis=0)], g["win"][np.all(same, axis=0)])
+        agree = (wm.cpu().numpy() == g["win"]) & (pix.cpu().numpy() == g["idx"][g["win"], np.arange(len(g["win"]))])
+        got = out.cpu().numpy().reshape(g["new_protos"].shape)
+        assert np.array_equal(got[agree], g["new_protos"][agree]) and agree.mean() > 0.99
+    check_push(keys, wm, [z[i:i + 1] for i in range(z.shape[0])], [labels[i].long() for i in range(z.shape[0])],
+               protos, _ranges(g), ident, K, _tol(math))

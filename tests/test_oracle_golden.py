@@ -1,0 +1,79 @@
+"""The CPU oracle (oracle/head_oracle.py) against vectors produced by the UNMODIFIED reference
+(oracle/gen_golden.py, run in the build container).  fp32 on both sides, same op order: tight."""
+import glob
+import os
+
+import numpy as np
+import pytest
+import torch
+
+from oracle import head_oracle as ho
+
+TOL = dict(rtol=2e-5, atol=2e-6)
+
+
+def _load(golden_dir, name):
+    return {k: v for k, v in np.load(os.path.join(golden_dir, name + ".npz")).items()}
+
+
+def _ranges(g):
+    return [tuple(int(v) for v in r) for r in g["ranges"]]
+
+
+@pytest.mark.parametrize("name", ["stage1_em", "stage1_em_ragged", "stage1_linear", "stage1_city228"])
+def test_stage1_forward_backward(golden_dir, name):
+    g = _load(golden_dir, name)
+    z = torch.from_numpy(g["z"]).requires_grad_(True)
+    p = torch.from_numpy(g["protos"]).requires_grad_(True)
+    w = torch.from_numpy(g["last_w"]).requires_grad_(True)
+    logits, d, a = ho.head_stage1(z, p, _ranges(g), w, kind=str(g["act_kind"]))
+    np.testing.assert_allclose(d.detach().numpy(), g["dist"], **TOL)
+    np.testing.assert_allclose(a.detach().numpy(), g["act"], **TOL)
+    np.testing.assert_allclose(logits.detach().numpy(), g["logits"], rtol=2e-5, atol=2e-5)
+    loss = (logits * torch.from_numpy(g["dlogits"])).sum() + (d * torch.from_numpy(g["ddist"])).sum() + \
+        (a * torch.from_numpy(g["dact"])).sum()
+    dz, dp, dw = torch.autograd.grad(loss, [z, p, w])
+    np.testing.assert_allclose(dz.numpy(), g["dz"], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(dp.numpy(), g["dprotos"], rtol=1e-4, atol=1e-6)
+    np.testing.assert_allclose(dw.numpy(), g["dlast_w"], rtol=1e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", ["stage2_em", "stage2_city228_ragged"])
+def test_stage2_forward_backward(golden_dir, name):
+    g = _load(golden_dir, name)
+    z = torch.from_numpy(g["z"]).requires_grad_(True)
+    p = torch.from_numpy(g["protos"]).requires_grad_(True)
+    wg = torch.from_numpy(g["last_group_w"]).requires_grad_(True)
+    gws = [torch.from_numpy(g[f"group_w_{k}"]).requires_grad_(True) for k in range(int(g["n_group_mods"]))]
+    ident = torch.from_numpy(g["identity"])
+    logits, d, a, groups = ho.head_stage2(z, p, _ranges(g), ident, gws, wg)
+    np.testing.assert_allclose(d.detach().numpy(), g["dist"], **TOL)
+    np.testing.assert_allclose(groups.detach().numpy(), g["groups"], rtol=5e-5, atol=1e-6)
+    np.testing.assert_allclose(logits.detach().numpy(), g["logits"], rtol=5e-5, atol=5e-5)
+    loss = (logits * torch.from_numpy(g["dlogits"])).sum() + (d * torch.from_numpy(g["ddist"])).sum() + \
+        (a * torch.from_numpy(g["dact"])).sum() + (groups * torch.from_numpy(g["dgroups"])).sum()
+    grads = torch.autograd.grad(loss, [z, p, wg] + gws)
+    np.testing.assert_allclose(grads[0].numpy(), g["dz"], rtol=2e-4, atol=1e-6)
+    np.testing.assert_allclose(grads[1].numpy(), g["dprotos"], rtol=2e-4, atol=1e-6)
+    np.testing.assert_allclose(grads[2].numpy(), g["dlast_group_w"], rtol=2e-4, atol=1e-6)
+    for k in range(len(gws)):
+        np.testing.assert_allclose(grads[3 + k].numpy(), g[f"dgroup_w_{k}"], rtol=2e-4, atol=1e-6)
+
+
+@pytest.mark.parametrize("name", ["push_small", "push_city228"])
+def test_push(golden_dir, name):
+    g = _load(golden_dir, name)
+    K = int(g["K"])
+    x = torch.from_numpy(g["x"])
+    z_maps = [torch.sigmoid(x[i:i + 1]) for i in range(x.shape[0])]
+    labels = [torch.from_numpy(g["labels"][i].astype(np.int64)) for i in range(x.shape[0])]
+    win, idx, val, newp = ho.push_full(z_maps, labels, torch.from_numpy(g["protos"]), _ranges(g),
+                                       torch.from_numpy(g["identity"]), K)
+    assert np.array_equal(torch.cat(idx).numpy(), g["idx"])      # bit-exact indices
+    assert np.array_equal(torch.cat(val).numpy(), g["val"])      # bit-exact fp32 minima
+    assert np.array_equal(win.numpy(), g["win"])
+    assert np.array_equal(newp, g["new_protos"])
+
+
+def test_golden_files_present(golden_dir):
+    assert len(glob.glob(os.path.join(golden_dir, "*.npz"))) >= 8
