@@ -8,8 +8,8 @@ import torch
 
 import scaleprotoseg_b200 as sps
 from oracle import head_oracle as ho
-from tests.standin_model import Stage1Standin, Stage2Standin
-from tests.test_gpu_parity import DEV, assert_grad, assert_rel
+from standin_model import Stage1Standin, Stage2Standin
+from test_gpu_parity import DEV, assert_grad, assert_rel
 
 pytestmark = pytest.mark.gpu
 TOL = 5e-5
