@@ -69,7 +69,7 @@ def head_stage1(z, protos, scale_ranges, last_w, kind: str = "log"):
     d = scale_l2_convolution(z, protos, scale_ranges)
     B, P, H, W = d.shape
     act = distance_2_similarity(d.permute(0, 2, 3, 1).contiguous().reshape(-1, P), kind)
-    logits = F.linear(act, last_w).reshape(B, H, W, -1)
+    logits = F.linear(act, last_w).reshape(B, H, W, last_w.shape[0])
     return logits, d, act
 
 
@@ -98,7 +98,7 @@ def head_stage2(z, protos, scale_ranges, identity, group_ws, last_group_w, kind:
     B, P, H, W = d.shape
     act = distance_2_similarity(d.permute(0, 2, 3, 1).contiguous().reshape(-1, P), kind)
     groups = torch.cat(compute_group(act, identity, group_ws), dim=-1)
-    logits = F.linear(groups, last_group_w).reshape(B, H, W, -1)
+    logits = F.linear(groups, last_group_w).reshape(B, H, W, last_group_w.shape[0])
     return logits, d, act, groups
 
 

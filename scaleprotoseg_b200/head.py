@@ -120,11 +120,12 @@ def head_backward_raw(z, protos, last_w, cfg: HeadConfig, dlogits, ddist, dact, 
     protos = protos.contiguous()
     B, H, W, S, D, P = _shape_of(z, protos, cfg)
     desc = make_desc(cfg, B, H, W, D, P)
-    dz = torch.empty_like(z) if need_dz else None
-    dp = torch.empty_like(protos) if need_dp else None
-    dw = torch.empty_like(last_w) if (need_dw and last_w is not None) else None
     if last_w is not None:
         last_w = last_w.contiguous()
+    # memory_format=contiguous: empty_like would inherit the strides of a transposed view
+    dz = torch.empty_like(z, memory_format=torch.contiguous_format) if need_dz else None
+    dp = torch.empty_like(protos, memory_format=torch.contiguous_format) if need_dp else None
+    dw = torch.empty_like(last_w, memory_format=torch.contiguous_format) if (need_dw and last_w is not None) else None
     if dlogits is not None:
         dlogits = dlogits.contiguous().view(-1, cfg.num_classes)
     if ddist is not None:
@@ -258,9 +259,9 @@ class GroupHeadFn(torch.autograd.Function):
         desc.scale_lo[0], desc.scale_lo[1] = 0, P
         gd = _group_desc(tables, G, Wg)
         need_da, need_dG, need_dWg = ctx.needs_input_grad[:3]
-        dact = torch.empty_like(act) if need_da else None
-        dG = torch.empty_like(G) if need_dG else None
-        dWg = torch.empty_like(Wg) if need_dWg else None
+        dact = torch.empty_like(act, memory_format=torch.contiguous_format) if need_da else None
+        dG = torch.empty_like(G, memory_format=torch.contiguous_format) if need_dG else None
+        dWg = torch.empty_like(Wg, memory_format=torch.contiguous_format) if need_dWg else None
         if dgroups is not None:
             dgroups = dgroups.contiguous()
         if dlogits is not None:
