@@ -43,9 +43,11 @@ typedef enum {
 #define SPS_ACT_LINEAR 1 /* -d */
 
 /* Arithmetic of the z.p contraction.  fp32 accumulation everywhere. */
-#define SPS_MATH_FP32 0 /* fp32 FFMA on CUDA cores: exact-operand mode used for gradient parity */
-#define SPS_MATH_TF32 1 /* tcgen05 kind::tf32, operands rounded to tf32 (rna); norms from the rounded operands */
-#define SPS_MATH_BF16 2 /* tcgen05 kind::f16 bf16 operands (fast mode) */
+#define SPS_MATH_FP32 0   /* fp32 FFMA on CUDA cores: exact-operand mode (gradient parity, pushed prototypes) */
+#define SPS_MATH_BF16X3 1 /* tcgen05 kind::f16, bf16 operands split hi+lo, 3 MMAs per product (16-bit mantissa) */
+#define SPS_MATH_BF16 2   /* tcgen05 kind::f16, bf16 operands rounded to nearest (8-bit mantissa) */
+#define SPS_MATH_F16 3    /* tcgen05 kind::f16, fp16 operands rounded to nearest (11-bit mantissa; |z|,|p| < 6e4) */
+#define SPS_MATH_F16X3 4  /* tcgen05 kind::f16, fp16 operands split hi+lo, 3 MMAs per product (22-bit mantissa) */
 
 /* flags */
 #define SPS_FLAG_DETERMINISTIC 1 /* backward reductions over N in a fixed order (no fp32 atomics) */
@@ -81,9 +83,14 @@ typedef struct SpsGroupDesc {
 
 int sps_version(void);
 const char* sps_last_error(void);
+/* Number of kernels this library has launched in this process (bench.py reports it as gpu_launches). */
+uint64_t sps_launch_count(void);
 
 /* Bytes of scratch sps_head_bwd needs for this shape (0 is possible). */
 size_t sps_workspace_bytes(const SpsHeadDesc* desc);
+/* Bytes of scratch sps_head_fwd / sps_push_scan need (packed 16-bit prototype images of the tensor-core
+ * modes; 0 for SPS_MATH_FP32). */
+size_t sps_head_fwd_workspace_bytes(const SpsHeadDesc* desc);
 
 /* Prototype head forward.
  * Replaces PPNetMultiScale._scale_l2_convolution + _l2_convolution + distance_2_similarity +
@@ -94,9 +101,10 @@ size_t sps_workspace_bytes(const SpsHeadDesc* desc);
  *   last_w   [K, P] fp32 or NULL (NULL: no logits, e.g. prototype_distances / push_forward / stage 2)
  *   logits   [N, K] fp32 or NULL (required iff last_w != NULL)
  *   dist     [B, P, H, W] fp32 or NULL   (NULL = fused mode, the map is never written to HBM)
- *   act      [N, P] fp32 or NULL */
+ *   act      [N, P] fp32 or NULL
+ *   workspace >= sps_head_fwd_workspace_bytes(desc) bytes (may be NULL when that is 0) */
 int sps_head_fwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w,
-                 float* logits, float* dist, float* act, void* stream);
+                 float* logits, float* dist, float* act, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Prototype head backward (what autograd derives from the lines above; driven by manual_backward,
  * segmentation/model/module_multiscale.py:292).  d and a are recomputed from z and protos.

@@ -4,8 +4,8 @@ Only the hot path lives here: csrc/ (CUDA kernels + the C ABI of include/scalepr
 ctypes binding, the autograd wrappers and the method patches that drop the kernels into the
 reference's own classes.  Backbone, losses, trainers and data loading stay the reference's.
 """
-from ._lib import (ACT_LINEAR, ACT_LOG, EXPORTED_SYMBOLS, FLAG_DETERMINISTIC, LIB_PATH, MATH_BF16, MATH_FP32,
-                   MATH_TF32)
+from ._lib import (ACT_LINEAR, ACT_LOG, EXPORTED_SYMBOLS, FLAG_DETERMINISTIC, LIB_PATH, MATH_BF16, MATH_BF16X3, MATH_F16,
+                   MATH_F16X3, MATH_FP32)
 from .head import (GroupHeadFn, HeadConfig, PrototypeHeadFn, build_group_tables, default_math, head_backward_raw,
                    head_forward_raw, set_default_math)
 from .install import install, install_on_classes, install_push, uninstall
@@ -13,5 +13,5 @@ from . import model_api, push
 
 __all__ = ["install", "install_on_classes", "install_push", "uninstall", "HeadConfig", "PrototypeHeadFn",
            "GroupHeadFn", "head_forward_raw", "head_backward_raw", "build_group_tables", "set_default_math",
-           "default_math", "push", "model_api", "MATH_FP32", "MATH_TF32", "MATH_BF16", "ACT_LOG", "ACT_LINEAR",
+           "default_math", "push", "model_api", "MATH_FP32", "MATH_BF16", "MATH_BF16X3", "MATH_F16", "MATH_F16X3", "ACT_LOG", "ACT_LINEAR",
            "LIB_PATH", "EXPORTED_SYMBOLS", "FLAG_DETERMINISTIC"]

@@ -8,11 +8,11 @@ import os
 
 SPS_MAX_SCALES = 8
 ACT_LOG, ACT_LINEAR = 0, 1
-MATH_FP32, MATH_TF32, MATH_BF16 = 0, 1, 2
+MATH_FP32, MATH_BF16X3, MATH_BF16, MATH_F16, MATH_F16X3 = 0, 1, 2, 3, 4
 FLAG_DETERMINISTIC = 1
 
 LIB_NAME = "libscaleproto_sm100.so"
-LIB_PATH = os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
+LIB_PATH = os.environ.get("SCALEPROTO_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
 
 
 class SpsHeadDesc(C.Structure):
@@ -40,8 +40,10 @@ _P = C.c_void_p
 _SIGNATURES = {
     "sps_version": (C.c_int, []),
     "sps_last_error": (C.c_char_p, []),
+    "sps_launch_count": (C.c_uint64, []),
     "sps_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc)]),
-    "sps_head_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, _P]),
+    "sps_head_fwd_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc)]),
+    "sps_head_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "sps_head_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "sps_group_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc), _P, _P, _P, _P]),
     "sps_group_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc)]),

@@ -2,6 +2,8 @@
 #include <stdarg.h>
 #include <string.h>
 
+#include <atomic>
+
 #include "common.cuh"
 
 namespace sps {
@@ -19,6 +21,9 @@ int cuda_fail(cudaError_t e, const char* what) {
   set_error("CUDA error %d (%s) at %s", (int)e, cudaGetErrorString(e), what);
   return SPS_ERR_CUDA;
 }
+
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
 
 int sm_count() {
   static int cached = 0;
@@ -44,8 +49,7 @@ int validate_desc(const SpsHeadDesc* d) {
   for (int s = 0; s < d->S; ++s)
     SPS_REQUIRE(d->scale_lo[s] <= d->scale_lo[s + 1], SPS_ERR_BAD_ARG, "scale_lo not monotone at scale %d", s);
   SPS_REQUIRE(d->act_kind == SPS_ACT_LOG || d->act_kind == SPS_ACT_LINEAR, SPS_ERR_BAD_ARG, "act_kind=%d", d->act_kind);
-  SPS_REQUIRE(d->math == SPS_MATH_FP32 || d->math == SPS_MATH_TF32 || d->math == SPS_MATH_BF16, SPS_ERR_BAD_ARG,
-              "math=%d", d->math);
+  SPS_REQUIRE(d->math >= SPS_MATH_FP32 && d->math <= SPS_MATH_F16X3, SPS_ERR_BAD_ARG, "math=%d", d->math);
   SPS_REQUIRE((long long)d->H * d->W < (1LL << 31), SPS_ERR_UNSUPPORTED, "H*W too large");
   return SPS_OK;
 }
@@ -60,6 +64,13 @@ int sps_version(void) { return SPS_ABI_VERSION; }
 
 const char* sps_last_error(void) { return g_err; }
 
+uint64_t sps_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
+
+size_t sps_head_fwd_workspace_bytes(const SpsHeadDesc* desc) {
+  if (validate_desc(desc) != SPS_OK || desc->math == SPS_MATH_FP32) return 0;
+  return head_fwd_tc_workspace(make_shape(desc));
+}
+
 size_t sps_workspace_bytes(const SpsHeadDesc* desc) {
   if (validate_desc(desc) != SPS_OK) return 0;
   HeadShape s = make_shape(desc);
@@ -67,7 +78,7 @@ size_t sps_workspace_bytes(const SpsHeadDesc* desc) {
 }
 
 int sps_head_fwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w, float* logits,
-                 float* dist, float* act, void* stream) {
+                 float* dist, float* act, void* workspace, size_t workspace_bytes, void* stream) {
   int rc = validate_desc(desc);
   if (rc != SPS_OK) return rc;
   HeadShape s = make_shape(desc);
@@ -77,7 +88,7 @@ int sps_head_fwd(const SpsHeadDesc* desc, const float* z, const float* protos, c
   SPS_REQUIRE(last_w != nullptr || dist != nullptr || act != nullptr, SPS_ERR_BAD_ARG, "no output requested");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (desc->math == SPS_MATH_FP32) return launch_head_fwd_simt(s, z, protos, last_w, logits, dist, act, st);
-  SPS_REQUIRE(false, SPS_ERR_UNSUPPORTED, "math mode %d not built yet", desc->math);
+  return launch_head_fwd_tc(s, desc->math, z, protos, last_w, logits, dist, act, workspace, workspace_bytes, st);
 }
 
 int sps_head_bwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w,

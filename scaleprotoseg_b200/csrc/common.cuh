@@ -52,6 +52,7 @@ inline HeadShape make_shape(const SpsHeadDesc* d) {
 
 int validate_desc(const SpsHeadDesc* d);
 int sm_count();
+void count_launch(int n = 1);
 
 // distance -> similarity (model_multiscale.py:324-330) and its derivative.
 __device__ __forceinline__ float act_of(float d, int kind, float eps) {
@@ -68,6 +69,9 @@ __device__ __forceinline__ float dact_dd(float d, int kind, float eps) {
 // launchers implemented in the .cu files
 int launch_head_fwd_simt(const HeadShape& s, const float* z, const float* protos, const float* last_w,
                          float* logits, float* dist, float* act, cudaStream_t st);
+size_t head_fwd_tc_workspace(const HeadShape& s);
+int launch_head_fwd_tc(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w,
+                       float* logits, float* dist, float* act, void* ws, size_t ws_bytes, cudaStream_t st);
 int launch_head_bwd_simt(const HeadShape& s, int flags, const float* z, const float* protos, const float* last_w,
                          const float* dlogits, const float* ddist, const float* dact, float* dz, float* dprotos,
                          float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st);

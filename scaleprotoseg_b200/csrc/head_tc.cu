@@ -1,0 +1,528 @@
+// Tensor-core prototype head (sm_100a): fused forward.
+//
+//   distance GEMM  (tcgen05.mma, fp16/bf16 operands, fp32 accumulation in TMEM)
+//       acc[n,p] = sum_k z_s(n)[k] * (-2 p_p[k])  +  |p_p|^2 * 1  +  1 * |z_s(n)|^2
+//     the two squared norms ride in one extra K step (each split in three 16-bit terms), so the
+//     accumulator already holds |z|^2 - 2 z.p + |p|^2 (segmentation/model/model_multiscale.py:267-279).
+//   epilogue       (tcgen05.ld -> registers)   d = max(acc, 0);  a = log((d+1)/(d+eps))  (:324-330)
+//                  optional dense stores of d (NCHW) and a (N x P); a is packed to 16 bit into shared memory
+//   logits GEMM    (tcgen05.mma)               logits[n,k] += a[n,p] * W[k,p]          (:243-244)
+//     accumulated in TMEM over every scale and chunk of the tile, so in fused mode no (N x P) map is
+//     ever written to HBM.
+//
+// Work decomposition: a tile is 128 consecutive positions (rows n = (b*H + h)*W + w, the order of
+// permute(0,2,3,1).reshape(-1,P), :369-370); the prototypes of each scale (ragged ranges allowed, :400-432)
+// are cut into chunks of 64.  One persistent CTA per SM walks tiles; inside a tile it walks the chunks.
+// Warp roles: warp 0 = MMA issuer (one thread), warp 1 = prototype-chunk producer (bulk async copies of the
+// packed images written by the pre-pass), warps 4-11 = epilogue (two per TMEM lane quarter, 32 columns
+// each), warps 12-15 = feature-tile loaders (NCHW fp32 -> 16-bit K-major swizzled tiles + row norms).
+#include "tc_common.cuh"
+
+namespace sps {
+namespace tc {
+
+#ifdef SPS_TIMELINE
+// Debug build only: per-role clock stamps of CTA 0 (role r, event e) -> g_tl[r * 1024 + e].
+__device__ long long g_tl[8 * 1024];
+#define TL(role, ev)                                                                    \
+  do {                                                                                  \
+    if (blockIdx.x == 0 && (ev) < 1024) g_tl[(role) * 1024 + (ev)] = clock64();          \
+  } while (0)
+#else
+#define TL(role, ev) do { } while (0)
+#endif
+
+// ---------------------------------------------------------------------------------------------
+// Pre-pass: packed prototype / last-layer images, one per chunk (layout in tc_common.cuh)
+// ---------------------------------------------------------------------------------------------
+template <typename X, int NSPLIT>
+__global__ void __launch_bounds__(256) proto_prep_kernel(const __grid_constant__ ChunkTable ct, int D, int P, int K,
+                                                          int act_kind, const float* __restrict__ protos,
+                                                          const float* __restrict__ last_w,
+                                                          unsigned char* __restrict__ img_base) {
+  const int c = blockIdx.x;
+  const int p0 = ct.p0[c], n = ct.n[c];
+  unsigned char* img = img_base + (size_t)c * ct.img_bytes;
+  __shared__ float pn[CN];
+  const int t = threadIdx.x;
+  if (t < CN) pn[t] = 0.f;
+  __syncthreads();
+  // operand rows: 4 threads per row, 16 k each
+  {
+    const int j = t >> 2, kq = (t & 3) * 16;
+    float part = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      const int k = kq + kk;
+      const float v = (j < n && k < D) ? -2.0f * __ldg(protos + (size_t)(p0 + j) * D + k) : 0.0f;
+      const X hi = Fmt<X>::from(v);
+      float eff = Fmt<X>::to(hi);
+      X lo = Fmt<X>::from(0.0f);
+      if (NSPLIT == 3) {
+        lo = Fmt<X>::from(v - eff);
+        eff += Fmt<X>::to(lo);
+      }
+      *reinterpret_cast<uint16_t*>(img + OFF_BHI + sw128_off(j, k)) = bits16(hi);
+      *reinterpret_cast<uint16_t*>(img + OFF_BLO + sw128_off(j, k)) = bits16(lo);
+      part = fmaf(0.5f * eff, 0.5f * eff, part);  // |p_eff|^2 of the operand the MMA really sees
+    }
+    part += __shfl_xor_sync(0xffffffffu, part, 1);
+    part += __shfl_xor_sync(0xffffffffu, part, 2);
+    if ((t & 3) == 0) pn[j] = part;
+  }
+  __syncthreads();
+  if (t < CN) {
+    X h, m, l;
+    split3<X>(pn[t], h, m, l);
+    const X one = Fmt<X>::from(1.0f), zero = Fmt<X>::from(0.0f);
+    const bool live = t < n;
+    for (int k = 0; k < 16; ++k) {
+      X v = zero;
+      if (live) v = k == 0 ? h : k == 1 ? m : k == 2 ? l : k < 6 ? one : zero;
+      *reinterpret_cast<uint16_t*>(img + OFF_BN + norm_off(t, k)) = bits16(v);
+    }
+  }
+  if (last_w != nullptr) {
+    const float sc = act_kind == SPS_ACT_LOG ? 0.69314718055994531f : 1.0f;  // the epilogue produces log2
+    for (int idx = t; idx < ct.kp * CN; idx += blockDim.x) {
+      const int k = idx / CN, j = idx % CN;
+      const float v = (k < K && j < n) ? sc * __ldg(last_w + (size_t)k * P + p0 + j) : 0.0f;
+      *reinterpret_cast<uint16_t*>(img + OFF_W2 + sw128_off(k, j)) = bits16(Fmt<X>::from(v));
+    }
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Forward kernel
+// ---------------------------------------------------------------------------------------------
+struct FwdParams {
+  HeadShape s;
+  ChunkTable ct;
+  const float* z;
+  const unsigned char* img;
+  float* logits;
+  float* dist;
+  float* act;
+  int n_tiles;
+};
+
+constexpr int NTHREADS = 512;
+constexpr int MAX_NST = 8;                   // prototype-chunk ring depth is chosen at launch (2..MAX_NST)
+constexpr int A_HI = TILE_M * 128;           // 16384
+constexpr int A_NORM = TILE_M * 32;          // 4096
+constexpr int P_BYTES = TILE_M * 128;        // 16384
+constexpr int TMEM_S0 = 0, TMEM_L0 = 2 * CN; // S double buffer at columns [0,128), logits after it
+
+template <int NSPLIT> __host__ __device__ constexpr int a_buf_bytes() { return (NSPLIT == 3 ? 2 : 1) * A_HI + A_NORM; }
+
+// shared memory plan: [A x2][P x2][B ring x nst][barriers]; offsets are computed, not tabulated, so that
+// a run-time buffer index never turns into a local-memory lookup
+struct SmemPlan {
+  int a_stride, p0, b0, b_stride, nst, bar_off, total;
+  __host__ __device__ int a_off(int i) const { return i * a_stride; }
+  __host__ __device__ int p_off(int i) const { return p0 + i * P_BYTES; }
+  __host__ __device__ int b_off(int i) const { return b0 + i * b_stride; }
+};
+template <int NSPLIT> __host__ __device__ inline SmemPlan smem_plan(int img_bytes) {
+  SmemPlan pl;
+  pl.a_stride = a_buf_bytes<NSPLIT>();
+  pl.p0 = 2 * pl.a_stride;
+  pl.b0 = pl.p0 + 2 * P_BYTES;
+  pl.b_stride = (img_bytes + 1023) / 1024 * 1024;
+  int nst = (227 * 1024 - 512 - 1024 - pl.b0) / pl.b_stride;
+  pl.nst = nst > MAX_NST ? MAX_NST : nst;
+  pl.bar_off = pl.b0 + pl.nst * pl.b_stride;
+  pl.total = pl.bar_off + 512 + 1024;  // barriers + slack to align the base to 1024
+  return pl;
+}
+
+// barrier indices
+enum { BAR_AFULL = 0, BAR_AEMPTY = 2, BAR_BFULL = 4, BAR_BEMPTY = 4 + MAX_NST, BAR_SFULL = 4 + 2 * MAX_NST,
+       BAR_SEMPTY = 6 + 2 * MAX_NST, BAR_PFULL = 8 + 2 * MAX_NST, BAR_PEMPTY = 10 + 2 * MAX_NST, BAR_LFULL = 12 + 2 * MAX_NST,
+       BAR_LEMPTY = 14 + 2 * MAX_NST, BAR_COUNT = 16 + 2 * MAX_NST };
+
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float lg2_approx(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
+template <typename X, int NSPLIT>
+__global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_constant__ FwdParams prm) {
+  extern __shared__ unsigned char smem_raw[];
+  const HeadShape& s = prm.s;
+  const ChunkTable& ct = prm.ct;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  unsigned char* gbase = smem_raw + (base - smem_u32(smem_raw));
+  const SmemPlan pl = smem_plan<NSPLIT>(ct.img_bytes);
+  const uint32_t bar0 = base + pl.bar_off;
+  auto bar = [&](int i) { return bar0 + 8u * (uint32_t)i; };
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + pl.bar_off + 8 * BAR_COUNT);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int NC = ct.n_chunks, KP = ct.kp, NST = pl.nst;
+  const bool has_w = KP > 0;
+  uint32_t tmem_cols = 32;
+  while ((int)tmem_cols < TMEM_L0 + 2 * KP) tmem_cols <<= 1;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar(BAR_AFULL + i), 4);    // one arrive per loader warp
+      mbar_init(bar(BAR_AEMPTY + i), 1);   // tcgen05.commit
+      mbar_init(bar(BAR_SFULL + i), 1);    // tcgen05.commit
+      mbar_init(bar(BAR_SEMPTY + i), 8);   // one arrive per epilogue warp
+      mbar_init(bar(BAR_PFULL + i), 8);
+      mbar_init(bar(BAR_PEMPTY + i), 1);
+      mbar_init(bar(BAR_LFULL + i), 1);
+      mbar_init(bar(BAR_LEMPTY + i), 4);   // epilogue warps 4..7 read the logits
+    }
+    for (int i = 0; i < MAX_NST; ++i) {
+      mbar_init(bar(BAR_BFULL + i), 1);
+      mbar_init(bar(BAR_BEMPTY + i), 1);
+    }
+    mbar_fence_init();
+  }
+  if (warp == 0) tmem_alloc(smem_u32((const void*)tmem_slot), tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  const int my_tiles = prm.n_tiles > (int)blockIdx.x ? (prm.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+
+  if (warp == 0) {
+    // ================================ MMA issuer ================================
+    // The whole warp walks the loop (waits are warp-uniform); one elected lane issues.  Keeping the warp
+    // converged matters: a lone lane spinning while its 31 siblings sit in the final barrier was scheduled
+    // at a fraction of the issue rate.
+    {
+      constexpr uint32_t ID1 = idesc_f16(Fmt<X>::id, TILE_M, CN);
+      const uint32_t ID2 = idesc_f16(Fmt<X>::id, TILE_M, KP);
+      const int U = my_tiles * NC;
+      uint32_t acount = 0;
+      for (int i = 0; i <= U; ++i) {
+        if (i < U) {  // distance GEMM of unit i
+          const int c = i % NC;
+          const bool first_of_scale = c == 0 || ct.scale[c] != ct.scale[c - 1];
+          const bool last_of_scale = c == NC - 1 || ct.scale[c + 1] != ct.scale[c];
+          const uint32_t ab = acount & 1, st = i % NST, sb = i & 1;
+          if (first_of_scale) mbar_wait(bar(BAR_AFULL + ab), (acount >> 1) & 1);
+          mbar_wait(bar(BAR_BFULL + st), (i / NST) & 1);
+          mbar_wait(bar(BAR_SEMPTY + sb), ((i >> 1) & 1) ^ 1);
+          tc_fence_after();
+          if (lane == 0) {
+            const uint32_t a_hi = base + pl.a_off(ab), a_lo = a_hi + A_HI;
+            const uint32_t a_n = a_hi + (NSPLIT == 3 ? 2 : 1) * A_HI;
+            const uint32_t b_hi = base + pl.b_off(st) + OFF_BHI, b_lo = base + pl.b_off(st) + OFF_BLO;
+            const uint32_t b_n = base + pl.b_off(st) + OFF_BN;
+            const uint32_t d = tmem + TMEM_S0 + sb * CN;
+            mma_f16(d, desc_noswz(a_n, NORM_LBO, NORM_SBO), desc_noswz(b_n, NORM_LBO, NORM_SBO), ID1, 0);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_hi + 32 * k), desc_sw128(b_hi + 32 * k), ID1, 1);
+            if (NSPLIT == 3) {
+#pragma unroll
+              for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_hi + 32 * k), desc_sw128(b_lo + 32 * k), ID1, 1);
+#pragma unroll
+              for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_lo + 32 * k), desc_sw128(b_hi + 32 * k), ID1, 1);
+            }
+            if (last_of_scale) mma_commit(bar(BAR_AEMPTY + ab));
+            mma_commit(bar(BAR_SFULL + sb));
+            if (!has_w) mma_commit(bar(BAR_BEMPTY + st));
+            TL(0, i);
+          }
+          __syncwarp();
+          if (last_of_scale) ++acount;
+        }
+        if (i > 0 && has_w) {  // logits GEMM of unit i-1
+          const int u = i - 1, c = u % NC, tl = u / NC;
+          const uint32_t pb = u & 1, st = u % NST, lb = tl & 1;
+          if (c == 0) mbar_wait(bar(BAR_LEMPTY + lb), ((tl >> 1) & 1) ^ 1);
+          mbar_wait(bar(BAR_PFULL + pb), (u >> 1) & 1);
+          tc_fence_after();
+          if (lane == 0) {
+            TL(1, u);
+            const uint32_t pa = base + pl.p_off(pb), w2 = base + pl.b_off(st) + OFF_W2;
+            const uint32_t d = tmem + TMEM_L0 + lb * KP;
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              mma_f16(d, desc_sw128(pa + 32 * k), desc_sw128(w2 + 32 * k), ID2, (c > 0 || k > 0) ? 1 : 0);
+            mma_commit(bar(BAR_PEMPTY + pb));
+            mma_commit(bar(BAR_BEMPTY + st));
+            if (c == NC - 1) mma_commit(bar(BAR_LFULL + lb));
+          }
+          __syncwarp();
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ================================ prototype-chunk producer ================================
+    {
+      const int U = my_tiles * NC;
+      const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128, bytes_n = CN * 32, bytes_w = KP * 128;
+      for (int i = 0; i < U; ++i) {
+        const int c = i % NC, st = i % NST;
+        mbar_wait(bar(BAR_BEMPTY + st), ((i / NST) & 1) ^ 1);
+        if (lane == 0) {
+          mbar_arrive_expect_tx(bar(BAR_BFULL + st), bytes_b + bytes_n + bytes_w);
+          const unsigned char* src = prm.img + (size_t)c * ct.img_bytes;
+          const uint32_t dst = base + pl.b_off(st);
+          bulk_g2s(dst + OFF_BHI, src + OFF_BHI, bytes_b, bar(BAR_BFULL + st));
+          bulk_g2s(dst + OFF_BN, src + OFF_BN, bytes_n, bar(BAR_BFULL + st));
+          if (has_w) bulk_g2s(dst + OFF_W2, src + OFF_W2, bytes_w, bar(BAR_BFULL + st));
+        }
+        __syncwarp();
+      }
+    }
+  } else if (warp >= 12) {
+    // ================================ feature-tile loaders ================================
+    const int m = threadIdx.x - 12 * 32;  // row of the tile
+    uint32_t acount = 0;
+    for (int ti = 0; ti < my_tiles; ++ti) {
+      const long long n = ((long long)blockIdx.x + (long long)ti * gridDim.x) * TILE_M + m;
+      const bool valid = n < s.N;
+      const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
+      const float* zrow = prm.z + b * (long long)s.C * s.HW + pix;
+      for (int c = 0; c < NC; ++c) {
+        if (!(c == 0 || ct.scale[c] != ct.scale[c - 1])) continue;
+        const int sc = ct.scale[c];
+        const uint32_t ab = acount & 1;
+        mbar_wait(bar(BAR_AEMPTY + ab), ((acount >> 1) & 1) ^ 1);
+        if (m == 0) TL(2, acount);
+        unsigned char* a_hi = gbase + pl.a_off(ab);
+        unsigned char* a_lo = a_hi + A_HI;
+        unsigned char* a_n = a_hi + (NSPLIT == 3 ? 2 : 1) * A_HI;
+        const float* zs = zrow + (long long)sc * s.D * s.HW;
+        float zn = 0.f;
+        float v[64];
+#pragma unroll
+        for (int k = 0; k < 64; ++k) v[k] = (valid && k < s.D) ? __ldg(zs + (long long)k * s.HW) : 0.0f;
+#pragma unroll
+        for (int g = 0; g < 8; ++g) {
+          uint32_t hw[4], lw[4];
+#pragma unroll
+          for (int q = 0; q < 4; ++q) {
+            const float v0 = v[g * 8 + 2 * q], v1 = v[g * 8 + 2 * q + 1];
+            hw[q] = Pack2<X>::pack(v0, v1);
+            float2 e = Pack2<X>::unpack(hw[q]);
+            if (NSPLIT == 3) {
+              lw[q] = Pack2<X>::pack(v0 - e.x, v1 - e.y);
+              const float2 el = Pack2<X>::unpack(lw[q]);
+              e.x += el.x;
+              e.y += el.y;
+            }
+            zn = fmaf(e.x, e.x, zn);
+            zn = fmaf(e.y, e.y, zn);
+          }
+          const uint32_t off = (uint32_t)m * 128u + ((((uint32_t)g) ^ ((uint32_t)m & 7u)) << 4);
+          *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+          if (NSPLIT == 3) *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+        }
+        {
+          X h, mm, l;
+          split3<X>(zn, h, mm, l);
+          const uint32_t one = bits16(Fmt<X>::from(1.0f));
+          const uint4 w0 = make_uint4(one | (one << 16), one | ((uint32_t)bits16(h) << 16),
+                                      (uint32_t)bits16(mm) | ((uint32_t)bits16(l) << 16), 0u);
+          *reinterpret_cast<uint4*>(a_n + norm_off(m, 0)) = w0;
+          *reinterpret_cast<uint4*>(a_n + norm_off(m, 8)) = make_uint4(0u, 0u, 0u, 0u);
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(BAR_AFULL + ab));
+        if (m == 0) TL(3, acount);
+        ++acount;
+      }
+    }
+  }
+  else if (warp >= 4) {
+    // ================================ epilogue ================================
+    const int ew = warp - 4, q = ew & 3, half = ew >> 2;  // q == warp % 4: the TMEM lane quarter this warp may read
+    const int m = q * 32 + lane;
+    const uint32_t lane_base = ((uint32_t)(q * 32)) << 16;
+    const float eps = s.eps, ome = 1.0f - s.eps;
+    const bool is_log = s.act_kind == SPS_ACT_LOG;
+    // Logits of tile `tj` (TMEM -> HBM).  Called one unit into the NEXT tile so that the epilogue never
+    // sits waiting for the last logits GEMM of a tile (the logits accumulator is double buffered).
+    auto store_logits = [&](int tj) {
+      const long long nn = ((long long)blockIdx.x + (long long)tj * gridDim.x) * TILE_M + m;
+      const uint32_t lb = tj & 1;
+      mbar_wait(bar(BAR_LFULL + lb), (tj >> 1) & 1);
+      tc_fence_after();
+      for (int k0 = 0; k0 < KP; k0 += 16) {
+        uint32_t lr[16];
+        tmem_ld16(tmem + lane_base + TMEM_L0 + lb * KP + k0, lr);
+        tmem_ld_wait();
+        if (nn < s.N) {
+#pragma unroll
+          for (int k = 0; k < 16; ++k)
+            if (k0 + k < s.K) prm.logits[nn * s.K + k0 + k] = __uint_as_float(lr[k]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(BAR_LEMPTY + lb));
+    };
+    const int defer_c = NC > 1 ? 1 : 0;
+    uint32_t u = 0;
+    for (int ti = 0; ti < my_tiles; ++ti) {
+      const long long n = ((long long)blockIdx.x + (long long)ti * gridDim.x) * TILE_M + m;
+      const bool valid = n < s.N;
+      const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
+      float* drow = prm.dist != nullptr ? prm.dist + b * (long long)s.P * s.HW + pix : nullptr;
+      float* arow = prm.act != nullptr ? prm.act + n * (long long)s.P : nullptr;
+      for (int c = 0; c < NC; ++c, ++u) {
+        const uint32_t sb = u & 1, pb = u & 1;
+        uint32_t r[32];
+        mbar_wait(bar(BAR_SFULL + sb), (u >> 1) & 1);
+        if (threadIdx.x == 128) TL(4, u);
+        tc_fence_after();
+        tmem_ld32(tmem + lane_base + TMEM_S0 + sb * CN + half * 32, r);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(BAR_SEMPTY + sb));
+        if (threadIdx.x == 128) TL(5, u);
+        const int col0 = half * 32, ncols = ct.n[c] - col0;  // live columns of this warp: [0, ncols)
+        const int p0 = ct.p0[c] + col0;
+        float av[32];  // log2 of the similarity ratio ('log'), or -d ('linear')
+        if (drow == nullptr && arow == nullptr) {  // fused mode: nothing but the logits leaves the SM
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float d = fmaxf(__uint_as_float(r[j]), 0.0f);
+            av[j] = is_log ? lg2_approx(fmaf(ome, rcp_approx(d + eps), 1.0f)) : -d;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float d = fmaxf(__uint_as_float(r[j]), 0.0f);
+            av[j] = is_log ? lg2_approx(fmaf(ome, rcp_approx(d + eps), 1.0f)) : -d;
+            if (drow != nullptr && valid && j < ncols) drow[(long long)(p0 + j) * s.HW] = d;
+          }
+          if (arow != nullptr && valid) {
+            const float sc = is_log ? 0.69314718055994531f : 1.0f;
+#pragma unroll
+            for (int j = 0; j < 32; ++j)
+              if (j < ncols) arow[p0 + j] = av[j] * sc;
+          }
+        }
+        if (threadIdx.x == 128) TL(6, u);
+        if (has_w) {
+          mbar_wait(bar(BAR_PEMPTY + pb), ((u >> 1) & 1) ^ 1);
+          unsigned char* prow = gbase + pl.p_off(pb) + (uint32_t)m * 128u;
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint32_t w[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) w[e] = Pack2<X>::pack(av[g * 8 + 2 * e], av[g * 8 + 2 * e + 1]);
+            *reinterpret_cast<uint4*>(prow + ((((uint32_t)(half * 4 + g)) ^ ((uint32_t)m & 7u)) << 4)) =
+                make_uint4(w[0], w[1], w[2], w[3]);
+          }
+          fence_proxy_async();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar(BAR_PFULL + pb));
+        }
+        if (threadIdx.x == 128) TL(7, u);
+        if (has_w && half == 0 && ti > 0 && c == defer_c) store_logits(ti - 1);
+      }
+    }
+    if (has_w && half == 0 && my_tiles > 0) store_logits(my_tiles - 1);
+  }
+
+  // ================================ teardown ================================
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 0) {
+    tc_fence_after();
+    tmem_dealloc(tmem, tmem_cols);
+  }
+}
+
+}  // namespace tc
+
+#ifdef SPS_TIMELINE
+extern "C" int sps_debug_timeline(long long* host, int count) {
+  return (int)cudaMemcpyFromSymbol(host, tc::g_tl, sizeof(long long) * (size_t)count);
+}
+#endif
+
+// ---------------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------------
+int build_chunk_table(const HeadShape& s, bool with_last_layer, tc::ChunkTable* ct) {
+  int nc = 0;
+  for (int sc = 0; sc < s.S; ++sc) {
+    for (int p0 = s.scale_lo[sc]; p0 < s.scale_lo[sc + 1]; p0 += tc::CN) {
+      SPS_REQUIRE(nc < tc::MAX_CHUNKS, SPS_ERR_UNSUPPORTED, "tensor-core head: more than %d prototype chunks (P=%d)",
+                  tc::MAX_CHUNKS, s.P);
+      ct->p0[nc] = p0;
+      ct->n[nc] = (short)(s.scale_lo[sc + 1] - p0 < tc::CN ? s.scale_lo[sc + 1] - p0 : tc::CN);
+      ct->scale[nc] = (short)sc;
+      ++nc;
+    }
+  }
+  ct->n_chunks = nc;
+  ct->kp = with_last_layer ? (s.K + 15) / 16 * 16 : 0;
+  ct->img_bytes = tc::chunk_img_bytes(ct->kp);
+  return SPS_OK;
+}
+
+size_t head_fwd_tc_workspace(const HeadShape& s) {
+  tc::ChunkTable ct;
+  if (build_chunk_table(s, true, &ct) != SPS_OK) return 0;
+  return (size_t)ct.n_chunks * ct.img_bytes + 1024;
+}
+
+template <typename X, int NSPLIT>
+static int launch_fwd_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const float* z, const float* protos,
+                           const float* last_w, float* logits, float* dist, float* act, unsigned char* img,
+                           cudaStream_t st) {
+  tc::proto_prep_kernel<X, NSPLIT><<<ct.n_chunks, 256, 0, st>>>(ct, s.D, s.P, s.K, s.act_kind, protos, last_w, img);
+  SPS_CUDA_TRY(cudaGetLastError());
+  count_launch();
+  tc::FwdParams prm;
+  prm.s = s;
+  prm.ct = ct;
+  prm.z = z;
+  prm.img = img;
+  prm.logits = logits;
+  prm.dist = dist;
+  prm.act = act;
+  prm.n_tiles = (int)((s.N + tc::TILE_M - 1) / tc::TILE_M);
+  const tc::SmemPlan pl = tc::smem_plan<NSPLIT>(ct.img_bytes);
+  SPS_REQUIRE(pl.nst >= 2 && pl.total <= 227 * 1024, SPS_ERR_UNSUPPORTED, "tensor-core head: %d bytes of shared memory needed (K=%d)",
+              pl.total, s.K);
+  SPS_CUDA_TRY(cudaFuncSetAttribute(tc::head_fwd_tc_kernel<X, NSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+  const int grid = prm.n_tiles < sm_count() ? prm.n_tiles : sm_count();
+  tc::head_fwd_tc_kernel<X, NSPLIT><<<grid, tc::NTHREADS, pl.total, st>>>(prm);
+  SPS_CUDA_TRY(cudaGetLastError());
+  count_launch();
+  return SPS_OK;
+}
+
+int launch_head_fwd_tc(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w,
+                       float* logits, float* dist, float* act, void* ws, size_t ws_bytes, cudaStream_t st) {
+  SPS_REQUIRE(s.D <= 64 && s.D % 8 == 0, SPS_ERR_UNSUPPORTED, "tensor-core head: D=%d must be a multiple of 8, <= 64", s.D);
+  SPS_REQUIRE(s.K <= 192, SPS_ERR_UNSUPPORTED, "tensor-core head: K=%d > 192 classes", s.K);
+  if (s.N == 0 || s.P == 0) return SPS_OK;
+  tc::ChunkTable ct;
+  int rc = build_chunk_table(s, last_w != nullptr, &ct);
+  if (rc != SPS_OK) return rc;
+  const size_t need = (size_t)ct.n_chunks * ct.img_bytes + 1024;
+  SPS_REQUIRE(ws != nullptr && ws_bytes >= need, SPS_ERR_WORKSPACE, "head_fwd workspace: need %zu bytes, got %zu", need,
+              ws_bytes);
+  unsigned char* img = reinterpret_cast<unsigned char*>(((uintptr_t)ws + 1023) & ~(uintptr_t)1023);
+  switch (math) {
+    case SPS_MATH_F16: return launch_fwd_tc_t<__half, 1>(s, ct, z, protos, last_w, logits, dist, act, img, st);
+    case SPS_MATH_F16X3: return launch_fwd_tc_t<__half, 3>(s, ct, z, protos, last_w, logits, dist, act, img, st);
+    case SPS_MATH_BF16: return launch_fwd_tc_t<__nv_bfloat16, 1>(s, ct, z, protos, last_w, logits, dist, act, img, st);
+    case SPS_MATH_BF16X3: return launch_fwd_tc_t<__nv_bfloat16, 3>(s, ct, z, protos, last_w, logits, dist, act, img, st);
+  }
+  SPS_REQUIRE(false, SPS_ERR_BAD_ARG, "math=%d is not a tensor-core mode", math);
+}
+
+}  // namespace sps

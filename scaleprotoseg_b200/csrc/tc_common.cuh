@@ -1,0 +1,226 @@
+// sm_100a primitives used by the tensor-core kernels: mbarrier, bulk async copy, tcgen05 (alloc /
+// mma / commit / ld), shared-memory matrix descriptors and the packed operand layouts shared by the
+// prototype pre-pass and the main kernels.
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_bf16.h>
+
+#include "common.cuh"
+
+namespace sps {
+namespace tc {
+
+// ---------------------------------------------------------------------------------------------
+// Addresses / barriers
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
+  uint32_t ok;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(ok)
+      : "r"(bar), "r"(parity)
+      : "memory");
+  return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
+  while (!mbar_try_wait(bar, parity)) {
+  }
+}
+
+// generic-proxy writes (st.shared) -> visible to the async proxy (tcgen05.mma / bulk copies)
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+// 1-D bulk copy global -> shared, completion counted on an mbarrier (UBLKCP). 16 B aligned, size % 16 == 0.
+__device__ __forceinline__ void bulk_g2s(uint32_t dst_smem, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(dst_smem),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t}"
+      : "=r"(pred));
+  return pred != 0;
+}
+
+__device__ __forceinline__ void named_bar_sync(int id, int nthreads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(nthreads) : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
+// tcgen05
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void tmem_alloc(uint32_t dst_smem, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(dst_smem), "r"(ncols) : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+
+// D[tmem] (+)= A[smem] * B[smem]^T, kind::f16 (fp16 or bf16 operands, fp32 accumulate). One thread issues.
+__device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+// Arrives on the mbarrier when every tcgen05 op issued so far by this thread has completed.
+// (implies tcgen05.fence::before_thread_sync)
+__device__ __forceinline__ void mma_commit(uint32_t bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
+
+// 32 lanes x 32 consecutive fp32 columns: thread t of the warp gets row (lane base + t).
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x32.b32"
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15,"
+      " %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15]), "=r"(r[16]),
+        "=r"(r[17]), "=r"(r[18]), "=r"(r[19]), "=r"(r[20]), "=r"(r[21]), "=r"(r[22]), "=r"(r[23]), "=r"(r[24]),
+        "=r"(r[25]), "=r"(r[26]), "=r"(r[27]), "=r"(r[28]), "=r"(r[29]), "=r"(r[30]), "=r"(r[31])
+      : "r"(taddr)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32"
+      "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr)
+      : "memory");
+}
+
+// ---------------------------------------------------------------------------------------------
+// Descriptors (bit layout: CUTLASS cute/arch/mma_sm100_desc.hpp; PTX ISA "tcgen05 matrix descriptor")
+// ---------------------------------------------------------------------------------------------
+// K-major operand tile, 128-byte swizzle: rows of 128 B, 8-row groups of 1024 B (SBO), base 1024-B aligned.
+__device__ __forceinline__ uint64_t desc_sw128(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) /*LBO (unused)*/ |
+         ((uint64_t)(1024 >> 4) << 32) /*SBO*/ | ((uint64_t)1 << 46) /*version*/ | ((uint64_t)2 << 61) /*SWIZZLE_128B*/;
+}
+// K-major operand, no swizzle, one 16-element K step: core matrices of 8 rows x 16 B; the two K halves are
+// `lbo` bytes apart, 8-row groups `sbo` bytes apart.
+__device__ __forceinline__ uint64_t desc_noswz(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(sbo >> 4) << 32) |
+         ((uint64_t)1 << 46);
+}
+// kind::f16 instruction descriptor: fp32 accumulate, A and B K-major, dense.
+enum : uint32_t { FMT_F16 = 0, FMT_BF16 = 1 };
+__host__ __device__ constexpr uint32_t idesc_f16(uint32_t fmt, int M, int N) {
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+}
+
+// byte offset of element (row r, k) inside a SW128 K-major tile of 2-byte elements with 64 k per row
+__host__ __device__ __forceinline__ uint32_t sw128_off(int r, int k) {
+  return (uint32_t)r * 128u + ((((uint32_t)k >> 3) ^ ((uint32_t)r & 7u)) << 4) + (((uint32_t)k & 7u) << 1);
+}
+// byte offset of element (row r, k<16) inside the no-swizzle 16-wide "norm" tile (LBO 128, SBO 256)
+__host__ __device__ __forceinline__ uint32_t norm_off(int r, int k) {
+  return (uint32_t)(r & 7) * 16u + (uint32_t)(r >> 3) * 256u + (uint32_t)(k >> 3) * 128u + (uint32_t)(k & 7) * 2u;
+}
+constexpr uint32_t NORM_LBO = 128, NORM_SBO = 256;
+
+// ---------------------------------------------------------------------------------------------
+// 16-bit operand formats.  X = __half or __nv_bfloat16.
+// ---------------------------------------------------------------------------------------------
+template <typename X> struct Fmt;
+template <> struct Fmt<__half> {
+  static constexpr uint32_t id = FMT_F16;
+  static __device__ __forceinline__ __half from(float v) { return __float2half_rn(v); }
+  static __device__ __forceinline__ float to(__half v) { return __half2float(v); }
+};
+template <> struct Fmt<__nv_bfloat16> {
+  static constexpr uint32_t id = FMT_BF16;
+  static __device__ __forceinline__ __nv_bfloat16 from(float v) { return __float2bfloat16_rn(v); }
+  static __device__ __forceinline__ float to(__nv_bfloat16 v) { return __bfloat162float(v); }
+};
+template <typename X> __device__ __forceinline__ uint16_t bits16(X v) { return *reinterpret_cast<uint16_t*>(&v); }
+
+// Two fp32 -> one packed 32-bit word of 16-bit values (lo = a, hi = b) with ONE F2FP instruction (the scalar
+// conversions go through the XU pipe, which the log-similarity epilogue already saturates), and back.
+template <typename X> struct Pack2;
+template <> struct Pack2<__half> {
+  static __device__ __forceinline__ uint32_t pack(float a, float b) {
+    __half2 h = __floats2half2_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+  static __device__ __forceinline__ float2 unpack(uint32_t w) { return __half22float2(*reinterpret_cast<__half2*>(&w)); }
+};
+template <> struct Pack2<__nv_bfloat16> {
+  static __device__ __forceinline__ uint32_t pack(float a, float b) {
+    __nv_bfloat162 h = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&h);
+  }
+  static __device__ __forceinline__ float2 unpack(uint32_t w) {
+    return make_float2(__uint_as_float(w << 16), __uint_as_float(w & 0xFFFF0000u));
+  }
+};
+
+// v ~= h + m + l with three 16-bit terms (used for the squared norms that ride in the extra K step)
+template <typename X> __device__ __forceinline__ void split3(float v, X& h, X& m, X& l) {
+  h = Fmt<X>::from(v);
+  float r = v - Fmt<X>::to(h);
+  m = Fmt<X>::from(r);
+  r -= Fmt<X>::to(m);
+  l = Fmt<X>::from(r);
+}
+
+// ---------------------------------------------------------------------------------------------
+// Prototype chunks.  The prototypes of every scale are cut into chunks of <= CN rows; the pre-pass writes
+// one packed image per chunk that the main kernels bulk-copy straight into shared memory:
+//   [Bhi  CN x 128 B  SW128]  rows j: -2 * p_(p0+j)            (hi part)
+//   [Blo  CN x 128 B  SW128]  lo part (zeros in the single-term modes)
+//   [Bn   CN x  32 B  noswz]  k=0..2: |p|^2 split in three; k=3..5: 1; rest 0
+//   [W2   KP x 128 B  SW128]  rows k: ln2 * W[k, p0+j]  ('log'; W itself for 'linear'); only with a last layer
+// ---------------------------------------------------------------------------------------------
+constexpr int CN = 64;          // prototypes per chunk (MMA N of the distance GEMM, K of the logits GEMM)
+constexpr int MAX_CHUNKS = 160;
+constexpr int TILE_M = 128;     // positions per tile (MMA M)
+
+struct ChunkTable {
+  int n_chunks;
+  int kp;                       // classes padded to a multiple of 16 (0: no last layer)
+  int img_bytes;                // bytes of one packed chunk image
+  int p0[MAX_CHUNKS];
+  short n[MAX_CHUNKS];
+  short scale[MAX_CHUNKS];
+};
+
+__host__ __device__ inline int chunk_img_bytes(int kp) { return 2 * CN * 128 + CN * 32 + kp * 128; }
+constexpr int OFF_BHI = 0, OFF_BLO = CN * 128, OFF_BN = 2 * CN * 128, OFF_W2 = 2 * CN * 128 + CN * 32;
+
+}  // namespace tc
+}  // namespace sps

@@ -13,7 +13,7 @@ from typing import List, Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import ACT_LINEAR, ACT_LOG, MATH_BF16, MATH_FP32, MATH_TF32, SpsGroupDesc, SpsHeadDesc
+from ._lib import ACT_LINEAR, ACT_LOG, MATH_BF16, MATH_BF16X3, MATH_F16, MATH_F16X3, MATH_FP32, SpsGroupDesc, SpsHeadDesc
 
 _DEFAULT_MATH = MATH_FP32
 
@@ -108,9 +108,11 @@ def head_forward_raw(z, protos, last_w, cfg: HeadConfig, want_dist: bool, want_a
     if want_act:
         act = torch.empty((N, P), device=z.device, dtype=torch.float32)
     desc = make_desc(cfg, B, H, W, D, P)
+    nbytes = int(lib.sps_head_fwd_workspace_bytes(C.byref(desc)))
+    ws = torch.empty(nbytes, device=z.device, dtype=torch.uint8) if nbytes else None
     with torch.cuda.device(z.device):
         _lib.check(lib.sps_head_fwd(C.byref(desc), _ptr(z), _ptr(protos), _ptr(last_w), _ptr(logits), _ptr(dist),
-                                    _ptr(act), _stream()), "sps_head_fwd")
+                                    _ptr(act), _ptr(ws), nbytes, _stream()), "sps_head_fwd")
     return logits, dist, act
 
 

@@ -36,12 +36,12 @@ def test_version_and_validation(built_lib):
     for i in range(9):
         d.scale_lo[i] = min(i, 4) * 6
     d.scale_lo[4] = 23  # does not end at P
-    rc = built_lib.sps_head_fwd(C.byref(d), None, None, None, None, None, None, None)
+    rc = built_lib.sps_head_fwd(C.byref(d), None, None, None, None, None, None, None, 0, None)
     assert rc == 1 and b"scale_lo" in built_lib.sps_last_error()
     d.scale_lo[4] = 24
     for i in range(5, 9):
         d.scale_lo[i] = 24
-    rc = built_lib.sps_head_fwd(C.byref(d), None, None, None, None, None, None, None)
+    rc = built_lib.sps_head_fwd(C.byref(d), None, None, None, None, None, None, None, 0, None)
     assert rc == 1 and b"NULL" in built_lib.sps_last_error()
     assert built_lib.sps_workspace_bytes(C.byref(d)) > 0
 
