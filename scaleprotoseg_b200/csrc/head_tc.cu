@@ -13,9 +13,11 @@
 // Work decomposition: a tile is 128 consecutive positions (rows n = (b*H + h)*W + w, the order of
 // permute(0,2,3,1).reshape(-1,P), :369-370); the prototypes of each scale (ragged ranges allowed, :400-432)
 // are cut into chunks of 64.  One persistent CTA per SM walks tiles; inside a tile it walks the chunks.
-// Warp roles: warp 0 = MMA issuer (one thread), warp 1 = prototype-chunk producer (bulk async copies of the
-// packed images written by the pre-pass), warps 4-11 = epilogue (two per TMEM lane quarter, 32 columns
-// each), warps 12-15 = feature-tile loaders (NCHW fp32 -> 16-bit K-major swizzled tiles + row norms).
+// Warp roles: warps 0-7 = epilogue (two per TMEM lane quarter, 32 columns each), warps 8-11 = feature-tile
+// loaders (NCHW fp32 -> 16-bit K-major swizzled tiles + row norms), warp 12 = prototype-chunk producer (bulk
+// async copies of the packed images written by the pre-pass), warp 13 = distance-GEMM issuer, warp 14 =
+// logits-GEMM issuer (one lane of each issues; tcgen05 work of one thread executes in issue order, so two
+// issuers keep the two dependency chains from blocking each other).
 #include "tc_common.cuh"
 
 namespace sps {
@@ -106,7 +108,8 @@ struct FwdParams {
   int n_tiles;
 };
 
-constexpr int NTHREADS = 512;
+constexpr int NTHREADS = 480;
+constexpr int WARP_EPI0 = 0, WARP_LOAD0 = 8, WARP_PROD = 12, WARP_MMA = 13, WARP_MMA2 = 14;
 constexpr int MAX_NST = 8;                   // prototype-chunk ring depth is chosen at launch (2..MAX_NST)
 constexpr int A_HI = TILE_M * 128;           // 16384
 constexpr int A_NORM = TILE_M * 32;          // 4096
@@ -187,7 +190,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
     }
     mbar_fence_init();
   }
-  if (warp == 0) tmem_alloc(smem_u32((const void*)tmem_slot), tmem_cols);
+  if (warp == WARP_MMA) tmem_alloc(smem_u32((const void*)tmem_slot), tmem_cols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
@@ -195,71 +198,75 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
 
   const int my_tiles = prm.n_tiles > (int)blockIdx.x ? (prm.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
 
-  if (warp == 0) {
-    // ================================ MMA issuer ================================
-    // The whole warp walks the loop (waits are warp-uniform); one elected lane issues.  Keeping the warp
-    // converged matters: a lone lane spinning while its 31 siblings sit in the final barrier was scheduled
-    // at a fraction of the issue rate.
-    {
-      constexpr uint32_t ID1 = idesc_f16(Fmt<X>::id, TILE_M, CN);
+  if (warp == WARP_MMA) {
+    // ================================ distance-GEMM issuer ================================
+    // The whole warp walks the loop (waits are warp-uniform); one lane issues.  The two GEMMs have their own
+    // issuer warps: with a single issuer the distance GEMM of unit i+1 queued behind the wait for the
+    // epilogue of unit i-1, and the epilogue starved (timeline in profiles/).
+    constexpr uint32_t ID1 = idesc_f16(Fmt<X>::id, TILE_M, CN);
+    const int U = my_tiles * NC;
+    uint32_t acount = 0;
+    int c = 0;
+    for (int i = 0; i < U; ++i) {
+      const bool first_of_scale = c == 0 || ct.scale[c] != ct.scale[c - 1];
+      const bool last_of_scale = c == NC - 1 || ct.scale[c + 1] != ct.scale[c];
+      const uint32_t ab = acount & 1, st = i % NST, sb = i & 1;
+      if (first_of_scale) mbar_wait(bar(BAR_AFULL + ab), (acount >> 1) & 1);
+      mbar_wait(bar(BAR_BFULL + st), (i / NST) & 1);
+      mbar_wait(bar(BAR_SEMPTY + sb), ((i >> 1) & 1) ^ 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t a_hi = base + pl.a_off(ab), a_lo = a_hi + A_HI;
+        const uint32_t a_n = a_hi + (NSPLIT == 3 ? 2 : 1) * A_HI;
+        const uint32_t b_hi = base + pl.b_off(st) + OFF_BHI, b_lo = base + pl.b_off(st) + OFF_BLO;
+        const uint32_t b_n = base + pl.b_off(st) + OFF_BN;
+        const uint32_t d = tmem + TMEM_S0 + sb * CN;
+        mma_f16(d, desc_noswz(a_n, NORM_LBO, NORM_SBO), desc_noswz(b_n, NORM_LBO, NORM_SBO), ID1, 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_hi + 32 * k), desc_sw128(b_hi + 32 * k), ID1, 1);
+        if (NSPLIT == 3) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_hi + 32 * k), desc_sw128(b_lo + 32 * k), ID1, 1);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_lo + 32 * k), desc_sw128(b_hi + 32 * k), ID1, 1);
+        }
+        mma_commit(bar(BAR_SFULL + sb));
+        if (last_of_scale) mma_commit(bar(BAR_AEMPTY + ab));
+        if (!has_w) mma_commit(bar(BAR_BEMPTY + st));
+        TL(0, i);
+      }
+      __syncwarp();
+      if (last_of_scale) ++acount;
+      if (++c == NC) c = 0;
+    }
+  } else if (warp == WARP_MMA2) {
+    // ================================ logits-GEMM issuer ================================
+    if (has_w) {
       const uint32_t ID2 = idesc_f16(Fmt<X>::id, TILE_M, KP);
       const int U = my_tiles * NC;
-      uint32_t acount = 0;
-      for (int i = 0; i <= U; ++i) {
-        if (i < U) {  // distance GEMM of unit i
-          const int c = i % NC;
-          const bool first_of_scale = c == 0 || ct.scale[c] != ct.scale[c - 1];
-          const bool last_of_scale = c == NC - 1 || ct.scale[c + 1] != ct.scale[c];
-          const uint32_t ab = acount & 1, st = i % NST, sb = i & 1;
-          if (first_of_scale) mbar_wait(bar(BAR_AFULL + ab), (acount >> 1) & 1);
-          mbar_wait(bar(BAR_BFULL + st), (i / NST) & 1);
-          mbar_wait(bar(BAR_SEMPTY + sb), ((i >> 1) & 1) ^ 1);
-          tc_fence_after();
-          if (lane == 0) {
-            const uint32_t a_hi = base + pl.a_off(ab), a_lo = a_hi + A_HI;
-            const uint32_t a_n = a_hi + (NSPLIT == 3 ? 2 : 1) * A_HI;
-            const uint32_t b_hi = base + pl.b_off(st) + OFF_BHI, b_lo = base + pl.b_off(st) + OFF_BLO;
-            const uint32_t b_n = base + pl.b_off(st) + OFF_BN;
-            const uint32_t d = tmem + TMEM_S0 + sb * CN;
-            mma_f16(d, desc_noswz(a_n, NORM_LBO, NORM_SBO), desc_noswz(b_n, NORM_LBO, NORM_SBO), ID1, 0);
+      int c = 0, tl = 0;
+      for (int u = 0; u < U; ++u) {
+        const uint32_t pb = u & 1, st = u % NST, lb = tl & 1;
+        if (c == 0) mbar_wait(bar(BAR_LEMPTY + lb), ((tl >> 1) & 1) ^ 1);
+        mbar_wait(bar(BAR_PFULL + pb), (u >> 1) & 1);
+        tc_fence_after();
+        if (lane == 0) {
+          TL(1, u);
+          const uint32_t pa = base + pl.p_off(pb), w2 = base + pl.b_off(st) + OFF_W2;
+          const uint32_t d = tmem + TMEM_L0 + lb * KP;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_hi + 32 * k), desc_sw128(b_hi + 32 * k), ID1, 1);
-            if (NSPLIT == 3) {
-#pragma unroll
-              for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_hi + 32 * k), desc_sw128(b_lo + 32 * k), ID1, 1);
-#pragma unroll
-              for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_lo + 32 * k), desc_sw128(b_hi + 32 * k), ID1, 1);
-            }
-            if (last_of_scale) mma_commit(bar(BAR_AEMPTY + ab));
-            mma_commit(bar(BAR_SFULL + sb));
-            if (!has_w) mma_commit(bar(BAR_BEMPTY + st));
-            TL(0, i);
-          }
-          __syncwarp();
-          if (last_of_scale) ++acount;
+          for (int k = 0; k < 4; ++k)
+            mma_f16(d, desc_sw128(pa + 32 * k), desc_sw128(w2 + 32 * k), ID2, (c > 0 || k > 0) ? 1 : 0);
+          mma_commit(bar(BAR_PEMPTY + pb));
+          mma_commit(bar(BAR_BEMPTY + st));
+          if (c == NC - 1) mma_commit(bar(BAR_LFULL + lb));
+          TL(2, u);
         }
-        if (i > 0 && has_w) {  // logits GEMM of unit i-1
-          const int u = i - 1, c = u % NC, tl = u / NC;
-          const uint32_t pb = u & 1, st = u % NST, lb = tl & 1;
-          if (c == 0) mbar_wait(bar(BAR_LEMPTY + lb), ((tl >> 1) & 1) ^ 1);
-          mbar_wait(bar(BAR_PFULL + pb), (u >> 1) & 1);
-          tc_fence_after();
-          if (lane == 0) {
-            TL(1, u);
-            const uint32_t pa = base + pl.p_off(pb), w2 = base + pl.b_off(st) + OFF_W2;
-            const uint32_t d = tmem + TMEM_L0 + lb * KP;
-#pragma unroll
-            for (int k = 0; k < 4; ++k)
-              mma_f16(d, desc_sw128(pa + 32 * k), desc_sw128(w2 + 32 * k), ID2, (c > 0 || k > 0) ? 1 : 0);
-            mma_commit(bar(BAR_PEMPTY + pb));
-            mma_commit(bar(BAR_BEMPTY + st));
-            if (c == NC - 1) mma_commit(bar(BAR_LFULL + lb));
-          }
-          __syncwarp();
-        }
+        __syncwarp();
+        if (++c == NC) { c = 0; ++tl; }
       }
     }
-  } else if (warp == 1) {
+  } else if (warp == WARP_PROD) {
     // ================================ prototype-chunk producer ================================
     {
       const int U = my_tiles * NC;
@@ -278,9 +285,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
         __syncwarp();
       }
     }
-  } else if (warp >= 12) {
+  } else if (warp >= WARP_LOAD0 && warp < WARP_PROD) {
     // ================================ feature-tile loaders ================================
-    const int m = threadIdx.x - 12 * 32;  // row of the tile
+    const int m = threadIdx.x - WARP_LOAD0 * 32;  // row of the tile
     uint32_t acount = 0;
     for (int ti = 0; ti < my_tiles; ++ti) {
       const long long n = ((long long)blockIdx.x + (long long)ti * gridDim.x) * TILE_M + m;
@@ -292,7 +299,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
         const int sc = ct.scale[c];
         const uint32_t ab = acount & 1;
         mbar_wait(bar(BAR_AEMPTY + ab), ((acount >> 1) & 1) ^ 1);
-        if (m == 0) TL(2, acount);
         unsigned char* a_hi = gbase + pl.a_off(ab);
         unsigned char* a_lo = a_hi + A_HI;
         unsigned char* a_n = a_hi + (NSPLIT == 3 ? 2 : 1) * A_HI;
@@ -334,14 +340,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(BAR_AFULL + ab));
-        if (m == 0) TL(3, acount);
         ++acount;
       }
     }
   }
-  else if (warp >= 4) {
+  else if (warp < WARP_LOAD0) {
     // ================================ epilogue ================================
-    const int ew = warp - 4, q = ew & 3, half = ew >> 2;  // q == warp % 4: the TMEM lane quarter this warp may read
+    const int ew = warp - WARP_EPI0, q = ew & 3, half = ew >> 2;  // q == warp % 4: the TMEM lane quarter this warp may read
     const int m = q * 32 + lane;
     const uint32_t lane_base = ((uint32_t)(q * 32)) << 16;
     const float eps = s.eps, ome = 1.0f - s.eps;
@@ -379,14 +384,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
         const uint32_t sb = u & 1, pb = u & 1;
         uint32_t r[32];
         mbar_wait(bar(BAR_SFULL + sb), (u >> 1) & 1);
-        if (threadIdx.x == 128) TL(4, u);
+        if (threadIdx.x == 0) TL(4, u);
         tc_fence_after();
         tmem_ld32(tmem + lane_base + TMEM_S0 + sb * CN + half * 32, r);
         tmem_ld_wait();
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(BAR_SEMPTY + sb));
-        if (threadIdx.x == 128) TL(5, u);
+        if (threadIdx.x == 0) TL(5, u);
         const int col0 = half * 32, ncols = ct.n[c] - col0;  // live columns of this warp: [0, ncols)
         const int p0 = ct.p0[c] + col0;
         float av[32];  // log2 of the similarity ratio ('log'), or -d ('linear')
@@ -410,7 +415,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
               if (j < ncols) arow[p0 + j] = av[j] * sc;
           }
         }
-        if (threadIdx.x == 128) TL(6, u);
+        if (threadIdx.x == 0) TL(6, u);
         if (has_w) {
           mbar_wait(bar(BAR_PEMPTY + pb), ((u >> 1) & 1) ^ 1);
           unsigned char* prow = gbase + pl.p_off(pb) + (uint32_t)m * 128u;
@@ -426,7 +431,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
           __syncwarp();
           if (lane == 0) mbar_arrive(bar(BAR_PFULL + pb));
         }
-        if (threadIdx.x == 128) TL(7, u);
+        if (threadIdx.x == 0) TL(7, u);
+        if (lane == 0) TL(3, 8 * u + ew);
         if (has_w && half == 0 && ti > 0 && c == defer_c) store_logits(ti - 1);
       }
     }
@@ -436,7 +442,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
   // ================================ teardown ================================
   tc_fence_before();
   __syncthreads();
-  if (warp == 0) {
+  if (warp == WARP_MMA) {
     tc_fence_after();
     tmem_dealloc(tmem, tmem_cols);
   }

@@ -16,8 +16,9 @@ lib = _lib.load()
 buf = (ctypes.c_longlong * 8192)()
 lib.sps_debug_timeline.argtypes = [ctypes.c_void_p, ctypes.c_int]
 print("rc", lib.sps_debug_timeline(buf, 8192))
-tl = [[buf[r * 1024 + e] for e in range(64)] for r in range(8)]
-t0 = min(v for r in tl for v in r if v > 0)
-names = ["mma1_issued", "mma2_pfull_seen", "load_start", "load_done", "epi_sfull", "epi_ld_done", "epi_math_done", "epi_unit_done"]
-for e in range(48):
-    print(e, " ".join(f"{names[r][:12]}={tl[r][e]-t0 if tl[r][e] else -1:7d}" for r in range(8)))
+g = lambda r, e: buf[r * 1024 + e]
+t0 = min(v for v in buf if v > 0)
+f = lambda v: f"{v - t0:6d}" if v else "    -1"
+for u in range(16, 30):
+    print(u, "mma1", f(g(0, u)), "| pfull", f(g(1, u)), "mma2", f(g(2, u)),
+          "| epi sfull", f(g(4, u)), "ld", f(g(5, u)), "math", f(g(6, u)), "done/warp", " ".join(f(g(3, 8*u+w)) for w in range(8)))
