@@ -1,0 +1,393 @@
+#!/usr/bin/env python
+"""bench.py — the ScaleProtoSeg prototype-head hot path on B200 (contract in DESIGN.md §Measurement).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--math f16x3|f16|bf16|bf16x3|fp32]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
+        bench.py --gpus N --steps K --warmup W
+
+A step is one forward+backward of the stage-1 prototype head over one synthetic batch (BASELINE.json
+configs[1]: B=16 maps of 256x65x65, P=760 prototypes in 4 scales, K=19 classes, fused mode: no
+distance / activation map is written to HBM).  Rank 0 prints ONE JSON line.
+
+  value        positions x prototypes per second, forward+backward, whole job (N independent replicas),
+               inputs resident in HBM, CUDA-event timed, max over ranks
+  e2e          the same metric through the public API (PrototypeHeadFn autograd) with the batch in pinned HOST
+               memory: H2D of z, D2H of logits and of the prototype / last-layer gradients inside the timed region
+  roofline     the dominant kernel phase against MEASURED_PEAKS.json
+  cpu_baseline the CPU oracle (port of the reference head, torch CPU, all host threads) on a bounded sample
+  push         secondary metric: patches/s of the push scan over 3000 Cityscapes-shaped maps sharded over N ranks
+`--impl reference` times the CPU port of the reference head on the host cores (rank 0 only).
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+import torch  # noqa: E402
+
+SEED = 20220227
+C2 = dict(B=16, H=65, W=65, S=4, D=64, P=760, K=19)       # BASELINE.json configs[1]
+PUSH = dict(n_maps=3000, H=129, W=257, P=760, K=19)         # configs[3], the reference's full-res push map
+CPU_SAMPLE_B = 1                                            # maps per CPU step (bounded sample)
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--math", default="f16x3", choices=["fp32", "bf16", "bf16x3", "f16", "f16x3"])
+    ap.add_argument("--no-push", action="store_true", help="skip the secondary push measurement")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--push-maps", type=int, default=PUSH["n_maps"])
+    return ap.parse_args()
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        d = json.load(open(path))
+        return dict(hbm=float(d["hbm_gbs"]), tensor_burst=float(d["bf16_tflops"]),
+                    tensor_sustained=float(d.get("bf16_tflops_sustained", d["bf16_tflops"])), source="measured")
+    return dict(hbm=6650.0, tensor_burst=1590.0, tensor_sustained=1400.0, source="fallback")
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.stop_flag, self.th = index, [], False, None
+
+    def _run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                parts = [p.strip() for p in out.strip().split(",")]
+                if len(parts) >= 6:
+                    self.rows.append(parts)
+            except Exception:
+                pass
+            time.sleep(0.05)
+
+    def start(self):
+        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th.start()
+
+    def stop(self):
+        self.stop_flag = True
+        if self.th is not None:
+            self.th.join(timeout=10)
+        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
+        mx = [int(r[1]) for r in self.rows if r[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.rows)}
+
+
+MATH = {"fp32": 0, "bf16x3": 1, "bf16": 2, "f16": 3, "f16x3": 4}
+N_SETS = 4   # rotating input sets: 4 x 69 MB of z > 126 MB of L2, so no step re-reads a cached batch
+
+
+def make_head_inputs(dev, gen_seed):
+    """SURVEY 8(d) synthetic inputs: z = sigmoid(randn), prototypes U[0,1), last layer +1 / -0.5."""
+    from oracle import head_oracle as ho  # synthetic-input helpers only
+    c = C2
+    g = torch.Generator(device=dev).manual_seed(gen_seed)
+    zs = [torch.sigmoid(torch.randn(c["B"], c["S"] * c["D"], c["H"], c["W"], device=dev, generator=g)) for _ in range(N_SETS)]
+    protos = torch.rand(c["P"], c["D"], 1, 1, device=dev, generator=g)
+    ident = ho.make_identity(c["P"], c["K"], c["S"])
+    last_w = ho.make_last_layer(ident).contiguous().to(dev)
+    n = c["B"] * c["H"] * c["W"]
+    dls = [torch.randn(n, c["K"], device=dev, generator=g) / n for _ in range(N_SETS)]
+    return zs, protos, last_w, dls, ident
+
+
+def event_ms(fn, iters, stream=None):
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record()
+    for i in range(iters):
+        fn(i)
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def run_ours(args):
+    import torch.distributed as dist
+    import scaleprotoseg_b200 as sps
+    from scaleprotoseg_b200 import _lib, push as spush
+    from oracle import head_oracle as ho
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device: there is no CPU fallback for the product path"
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    if not os.path.exists(_lib.LIB_PATH):
+        import __graft_entry__ as ge
+        ge.build()
+    lib = _lib.load()
+    c = C2
+    math = MATH[args.math]
+    cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(c["P"], c["S"]), c["K"], math=math)
+    # backward: the tensor-core backward when the library has one for this mode, else the fp32 CUDA-core kernels
+    cfg_bwd = cfg if getattr(sps, "HAS_TC_BACKWARD", False) else sps.HeadConfig.from_ranges(
+        ho.uniform_ranges(c["P"], c["S"]), c["K"], math=sps.MATH_FP32)
+    zs, protos, last_w, dls, ident = make_head_inputs(dev, SEED + rank)
+    p2 = protos.view(c["P"], c["D"])
+    units = c["B"] * c["H"] * c["W"] * c["P"]           # (position, prototype) pairs per step per GPU
+
+    def fwd(i):
+        return sps.head_forward_raw(zs[i % N_SETS], p2, last_w, cfg, False, False)[0]
+
+    def bwd(i):
+        return sps.head_backward_raw(zs[i % N_SETS], p2, last_w, cfg_bwd, dls[i % N_SETS], None, None, True, True, True)
+
+    def step(i):
+        fwd(i)
+        bwd(i)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    barrier()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = int(lib.sps_launch_count())
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    e0.record()
+    for i in range(args.steps):
+        step(i)
+    e1.record()
+    barrier()
+    launches = int(lib.sps_launch_count()) - l0
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    ms_per_step = ms.item() / args.steps
+    value = world * units / (ms_per_step * 1e-3)
+
+    # per-phase device time (rank 0 reports): which kernel dominates, and its roofline
+    t_fwd = event_ms(fwd, args.steps)
+    t_bwd = event_ms(bwd, args.steps)
+    clocks = sampler.stop() if rank == 0 else None
+    return dict(world=world, rank=rank, dev=dev, dist=dist, sps=sps, spush=spush, lib=lib, ho=ho, cfg=cfg, cfg_bwd=cfg_bwd,
+                zs=zs, protos=protos, p2=p2, last_w=last_w, dls=dls, ident=ident, units=units, ms_per_step=ms_per_step,
+                value=value, launches=launches, t_fwd=t_fwd, t_bwd=t_bwd, clocks=clocks, barrier=barrier)
+
+
+def measure_e2e(ctx, args):
+    """fwd+bwd through the public autograd API with HOST buffers: H2D of the batch, D2H of logits + parameter grads."""
+    sps, dev, c = ctx["sps"], ctx["dev"], C2
+    n = c["B"] * c["H"] * c["W"]
+    z_host = [z.cpu().pin_memory() for z in ctx["zs"][:2]]
+    dl_host = [d.cpu().pin_memory() for d in ctx["dls"][:2]]
+    logits_host = torch.empty(n, c["K"]).pin_memory()
+    dp_host = torch.empty(c["P"], c["D"], 1, 1).pin_memory()
+    dw_host = torch.empty(c["K"], c["P"]).pin_memory()
+    protos = ctx["protos"].clone().requires_grad_(True)
+    last_w = ctx["last_w"].clone().requires_grad_(True)
+
+    def step(i):
+        z = z_host[i % 2].to(dev, non_blocking=True).requires_grad_(True)   # dz is produced too (goes to the backbone)
+        dl = dl_host[i % 2].to(dev, non_blocking=True)
+        protos.grad = last_w.grad = None
+        logits, _, _ = sps.PrototypeHeadFn.apply(z, protos, last_w, ctx["cfg"], False, False)
+        logits.backward(dl)
+        logits_host.copy_(logits.detach(), non_blocking=True)
+        dp_host.copy_(protos.grad, non_blocking=True)
+        dw_host.copy_(last_w.grad, non_blocking=True)
+
+    for i in range(3):
+        step(i)
+    ctx["barrier"]()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        step(i)
+    e1.record()
+    ctx["barrier"]()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if ctx["world"] > 1:
+        ctx["dist"].all_reduce(ms, op=ctx["dist"].ReduceOp.MAX)
+    per = ms.item() / args.steps
+    h2d = z_host[0].numel() * 4 + dl_host[0].numel() * 4
+    d2h = (logits_host.numel() + dp_host.numel() + dw_host.numel()) * 4
+    return {"value": ctx["world"] * ctx["units"] / (per * 1e-3), "unit": "positions*prototypes/s", "ms_per_step": per,
+            "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h}
+
+
+def measure_push(ctx, args):
+    """Push scan (configs[3]): n_maps Cityscapes-shaped maps sharded over the ranks, one min all-reduce of packed keys."""
+    sps, spush, ho, dev, world, rank = ctx["sps"], ctx["spush"], ctx["ho"], ctx["dev"], ctx["world"], ctx["rank"]
+    p = PUSH
+    per_rank = (args.push_maps + world - 1) // world
+    lo = rank * per_rank
+    n_local = max(0, min(args.push_maps, lo + per_rank) - lo)
+    pool = min(n_local, 64)            # distinct resident maps (64 x 34 MB = 2.2 GB >> L2), cycled to cover the shard
+    g = torch.Generator(device=dev).manual_seed(SEED + 17 * rank)
+    z = torch.sigmoid(torch.randn(pool, 256, p["H"], p["W"], device=dev, generator=g))
+    labels = torch.stack([ho.make_labels(lo + i, p["H"], p["W"], p["K"], absent_class=3) for i in range(pool)]).to(torch.int16).to(dev)
+    cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(p["P"], 4), p["K"], math=ctx["cfg"].math if PUSH_TC(sps) else sps.MATH_FP32)
+    pc = spush.proto_class_of(ctx["ident"]).to(dev)
+    keys = torch.empty(n_local, p["P"], device=dev, dtype=torch.int64)
+    batch = 16
+
+    def scan_all():
+        for i in range(0, n_local, batch):
+            b = min(batch, n_local - i)
+            j = i % pool
+            if j + b > pool:
+                j = 0
+            spush.scan_maps(z[j:j + b], labels[j:j + b], ctx["protos"], pc, cfg, keys_out=keys[i:i + b])
+        best = spush.reduce_keys(keys, lo)
+        if world > 1:
+            ctx["dist"].all_reduce(best, op=ctx["dist"].ReduceOp.MIN)
+        return best
+
+    scan_all()
+    ctx["barrier"]()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    scan_all()
+    e1.record()
+    ctx["barrier"]()
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    if world > 1:
+        ctx["dist"].all_reduce(ms, op=ctx["dist"].ReduceOp.MAX)
+    patches = args.push_maps * p["H"] * p["W"]
+    return {"value": patches / (ms.item() * 1e-3), "unit": "patches/s", "ms": ms.item(), "scaling": "strong",
+            "workload": f"{args.push_maps} maps 256x{p['H']}x{p['W']} fp32, P={p['P']}, sharded {world}-way, "
+                        f"{pool} distinct resident maps per rank cycled, one NCCL min all-reduce of {p['P']} packed keys",
+            "math": "fp32" if cfg.math == 0 else args.math}
+
+
+def PUSH_TC(sps):
+    return bool(getattr(sps, "HAS_TC_PUSH", False))
+
+
+def cpu_head_step(ho, z, protos, last_w, ranges, dl):
+    zr, pr, wr = z.clone().requires_grad_(True), protos.clone().requires_grad_(True), last_w.clone().requires_grad_(True)
+    logits, _, _ = ho.head_stage1(zr, pr, ranges, wr)
+    logits.backward(dl)
+    return logits
+
+
+def measure_cpu(steps, warmup):
+    """The CPU port of the reference head (oracle/head_oracle.py: same op sequence as model_multiscale.py:256-388),
+    fwd+bwd on CPU_SAMPLE_B maps per step, all host threads."""
+    from oracle import head_oracle as ho
+    c = C2
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    g = torch.Generator().manual_seed(SEED)
+    z = torch.sigmoid(torch.randn(CPU_SAMPLE_B, c["S"] * c["D"], c["H"], c["W"], generator=g))
+    protos = torch.rand(c["P"], c["D"], 1, 1, generator=g)
+    last_w = ho.make_last_layer(ho.make_identity(c["P"], c["K"], c["S"])).contiguous()
+    ranges = ho.uniform_ranges(c["P"], c["S"])
+    n = CPU_SAMPLE_B * c["H"] * c["W"]
+    dl = (torch.randn(n, c["K"], generator=g) / n).view(CPU_SAMPLE_B, c["H"], c["W"], c["K"])
+    for _ in range(warmup):
+        cpu_head_step(ho, z, protos, last_w, ranges, dl)
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        cpu_head_step(ho, z, protos, last_w, ranges, dl)
+    dt = (time.perf_counter() - t0) / steps
+    units = n * c["P"]
+    return {"value": units / dt, "unit": "positions*prototypes/s", "cores": cores, "kind": "port",
+            "sample": f"{CPU_SAMPLE_B} map(s) of 256x{c['H']}x{c['W']} per step, P={c['P']}, K={c['K']}, fp32 torch CPU, "
+                      f"{steps} steps after {warmup} warm-up", "ms_per_step": dt * 1e3}
+
+
+def config_dict(args, world):
+    c = C2
+    return {"workload": f"ScaleProtoSeg Cityscapes head fwd+bwd (BASELINE.json configs[1]): B={c['B']} maps 256x{c['H']}x{c['W']} "
+                        f"fp32 NCHW, P={c['P']} (4 scales x 190), K={c['K']}, D={c['D']}; fused mode (logits + dz, dprototypes, dW; "
+                        f"no distance map in HBM)",
+            "replicas": world, "l2": f"{N_SETS} rotating input sets ({N_SETS} x 69 MB z > 126 MB L2)", "math": args.math}
+
+
+def main():
+    args = parse_args()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    base = {"metric": "feature-positions x prototypes per second, prototype head fwd+bwd", "unit": "positions*prototypes/s",
+            "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "data": "synthetic", "config": config_dict(args, world)}
+    if args.impl == "reference":
+        if rank != 0:
+            return
+        steps = max(1, min(args.steps, 10))
+        cpu = measure_cpu(steps, max(1, min(args.warmup, 2)))
+        out = dict(base)
+        out.update({"impl": "reference", "value": cpu["value"], "ms_per_step": cpu["ms_per_step"], "dtype": "f32",
+                    "steps": steps, "cpu_baseline": cpu, "gpu_launches": 0,
+                    "e2e": {"value": cpu["value"], "unit": cpu["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
+        print(json.dumps(out), flush=True)
+        return
+
+    ctx = run_ours(args)
+    e2e = measure_e2e(ctx, args)
+    push = None if args.no_push else measure_push(ctx, args)
+    if ctx["world"] > 1:
+        ctx["barrier"]()
+    if rank != 0:
+        if ctx["world"] > 1:
+            ctx["dist"].destroy_process_group()
+        return
+    c, pk = C2, peaks()
+    n = c["B"] * c["H"] * c["W"]
+    # dominant phase and its roofline (algorithmic counts: SURVEY 8(d), restated in DESIGN.md)
+    phases = {
+        "forward (head_fwd_tc_kernel)": dict(ms=ctx["t_fwd"], flops=ctx["units"] * (2 * c["D"] + 2 * c["K"]),
+                                             bytes=n * (c["S"] * c["D"] * 4 + 4 * c["K"])),
+        "backward (head_bwd kernels)": dict(ms=ctx["t_bwd"], flops=ctx["units"] * (4 * c["D"] + 4 * c["K"]),
+                                            bytes=n * (2 * c["S"] * c["D"] * 4 + 4 * c["K"])),
+    }
+    name = max(phases, key=lambda k: phases[k]["ms"])
+    ph = phases[name]
+    t = ph["ms"] * 1e-3
+    tensor_frac = ph["flops"] / t / 1e12 / pk["tensor_sustained"]
+    hbm_frac = ph["bytes"] / t / 1e9 / pk["hbm"]
+    if tensor_frac >= hbm_frac:
+        roof = {"bound": "tensor", "achieved": ph["flops"] / t / 1e12, "peak": pk["tensor_sustained"], "unit": "TFLOP/s", "frac": tensor_frac}
+    else:
+        roof = {"bound": "hbm", "achieved": ph["bytes"] / t / 1e9, "peak": pk["hbm"], "unit": "GB/s", "frac": hbm_frac}
+    roof.update({"kernel": name, "ms_per_launch": ph["ms"], "peak_source": pk["source"] + " (sustained bf16 / copy)", "traffic": None,
+                 "phases_ms": {k: v["ms"] for k, v in phases.items()}, "tensor_frac": tensor_frac, "hbm_frac": hbm_frac})
+    out = dict(base)
+    out.update({"value": ctx["value"], "ms_per_step": ctx["ms_per_step"], "dtype": args.math + " operands, f32 accumulate",
+                "clocks": ctx["clocks"], "e2e": e2e, "gpu_launches": ctx["launches"], "roofline": roof})
+    if push is not None:
+        out["push"] = push
+    if not args.no_cpu and ctx["world"] == 1:
+        out["cpu_baseline"] = measure_cpu(8, 2)
+    if ctx["world"] > 1:
+        ctx["dist"].destroy_process_group()
+    print(json.dumps(out), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -71,6 +71,7 @@ int launch_group_fwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
   SPS_CUDA_TRY(cudaFuncSetAttribute(group_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   long long tiles = (s.N + GTM - 1) / GTM;
   group_fwd_kernel<<<(unsigned)tiles, GNT, smem, st>>>(s, g, act, groups, logits);
+  count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;
 }
@@ -167,6 +168,7 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
   SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_pos_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   long long tiles = (s.N + GTM - 1) / GTM;
   group_bwd_pos_kernel<<<(unsigned)tiles, GNT, smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre);
+  count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   long long split = (s.N + 255) / 256;
   if (split > 64) split = 64;
@@ -174,11 +176,13 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
   if (dG != nullptr) {
     dim3 grid(g.Kc, (unsigned)split);
     group_bwd_dG_kernel<<<grid, 128, 0, st>>>(s, g, act, ws_dpre, dG);
+    count_launch();
     SPS_CUDA_TRY(cudaGetLastError());
   }
   if (dWg != nullptr && dlogits != nullptr) {
     dim3 grid((s.K * Gt + 255) / 256, (unsigned)split);
     group_bwd_dWg_kernel<<<grid, 256, 0, st>>>(s, Gt, dlogits, ws_groups, dWg);
+    count_launch();
     SPS_CUDA_TRY(cudaGetLastError());
   }
   return SPS_OK;

@@ -103,6 +103,7 @@ static int launch_fwd_t(const HeadShape& s, const float* z, const float* protos,
   SPS_CUDA_TRY(cudaFuncSetAttribute(head_fwd_simt_kernel<KACC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   long long tiles = (s.N + TM - 1) / TM;
   head_fwd_simt_kernel<KACC><<<(unsigned)tiles, NT, smem, st>>>(s, z, protos, last_w, logits, dist, act);
+  count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;
 }
@@ -424,6 +425,7 @@ static int launch_dp_t(const HeadShape& s, int nsplit, const float* z, const flo
   SPS_CUDA_TRY(cudaFuncSetAttribute(head_bwd_dp_kernel<KACC>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid(count_chunks(s), nsplit);
   head_bwd_dp_kernel<KACC><<<grid, NT, smem, st>>>(s, z, protos, last_w, dlogits, ddist, dact, part_dp, part_dw);
+  count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;
 }
@@ -439,6 +441,7 @@ int launch_head_bwd_simt(const HeadShape& s, int flags, const float* z, const fl
     SPS_CUDA_TRY(cudaFuncSetAttribute(head_bwd_dz_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     long long tiles = (s.N + TM - 1) / TM;
     head_bwd_dz_kernel<<<(unsigned)tiles, NT, smem, st>>>(s, z, protos, last_w, dlogits, ddist, dact, dz);
+    count_launch();
     SPS_CUDA_TRY(cudaGetLastError());
   }
   const bool want_dw = dlast_w != nullptr && last_w != nullptr && dlogits != nullptr;
@@ -460,10 +463,12 @@ int launch_head_bwd_simt(const HeadShape& s, int flags, const float* z, const fl
     if (dprotos != nullptr) {
       long long cnt = (long long)s.P * s.D;
       reduce_partials_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(part_dp, nsplit, cnt, dprotos);
+      count_launch();
     }
     if (want_dw) {
       long long cnt = (long long)s.K * s.P;
       reduce_partials_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(part_dw, nsplit, cnt, dlast_w);
+      count_launch();
     }
     SPS_CUDA_TRY(cudaGetLastError());
   }

@@ -94,12 +94,14 @@ int launch_push_scan_simt(const HeadShape& s, const float* z, const float* proto
   if (count == 0) return SPS_OK;
   const unsigned long long init = ((unsigned long long)0x501502F9u) << 32;  // bits(1e10f)
   fill_keys_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(keys, count, init);
+  count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   if (s.HW == 0) return SPS_OK;
   size_t smem = fwd_smem_bytes(0);
   SPS_CUDA_TRY(cudaFuncSetAttribute(push_scan_simt_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   dim3 grid((s.HW + TM - 1) / TM, s.B);
   push_scan_simt_kernel<<<grid, NT, smem, st>>>(s, z, protos, labels, proto_class, keys);
+  count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;
 }
@@ -126,6 +128,7 @@ int launch_push_reduce(const unsigned long long* keys, int n_maps, int P, uint32
   if (split > 128) split = 128;
   dim3 grid((P + 127) / 128, split);
   push_reduce_kernel<<<grid, 128, 0, st>>>(keys, n_maps, P, map_base, best);
+  count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;
 }
@@ -149,6 +152,7 @@ int launch_push_gather(const HeadShape& s, const float* z, const unsigned long l
                        float* out, cudaStream_t st) {
   if (s.P == 0 || n_maps == 0) return SPS_OK;
   push_gather_kernel<<<s.P, 64, 0, st>>>(s, z, keys, best, n_maps, map_base, proto_scale, out);
+  count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;
 }
