@@ -11,6 +11,8 @@ from .head import (GroupHeadFn, HeadConfig, PrototypeHeadFn, build_group_tables,
 from .install import install, install_on_classes, install_push, uninstall
 from . import model_api, push
 
+HAS_TC_BACKWARD = True   # sps_head_bwd runs the tcgen05 backward for the fused-mode step in the 16-bit math modes
+
 __all__ = ["install", "install_on_classes", "install_push", "uninstall", "HeadConfig", "PrototypeHeadFn",
            "GroupHeadFn", "head_forward_raw", "head_backward_raw", "build_group_tables", "set_default_math",
            "default_math", "push", "model_api", "MATH_FP32", "MATH_BF16", "MATH_BF16X3", "MATH_F16", "MATH_F16X3", "ACT_LOG", "ACT_LINEAR",

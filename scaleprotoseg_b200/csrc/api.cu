@@ -74,7 +74,9 @@ size_t sps_head_fwd_workspace_bytes(const SpsHeadDesc* desc) {
 size_t sps_workspace_bytes(const SpsHeadDesc* desc) {
   if (validate_desc(desc) != SPS_OK) return 0;
   HeadShape s = make_shape(desc);
-  return head_bwd_simt_workspace(s, desc->flags);
+  size_t a = head_bwd_simt_workspace(s, desc->flags);
+  size_t b = desc->math != SPS_MATH_FP32 ? head_bwd_tc_workspace(s) : 0;
+  return a > b ? a : b;
 }
 
 int sps_head_fwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w, float* logits,
@@ -100,6 +102,10 @@ int sps_head_bwd(const SpsHeadDesc* desc, const float* z, const float* protos, c
   SPS_REQUIRE(z != nullptr && protos != nullptr, SPS_ERR_BAD_ARG, "z/protos NULL");
   SPS_REQUIRE(dlogits == nullptr || last_w != nullptr, SPS_ERR_BAD_ARG, "dlogits given without last_w");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  // fused-mode step (upstream gradient = dlogits only) in a tensor-core math mode: tcgen05 backward;
+  // gradients arriving through the dense maps (ddist / dact) or SPS_MATH_FP32: exact-operand CUDA-core kernels
+  if (head_bwd_tc_supported(s, desc->math, last_w, dlogits, ddist, dact))
+    return launch_head_bwd_tc(s, desc->math, z, protos, last_w, dlogits, dz, dprotos, dlast_w, workspace, workspace_bytes, st);
   return launch_head_bwd_simt(s, desc->flags, z, protos, last_w, dlogits, ddist, dact, dz, dprotos, dlast_w, workspace,
                               workspace_bytes, st);
 }

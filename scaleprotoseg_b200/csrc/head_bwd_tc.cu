@@ -1,0 +1,585 @@
+// Tensor-core prototype head (sm_100a): fused backward for the fused-mode step (upstream gradient = dlogits).
+// What autograd derives from segmentation/model/model_multiscale.py:256-281, 324-330, 243-244 of the reference;
+// d and a are recomputed from z and the prototypes instead of being read back from saved (N x P) maps.
+//
+//   S   = |z|^2 - 2 z.p + |p|^2            distance GEMM, as in the forward                     (tcgen05, K-major)
+//   dA  = dlogits . W                       [128 n x 64 p] = DL[128 x 32k] . W3[64 x 32k]^T     (tcgen05, SW64 tiles)
+//   d = max(S,0);  a' = -(1-eps)/((d+1)(d+eps));  a = log((d+1)/(d+eps));  gamma = [S>0] dA a'   (epilogue)
+//   dz_s  += gamma . (-2 p)                 [128 n x 64 c], K = prototypes: B = the SAME packed prototype tile,
+//                                           read as an MN-major operand                           (tcgen05)
+//   dp^T  += gamma^T . z_s                  [64 p x 64 c], K = positions: gamma and z tiles read MN-major (M = 64)
+//   dW^T  += a^T . dlogits                  [64 p x 32 k], K = positions                         (M = 64, lanes +16)
+//   csum  += gamma^T . 1                    [64 p x 8]: the ones live in the z tile's norm columns
+//   dz = (acc + 2 z sum_p gamma)/G,  dp = (2 p csum - 2 acc)/G,  dW = ln2 acc / G
+//
+// One CTA owns ONE scale (up to 3 prototype chunks of 64) and a strided set of position tiles, so the dp / dW /
+// csum accumulators of its chunks stay in TMEM for the whole kernel and dz of a (tile, scale) is complete inside
+// the CTA: no atomics on dz.  Partial dp / dW of the CTAs of a scale go to the workspace and a fixed-order
+// second pass adds them (deterministic).  dlogits is scaled by a power of two G (from its max) so that the 16-bit
+// gamma / dlogits tiles stay in the normal range; G is divided out at the end (exact).
+//
+// TMEM (512 columns): S x2 [0,128), dA x2 [128,256), dz [256,320), chunk j accumulators [320+64j, 384+64j):
+//   lanes 0-15 (+32q): dp^T 64 columns; lanes 16-31 (+32q): dW^T columns [0,32), csum columns [32,40).
+#include "tc_common.cuh"
+
+namespace sps {
+namespace tcb {
+using namespace sps::tc;
+
+constexpr int GROUP_CHUNKS = 3;   // chunks per CTA (TMEM budget)
+constexpr int MAX_GROUPS = 64;
+constexpr int KP_BWD = 32;        // classes padded (this kernel: K <= 32)
+constexpr int BIMG = CN * 128 + CN * 32 + CN * 64;   // per chunk: BH 8 KB | BN 2 KB | W3 4 KB
+constexpr int BOFF_BH = 0, BOFF_BN = CN * 128, BOFF_W3 = CN * 128 + CN * 32;
+
+struct GroupTable {
+  int n_groups;
+  int c0[MAX_GROUPS];        // first chunk
+  short nch[MAX_GROUPS];     // chunks in the group (1..3)
+  short scale[MAX_GROUPS];
+  short cta0[MAX_GROUPS];    // first CTA of the group
+  short ncta[MAX_GROUPS];    // CTAs working on the group
+  short multi[MAX_GROUPS];   // 1: the scale is shared by several groups -> dz is accumulated with atomics
+};
+
+struct BwdParams {
+  HeadShape s;
+  ChunkTable ct;
+  GroupTable gt;
+  const float* z;
+  const float* protos;
+  const float* dlogits;
+  const unsigned char* img;     // packed chunk images (BIMG each)
+  const unsigned int* amax_bits;  // max |dlogits| as float bits
+  float* dz;
+  float* part_dp;               // [nsplit][P*D]
+  float* part_dw;               // [nsplit][K*P]
+  int n_tiles;
+};
+
+template <typename X>
+__global__ void __launch_bounds__(256) bwd_prep_kernel(const __grid_constant__ ChunkTable ct, int D, int P, int K,
+                                                        const float* __restrict__ protos, const float* __restrict__ last_w,
+                                                        unsigned char* __restrict__ img_base) {
+  const int c = blockIdx.x, t = threadIdx.x;
+  const int p0 = ct.p0[c], n = ct.n[c];
+  unsigned char* img = img_base + (size_t)c * BIMG;
+  __shared__ float pn[CN];
+  {
+    const int j = t >> 2, kq = (t & 3) * 16;
+    float part = 0.f;
+#pragma unroll
+    for (int kk = 0; kk < 16; ++kk) {
+      const int k = kq + kk;
+      const float v = (j < n && k < D) ? -2.0f * __ldg(protos + (size_t)(p0 + j) * D + k) : 0.0f;
+      const X hi = Fmt<X>::from(v);
+      const float eff = Fmt<X>::to(hi);
+      *reinterpret_cast<uint16_t*>(img + BOFF_BH + sw128_off(j, k)) = bits16(hi);
+      part = fmaf(0.5f * eff, 0.5f * eff, part);
+    }
+    part += __shfl_xor_sync(0xffffffffu, part, 1);
+    part += __shfl_xor_sync(0xffffffffu, part, 2);
+    if ((t & 3) == 0) pn[j] = part;
+  }
+  __syncthreads();
+  if (t < CN) {
+    X h, m, l;
+    split3<X>(pn[t], h, m, l);
+    const X one = Fmt<X>::from(1.0f), zero = Fmt<X>::from(0.0f);
+    const bool live = t < n;
+    for (int k = 0; k < 16; ++k) {
+      X v = zero;
+      if (live) v = k == 0 ? h : k == 1 ? m : k == 2 ? l : k < 6 ? one : zero;
+      *reinterpret_cast<uint16_t*>(img + BOFF_BN + norm_off(t, k)) = bits16(v);
+    }
+  }
+  for (int idx = t; idx < CN * KP_BWD; idx += blockDim.x) {
+    const int j = idx / KP_BWD, k = idx % KP_BWD;
+    const float v = (k < K && j < n) ? __ldg(last_w + (size_t)k * P + p0 + j) : 0.0f;
+    *reinterpret_cast<uint16_t*>(img + BOFF_W3 + sw64_off(j, k)) = bits16(Fmt<X>::from(v));
+  }
+}
+
+__global__ void amax_kernel(const float* __restrict__ x, long long count, unsigned int* __restrict__ out) {
+  float m = 0.f;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x)
+    m = fmaxf(m, fabsf(__ldg(x + i)));
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+  if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out, __float_as_uint(m));
+}
+
+// power-of-two scale that brings max|dlogits| to [2^-5, 2^-4)
+__device__ __forceinline__ float grad_scale(unsigned int amax_bits) {
+  const float a = __uint_as_float(amax_bits);
+  if (!(a > 0.f) || !isfinite(a)) return 1.0f;
+  int e;
+  frexpf(a, &e);  // a = f * 2^e, f in [0.5, 1)
+  int g = -4 - e;
+  g = g > 100 ? 100 : (g < -100 ? -100 : g);
+  return ldexpf(1.0f, g);
+}
+
+constexpr int NTHREADS = 480;
+constexpr int WARP_LOAD0 = 8, WARP_I1 = 12, WARP_I2 = 13, WARP_RES = 14;
+constexpr int A_BUF = TILE_M * 128 + TILE_M * 32 + TILE_M * 64;   // z tile 16 KB | norm 4 KB | DL tile 8 KB
+constexpr int AOFF_Z = 0, AOFF_N = TILE_M * 128, AOFF_DL = TILE_M * 128 + TILE_M * 32;
+constexpr int G_BUF = 2 * TILE_M * 128;                            // gamma tile 16 KB | a tile 16 KB
+constexpr int SM_RES = 0;                                          // resident chunk images: 3 * BIMG (42 KB)
+constexpr int SM_A = (GROUP_CHUNKS * BIMG + 1023) / 1024 * 1024;
+constexpr int SM_G = SM_A + 2 * A_BUF;
+constexpr int SM_SG = SM_G + 2 * G_BUF;                            // sgbuf[2 parity][2 half][128] floats
+constexpr int SM_BAR = SM_SG + 2 * 2 * 128 * 4;
+constexpr int SM_TOTAL = SM_BAR + 256 + 1024;
+constexpr int T_S = 0, T_DA = 128, T_DZ = 256, T_ACC = 320;
+enum { B_AFULL = 0, B_AEMPTY = 2, B_SFULL = 4, B_SEMPTY = 6, B_GFULL = 8, B_GEMPTY = 10, B_DZFULL = 12, B_DZEMPTY = 13,
+       B_RES = 14, B_ACC = 15, B_COUNT = 16 };
+
+template <typename X>
+__global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_constant__ BwdParams prm) {
+  extern __shared__ unsigned char smem_raw[];
+  const HeadShape& s = prm.s;
+  const ChunkTable& ct = prm.ct;
+  const GroupTable& gt = prm.gt;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  unsigned char* gbase = smem_raw + (base - smem_u32(smem_raw));
+  auto bar = [&](int i) { return base + SM_BAR + 8u * (uint32_t)i; };
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + SM_BAR + 8 * B_COUNT);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+  // which group (scale + up to 3 chunks) and which tiles this CTA owns
+  int g = 0;
+  while (g + 1 < gt.n_groups && (int)blockIdx.x >= gt.cta0[g + 1]) ++g;
+  const int cta_local = (int)blockIdx.x - gt.cta0[g], ncta = gt.ncta[g];
+  const int nch = gt.nch[g], c0 = gt.c0[g], sc = gt.scale[g];
+  const bool multi = gt.multi[g] != 0;
+  const int my_tiles = prm.n_tiles > cta_local ? (prm.n_tiles - 1 - cta_local) / ncta + 1 : 0;
+  const int U = my_tiles * nch;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar(B_AFULL + i), 4);
+      mbar_init(bar(B_AEMPTY + i), 9);   // 8 epilogue warps (dz read z from smem) + 1 commit (dp GEMM read it)
+      mbar_init(bar(B_SFULL + i), 1);
+      mbar_init(bar(B_SEMPTY + i), 8);
+      mbar_init(bar(B_GFULL + i), 8);
+      mbar_init(bar(B_GEMPTY + i), 1);
+    }
+    mbar_init(bar(B_DZFULL), 1);
+    mbar_init(bar(B_DZEMPTY), 8);
+    mbar_init(bar(B_RES), 1);
+    mbar_init(bar(B_ACC), 1);
+    mbar_fence_init();
+  }
+  if (warp == WARP_I1) tmem_alloc(smem_u32((const void*)tmem_slot), 512);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+  constexpr uint32_t FM = Fmt<X>::id;
+
+  if (warp == WARP_RES) {
+    if (lane == 0) {
+      mbar_arrive_expect_tx(bar(B_RES), (uint32_t)nch * BIMG);
+      for (int j = 0; j < nch; ++j)
+        bulk_g2s(base + SM_RES + j * BIMG, prm.img + (size_t)(c0 + j) * BIMG, BIMG, bar(B_RES));
+    }
+  } else if (warp == WARP_I1) {
+    // ================= issuer 1: distance GEMM + dA GEMM of every unit =================
+    constexpr uint32_t ID = idesc_f16(FM, TILE_M, CN);
+    mbar_wait(bar(B_RES), 0);
+    int j = 0, ti = 0;
+    for (int u = 0; u < U; ++u) {
+      const uint32_t ab = ti & 1, sb = u & 1;
+      if (j == 0) mbar_wait(bar(B_AFULL + ab), (ti >> 1) & 1);
+      mbar_wait(bar(B_SEMPTY + sb), ((u >> 1) & 1) ^ 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t ab0 = base + SM_A + ab * A_BUF, img = base + SM_RES + j * BIMG;
+        const uint32_t dS = tmem + T_S + sb * CN, dA = tmem + T_DA + sb * CN;
+        mma_f16(dS, desc_noswz(ab0 + AOFF_N, NORM_LBO, NORM_SBO), desc_noswz(img + BOFF_BN, NORM_LBO, NORM_SBO), ID, 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) mma_f16(dS, desc_sw128(ab0 + AOFF_Z + 32 * k), desc_sw128(img + BOFF_BH + 32 * k), ID, 1);
+#pragma unroll
+        for (int k = 0; k < 2; ++k) mma_f16(dA, desc_k_sw64(ab0 + AOFF_DL + 32 * k), desc_k_sw64(img + BOFF_W3 + 32 * k), ID, k);
+        mma_commit(bar(B_SFULL + sb));
+      }
+      __syncwarp();
+      if (++j == nch) { j = 0; ++ti; }
+    }
+  } else if (warp == WARP_I2) {
+    // ================= issuer 2: dz, dp^T, dW^T, csum GEMMs (consume the gamma / a tiles) =================
+    constexpr uint32_t ID4 = idesc_f16_major(FM, TILE_M, CN, 0, 1);
+    constexpr uint32_t ID5A = idesc_f16_major(FM, 64, 64, 1, 1);
+    constexpr uint32_t ID5B = idesc_f16_major(FM, 64, KP_BWD, 1, 1);
+    constexpr uint32_t ID5C = idesc_f16_major(FM, 64, 8, 1, 1);
+    mbar_wait(bar(B_RES), 0);
+    int j = 0, ti = 0;
+    for (int u = 0; u < U; ++u) {
+      const uint32_t ab = ti & 1, gb = u & 1;
+      mbar_wait(bar(B_GFULL + gb), (u >> 1) & 1);
+      if (j == 0) mbar_wait(bar(B_DZEMPTY), (ti & 1) ^ 1);
+      tc_fence_after();
+      if (lane == 0) {
+        const uint32_t ab0 = base + SM_A + ab * A_BUF, img = base + SM_RES + j * BIMG;
+        const uint32_t gam = base + SM_G + gb * G_BUF, act = gam + TILE_M * 128;
+        const uint32_t acc = tmem + T_ACC + 64 * j;
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+          mma_f16(tmem + T_DZ, desc_sw128(gam + 32 * k), desc_mn_sw128(img + BOFF_BH + 2048 * k, 0), ID4, (j > 0 || k > 0) ? 1 : 0);
+#pragma unroll
+        for (int k = 0; k < 8; ++k) {
+          const uint32_t accum = (ti > 0 || k > 0) ? 1 : 0;
+          mma_f16(acc, desc_mn_sw128(gam + 2048 * k, 0), desc_mn_sw128(ab0 + AOFF_Z + 2048 * k, 0), ID5A, accum);
+          mma_f16(acc + (16u << 16), desc_mn_sw128(act + 2048 * k, 0), desc_mn_sw64(ab0 + AOFF_DL + 1024 * k, 0), ID5B, accum);
+          mma_f16(acc + (16u << 16) + 32, desc_mn_sw128(gam + 2048 * k, 0),
+                  (uint64_t)(((ab0 + AOFF_N + 512 * k) & 0x3FFFF) >> 4) | ((uint64_t)(256 >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) |
+                      ((uint64_t)1 << 46),
+                  ID5C, accum);
+        }
+        mma_commit(bar(B_GEMPTY + gb));
+        if (j == nch - 1) {
+          mma_commit(bar(B_DZFULL));
+          mma_commit(bar(B_AEMPTY + ab));
+        }
+        if (u == U - 1) mma_commit(bar(B_ACC));
+      }
+      __syncwarp();
+      if (++j == nch) { j = 0; ++ti; }
+    }
+  } else if (warp >= WARP_LOAD0 && warp < WARP_I1) {
+    // ================= loaders: z_s tile (16-bit, K-major swizzled) + norms + scaled dlogits tile =================
+    const int m = threadIdx.x - WARP_LOAD0 * 32;
+    const float G = grad_scale(__ldg(prm.amax_bits));
+    for (int ti = 0; ti < my_tiles; ++ti) {
+      const long long n = ((long long)cta_local + (long long)ti * ncta) * TILE_M + m;
+      const bool valid = n < s.N;
+      const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
+      const float* zs = prm.z + b * (long long)s.C * s.HW + pix + (long long)sc * s.D * s.HW;
+      const uint32_t ab = ti & 1;
+      mbar_wait(bar(B_AEMPTY + ab), ((ti >> 1) & 1) ^ 1);
+      unsigned char* a0 = gbase + SM_A + ab * A_BUF;
+      float v[64];
+#pragma unroll
+      for (int k = 0; k < 64; ++k) v[k] = (valid && k < s.D) ? __ldg(zs + (long long)k * s.HW) : 0.0f;
+      float dl[KP_BWD];
+#pragma unroll
+      for (int k = 0; k < KP_BWD; ++k) dl[k] = (valid && k < s.K) ? __ldg(prm.dlogits + n * s.K + k) * G : 0.0f;
+      float zn = 0.f;
+#pragma unroll
+      for (int gq = 0; gq < 8; ++gq) {
+        uint32_t hw[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) {
+          hw[q] = Pack2<X>::pack(v[gq * 8 + 2 * q], v[gq * 8 + 2 * q + 1]);
+          const float2 e = Pack2<X>::unpack(hw[q]);
+          zn = fmaf(e.x, e.x, zn);
+          zn = fmaf(e.y, e.y, zn);
+        }
+        *reinterpret_cast<uint4*>(a0 + AOFF_Z + (uint32_t)m * 128u + ((((uint32_t)gq) ^ ((uint32_t)m & 7u)) << 4)) =
+            make_uint4(hw[0], hw[1], hw[2], hw[3]);
+      }
+      {
+        X h, mm, l;
+        split3<X>(zn, h, mm, l);
+        const uint32_t one = bits16(Fmt<X>::from(1.0f));
+        *reinterpret_cast<uint4*>(a0 + AOFF_N + norm_off(m, 0)) =
+            make_uint4(one | (one << 16), one | ((uint32_t)bits16(h) << 16), (uint32_t)bits16(mm) | ((uint32_t)bits16(l) << 16), 0u);
+        *reinterpret_cast<uint4*>(a0 + AOFF_N + norm_off(m, 8)) = make_uint4(0u, 0u, 0u, 0u);
+      }
+#pragma unroll
+      for (int gq = 0; gq < 4; ++gq) {
+        uint32_t w[4];
+#pragma unroll
+        for (int q = 0; q < 4; ++q) w[q] = Pack2<X>::pack(dl[gq * 8 + 2 * q], dl[gq * 8 + 2 * q + 1]);
+        *reinterpret_cast<uint4*>(a0 + AOFF_DL + (uint32_t)m * 64u + ((((uint32_t)gq) ^ (((uint32_t)m >> 1) & 3u)) << 4)) =
+            make_uint4(w[0], w[1], w[2], w[3]);
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(B_AFULL + ab));
+    }
+  }
+  else if (warp < WARP_LOAD0) {
+    // ================= epilogue: gamma / a tiles, row sums, dz read-out, final accumulator read-out =================
+    const int q = warp & 3, half = warp >> 2;
+    const int m = q * 32 + lane;
+    const uint32_t lane_base = ((uint32_t)(q * 32)) << 16;
+    const float eps = s.eps, ome = 1.0f - s.eps;
+    const bool is_log = s.act_kind == SPS_ACT_LOG;
+    const float G = grad_scale(__ldg(prm.amax_bits)), invG = 1.0f / G;
+    float* sgbuf = reinterpret_cast<float*>(gbase + SM_SG);
+    int u = 0;
+    for (int ti = 0; ti < my_tiles; ++ti) {
+      const long long n = ((long long)cta_local + (long long)ti * ncta) * TILE_M + m;
+      const bool valid = n < s.N;
+      const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
+      const uint32_t ab = ti & 1;
+      float sg = 0.f;
+      for (int j = 0; j < nch; ++j, ++u) {
+        const uint32_t sb = u & 1, gb = u & 1;
+        uint32_t rs[32], ra[32];
+        mbar_wait(bar(B_SFULL + sb), (u >> 1) & 1);
+        tc_fence_after();
+        tmem_ld32(tmem + lane_base + T_S + sb * CN + half * 32, rs);
+        tmem_ld32(tmem + lane_base + T_DA + sb * CN + half * 32, ra);
+        tmem_ld_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(B_SEMPTY + sb));
+        uint32_t gw[16], aw[16];
+#pragma unroll
+        for (int e = 0; e < 16; ++e) {
+          float gm[2], a2[2];
+#pragma unroll
+          for (int h = 0; h < 2; ++h) {
+            const float sv = __uint_as_float(rs[2 * e + h]), dav = __uint_as_float(ra[2 * e + h]);
+            const float d = fmaxf(sv, 0.0f);
+            float ap, av;
+            if (is_log) {
+              const float s1 = d + 1.0f, ru = rcp_approx(s1 * (d + eps));
+              ap = -ome * ru;
+              av = lg2_approx(s1 * s1 * ru);
+            } else {
+              ap = -1.0f;
+              av = -d;
+            }
+            gm[h] = sv > 0.0f ? dav * ap : 0.0f;
+            a2[h] = av;
+            sg += gm[h];
+          }
+          gw[e] = Pack2<X>::pack(gm[0], gm[1]);
+          aw[e] = Pack2<X>::pack(a2[0], a2[1]);
+        }
+        mbar_wait(bar(B_GEMPTY + gb), ((u >> 1) & 1) ^ 1);
+        unsigned char* grow = gbase + SM_G + gb * G_BUF + (uint32_t)m * 128u;
+#pragma unroll
+        for (int gq = 0; gq < 4; ++gq) {
+          const uint32_t off = (((uint32_t)(half * 4 + gq)) ^ ((uint32_t)m & 7u)) << 4;
+          *reinterpret_cast<uint4*>(grow + off) = make_uint4(gw[4 * gq], gw[4 * gq + 1], gw[4 * gq + 2], gw[4 * gq + 3]);
+          *reinterpret_cast<uint4*>(grow + TILE_M * 128 + off) = make_uint4(aw[4 * gq], aw[4 * gq + 1], aw[4 * gq + 2], aw[4 * gq + 3]);
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(B_GFULL + gb));
+      }
+      // ---- dz of this (tile, scale): acc + 2 z sum_p gamma ----
+      float* sgb = sgbuf + (ti & 1) * 256;
+      sgb[half * 128 + m] = sg;
+      named_bar_sync(1, 256);
+      const float tot = sgb[m] + sgb[128 + m];
+      uint32_t rd[32];
+      mbar_wait(bar(B_DZFULL), ti & 1);
+      tc_fence_after();
+      tmem_ld32(tmem + lane_base + T_DZ + half * 32, rd);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(B_DZEMPTY));
+      const unsigned char* zrow = gbase + SM_A + ab * A_BUF + AOFF_Z + (uint32_t)m * 128u;
+      float* dzp = prm.dz + b * (long long)s.C * s.HW + (long long)sc * s.D * s.HW + pix;
+#pragma unroll
+      for (int gq = 0; gq < 4; ++gq) {
+        const uint4 zz = *reinterpret_cast<const uint4*>(zrow + ((((uint32_t)(half * 4 + gq)) ^ ((uint32_t)m & 7u)) << 4));
+        const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          const float2 zf = Pack2<X>::unpack(zw[e]);
+          const int c = half * 32 + gq * 8 + 2 * e;
+          const float v0 = (__uint_as_float(rd[gq * 8 + 2 * e]) + 2.0f * zf.x * tot) * invG;
+          const float v1 = (__uint_as_float(rd[gq * 8 + 2 * e + 1]) + 2.0f * zf.y * tot) * invG;
+          if (prm.dz != nullptr && valid && c < s.D) {
+            if (multi) atomicAdd(dzp + (long long)c * s.HW, v0); else dzp[(long long)c * s.HW] = v0;
+          }
+          if (prm.dz != nullptr && valid && c + 1 < s.D) {
+            if (multi) atomicAdd(dzp + (long long)(c + 1) * s.HW, v1); else dzp[(long long)(c + 1) * s.HW] = v1;
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(B_AEMPTY + ab));
+    }
+    // ---- partial dp / dW of this CTA ----
+    if (U > 0) {
+      mbar_wait(bar(B_ACC), 0);
+      tc_fence_after();
+      float* cs = sgbuf;  // csum exchange [3][64]
+      named_bar_sync(1, 256);
+      uint32_t racc[GROUP_CHUNKS][32];
+      for (int j = 0; j < nch; ++j) {
+        tmem_ld32(tmem + lane_base + T_ACC + 64 * j + half * 32, racc[j]);
+        tmem_ld_wait();
+        if (half == 1 && lane >= 16) cs[j * 64 + q * 16 + lane - 16] = __uint_as_float(racc[j][0]);
+      }
+      named_bar_sync(1, 256);
+      const float wsc = (is_log ? 0.69314718055994531f : 1.0f) * invG;
+      for (int j = 0; j < nch; ++j) {
+        const int c = c0 + j, p0 = ct.p0[c], nc = ct.n[c];
+        if (lane < 16) {
+          const int pl = q * 16 + lane;
+          if (pl < nc) {
+            const float csum = cs[j * 64 + pl];
+            const float* prow = prm.protos + (size_t)(p0 + pl) * s.D;
+            float* out = prm.part_dp + (size_t)cta_local * s.P * s.D + (size_t)(p0 + pl) * s.D;
+#pragma unroll
+            for (int e = 0; e < 32; ++e) {
+              const int cc = half * 32 + e;
+              if (cc < s.D) out[cc] = (2.0f * __ldg(prow + cc) * csum - 2.0f * __uint_as_float(racc[j][e])) * invG;
+            }
+          }
+        } else if (half == 0) {
+          const int pl = q * 16 + lane - 16;
+          if (pl < nc) {
+            float* out = prm.part_dw + (size_t)cta_local * s.K * s.P + p0 + pl;
+#pragma unroll
+            for (int e = 0; e < 32; ++e)
+              if (e < s.K) out[(size_t)e * s.P] = __uint_as_float(racc[j][e]) * wsc;
+          }
+        }
+      }
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == WARP_I1) {
+    tc_fence_after();
+    tmem_dealloc(tmem, 512);
+  }
+}
+
+__global__ void bwd_reduce_kernel(const float* __restrict__ part, int nsplit, long long count, float* __restrict__ out) {
+  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  float a = 0.f;
+  for (int sp = 0; sp < nsplit; ++sp) a += part[(long long)sp * count + i];
+  out[i] = a;
+}
+
+}  // namespace tcb
+
+// ---------------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------------
+int build_chunk_table(const HeadShape& s, bool with_last_layer, tc::ChunkTable* ct);
+
+static int build_group_table(const tc::ChunkTable& ct, int n_tiles, int n_sm, tcb::GroupTable* gt) {
+  int ng = 0;
+  for (int c = 0; c < ct.n_chunks;) {
+    int e = c + 1;
+    while (e < ct.n_chunks && ct.scale[e] == ct.scale[c] && e - c < tcb::GROUP_CHUNKS) ++e;
+    SPS_REQUIRE(ng < tcb::MAX_GROUPS, SPS_ERR_UNSUPPORTED, "tensor-core backward: more than %d chunk groups", tcb::MAX_GROUPS);
+    gt->c0[ng] = c;
+    gt->nch[ng] = (short)(e - c);
+    gt->scale[ng] = ct.scale[c];
+    ++ng;
+    c = e;
+  }
+  gt->n_groups = ng;
+  for (int g = 0; g < ng; ++g) {
+    bool multi = false;
+    for (int h = 0; h < ng; ++h) multi |= (h != g && gt->scale[h] == gt->scale[g]);
+    gt->multi[g] = multi ? 1 : 0;
+  }
+  // CTAs per group proportional to its chunks, at least 1, at most one per tile
+  SPS_REQUIRE(ng <= n_sm, SPS_ERR_UNSUPPORTED, "tensor-core backward: %d chunk groups exceed %d SMs", ng, n_sm);
+  int left = n_sm - ng, total = ct.n_chunks, next = 0;
+  for (int g = 0; g < ng; ++g) {
+    int extra = (int)((long long)(n_sm - ng) * gt->nch[g] / total);
+    if (extra > left) extra = left;
+    int n = 1 + extra;
+    if (n > n_tiles) n = n_tiles;
+    if (n < 1) n = 1;
+    left -= (n - 1);
+    gt->cta0[g] = (short)next;
+    gt->ncta[g] = (short)n;
+    next += n;
+  }
+  return next;  // grid size
+}
+
+static int bwd_nsplit(const tcb::GroupTable& gt) {
+  int m = 1;
+  for (int g = 0; g < gt.n_groups; ++g) m = gt.ncta[g] > m ? gt.ncta[g] : m;
+  return m;
+}
+
+bool head_bwd_tc_supported(const HeadShape& s, int math, const float* last_w, const float* dlogits, const float* ddist,
+                           const float* dact) {
+  return math != SPS_MATH_FP32 && last_w != nullptr && dlogits != nullptr && ddist == nullptr && dact == nullptr &&
+         s.K <= tcb::KP_BWD && s.D <= 64 && s.D % 8 == 0 && s.N > 0 && s.P > 0;
+}
+
+size_t head_bwd_tc_workspace(const HeadShape& s) {
+  tc::ChunkTable ct;
+  if (build_chunk_table(s, true, &ct) != SPS_OK) return 0;
+  tcb::GroupTable gt;
+  const int n_tiles = (int)((s.N + tc::TILE_M - 1) / tc::TILE_M);
+  if (build_group_table(ct, n_tiles > 0 ? n_tiles : 1, sm_count(), &gt) <= 0) return 0;
+  const size_t nsplit = (size_t)bwd_nsplit(gt);
+  return 1024 + (size_t)ct.n_chunks * tcb::BIMG + 256 + sizeof(float) * nsplit * ((size_t)s.P * s.D + (size_t)s.K * s.P);
+}
+
+template <typename X>
+static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* protos, const float* last_w, const float* dlogits,
+                           float* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st) {
+  tcb::BwdParams prm;
+  int rc = build_chunk_table(s, true, &prm.ct);
+  if (rc != SPS_OK) return rc;
+  prm.n_tiles = (int)((s.N + tc::TILE_M - 1) / tc::TILE_M);
+  const int grid = build_group_table(prm.ct, prm.n_tiles, sm_count(), &prm.gt);
+  if (grid <= 0) return SPS_ERR_UNSUPPORTED;
+  const int nsplit = bwd_nsplit(prm.gt);
+  const size_t need = head_bwd_tc_workspace(s);
+  SPS_REQUIRE(ws != nullptr && ws_bytes >= need, SPS_ERR_WORKSPACE, "head_bwd workspace: need %zu bytes, got %zu", need, ws_bytes);
+  unsigned char* img = reinterpret_cast<unsigned char*>(((uintptr_t)ws + 1023) & ~(uintptr_t)1023);
+  unsigned int* amax = reinterpret_cast<unsigned int*>(img + (size_t)prm.ct.n_chunks * tcb::BIMG);
+  float* part_dp = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(amax) + 256);
+  float* part_dw = part_dp + (size_t)nsplit * s.P * s.D;
+  const size_t part_bytes = sizeof(float) * (size_t)nsplit * ((size_t)s.P * s.D + (size_t)s.K * s.P);
+  SPS_CUDA_TRY(cudaMemsetAsync(amax, 0, 256 + part_bytes, st));
+  bool any_multi = false;
+  for (int g = 0; g < prm.gt.n_groups; ++g) any_multi |= prm.gt.multi[g] != 0;
+  if (dz != nullptr && any_multi) SPS_CUDA_TRY(cudaMemsetAsync(dz, 0, sizeof(float) * (size_t)s.B * s.C * s.HW, st));
+  tcb::amax_kernel<<<sm_count(), 256, 0, st>>>(dlogits, s.N * s.K, amax);
+  count_launch();
+  tcb::bwd_prep_kernel<X><<<prm.ct.n_chunks, 256, 0, st>>>(prm.ct, s.D, s.P, s.K, protos, last_w, img);
+  count_launch();
+  SPS_CUDA_TRY(cudaGetLastError());
+  prm.s = s;
+  prm.z = z;
+  prm.protos = protos;
+  prm.dlogits = dlogits;
+  prm.img = img;
+  prm.amax_bits = amax;
+  prm.dz = dz;
+  prm.part_dp = part_dp;
+  prm.part_dw = part_dw;
+  SPS_CUDA_TRY(cudaFuncSetAttribute(tcb::head_bwd_tc_kernel<X>, cudaFuncAttributeMaxDynamicSharedMemorySize, tcb::SM_TOTAL));
+  tcb::head_bwd_tc_kernel<X><<<grid, tcb::NTHREADS, tcb::SM_TOTAL, st>>>(prm);
+  count_launch();
+  SPS_CUDA_TRY(cudaGetLastError());
+  if (dprotos != nullptr) {
+    const long long cnt = (long long)s.P * s.D;
+    tcb::bwd_reduce_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(part_dp, nsplit, cnt, dprotos);
+    count_launch();
+  }
+  if (dlast_w != nullptr) {
+    const long long cnt = (long long)s.K * s.P;
+    tcb::bwd_reduce_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(part_dw, nsplit, cnt, dlast_w);
+    count_launch();
+  }
+  SPS_CUDA_TRY(cudaGetLastError());
+  return SPS_OK;
+}
+
+int launch_head_bwd_tc(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w,
+                       const float* dlogits, float* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes,
+                       cudaStream_t st) {
+  // the backward runs single-term 16-bit operands (the split modes only sharpen the forward distances)
+  if (math == SPS_MATH_BF16 || math == SPS_MATH_BF16X3)
+    return launch_bwd_tc_t<__nv_bfloat16>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
+  return launch_bwd_tc_t<__half>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
+}
+
+}  // namespace sps

@@ -144,17 +144,6 @@ enum { BAR_AFULL = 0, BAR_AEMPTY = 2, BAR_BFULL = 4, BAR_BEMPTY = 4 + MAX_NST, B
        BAR_SEMPTY = 6 + 2 * MAX_NST, BAR_PFULL = 8 + 2 * MAX_NST, BAR_PEMPTY = 10 + 2 * MAX_NST, BAR_LFULL = 12 + 2 * MAX_NST,
        BAR_LEMPTY = 14 + 2 * MAX_NST, BAR_COUNT = 16 + 2 * MAX_NST };
 
-__device__ __forceinline__ float rcp_approx(float x) {
-  float y;
-  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-__device__ __forceinline__ float lg2_approx(float x) {
-  float y;
-  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
-  return y;
-}
-
 template <typename X, int NSPLIT>
 __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_constant__ FwdParams prm) {
   extern __shared__ unsigned char smem_raw[];

@@ -143,6 +143,42 @@ __host__ __device__ constexpr uint32_t idesc_f16(uint32_t fmt, int M, int N) {
   return (1u << 4) | (fmt << 7) | (fmt << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
 }
 
+// MN-major operand, 128-byte swizzle (rows = K index, 64 MN elements per 128-B row; 8 K rows = 1024 B (SBO);
+// further blocks of 64 MN elements `lbo` bytes apart).  The SAME bytes as a K-major SW128 tile whose rows are the
+// K index of this view: the swizzle is a function of the byte address only.  Advance 16 K = +2048 B.
+__device__ __forceinline__ uint64_t desc_mn_sw128(uint32_t smem_addr, uint32_t lbo) {
+  return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(1024 >> 4) << 32) |
+         ((uint64_t)1 << 46) | ((uint64_t)2 << 61);
+}
+// 64-byte swizzle: rows of 64 B (32 elements), 8 rows = 512 B.  K-major (rows = MN index, advance 16 K = +32 B)
+// and MN-major (rows = K index, 32 MN elements per row, advance 16 K = +1024 B) views of the same bytes.
+__device__ __forceinline__ uint64_t desc_k_sw64(uint32_t smem_addr) {
+  return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)(512 >> 4) << 32) | ((uint64_t)1 << 46) |
+         ((uint64_t)4 << 61);
+}
+__device__ __forceinline__ uint64_t desc_mn_sw64(uint32_t smem_addr, uint32_t lbo) {
+  return (uint64_t)((smem_addr & 0x3FFFF) >> 4) | ((uint64_t)(lbo >> 4) << 16) | ((uint64_t)(512 >> 4) << 32) |
+         ((uint64_t)1 << 46) | ((uint64_t)4 << 61);
+}
+__host__ __device__ __forceinline__ uint32_t sw64_off(int r, int k) {  // row r (64 B), element k < 32
+  return (uint32_t)r * 64u + ((((uint32_t)k >> 3) ^ (((uint32_t)r >> 1) & 3u)) << 4) + (((uint32_t)k & 7u) << 1);
+}
+// instruction descriptor with explicit majors (0 = K-major, 1 = MN-major)
+__host__ __device__ constexpr uint32_t idesc_f16_major(uint32_t fmt, int M, int N, uint32_t a_mn, uint32_t b_mn) {
+  return idesc_f16(fmt, M, N) | (a_mn << 15) | (b_mn << 16);
+}
+
+__device__ __forceinline__ float rcp_approx(float x) {
+  float y;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+__device__ __forceinline__ float lg2_approx(float x) {
+  float y;
+  asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+
 // byte offset of element (row r, k) inside a SW128 K-major tile of 2-byte elements with 64 k per row
 __host__ __device__ __forceinline__ uint32_t sw128_off(int r, int k) {
   return (uint32_t)r * 128u + ((((uint32_t)k >> 3) ^ ((uint32_t)r & 7u)) << 4) + (((uint32_t)k & 7u) << 1);
