@@ -29,8 +29,10 @@ using namespace sps::tc;
 constexpr int GROUP_CHUNKS = 3;   // chunks per CTA (TMEM budget)
 constexpr int MAX_GROUPS = 64;
 constexpr int KP_BWD = 32;        // classes padded (this kernel: K <= 32)
-constexpr int BIMG = CN * 128 + CN * 32 + CN * 64;   // per chunk: BH 8 KB | BN 2 KB | W3 4 KB
-constexpr int BOFF_BH = 0, BOFF_BN = CN * 128, BOFF_W3 = CN * 128 + CN * 32;
+// per chunk: BH 8 KB | BN 2 KB | W3 4 KB | BL 8 KB (lo part of -2p; copied to shared memory only in the split mode)
+constexpr int BIMG = CN * 128 + CN * 32 + CN * 64 + CN * 128;
+constexpr int BOFF_BH = 0, BOFF_BN = CN * 128, BOFF_W3 = CN * 128 + CN * 32, BOFF_BL = CN * 128 + CN * 32 + CN * 64;
+template <int NSPLIT> __host__ __device__ constexpr int bimg_smem() { return NSPLIT == 3 ? BIMG : BOFF_BL; }
 
 struct GroupTable {
   int n_groups;
@@ -57,7 +59,7 @@ struct BwdParams {
   int n_tiles;
 };
 
-template <typename X>
+template <typename X, int NSPLIT>
 __global__ void __launch_bounds__(256) bwd_prep_kernel(const __grid_constant__ ChunkTable ct, int D, int P, int K,
                                                         const float* __restrict__ protos, const float* __restrict__ last_w,
                                                         unsigned char* __restrict__ img_base) {
@@ -73,8 +75,14 @@ __global__ void __launch_bounds__(256) bwd_prep_kernel(const __grid_constant__ C
       const int k = kq + kk;
       const float v = (j < n && k < D) ? -2.0f * __ldg(protos + (size_t)(p0 + j) * D + k) : 0.0f;
       const X hi = Fmt<X>::from(v);
-      const float eff = Fmt<X>::to(hi);
+      float eff = Fmt<X>::to(hi);
+      X lo = Fmt<X>::from(0.0f);
+      if (NSPLIT == 3) {
+        lo = Fmt<X>::from(v - eff);
+        eff += Fmt<X>::to(lo);
+      }
       *reinterpret_cast<uint16_t*>(img + BOFF_BH + sw128_off(j, k)) = bits16(hi);
+      *reinterpret_cast<uint16_t*>(img + BOFF_BL + sw128_off(j, k)) = bits16(lo);
       part = fmaf(0.5f * eff, 0.5f * eff, part);
     }
     part += __shfl_xor_sync(0xffffffffu, part, 1);
@@ -122,21 +130,28 @@ __device__ __forceinline__ float grad_scale(unsigned int amax_bits) {
 
 constexpr int NTHREADS = 480;
 constexpr int WARP_LOAD0 = 8, WARP_I1 = 12, WARP_I2 = 13, WARP_RES = 14;
-constexpr int A_BUF = TILE_M * 128 + TILE_M * 32 + TILE_M * 64;   // z tile 16 KB | norm 4 KB | DL tile 8 KB
-constexpr int AOFF_Z = 0, AOFF_N = TILE_M * 128, AOFF_DL = TILE_M * 128 + TILE_M * 32;
+// A buffer: z tile 16 KB | norm 4 KB | DL tile 8 KB | z lo tile 16 KB (split mode)
+constexpr int AOFF_Z = 0, AOFF_N = TILE_M * 128, AOFF_DL = TILE_M * 128 + TILE_M * 32, AOFF_ZL = TILE_M * 128 + TILE_M * 32 + TILE_M * 64;
 constexpr int G_BUF = 2 * TILE_M * 128;                            // gamma tile 16 KB | a tile 16 KB
-constexpr int SM_RES = 0;                                          // resident chunk images: 3 * BIMG (42 KB)
-constexpr int SM_A = (GROUP_CHUNKS * BIMG + 1023) / 1024 * 1024;
-constexpr int SM_G = SM_A + 2 * A_BUF;
-constexpr int SM_SG = SM_G + 2 * G_BUF;                            // sgbuf[2 parity][2 half][128] floats
-constexpr int SM_BAR = SM_SG + 2 * 2 * 128 * 4;
-constexpr int SM_TOTAL = SM_BAR + 256 + 1024;
+template <int NSPLIT> struct Lay {
+  static constexpr int A_BUF = AOFF_ZL + (NSPLIT == 3 ? TILE_M * 128 : 0);
+  static constexpr int RES = bimg_smem<NSPLIT>();                  // resident bytes per chunk
+  static constexpr int SM_RES = 0;
+  static constexpr int SM_A = (GROUP_CHUNKS * RES + 1023) / 1024 * 1024;
+  static constexpr int SM_G = SM_A + 2 * A_BUF;
+  static constexpr int SM_SG = SM_G + 2 * G_BUF;                   // sgbuf[2 parity][2 half][128] floats
+  static constexpr int SM_BAR = SM_SG + 2 * 2 * 128 * 4;
+  static constexpr int SM_TOTAL = SM_BAR + 256 + 1024;
+};
 constexpr int T_S = 0, T_DA = 128, T_DZ = 256, T_ACC = 320;
 enum { B_AFULL = 0, B_AEMPTY = 2, B_SFULL = 4, B_SEMPTY = 6, B_GFULL = 8, B_GEMPTY = 10, B_DZFULL = 12, B_DZEMPTY = 13,
        B_RES = 14, B_ACC = 15, B_COUNT = 16 };
 
-template <typename X>
+template <typename X, int NSPLIT>
 __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_constant__ BwdParams prm) {
+  using L = Lay<NSPLIT>;
+  constexpr int A_BUF = L::A_BUF, RES = L::RES, SM_RES = L::SM_RES, SM_A = L::SM_A, SM_G = L::SM_G, SM_SG = L::SM_SG,
+                SM_BAR = L::SM_BAR;
   extern __shared__ unsigned char smem_raw[];
   const HeadShape& s = prm.s;
   const ChunkTable& ct = prm.ct;
@@ -180,9 +195,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
 
   if (warp == WARP_RES) {
     if (lane == 0) {
-      mbar_arrive_expect_tx(bar(B_RES), (uint32_t)nch * BIMG);
+      mbar_arrive_expect_tx(bar(B_RES), (uint32_t)nch * RES);
       for (int j = 0; j < nch; ++j)
-        bulk_g2s(base + SM_RES + j * BIMG, prm.img + (size_t)(c0 + j) * BIMG, BIMG, bar(B_RES));
+        bulk_g2s(base + SM_RES + j * RES, prm.img + (size_t)(c0 + j) * BIMG, RES, bar(B_RES));
     }
   } else if (warp == WARP_I1) {
     // ================= issuer 1: distance GEMM + dA GEMM of every unit =================
@@ -195,11 +210,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       mbar_wait(bar(B_SEMPTY + sb), ((u >> 1) & 1) ^ 1);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t ab0 = base + SM_A + ab * A_BUF, img = base + SM_RES + j * BIMG;
+        const uint32_t ab0 = base + SM_A + ab * A_BUF, img = base + SM_RES + j * RES;
         const uint32_t dS = tmem + T_S + sb * CN, dA = tmem + T_DA + sb * CN;
         mma_f16(dS, desc_noswz(ab0 + AOFF_N, NORM_LBO, NORM_SBO), desc_noswz(img + BOFF_BN, NORM_LBO, NORM_SBO), ID, 0);
 #pragma unroll
         for (int k = 0; k < 4; ++k) mma_f16(dS, desc_sw128(ab0 + AOFF_Z + 32 * k), desc_sw128(img + BOFF_BH + 32 * k), ID, 1);
+        if (NSPLIT == 3) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) mma_f16(dS, desc_sw128(ab0 + AOFF_Z + 32 * k), desc_sw128(img + BOFF_BL + 32 * k), ID, 1);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) mma_f16(dS, desc_sw128(ab0 + AOFF_ZL + 32 * k), desc_sw128(img + BOFF_BH + 32 * k), ID, 1);
+        }
 #pragma unroll
         for (int k = 0; k < 2; ++k) mma_f16(dA, desc_k_sw64(ab0 + AOFF_DL + 32 * k), desc_k_sw64(img + BOFF_W3 + 32 * k), ID, k);
         mma_commit(bar(B_SFULL + sb));
@@ -221,7 +242,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       if (j == 0) mbar_wait(bar(B_DZEMPTY), (ti & 1) ^ 1);
       tc_fence_after();
       if (lane == 0) {
-        const uint32_t ab0 = base + SM_A + ab * A_BUF, img = base + SM_RES + j * BIMG;
+        const uint32_t ab0 = base + SM_A + ab * A_BUF, img = base + SM_RES + j * RES;
         const uint32_t gam = base + SM_G + gb * G_BUF, act = gam + TILE_M * 128;
         const uint32_t acc = tmem + T_ACC + 64 * j;
 #pragma unroll
@@ -268,16 +289,24 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       float zn = 0.f;
 #pragma unroll
       for (int gq = 0; gq < 8; ++gq) {
-        uint32_t hw[4];
+        uint32_t hw[4], lw[4];
 #pragma unroll
         for (int q = 0; q < 4; ++q) {
-          hw[q] = Pack2<X>::pack(v[gq * 8 + 2 * q], v[gq * 8 + 2 * q + 1]);
-          const float2 e = Pack2<X>::unpack(hw[q]);
+          const float v0 = v[gq * 8 + 2 * q], v1 = v[gq * 8 + 2 * q + 1];
+          hw[q] = Pack2<X>::pack(v0, v1);
+          float2 e = Pack2<X>::unpack(hw[q]);
+          if (NSPLIT == 3) {
+            lw[q] = Pack2<X>::pack(v0 - e.x, v1 - e.y);
+            const float2 el = Pack2<X>::unpack(lw[q]);
+            e.x += el.x;
+            e.y += el.y;
+          }
           zn = fmaf(e.x, e.x, zn);
           zn = fmaf(e.y, e.y, zn);
         }
-        *reinterpret_cast<uint4*>(a0 + AOFF_Z + (uint32_t)m * 128u + ((((uint32_t)gq) ^ ((uint32_t)m & 7u)) << 4)) =
-            make_uint4(hw[0], hw[1], hw[2], hw[3]);
+        const uint32_t zoff = (uint32_t)m * 128u + ((((uint32_t)gq) ^ ((uint32_t)m & 7u)) << 4);
+        *reinterpret_cast<uint4*>(a0 + AOFF_Z + zoff) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+        if (NSPLIT == 3) *reinterpret_cast<uint4*>(a0 + AOFF_ZL + zoff) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
       }
       {
         X h, mm, l;
@@ -380,11 +409,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       float* dzp = prm.dz + b * (long long)s.C * s.HW + (long long)sc * s.D * s.HW + pix;
 #pragma unroll
       for (int gq = 0; gq < 4; ++gq) {
-        const uint4 zz = *reinterpret_cast<const uint4*>(zrow + ((((uint32_t)(half * 4 + gq)) ^ ((uint32_t)m & 7u)) << 4));
+        const uint32_t zo = (((uint32_t)(half * 4 + gq)) ^ ((uint32_t)m & 7u)) << 4;
+        const uint4 zz = *reinterpret_cast<const uint4*>(zrow + zo);
         const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
+        uint32_t zlw[4] = {0u, 0u, 0u, 0u};
+        if (NSPLIT == 3) {
+          const uint4 zl = *reinterpret_cast<const uint4*>(zrow + (AOFF_ZL - AOFF_Z) + zo);
+          zlw[0] = zl.x, zlw[1] = zl.y, zlw[2] = zl.z, zlw[3] = zl.w;
+        }
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
-          const float2 zf = Pack2<X>::unpack(zw[e]);
+          float2 zf = Pack2<X>::unpack(zw[e]);
+          if (NSPLIT == 3) {
+            const float2 zl2 = Pack2<X>::unpack(zlw[e]);
+            zf.x += zl2.x;
+            zf.y += zl2.y;
+          }
           const int c = half * 32 + gq * 8 + 2 * e;
           const float v0 = (__uint_as_float(rd[gq * 8 + 2 * e]) + 2.0f * zf.x * tot) * invG;
           const float v1 = (__uint_as_float(rd[gq * 8 + 2 * e + 1]) + 2.0f * zf.y * tot) * invG;
@@ -520,7 +560,7 @@ size_t head_bwd_tc_workspace(const HeadShape& s) {
   return 1024 + (size_t)ct.n_chunks * tcb::BIMG + 256 + sizeof(float) * nsplit * ((size_t)s.P * s.D + (size_t)s.K * s.P);
 }
 
-template <typename X>
+template <typename X, int NSPLIT>
 static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* protos, const float* last_w, const float* dlogits,
                            float* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st) {
   tcb::BwdParams prm;
@@ -543,7 +583,7 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   if (dz != nullptr && any_multi) SPS_CUDA_TRY(cudaMemsetAsync(dz, 0, sizeof(float) * (size_t)s.B * s.C * s.HW, st));
   tcb::amax_kernel<<<sm_count(), 256, 0, st>>>(dlogits, s.N * s.K, amax);
   count_launch();
-  tcb::bwd_prep_kernel<X><<<prm.ct.n_chunks, 256, 0, st>>>(prm.ct, s.D, s.P, s.K, protos, last_w, img);
+  tcb::bwd_prep_kernel<X, NSPLIT><<<prm.ct.n_chunks, 256, 0, st>>>(prm.ct, s.D, s.P, s.K, protos, last_w, img);
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   prm.s = s;
@@ -555,8 +595,10 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   prm.dz = dz;
   prm.part_dp = part_dp;
   prm.part_dw = part_dw;
-  SPS_CUDA_TRY(cudaFuncSetAttribute(tcb::head_bwd_tc_kernel<X>, cudaFuncAttributeMaxDynamicSharedMemorySize, tcb::SM_TOTAL));
-  tcb::head_bwd_tc_kernel<X><<<grid, tcb::NTHREADS, tcb::SM_TOTAL, st>>>(prm);
+  constexpr int SMEM = tcb::Lay<NSPLIT>::SM_TOTAL;
+  static_assert(SMEM <= 227 * 1024, "backward kernel shared memory");
+  SPS_CUDA_TRY(cudaFuncSetAttribute(tcb::head_bwd_tc_kernel<X, NSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  tcb::head_bwd_tc_kernel<X, NSPLIT><<<grid, tcb::NTHREADS, SMEM, st>>>(prm);
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   if (dprotos != nullptr) {
@@ -576,10 +618,14 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
 int launch_head_bwd_tc(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w,
                        const float* dlogits, float* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes,
                        cudaStream_t st) {
-  // the backward runs single-term 16-bit operands (the split modes only sharpen the forward distances)
-  if (math == SPS_MATH_BF16 || math == SPS_MATH_BF16X3)
-    return launch_bwd_tc_t<__nv_bfloat16>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
-  return launch_bwd_tc_t<__half>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
+  // the split modes recompute the distances with the 3-term product (a' = da/dd is as sensitive to d as a is);
+  // the gradient GEMMs themselves run single-term 16-bit operands with fp32 accumulation
+  switch (math) {
+    case SPS_MATH_BF16: return launch_bwd_tc_t<__nv_bfloat16, 1>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
+    case SPS_MATH_BF16X3: return launch_bwd_tc_t<__nv_bfloat16, 3>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
+    case SPS_MATH_F16X3: return launch_bwd_tc_t<__half, 3>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
+    default: return launch_bwd_tc_t<__half, 1>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
+  }
 }
 
 }  // namespace sps

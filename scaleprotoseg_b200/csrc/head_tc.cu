@@ -89,7 +89,10 @@ __global__ void __launch_bounds__(256) proto_prep_kernel(const __grid_constant__
     for (int idx = t; idx < ct.kp * CN; idx += blockDim.x) {
       const int k = idx / CN, j = idx % CN;
       const float v = (k < K && j < n) ? sc * __ldg(last_w + (size_t)k * P + p0 + j) : 0.0f;
-      *reinterpret_cast<uint16_t*>(img + OFF_W2 + sw128_off(k, j)) = bits16(Fmt<X>::from(v));
+      const X hi = Fmt<X>::from(v);
+      *reinterpret_cast<uint16_t*>(img + OFF_W2 + sw128_off(k, j)) = bits16(hi);
+      *reinterpret_cast<uint16_t*>(img + OFF_W2 + ct.kp * 128 + sw128_off(k, j)) =
+          bits16(Fmt<X>::from(NSPLIT == 3 ? v - Fmt<X>::to(hi) : 0.0f));
     }
   }
 }
@@ -123,14 +126,16 @@ template <int NSPLIT> __host__ __device__ constexpr int a_buf_bytes() { return (
 struct SmemPlan {
   int a_stride, p0, b0, b_stride, nst, bar_off, total;
   __host__ __device__ int a_off(int i) const { return i * a_stride; }
-  __host__ __device__ int p_off(int i) const { return p0 + i * P_BYTES; }
+  int p_stride;
+  __host__ __device__ int p_off(int i) const { return p0 + i * p_stride; }
   __host__ __device__ int b_off(int i) const { return b0 + i * b_stride; }
 };
 template <int NSPLIT> __host__ __device__ inline SmemPlan smem_plan(int img_bytes) {
   SmemPlan pl;
   pl.a_stride = a_buf_bytes<NSPLIT>();
   pl.p0 = 2 * pl.a_stride;
-  pl.b0 = pl.p0 + 2 * P_BYTES;
+  pl.p_stride = (NSPLIT == 3 ? 2 : 1) * P_BYTES;   // a tile (hi) [+ lo tile]
+  pl.b0 = pl.p0 + 2 * pl.p_stride;
   pl.b_stride = (img_bytes + 1023) / 1024 * 1024;
   int nst = (227 * 1024 - 512 - 1024 - pl.b0) / pl.b_stride;
   pl.nst = nst > MAX_NST ? MAX_NST : nst;
@@ -246,6 +251,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
 #pragma unroll
           for (int k = 0; k < 4; ++k)
             mma_f16(d, desc_sw128(pa + 32 * k), desc_sw128(w2 + 32 * k), ID2, (c > 0 || k > 0) ? 1 : 0);
+          if (NSPLIT == 3) {  // a_hi.W_lo + a_lo.W_hi
+#pragma unroll
+            for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pa + 32 * k), desc_sw128(w2 + KP * 128 + 32 * k), ID2, 1);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pa + P_BYTES + 32 * k), desc_sw128(w2 + 32 * k), ID2, 1);
+          }
           mma_commit(bar(BAR_PEMPTY + pb));
           mma_commit(bar(BAR_BEMPTY + st));
           if (c == NC - 1) mma_commit(bar(BAR_LFULL + lb));
@@ -259,7 +270,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
     // ================================ prototype-chunk producer ================================
     {
       const int U = my_tiles * NC;
-      const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128, bytes_n = CN * 32, bytes_w = KP * 128;
+      const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128, bytes_n = CN * 32, bytes_w = (NSPLIT == 3 ? 2 : 1) * KP * 128;
       for (int i = 0; i < U; ++i) {
         const int c = i % NC, st = i % NST;
         mbar_wait(bar(BAR_BEMPTY + st), ((i / NST) & 1) ^ 1);
@@ -410,11 +421,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
           unsigned char* prow = gbase + pl.p_off(pb) + (uint32_t)m * 128u;
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
-            uint32_t w[4];
+            uint32_t w[4], wl[4];
 #pragma unroll
-            for (int e = 0; e < 4; ++e) w[e] = Pack2<X>::pack(av[g * 8 + 2 * e], av[g * 8 + 2 * e + 1]);
-            *reinterpret_cast<uint4*>(prow + ((((uint32_t)(half * 4 + g)) ^ ((uint32_t)m & 7u)) << 4)) =
-                make_uint4(w[0], w[1], w[2], w[3]);
+            for (int e = 0; e < 4; ++e) {
+              const float x0 = av[g * 8 + 2 * e], x1 = av[g * 8 + 2 * e + 1];
+              w[e] = Pack2<X>::pack(x0, x1);
+              if (NSPLIT == 3) {
+                const float2 h = Pack2<X>::unpack(w[e]);
+                wl[e] = Pack2<X>::pack(x0 - h.x, x1 - h.y);
+              }
+            }
+            const uint32_t poff = (((uint32_t)(half * 4 + g)) ^ ((uint32_t)m & 7u)) << 4;
+            *reinterpret_cast<uint4*>(prow + poff) = make_uint4(w[0], w[1], w[2], w[3]);
+            if (NSPLIT == 3) *reinterpret_cast<uint4*>(prow + P_BYTES + poff) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
           }
           fence_proxy_async();
           __syncwarp();

@@ -241,6 +241,7 @@ template <typename X> __device__ __forceinline__ void split3(float v, X& h, X& m
 //   [Blo  CN x 128 B  SW128]  lo part (zeros in the single-term modes)
 //   [Bn   CN x  32 B  noswz]  k=0..2: |p|^2 split in three; k=3..5: 1; rest 0
 //   [W2   KP x 128 B  SW128]  rows k: ln2 * W[k, p0+j]  ('log'; W itself for 'linear'); only with a last layer
+//   [W2lo KP x 128 B  SW128]  lo part of W2 (used by the split modes)
 // ---------------------------------------------------------------------------------------------
 constexpr int CN = 64;          // prototypes per chunk (MMA N of the distance GEMM, K of the logits GEMM)
 constexpr int MAX_CHUNKS = 160;
@@ -255,7 +256,7 @@ struct ChunkTable {
   short scale[MAX_CHUNKS];
 };
 
-__host__ __device__ inline int chunk_img_bytes(int kp) { return 2 * CN * 128 + CN * 32 + kp * 128; }
+__host__ __device__ inline int chunk_img_bytes(int kp) { return 2 * CN * 128 + CN * 32 + 2 * kp * 128; }
 constexpr int OFF_BHI = 0, OFF_BLO = CN * 128, OFF_BN = 2 * CN * 128, OFF_W2 = 2 * CN * 128 + CN * 32;
 
 }  // namespace tc

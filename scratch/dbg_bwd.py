@@ -19,7 +19,7 @@ def run(B, H, W, P, K, math, ranges=None, scale=1.0):
     dz1, dp1, dw1 = sps.head_backward_raw(z, protos, Wl, ctc, dl, None, None, True, True, True)
     torch.cuda.synchronize()
     print((B, H, W, P, K), "math", math, f"dz {nerr(dz1, dz0):.2e} dp {nerr(dp1, dp0):.2e} dW {nerr(dw1, dw0):.2e}", flush=True)
-for math in (sps.MATH_F16, sps.MATH_BF16):
+for math in (sps.MATH_F16, sps.MATH_F16X3, sps.MATH_BF16X3):
     run(1, 9, 9, 24, 2, math)
     run(2, 9, 7, 228, 19, math)
     run(1, 33, 40, 760, 19, math)
@@ -31,7 +31,7 @@ B, H, W, P, K = 16, 65, 65, 760, 19
 z = torch.sigmoid(torch.randn(B, 256, H, W, device=dev)); protos = torch.rand(P, 64, device=dev)
 Wl = ho.make_last_layer(ho.make_identity(P, K, 4)).contiguous().to(dev)
 dl = torch.randn(B*H*W, K, device=dev) / (B*H*W)
-for math in (sps.MATH_FP32, sps.MATH_F16):
+for math in (sps.MATH_F16, sps.MATH_F16X3):
     cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, 4), K, math=math)
     for _ in range(3): sps.head_backward_raw(z, protos, Wl, cfg, dl, None, None, True, True, True)
     torch.cuda.synchronize()
