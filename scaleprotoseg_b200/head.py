@@ -15,7 +15,9 @@ import torch
 from . import _lib
 from ._lib import ACT_LINEAR, ACT_LOG, MATH_BF16, MATH_BF16X3, MATH_F16, MATH_F16X3, MATH_FP32, SpsGroupDesc, SpsHeadDesc
 
-_DEFAULT_MATH = MATH_FP32
+# what install() uses: tcgen05 kernels with 3-term fp16 products (fp32-class distances, |z|,|p| < 6e4 — the
+# reference's add-on layers end in a Sigmoid, segmentation/model/model_multiscale.py:206-208)
+_DEFAULT_MATH = MATH_F16X3
 
 
 def set_default_math(math: int):

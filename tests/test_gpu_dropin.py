@@ -15,6 +15,16 @@ pytestmark = pytest.mark.gpu
 TOL = 5e-5
 
 
+@pytest.fixture(autouse=True)
+def _exact_math():
+    """The drop-in behaviour tests run the exact-operand mode so they can hold the tight bound; the default
+    (tensor-core) mode has its own test below."""
+    old = sps.default_math()
+    sps.set_default_math(sps.MATH_FP32)
+    yield
+    sps.set_default_math(old)
+
+
 def _patched(cls):
     """A patched subclass so the un-patched class keeps serving as the CPU oracle."""
     sub = type(cls.__name__ + "Patched", (cls,), {})
@@ -175,3 +185,21 @@ def test_full_size_properties(built_lib):
     lr, dr, ar = ho.head_stage1(zc, p.cpu().view(P, 64, 1, 1), ho.uniform_ranges(P, 4), w.cpu())
     assert_rel(lg[sel.to(DEV)], lr.view(257, K), TOL, "logits subset")
     assert_rel(ag[sel.to(DEV)], ar, TOL, "act subset")
+
+
+def test_default_math_is_tensor_core_and_training_step_matches(patched_classes):
+    """install() defaults to the tcgen05 kernels (3-term fp16 products).  One training-style step through the
+    patched model: logits-only loss -> fused forward + tensor-core backward; the parameter gradients match the
+    un-patched CPU model within the north-star tolerance."""
+    assert sps.head.__dict__["_DEFAULT_MATH"] == sps.MATH_F16X3
+    sps.set_default_math(sps.MATH_F16X3)
+    ref, got = _pair(Stage1Standin, patched_classes[0], 228, 19)
+    x = torch.randn(2, 256, 9, 9)
+    lr, dr = ref.forward(x)
+    lg, dg = got.forward(x.to(DEV))
+    assert_rel(lg, lr, 1e-3, "logits"), assert_rel(dg, dr, 1e-3, "dist")
+    target = torch.randint(0, 19, (2, 9, 9))
+    torch.nn.functional.cross_entropy(lr.permute(0, 3, 1, 2), target).backward()
+    torch.nn.functional.cross_entropy(lg.permute(0, 3, 1, 2), target.to(DEV)).backward()
+    assert_grad(got.prototype_vectors.grad, ref.prototype_vectors.grad, 1e-3, "dprotos")
+    assert_grad(got.last_layer.weight.grad, ref.last_layer.weight.grad, 1e-3, "dlast")

@@ -8,7 +8,10 @@ Tolerances (BASELINE.json north_star: rel 1e-3):
   gradients   |err| <= 1e-3 * max|ref|            (per tensor, normalised by its largest entry)
   push        indices bit-exact where the runner-up is further than the distance tolerance, otherwise the
               distance at the returned index must be within tolerance of the oracle minimum.
-SPS_MATH_FP32 (exact operands) is held to 20x tighter bounds.
+SPS_MATH_FP32 (exact operands) is held to 20x tighter bounds.  The tensor-core modes:
+  F16X3 / BF16X3  (3-term split products)  the 1e-3 bounds above on every output and gradient
+  F16             (fp16 operands, rounded)  distances / logits 2e-3 (measured 6e-4), gradients 2e-3
+  BF16            (bf16 operands, rounded)  distances / logits 1.5e-2 (8-bit mantissa), gradients 1.5e-2
 """
 import os
 
@@ -25,8 +28,11 @@ DEV = "cuda:0"
 MATHS = [sps.MATH_FP32]
 
 
+TC_MATHS = [sps.MATH_F16X3, sps.MATH_BF16X3, sps.MATH_F16, sps.MATH_BF16]
+
+
 def _tol(math):
-    return 5e-5 if math == sps.MATH_FP32 else 1e-3
+    return {sps.MATH_FP32: 5e-5, sps.MATH_F16X3: 1e-3, sps.MATH_BF16X3: 1e-3, sps.MATH_F16: 2e-3, sps.MATH_BF16: 1.5e-2}[math]
 
 
 def assert_rel(got, ref, tol, name, floor=1.0):
@@ -158,3 +164,83 @@ def test_push_golden(built_lib, golden_dir, name, math):
         assert np.array_equal(got[agree], g["new_protos"][agree]) and agree.mean() > 0.99
     check_push(keys, wm, [z[i:i + 1] for i in range(z.shape[0])], [labels[i].long() for i in range(z.shape[0])],
                protos, _ranges(g), ident, K, _tol(math))
+
+
+# ---------------------------------------------------------------------------------------------
+# Tensor-core (tcgen05) modes
+# ---------------------------------------------------------------------------------------------
+def _grad_tol(math):
+    return {sps.MATH_F16X3: 1e-3, sps.MATH_F16: 2e-3, sps.MATH_BF16X3: 1.5e-2, sps.MATH_BF16: 1.5e-2}[math]
+
+
+@pytest.mark.parametrize("math", TC_MATHS)
+@pytest.mark.parametrize("name", ["stage1_em", "stage1_em_ragged", "stage1_city228"])
+def test_stage1_golden_tensor_core(built_lib, golden_dir, name, math):
+    """Golden vectors of the unmodified reference through the tcgen05 forward (dense mode) and, for the gradient
+    that arrives through the logits only, the tcgen05 backward."""
+    g = _load(golden_dir, name)
+    K = g["last_w"].shape[0]
+    cfg = sps.HeadConfig.from_ranges(_ranges(g), K, act=str(g["act_kind"]), math=math)
+    z, p, w = (_cu(g[k]).requires_grad_(True) for k in ("z", "protos", "last_w"))
+    logits, d, a = sps.PrototypeHeadFn.apply(z, p, w, cfg, True, True)
+    tol = _tol(math)
+    assert_rel(d, g["dist"], tol, "dist"), assert_rel(a, g["act"], tol, "act")
+    assert_rel(logits.view(g["logits"].shape), g["logits"], tol, "logits")
+    # all three upstream gradients (dense ones go through the exact-operand kernels)
+    loss = (logits.view(g["logits"].shape) * _cu(g["dlogits"])).sum() + (d * _cu(g["ddist"])).sum() + (a * _cu(g["dact"])).sum()
+    dz, dp, dw = torch.autograd.grad(loss, [z, p, w])
+    assert_grad(dz, g["dz"], 1e-3, "dz"), assert_grad(dp, g["dprotos"], 1e-3, "dprotos"), assert_grad(dw, g["dlast_w"], 1e-3, "dlast_w")
+
+
+@pytest.mark.parametrize("math", TC_MATHS)
+@pytest.mark.parametrize("shape", [(2, 9, 7, 228, 19, None), (1, 33, 40, 760, 19, None),
+                                   (2, 20, 20, 221, 19, [(0, 50), (50, 121), (121, 130), (130, 221)]),
+                                   (1, 12, 11, 1100, 7, [(0, 500), (500, 700), (700, 900), (900, 1100)])])
+def test_tensor_core_fwd_bwd_vs_oracle(built_lib, shape, math):
+    """Fused-mode step (logits out, dlogits in) on seeded inputs: tcgen05 forward + tcgen05 backward against the
+    CPU oracle's autograd; uniform and ragged scale ranges, a scale wider than one CTA group (500 prototypes),
+    a random last layer."""
+    B, H, W, P, K, ranges = shape
+    gen = torch.Generator().manual_seed(ho.SEED + P)
+    z = torch.sigmoid(torch.randn(B, 256, H, W, generator=gen))
+    protos = torch.rand(P, 64, 1, 1, generator=gen)
+    last_w = ho.make_last_layer(ho.make_identity(P, K, 4)).contiguous() if ranges is None else torch.randn(K, P, generator=gen)
+    ranges = ranges or ho.uniform_ranges(P, 4)
+    N = B * H * W
+    dl = torch.randn(B, H, W, K, generator=gen) / N
+    zr, pr, wr = z.clone().requires_grad_(True), protos.clone().requires_grad_(True), last_w.clone().requires_grad_(True)
+    lo, _, ao = ho.head_stage1(zr, pr, ranges, wr)
+    lo.backward(dl)
+    cfg = sps.HeadConfig.from_ranges(ranges, K, math=math)
+    zc, pc, wc = (t.to(DEV).requires_grad_(True) for t in (z, protos, last_w))
+    lg, dnone, anone = sps.PrototypeHeadFn.apply(zc, pc, wc, cfg, False, False)
+    assert dnone is None and anone is None            # fused mode: no (N x P) map exists
+    lg.view(B, H, W, K).backward(dl.to(DEV))
+    if math in (sps.MATH_F16X3, sps.MATH_BF16X3):
+        assert_rel(lg.view(B, H, W, K), lo, _tol(math), "logits")
+    else:
+        # rounded 16-bit operands: the error of a P-term sum is bounded relative to sum_p |a W|, not to |logit|
+        bound = (ao.detach().abs() @ wr.detach().abs().t()).clamp_min(1.0)
+        err = ((lg.detach().cpu().double() - lo.detach().reshape(-1, K).double()).abs() / bound.double()).max().item()
+        assert err <= _tol(math), f"logits: {err:.3e} of sum|aW| > {_tol(math):.1e}"
+    gt = _grad_tol(math)
+    assert_grad(zc.grad, zr.grad, gt, "dz"), assert_grad(pc.grad, pr.grad, gt, "dprotos"), assert_grad(wc.grad, wr.grad, gt, "dlast_w")
+
+
+def test_tensor_core_pushed_prototype(built_lib):
+    """d -> 0 (a prototype equal to a feature vector, as after push): the split mode keeps fp32-class
+    distances where the slope of the log similarity is 1/eps."""
+    P, K = 24, 2
+    cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, 4), K, math=sps.MATH_F16X3)
+    z = torch.sigmoid(torch.randn(1, 256, 4, 4, generator=torch.Generator().manual_seed(3)))
+    p = torch.rand(P, 64, generator=torch.Generator().manual_seed(4))
+    p[7] = z[0, 64:128, 2, 3]
+    w = ho.make_last_layer(ho.make_identity(P, K, 4)).contiguous()
+    lg, dg, ag = sps.head_forward_raw(z.to(DEV), p.to(DEV), w.to(DEV), cfg, True, True)
+    lr, dr, ar = ho.head_stage1(z, p.view(P, 64, 1, 1), ho.uniform_ranges(P, 4), w)
+    assert dg[0, 7, 2, 3].item() <= 2e-5
+    assert_rel(dg, dr, 1e-3, "dist")
+    keep = torch.ones_like(ar, dtype=torch.bool)
+    keep[2 * 4 + 3, 7] = False                         # the d ~ 1e-6 element itself: |a| > 7 on both sides
+    assert ag[2 * 4 + 3, 7].item() > 7.0
+    assert_rel(ag[keep], ar[keep], 1e-3, "act")
