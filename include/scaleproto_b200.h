@@ -138,9 +138,10 @@ int sps_group_bwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* a
  *               segmentation/data/dataset.py:22-30); 0 = void, c+1 = class c
  *   proto_class [P] int32 class of each prototype (argmax of prototype_class_identity)
  *   keys        [B, P] uint64, OVERWRITTEN: (float_bits(min masked distance) << 32) | flat index h*W+w
- *               of its first occurrence; (bits(1e10f) << 32) | 0 when the class is absent. */
+ *               of its first occurrence; (bits(1e10f) << 32) | 0 when the class is absent.
+ *   workspace   >= sps_head_fwd_workspace_bytes(desc) bytes (NULL / 0 for SPS_MATH_FP32) */
 int sps_push_scan(const SpsHeadDesc* desc, const float* z, const float* protos, const int16_t* labels,
-                  const int32_t* proto_class, uint64_t* keys, void* stream);
+                  const int32_t* proto_class, uint64_t* keys, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Dataset arg-min over maps (push_multiscale_optimization.py:135-137, argmin(dim=0): first map wins).
  *   keys [n_maps, P] from sps_push_scan; map_base = global index of keys row 0 (shard offset).

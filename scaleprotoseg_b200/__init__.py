@@ -11,7 +11,8 @@ from .head import (GroupHeadFn, HeadConfig, PrototypeHeadFn, build_group_tables,
 from .install import install, install_on_classes, install_push, uninstall
 from . import model_api, push
 
-PUSH_MATH = MATH_FP32     # math mode the push scan runs in
+PUSH_MATH = MATH_F16X3    # math mode the push scan runs in (tcgen05, 3-term fp16 products)
+HAS_TC_PUSH = True
 HAS_TC_BACKWARD = True   # sps_head_bwd runs the tcgen05 backward for the fused-mode step in the 16-bit math modes
 
 __all__ = ["install", "install_on_classes", "install_push", "uninstall", "HeadConfig", "PrototypeHeadFn",

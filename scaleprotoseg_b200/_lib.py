@@ -49,7 +49,7 @@ _SIGNATURES = {
     "sps_group_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc)]),
     "sps_group_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc), _P, _P, _P, _P, _P, _P, _P,
                                 C.c_size_t, _P]),
-    "sps_push_scan": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P]),
+    "sps_push_scan": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "sps_push_reduce": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint32, _P, _P]),
     "sps_push_gather": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, C.c_int32, C.c_uint32, _P, _P, _P]),
 }

@@ -151,7 +151,7 @@ int sps_group_bwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* a
 }
 
 int sps_push_scan(const SpsHeadDesc* desc, const float* z, const float* protos, const int16_t* labels,
-                  const int32_t* proto_class, uint64_t* keys, void* stream) {
+                  const int32_t* proto_class, uint64_t* keys, void* workspace, size_t workspace_bytes, void* stream) {
   int rc = validate_desc(desc);
   if (rc != SPS_OK) return rc;
   SPS_REQUIRE(z && protos && labels && proto_class && keys, SPS_ERR_BAD_ARG, "push_scan: NULL argument");
@@ -159,7 +159,10 @@ int sps_push_scan(const SpsHeadDesc* desc, const float* z, const float* protos, 
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   if (desc->math == SPS_MATH_FP32)
     return launch_push_scan_simt(s, z, protos, labels, proto_class, reinterpret_cast<unsigned long long*>(keys), st);
-  SPS_REQUIRE(false, SPS_ERR_UNSUPPORTED, "math mode %d not built yet", desc->math);
+  rc = launch_push_fill(reinterpret_cast<unsigned long long*>(keys), (long long)s.B * s.P, st);
+  if (rc != SPS_OK || s.B == 0 || s.P == 0 || s.HW == 0) return rc;
+  return launch_push_scan_tc(s, desc->math, z, protos, labels, proto_class, reinterpret_cast<unsigned long long*>(keys),
+                             workspace, workspace_bytes, st);
 }
 
 int sps_push_reduce(const uint64_t* keys, int32_t n_maps, int32_t P, uint32_t map_base, uint64_t* best,

@@ -485,6 +485,20 @@ int build_chunk_table(const HeadShape& s, bool with_last_layer, tc::ChunkTable* 
   return SPS_OK;
 }
 
+int launch_proto_prep(const HeadShape& s, int math, const tc::ChunkTable& ct, const float* protos, const float* last_w,
+                      unsigned char* img, cudaStream_t st) {
+  switch (math) {
+    case SPS_MATH_F16: tc::proto_prep_kernel<__half, 1><<<ct.n_chunks, 256, 0, st>>>(ct, s.D, s.P, s.K, s.act_kind, protos, last_w, img); break;
+    case SPS_MATH_F16X3: tc::proto_prep_kernel<__half, 3><<<ct.n_chunks, 256, 0, st>>>(ct, s.D, s.P, s.K, s.act_kind, protos, last_w, img); break;
+    case SPS_MATH_BF16: tc::proto_prep_kernel<__nv_bfloat16, 1><<<ct.n_chunks, 256, 0, st>>>(ct, s.D, s.P, s.K, s.act_kind, protos, last_w, img); break;
+    case SPS_MATH_BF16X3: tc::proto_prep_kernel<__nv_bfloat16, 3><<<ct.n_chunks, 256, 0, st>>>(ct, s.D, s.P, s.K, s.act_kind, protos, last_w, img); break;
+    default: SPS_REQUIRE(false, SPS_ERR_BAD_ARG, "math=%d is not a tensor-core mode", math);
+  }
+  count_launch();
+  SPS_CUDA_TRY(cudaGetLastError());
+  return SPS_OK;
+}
+
 size_t head_fwd_tc_workspace(const HeadShape& s) {
   tc::ChunkTable ct;
   if (build_chunk_table(s, true, &ct) != SPS_OK) return 0;

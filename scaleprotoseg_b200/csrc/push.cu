@@ -87,6 +87,15 @@ __global__ void __launch_bounds__(NT) push_scan_simt_kernel(HeadShape s, const f
   }
 }
 
+int launch_push_fill(unsigned long long* keys, long long count, cudaStream_t st) {
+  if (count == 0) return SPS_OK;
+  const unsigned long long init = ((unsigned long long)0x501502F9u) << 32;  // bits(1e10f)
+  fill_keys_kernel<<<(unsigned)((count + 255) / 256), 256, 0, st>>>(keys, count, init);
+  count_launch();
+  SPS_CUDA_TRY(cudaGetLastError());
+  return SPS_OK;
+}
+
 int launch_push_scan_simt(const HeadShape& s, const float* z, const float* protos, const int16_t* labels,
                           const int32_t* proto_class, unsigned long long* keys, cudaStream_t st) {
   SPS_REQUIRE(s.D <= MAXD && s.D % 4 == 0, SPS_ERR_UNSUPPORTED, "fp32 push: D=%d must be a multiple of 4, <= %d", s.D, MAXD);

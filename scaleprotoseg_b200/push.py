@@ -51,9 +51,11 @@ def scan_maps(z: torch.Tensor, labels: torch.Tensor, protos: torch.Tensor, proto
     proto_class = proto_class.to(device=z.device, dtype=torch.int32).contiguous()
     keys = keys_out if keys_out is not None else torch.empty((B, P), device=z.device, dtype=torch.int64)
     desc = make_desc(cfg, B, H, W, D, P)
+    nbytes = int(lib.sps_head_fwd_workspace_bytes(C.byref(desc)))
+    ws = torch.empty(nbytes, device=z.device, dtype=torch.uint8) if nbytes else None
     with torch.cuda.device(z.device):
         _lib.check(lib.sps_push_scan(C.byref(desc), _ptr(z), _ptr(p2), _ptr(labels), _ptr(proto_class), _ptr(keys),
-                                     _stream()), "sps_push_scan")
+                                     _ptr(ws), nbytes, _stream()), "sps_push_scan")
     return keys
 
 

@@ -142,7 +142,7 @@ def check_push(keys, win_map, z_maps, labels, protos, ranges, ident, K, tol):
     return win_o
 
 
-@pytest.mark.parametrize("math", MATHS)
+@pytest.mark.parametrize("math", MATHS + [sps.MATH_F16X3, sps.MATH_F16, sps.MATH_BF16X3])
 @pytest.mark.parametrize("name", ["push_small", "push_city228"])
 def test_push_golden(built_lib, golden_dir, name, math):
     g = _load(golden_dir, name)
@@ -244,3 +244,26 @@ def test_tensor_core_pushed_prototype(built_lib):
     keep[2 * 4 + 3, 7] = False                         # the d ~ 1e-6 element itself: |a| > 7 on both sides
     assert ag[2 * 4 + 3, 7].item() > 7.0
     assert_rel(ag[keep], ar[keep], 1e-3, "act")
+
+
+@pytest.mark.parametrize("math", [sps.MATH_F16X3, sps.MATH_F16])
+def test_push_tensor_core_large_map(built_lib, math):
+    """Maps whose size is not a multiple of the 128-position tile, several maps per launch, ragged scale ranges
+    wider than one CTA group (300 prototypes in a scale), a class absent from every map, a void-only map."""
+    K, S = 6, 4
+    ranges = [(0, 300), (300, 366), (366, 372), (372, 480)]
+    P = 480
+    gen = torch.Generator().manual_seed(ho.SEED + 5)
+    ident = torch.zeros(P, K)
+    ident[torch.arange(P), torch.randint(0, K, (P,), generator=gen)] = 1
+    protos = torch.rand(P, 64, 1, 1, generator=gen)
+    n, h, w = 5, 23, 31
+    z = torch.sigmoid(torch.randn(n, 256, h, w, generator=gen))
+    labels = torch.stack([ho.make_labels(i, h, w, K, absent_class=2) for i in range(n)])
+    labels[3] = 0
+    cfg = sps.HeadConfig.from_ranges(ranges, K, math=math)
+    pc = spush.proto_class_of(ident)
+    keys = spush.scan_maps(z.to(DEV), labels.to(torch.int16).to(DEV), protos.to(DEV), pc, cfg)
+    best = spush.reduce_keys(keys, 0)
+    win, _ = spush.decode_keys(best)
+    check_push(keys, win, [z[i:i + 1] for i in range(n)], [labels[i] for i in range(n)], protos, ranges, ident, K, _tol(math))
