@@ -13,6 +13,7 @@ from test_gpu_parity import DEV, assert_grad, assert_rel
 
 pytestmark = pytest.mark.gpu
 TOL = 5e-5
+IMPORT_TIME_DEFAULT = sps.default_math()   # before the autouse fixture below switches to the exact mode
 
 
 @pytest.fixture(autouse=True)
@@ -191,7 +192,7 @@ def test_default_math_is_tensor_core_and_training_step_matches(patched_classes):
     """install() defaults to the tcgen05 kernels (3-term fp16 products).  One training-style step through the
     patched model: logits-only loss -> fused forward + tensor-core backward; the parameter gradients match the
     un-patched CPU model within the north-star tolerance."""
-    assert sps.head.__dict__["_DEFAULT_MATH"] == sps.MATH_F16X3
+    assert IMPORT_TIME_DEFAULT == sps.MATH_F16X3
     sps.set_default_math(sps.MATH_F16X3)
     ref, got = _pair(Stage1Standin, patched_classes[0], 228, 19)
     x = torch.randn(2, 256, 9, 9)
