@@ -13,7 +13,8 @@
 // Work decomposition: a tile is 128 consecutive positions (rows n = (b*H + h)*W + w, the order of
 // permute(0,2,3,1).reshape(-1,P), :369-370); the prototypes of each scale (ragged ranges allowed, :400-432)
 // are cut into chunks of 64.  One persistent CTA per SM walks tiles; inside a tile it walks the chunks.
-// Warp roles: warps 0-7 = epilogue (two per TMEM lane quarter, 32 columns each), warps 8-11 = feature-tile
+// Warp roles: warps 0-7 = epilogue (two per TMEM lane quarter; warps 0-3 take the even units, warps 4-7 the odd
+// ones, so the two warps of an SM sub-partition run out of phase), warps 8-11 = feature-tile
 // loaders (NCHW fp32 -> 16-bit K-major swizzled tiles + row norms), warp 12 = prototype-chunk producer (bulk
 // async copies of the packed images written by the pre-pass), warp 13 = distance-GEMM issuer, warp 14 =
 // logits-GEMM issuer (one lane of each issues; tcgen05 work of one thread executes in issue order, so two
@@ -172,8 +173,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       mbar_init(bar(BAR_AFULL + i), 4);    // one arrive per loader warp
       mbar_init(bar(BAR_AEMPTY + i), 1);   // tcgen05.commit
       mbar_init(bar(BAR_SFULL + i), 1);    // tcgen05.commit
-      mbar_init(bar(BAR_SEMPTY + i), 8);   // one arrive per epilogue warp
-      mbar_init(bar(BAR_PFULL + i), 8);
+      mbar_init(bar(BAR_SEMPTY + i), 4);   // one arrive per epilogue warp of the set that owns the buffer
+      mbar_init(bar(BAR_PFULL + i), 4);
       mbar_init(bar(BAR_PEMPTY + i), 1);
       mbar_init(bar(BAR_LFULL + i), 1);
       mbar_init(bar(BAR_LEMPTY + i), 4);   // epilogue warps 4..7 read the logits
@@ -205,9 +206,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       const bool first_of_scale = c == 0 || ct.scale[c] != ct.scale[c - 1];
       const bool last_of_scale = c == NC - 1 || ct.scale[c + 1] != ct.scale[c];
       const uint32_t ab = acount & 1, st = i % NST, sb = i & 1;
+      if (lane == 0) TL(5, i);
       if (first_of_scale) mbar_wait(bar(BAR_AFULL + ab), (acount >> 1) & 1);
+      if (lane == 0) TL(6, i);
       mbar_wait(bar(BAR_BFULL + st), (i / NST) & 1);
+      if (lane == 0) TL(4, i);
       mbar_wait(bar(BAR_SEMPTY + sb), ((i >> 1) & 1) ^ 1);
+      if (lane == 0) TL(7, i);
       tc_fence_after();
       if (lane == 0) {
         const uint32_t a_hi = base + pl.a_off(ab), a_lo = a_hi + A_HI;
@@ -287,61 +292,53 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
     }
   } else if (warp >= WARP_LOAD0 && warp < WARP_PROD) {
     // ================================ feature-tile loaders ================================
+    // Work list: (tile, scale) pairs in the order the distance-GEMM issuer consumes them.  Software pipeline: the
+    // loads of pair i+1 are issued half by half while pair i is converted, and before the wait for its buffer.
     const int m = threadIdx.x - WARP_LOAD0 * 32;  // row of the tile
+    const uint32_t hw = (uint32_t)s.HW;
+    auto row_ptr = [&](int ti, int c) -> const float* {
+      long long n = ((long long)blockIdx.x + (long long)ti * gridDim.x) * TILE_M + m;
+      if (n >= s.N) n = s.N - 1;  // rows past the end read a valid row; their results are never stored
+      const long long b = n / s.HW, pix = n % s.HW;
+      return prm.z + (b * (long long)s.C + (long long)ct.scale[c] * s.D) * s.HW + pix;
+    };
+    auto advance = [&](int& ti, int& c) {  // first chunk of the next scale, wrapping to the next tile
+      const int sc = ct.scale[c];
+      do { ++c; } while (c < NC && ct.scale[c] == sc);
+      if (c == NC) { c = 0; ++ti; }
+    };
+    ZStage<X, NSPLIT> zst;
+    int ti = 0, c = 0;
     uint32_t acount = 0;
-    for (int ti = 0; ti < my_tiles; ++ti) {
-      const long long n = ((long long)blockIdx.x + (long long)ti * gridDim.x) * TILE_M + m;
-      const bool valid = n < s.N;
-      const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
-      const float* zrow = prm.z + b * (long long)s.C * s.HW + pix;
-      for (int c = 0; c < NC; ++c) {
-        if (!(c == 0 || ct.scale[c] != ct.scale[c - 1])) continue;
-        const int sc = ct.scale[c];
-        const uint32_t ab = acount & 1;
-        mbar_wait(bar(BAR_AEMPTY + ab), ((acount >> 1) & 1) ^ 1);
-        unsigned char* a_hi = gbase + pl.a_off(ab);
-        unsigned char* a_lo = a_hi + A_HI;
-        unsigned char* a_n = a_hi + (NSPLIT == 3 ? 2 : 1) * A_HI;
-        const float* zs = zrow + (long long)sc * s.D * s.HW;
-        float zn = 0.f;
-        float v[64];
-#pragma unroll
-        for (int k = 0; k < 64; ++k) v[k] = (valid && k < s.D) ? __ldg(zs + (long long)k * s.HW) : 0.0f;
-#pragma unroll
-        for (int g = 0; g < 8; ++g) {
-          uint32_t hw[4], lw[4];
-#pragma unroll
-          for (int q = 0; q < 4; ++q) {
-            const float v0 = v[g * 8 + 2 * q], v1 = v[g * 8 + 2 * q + 1];
-            hw[q] = Pack2<X>::pack(v0, v1);
-            float2 e = Pack2<X>::unpack(hw[q]);
-            if (NSPLIT == 3) {
-              lw[q] = Pack2<X>::pack(v0 - e.x, v1 - e.y);
-              const float2 el = Pack2<X>::unpack(lw[q]);
-              e.x += el.x;
-              e.y += el.y;
-            }
-            zn = fmaf(e.x, e.x, zn);
-            zn = fmaf(e.y, e.y, zn);
-          }
-          const uint32_t off = (uint32_t)m * 128u + ((((uint32_t)g) ^ ((uint32_t)m & 7u)) << 4);
-          *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
-          if (NSPLIT == 3) *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
-        }
-        {
-          X h, mm, l;
-          split3<X>(zn, h, mm, l);
-          const uint32_t one = bits16(Fmt<X>::from(1.0f));
-          const uint4 w0 = make_uint4(one | (one << 16), one | ((uint32_t)bits16(h) << 16),
-                                      (uint32_t)bits16(mm) | ((uint32_t)bits16(l) << 16), 0u);
-          *reinterpret_cast<uint4*>(a_n + norm_off(m, 0)) = w0;
-          *reinterpret_cast<uint4*>(a_n + norm_off(m, 8)) = make_uint4(0u, 0u, 0u, 0u);
-        }
-        fence_proxy_async();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar(BAR_AFULL + ab));
-        ++acount;
-      }
+    const float* cur = nullptr;
+    if (my_tiles > 0) {
+      cur = row_ptr(0, 0);
+      zst.issue_half(0, cur, hw, s.D);
+      zst.issue_half(1, cur, hw, s.D);
+    }
+    while (ti < my_tiles) {
+      int nti = ti, nc = c;
+      advance(nti, nc);
+      const bool have_next = nti < my_tiles;
+      const float* nxt = have_next ? row_ptr(nti, nc) : cur;
+      const uint32_t ab = acount & 1;
+      mbar_wait(bar(BAR_AEMPTY + ab), ((acount >> 1) & 1) ^ 1);
+      unsigned char* a_hi = gbase + pl.a_off(ab);
+      unsigned char* a_lo = a_hi + A_HI;
+      unsigned char* a_n = a_hi + (NSPLIT == 3 ? 2 : 1) * A_HI;
+      float zn = 0.f;
+      zst.convert_half(0, m, a_hi, a_lo, zn);
+      if (have_next) zst.issue_half(0, nxt, hw, s.D);
+      zst.convert_half(1, m, a_hi, a_lo, zn);
+      ZStage<X, NSPLIT>::store_norm(m, a_n, zn);
+      if (have_next) zst.issue_half(1, nxt, hw, s.D);
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(BAR_AFULL + ab));
+      ++acount;
+      ti = nti;
+      c = nc;
+      cur = nxt;
     }
   }
   else if (warp < WARP_LOAD0) {
@@ -372,27 +369,40 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(BAR_LEMPTY + lb));
     };
+    // The two warps of a lane quarter (ew and ew+4 share an SM sub-partition) take ALTERNATE units: set 0 (warps
+    // 0-3) the even ones, set 1 (warps 4-7) the odd ones, each walking both 32-column halves of its unit.  In
+    // lock-step both warps sat in the MUFU phase together (XU pipe saturated) and then in the pack / store / wait
+    // phase together (XU idle); out of phase one warp's MUFU work hides under the other's packing and waiting.
+    const int set = half;
     const int defer_c = NC > 1 ? 1 : 0;
-    uint32_t u = 0;
-    for (int ti = 0; ti < my_tiles; ++ti) {
-      const long long n = ((long long)blockIdx.x + (long long)ti * gridDim.x) * TILE_M + m;
+    int next_store = 0;   // set 0: next tile whose logits go to HBM
+    const int U = my_tiles * NC;
+    int ti = 0, c = 0;
+    long long n = (long long)blockIdx.x * TILE_M + m;
+    if (set == 1) { c = 1; if (c >= NC) { c = 0; ti = 1; n += (long long)gridDim.x * TILE_M; } }
+    for (int u = set; u < U; u += 2) {
       const bool valid = n < s.N;
       const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
       float* drow = prm.dist != nullptr ? prm.dist + b * (long long)s.P * s.HW + pix : nullptr;
       float* arow = prm.act != nullptr ? prm.act + n * (long long)s.P : nullptr;
-      for (int c = 0; c < NC; ++c, ++u) {
-        const uint32_t sb = u & 1, pb = u & 1;
+      const uint32_t sb = u & 1, pb = u & 1, ph = (u >> 1) & 1;
+      if (lane == 0 && q == 0) TL(3, 8 * u + 0);
+      mbar_wait(bar(BAR_SFULL + sb), ph);
+      if (lane == 0 && q == 0) TL(3, 8 * u + 1);
+      tc_fence_after();
+      unsigned char* prow = gbase + pl.p_off(pb) + (uint32_t)m * 128u;
+#pragma unroll 1
+      for (int hf = 0; hf < 2; ++hf) {
         uint32_t r[32];
-        mbar_wait(bar(BAR_SFULL + sb), (u >> 1) & 1);
-        if (threadIdx.x == 0) TL(4, u);
-        tc_fence_after();
-        tmem_ld32(tmem + lane_base + TMEM_S0 + sb * CN + half * 32, r);
+        tmem_ld32(tmem + lane_base + TMEM_S0 + sb * CN + hf * 32, r);
         tmem_ld_wait();
-        tc_fence_before();
-        __syncwarp();
-        if (lane == 0) mbar_arrive(bar(BAR_SEMPTY + sb));
-        if (threadIdx.x == 0) TL(5, u);
-        const int col0 = half * 32, ncols = ct.n[c] - col0;  // live columns of this warp: [0, ncols)
+        if (lane == 0 && q == 0) TL(3, 8 * u + 2 + 2 * hf);
+        if (hf == 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar(BAR_SEMPTY + sb));
+        }
+        const int col0 = hf * 32, ncols = ct.n[c] - col0;  // live columns of this half: [0, ncols)
         const int p0 = ct.p0[c] + col0;
         float av[32];  // log2 of the similarity ratio ('log'), or -d ('linear')
         if (drow == nullptr && arow == nullptr) {  // fused mode: nothing but the logits leaves the SM
@@ -415,10 +425,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
               if (j < ncols) arow[p0 + j] = av[j] * sc;
           }
         }
-        if (threadIdx.x == 0) TL(6, u);
         if (has_w) {
-          mbar_wait(bar(BAR_PEMPTY + pb), ((u >> 1) & 1) ^ 1);
-          unsigned char* prow = gbase + pl.p_off(pb) + (uint32_t)m * 128u;
+          if (hf == 0) mbar_wait(bar(BAR_PEMPTY + pb), ph ^ 1);
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             uint32_t w[4], wl[4];
@@ -431,20 +439,29 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
                 wl[e] = Pack2<X>::pack(x0 - h.x, x1 - h.y);
               }
             }
-            const uint32_t poff = (((uint32_t)(half * 4 + g)) ^ ((uint32_t)m & 7u)) << 4;
+            const uint32_t poff = (((uint32_t)(hf * 4 + g)) ^ ((uint32_t)m & 7u)) << 4;
             *reinterpret_cast<uint4*>(prow + poff) = make_uint4(w[0], w[1], w[2], w[3]);
             if (NSPLIT == 3) *reinterpret_cast<uint4*>(prow + P_BYTES + poff) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
           }
-          fence_proxy_async();
-          __syncwarp();
-          if (lane == 0) mbar_arrive(bar(BAR_PFULL + pb));
         }
-        if (threadIdx.x == 0) TL(7, u);
-        if (lane == 0) TL(3, 8 * u + ew);
-        if (has_w && half == 0 && ti > 0 && c == defer_c) store_logits(ti - 1);
+        if (lane == 0 && q == 0) TL(3, 8 * u + 3 + 2 * hf);
       }
+      if (has_w) {
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(BAR_PFULL + pb));
+      }
+      if (lane == 0 && q == 0) TL(3, 8 * u + 7);
+      if (has_w && set == 0) {
+        while (next_store < ti - 1) store_logits(next_store++);
+        if (next_store == ti - 1 && c >= defer_c) store_logits(next_store++);
+      }
+      // advance two units
+      c += 2;
+      while (c >= NC) { c -= NC; ++ti; n += (long long)gridDim.x * TILE_M; }
     }
-    if (has_w && half == 0 && my_tiles > 0) store_logits(my_tiles - 1);
+    if (has_w && set == 0)
+      while (next_store < my_tiles) store_logits(next_store++);
   }
 
   // ================================ teardown ================================

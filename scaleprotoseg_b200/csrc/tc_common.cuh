@@ -235,6 +235,61 @@ template <typename X> __device__ __forceinline__ void split3(float v, X& h, X& m
 }
 
 // ---------------------------------------------------------------------------------------------
+// Feature-row staging shared by the forward, backward and push loaders.  One thread owns one position (row m
+// of a 128-row tile) and the 64 channels of one scale: 64 coalesced LDGs (32 consecutive positions per warp and
+// channel), then the 16-bit K-major SW128 tile(s) and the squared norm of the operand the MMA really sees.
+// The 64 values are staged in two halves of 32 so that the loads of the NEXT row can be issued while the current
+// half is still being converted (software pipeline across tiles; see the loader loops).
+// ---------------------------------------------------------------------------------------------
+template <typename X, int NSPLIT> struct ZStage {
+  float v[64];
+  // zs: channel 0 of this row (a VALID address: callers clamp out-of-range rows); hw: channel pitch in elements
+  __device__ __forceinline__ void issue_half(int h, const float* __restrict__ zs, uint32_t hw, int D) {
+    if (D == 64) {
+#pragma unroll
+      for (int k = 0; k < 32; ++k) v[h * 32 + k] = __ldg(zs + (size_t)((uint32_t)(h * 32 + k) * hw));
+    } else {
+#pragma unroll
+      for (int k = 0; k < 32; ++k) v[h * 32 + k] = (h * 32 + k < D) ? __ldg(zs + (size_t)((uint32_t)(h * 32 + k) * hw)) : 0.0f;
+    }
+  }
+  // converts channels [32h, 32h+32) of row m into a_hi (and a_lo); accumulates the squared norm
+  __device__ __forceinline__ void convert_half(int h, int m, unsigned char* a_hi, unsigned char* a_lo, float& zn) {
+#pragma unroll
+    for (int g4 = 0; g4 < 4; ++g4) {
+      const int g = h * 4 + g4;
+      uint32_t hw_[4], lw_[4];
+#pragma unroll
+      for (int q = 0; q < 4; ++q) {
+        const float v0 = v[g * 8 + 2 * q], v1 = v[g * 8 + 2 * q + 1];
+        hw_[q] = Pack2<X>::pack(v0, v1);
+        float2 e = Pack2<X>::unpack(hw_[q]);
+        if (NSPLIT == 3) {
+          lw_[q] = Pack2<X>::pack(v0 - e.x, v1 - e.y);
+          const float2 el = Pack2<X>::unpack(lw_[q]);
+          e.x += el.x;
+          e.y += el.y;
+        }
+        zn = fmaf(e.x, e.x, zn);
+        zn = fmaf(e.y, e.y, zn);
+      }
+      const uint32_t off = (uint32_t)m * 128u + ((((uint32_t)g) ^ ((uint32_t)m & 7u)) << 4);
+      *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hw_[0], hw_[1], hw_[2], hw_[3]);
+      if (NSPLIT == 3) *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lw_[0], lw_[1], lw_[2], lw_[3]);
+    }
+  }
+  // the extra K step of row m: [1, 1, 1, zn_hi, zn_mid, zn_lo, 0 ...]
+  static __device__ __forceinline__ void store_norm(int m, unsigned char* a_n, float zn) {
+    X h, mm, l;
+    split3<X>(zn, h, mm, l);
+    const uint32_t one = bits16(Fmt<X>::from(1.0f));
+    *reinterpret_cast<uint4*>(a_n + norm_off(m, 0)) = make_uint4(one | (one << 16), one | ((uint32_t)bits16(h) << 16),
+                                                                 (uint32_t)bits16(mm) | ((uint32_t)bits16(l) << 16), 0u);
+    *reinterpret_cast<uint4*>(a_n + norm_off(m, 8)) = make_uint4(0u, 0u, 0u, 0u);
+  }
+};
+
+// ---------------------------------------------------------------------------------------------
 // Prototype chunks.  The prototypes of every scale are cut into chunks of <= CN rows; the pre-pass writes
 // one packed image per chunk that the main kernels bulk-copy straight into shared memory:
 //   [Bhi  CN x 128 B  SW128]  rows j: -2 * p_(p0+j)            (hi part)

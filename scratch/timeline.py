@@ -19,6 +19,6 @@ print("rc", lib.sps_debug_timeline(buf, 8192))
 g = lambda r, e: buf[r * 1024 + e]
 t0 = min(v for v in buf if v > 0)
 f = lambda v: f"{v - t0:6d}" if v else "    -1"
-for u in range(16, 30):
-    print(u, "mma1", f(g(0, u)), "| pfull", f(g(1, u)), "mma2", f(g(2, u)),
-          "| epi sfull", f(g(4, u)), "ld", f(g(5, u)), "math", f(g(6, u)), "done/warp", " ".join(f(g(3, 8*u+w)) for w in range(8)))
+for u in range(24, 50):
+    print(u, "mma1: start", f(g(5, u)), "afull", f(g(6, u)), "bfull", f(g(4, u)), "sempty", f(g(7, u)), "issued", f(g(0, u)),
+          "| mma2 pfull", f(g(1, u)), "issued", f(g(2, u)), "| epi top/sfull/ld0/st0/ld1/st1/done", " ".join(f(g(3, 8*u+k)) for k in (0,1,2,3,4,5,7)))
