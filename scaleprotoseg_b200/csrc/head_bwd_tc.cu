@@ -270,52 +270,41 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
     }
   } else if (warp >= WARP_LOAD0 && warp < WARP_I1) {
     // ================= loaders: z_s tile (16-bit, K-major swizzled) + norms + scaled dlogits tile =================
+    // Software pipeline: the feature loads of tile ti+1 are issued half by half while tile ti is converted.
     const int m = threadIdx.x - WARP_LOAD0 * 32;
     const float G = grad_scale(__ldg(prm.amax_bits));
+    const uint32_t hw = (uint32_t)s.HW;
+    auto row_of = [&](int ti) -> long long { return ((long long)cta_local + (long long)ti * ncta) * TILE_M + m; };
+    auto row_ptr = [&](int ti) -> const float* {
+      long long n = row_of(ti);
+      if (n >= s.N) n = s.N - 1;  // rows past the end read a valid row; their dlogits are zero and nothing is stored
+      const long long b = n / s.HW, pix = n % s.HW;
+      return prm.z + (b * (long long)s.C + (long long)sc * s.D) * s.HW + pix;
+    };
+    ZStage<X, NSPLIT> zst;
+    const float* cur = nullptr;
+    if (my_tiles > 0) {
+      cur = row_ptr(0);
+      zst.issue_half(0, cur, hw, s.D);
+      zst.issue_half(1, cur, hw, s.D);
+    }
     for (int ti = 0; ti < my_tiles; ++ti) {
-      const long long n = ((long long)cta_local + (long long)ti * ncta) * TILE_M + m;
+      const long long n = row_of(ti);
       const bool valid = n < s.N;
-      const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
-      const float* zs = prm.z + b * (long long)s.C * s.HW + pix + (long long)sc * s.D * s.HW;
-      const uint32_t ab = ti & 1;
-      mbar_wait(bar(B_AEMPTY + ab), ((ti >> 1) & 1) ^ 1);
-      unsigned char* a0 = gbase + SM_A + ab * A_BUF;
-      float v[64];
-#pragma unroll
-      for (int k = 0; k < 64; ++k) v[k] = (valid && k < s.D) ? __ldg(zs + (long long)k * s.HW) : 0.0f;
+      const bool have_next = ti + 1 < my_tiles;
+      const float* nxt = have_next ? row_ptr(ti + 1) : cur;
       float dl[KP_BWD];
 #pragma unroll
       for (int k = 0; k < KP_BWD; ++k) dl[k] = (valid && k < s.K) ? __ldg(prm.dlogits + n * s.K + k) * G : 0.0f;
+      const uint32_t ab = ti & 1;
+      mbar_wait(bar(B_AEMPTY + ab), ((ti >> 1) & 1) ^ 1);
+      unsigned char* a0 = gbase + SM_A + ab * A_BUF;
       float zn = 0.f;
-#pragma unroll
-      for (int gq = 0; gq < 8; ++gq) {
-        uint32_t hw[4], lw[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float v0 = v[gq * 8 + 2 * q], v1 = v[gq * 8 + 2 * q + 1];
-          hw[q] = Pack2<X>::pack(v0, v1);
-          float2 e = Pack2<X>::unpack(hw[q]);
-          if (NSPLIT == 3) {
-            lw[q] = Pack2<X>::pack(v0 - e.x, v1 - e.y);
-            const float2 el = Pack2<X>::unpack(lw[q]);
-            e.x += el.x;
-            e.y += el.y;
-          }
-          zn = fmaf(e.x, e.x, zn);
-          zn = fmaf(e.y, e.y, zn);
-        }
-        const uint32_t zoff = (uint32_t)m * 128u + ((((uint32_t)gq) ^ ((uint32_t)m & 7u)) << 4);
-        *reinterpret_cast<uint4*>(a0 + AOFF_Z + zoff) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
-        if (NSPLIT == 3) *reinterpret_cast<uint4*>(a0 + AOFF_ZL + zoff) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
-      }
-      {
-        X h, mm, l;
-        split3<X>(zn, h, mm, l);
-        const uint32_t one = bits16(Fmt<X>::from(1.0f));
-        *reinterpret_cast<uint4*>(a0 + AOFF_N + norm_off(m, 0)) =
-            make_uint4(one | (one << 16), one | ((uint32_t)bits16(h) << 16), (uint32_t)bits16(mm) | ((uint32_t)bits16(l) << 16), 0u);
-        *reinterpret_cast<uint4*>(a0 + AOFF_N + norm_off(m, 8)) = make_uint4(0u, 0u, 0u, 0u);
-      }
+      zst.convert_half(0, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
+      if (have_next) zst.issue_half(0, nxt, hw, s.D);
+      zst.convert_half(1, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
+      ZStage<X, NSPLIT>::store_norm(m, a0 + AOFF_N, zn);
+      if (have_next) zst.issue_half(1, nxt, hw, s.D);
 #pragma unroll
       for (int gq = 0; gq < 4; ++gq) {
         uint32_t w[4];
@@ -327,6 +316,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(B_AFULL + ab));
+      cur = nxt;
     }
   }
   else if (warp < WARP_LOAD0) {
@@ -338,12 +328,61 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
     const bool is_log = s.act_kind == SPS_ACT_LOG;
     const float G = grad_scale(__ldg(prm.amax_bits)), invG = 1.0f / G;
     float* sgbuf = reinterpret_cast<float*>(gbase + SM_SG);
-    int u = 0;
-    for (int ti = 0; ti < my_tiles; ++ti) {
-      const long long n = ((long long)cta_local + (long long)ti * ncta) * TILE_M + m;
+    // dz of (tile tj, this scale): acc + 2 z sum_p gamma.  Called one unit into the NEXT tile, so the epilogue never
+    // sits waiting for the last dz GEMM of a tile (the issuer only needs the read-out before it overwrites T_DZ).
+    auto dz_readout = [&](int tj) {
+      const long long n = ((long long)cta_local + (long long)tj * ncta) * TILE_M + m;
       const bool valid = n < s.N;
       const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
-      const uint32_t ab = ti & 1;
+      const uint32_t ab = tj & 1;
+      const int ti = tj;
+      float* sgb = sgbuf + (ti & 1) * 256;
+      named_bar_sync(1, 256);
+      const float tot = sgb[m] + sgb[128 + m];
+      uint32_t rd[32];
+      mbar_wait(bar(B_DZFULL), ti & 1);
+      tc_fence_after();
+      tmem_ld32(tmem + lane_base + T_DZ + half * 32, rd);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(B_DZEMPTY));
+      const unsigned char* zrow = gbase + SM_A + ab * A_BUF + AOFF_Z + (uint32_t)m * 128u;
+      float* dzp = prm.dz + b * (long long)s.C * s.HW + (long long)sc * s.D * s.HW + pix;
+#pragma unroll
+      for (int gq = 0; gq < 4; ++gq) {
+        const uint32_t zo = (((uint32_t)(half * 4 + gq)) ^ ((uint32_t)m & 7u)) << 4;
+        const uint4 zz = *reinterpret_cast<const uint4*>(zrow + zo);
+        const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
+        uint32_t zlw[4] = {0u, 0u, 0u, 0u};
+        if (NSPLIT == 3) {
+          const uint4 zl = *reinterpret_cast<const uint4*>(zrow + (AOFF_ZL - AOFF_Z) + zo);
+          zlw[0] = zl.x, zlw[1] = zl.y, zlw[2] = zl.z, zlw[3] = zl.w;
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+          float2 zf = Pack2<X>::unpack(zw[e]);
+          if (NSPLIT == 3) {
+            const float2 zl2 = Pack2<X>::unpack(zlw[e]);
+            zf.x += zl2.x;
+            zf.y += zl2.y;
+          }
+          const int c = half * 32 + gq * 8 + 2 * e;
+          const float v0 = (__uint_as_float(rd[gq * 8 + 2 * e]) + 2.0f * zf.x * tot) * invG;
+          const float v1 = (__uint_as_float(rd[gq * 8 + 2 * e + 1]) + 2.0f * zf.y * tot) * invG;
+          if (prm.dz != nullptr && valid && c < s.D) {
+            if (multi) atomicAdd(dzp + (long long)c * s.HW, v0); else dzp[(long long)c * s.HW] = v0;
+          }
+          if (prm.dz != nullptr && valid && c + 1 < s.D) {
+            if (multi) atomicAdd(dzp + (long long)(c + 1) * s.HW, v1); else dzp[(long long)(c + 1) * s.HW] = v1;
+          }
+        }
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(B_AEMPTY + ab));
+    };
+    int u = 0;
+    for (int ti = 0; ti < my_tiles; ++ti) {
       float sg = 0.f;
       for (int j = 0; j < nch; ++j, ++u) {
         const uint32_t sb = u & 1, gb = u & 1;
@@ -391,54 +430,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(B_GFULL + gb));
+        if (j == 0 && ti > 0) dz_readout(ti - 1);
       }
-      // ---- dz of this (tile, scale): acc + 2 z sum_p gamma ----
-      float* sgb = sgbuf + (ti & 1) * 256;
-      sgb[half * 128 + m] = sg;
-      named_bar_sync(1, 256);
-      const float tot = sgb[m] + sgb[128 + m];
-      uint32_t rd[32];
-      mbar_wait(bar(B_DZFULL), ti & 1);
-      tc_fence_after();
-      tmem_ld32(tmem + lane_base + T_DZ + half * 32, rd);
-      tmem_ld_wait();
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar(B_DZEMPTY));
-      const unsigned char* zrow = gbase + SM_A + ab * A_BUF + AOFF_Z + (uint32_t)m * 128u;
-      float* dzp = prm.dz + b * (long long)s.C * s.HW + (long long)sc * s.D * s.HW + pix;
-#pragma unroll
-      for (int gq = 0; gq < 4; ++gq) {
-        const uint32_t zo = (((uint32_t)(half * 4 + gq)) ^ ((uint32_t)m & 7u)) << 4;
-        const uint4 zz = *reinterpret_cast<const uint4*>(zrow + zo);
-        const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
-        uint32_t zlw[4] = {0u, 0u, 0u, 0u};
-        if (NSPLIT == 3) {
-          const uint4 zl = *reinterpret_cast<const uint4*>(zrow + (AOFF_ZL - AOFF_Z) + zo);
-          zlw[0] = zl.x, zlw[1] = zl.y, zlw[2] = zl.z, zlw[3] = zl.w;
-        }
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          float2 zf = Pack2<X>::unpack(zw[e]);
-          if (NSPLIT == 3) {
-            const float2 zl2 = Pack2<X>::unpack(zlw[e]);
-            zf.x += zl2.x;
-            zf.y += zl2.y;
-          }
-          const int c = half * 32 + gq * 8 + 2 * e;
-          const float v0 = (__uint_as_float(rd[gq * 8 + 2 * e]) + 2.0f * zf.x * tot) * invG;
-          const float v1 = (__uint_as_float(rd[gq * 8 + 2 * e + 1]) + 2.0f * zf.y * tot) * invG;
-          if (prm.dz != nullptr && valid && c < s.D) {
-            if (multi) atomicAdd(dzp + (long long)c * s.HW, v0); else dzp[(long long)c * s.HW] = v0;
-          }
-          if (prm.dz != nullptr && valid && c + 1 < s.D) {
-            if (multi) atomicAdd(dzp + (long long)(c + 1) * s.HW, v1); else dzp[(long long)(c + 1) * s.HW] = v1;
-          }
-        }
-      }
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar(B_AEMPTY + ab));
+      sgbuf[(ti & 1) * 256 + half * 128 + m] = sg;   // row sums of gamma of this tile (read after the named barrier in dz_readout)
     }
+    if (my_tiles > 0) dz_readout(my_tiles - 1);
     // ---- partial dp / dW of this CTA ----
     if (U > 0) {
       mbar_wait(bar(B_ACC), 0);
