@@ -60,11 +60,13 @@ template <int NSPLIT> struct PLay {
   static constexpr int SM_BAR = SM_LAB + LAB_RING * TILE_M * 4;
   static constexpr int SM_TOTAL = SM_BAR + 256 + 1024;
 };
-enum { PB_ZFULL = 0, PB_ZEMPTY = 8, PB_DFULL = 16, PB_DEMPTY = 18, PB_RES = 20, PB_COUNT = 21 };
+enum { PB_ZFULL = 0, PB_ZEMPTY = 8, PB_DFULL = 16, PB_DEMPTY = 18, PB_RES = 20, PB_RES2 = 21, PB_COUNT = 22 };
 
 __device__ __forceinline__ unsigned long long absent_key64() { return ((unsigned long long)0x501502F9u) << 32; }  // 1e10f
 
-template <typename X, int NSPLIT>
+// MASKED: the class mask rides in the norm K step of the GEMM (labels <= MASK_MAX_LABEL, see ZStage::store_norm_mask)
+// and the epilogue is a plain running minimum; otherwise the epilogue compares labels element by element.
+template <typename X, int NSPLIT, bool MASKED>
 __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_constant__ PushParams prm) {
   using L = PLay<NSPLIT>;
   extern __shared__ unsigned char smem_raw[];
@@ -97,6 +99,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       mbar_init(bar(PB_DEMPTY + i), 8);
     }
     mbar_init(bar(PB_RES), 1);
+    mbar_init(bar(PB_RES2), 1);
     mbar_fence_init();
   }
   fence_proxy_async();
@@ -118,10 +121,25 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
         bulk_g2s(dst + L::ROFF_N + half * CN * 32, src + OFF_BN, CN * 32, bar(PB_RES));
       }
     }
+    if (MASKED) {
+      // prototype side of the class mask: a 1 in the slot of each digit of the prototype's label value
+      mbar_wait(bar(PB_RES), 0);
+      for (int r = lane; r < 2 * TILE_M; r += 32) {
+        const int jr = r >> 6, jj = r & 63;
+        if (jr < nch && jj < ct.n[c0 + jr]) {
+          const int cls1 = __ldg(prm.proto_class + ct.p0[c0 + jr] + jj) + 1;
+          ZStage<X, NSPLIT>::write_proto_mask(gbase + L::SM_RES + (r >> 7) * L::RES_T + L::ROFF_N, r & 127, cls1);
+        }
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(PB_RES2));
+    }
   } else if (warp == WARP_MMA) {
     // ================================ MMA issuer ================================
     constexpr uint32_t ID = idesc_f16(Fmt<X>::id, TILE_M, TILE_M);
     mbar_wait(bar(PB_RES), 0);
+    if (MASKED) mbar_wait(bar(PB_RES2), 0);
     for (int i = 0; i < my_tiles; ++i) {
       const int st = i % L::NSTAGE, db = i & 1;
       mbar_wait(bar(PB_ZFULL + st), (i / L::NSTAGE) & 1);
@@ -148,54 +166,50 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
     }
   } else if (warp >= WARP_LOAD0 && warp < WARP_MMA) {
     // ================================ feature loaders (two groups of 4 warps, alternate tiles) ================================
+    // Software pipeline per group: the feature loads of the group's next tile are issued half by half while the
+    // current one is converted, and before the wait for its stage.
     const int lt = threadIdx.x - WARP_LOAD0 * 32, grp = lt >> 7, m = lt & 127;
-    for (int i = grp; i < my_tiles; i += 2) {
+    const uint32_t hw = (uint32_t)s.HW;
+    auto row_ptr = [&](int i, long long& b, int& pix) -> const float* {
       const long long t = t_lo + i;
-      const long long b = t / prm.tiles_per_map;
-      const int pix = (int)(t % prm.tiles_per_map) * TILE_M + m;
-      const bool valid = pix < s.HW;
-      const float* zs = prm.z + (b * s.C + (long long)sc * s.D) * s.HW + pix;
+      b = t / prm.tiles_per_map;
+      pix = (int)(t % prm.tiles_per_map) * TILE_M + m;
+      const int px = pix < s.HW ? pix : s.HW - 1;  // rows past the end of the map read a valid row; their label is void
+      return prm.z + (b * s.C + (long long)sc * s.D) * s.HW + px;
+    };
+    ZStage<X, NSPLIT> zst;
+    long long b = 0, nb = 0;
+    int pix = 0, npix = 0;
+    const float* cur = nullptr;
+    if (grp < my_tiles) {
+      cur = row_ptr(grp, b, pix);
+      zst.issue_half(0, cur, hw, s.D);
+      zst.issue_half(1, cur, hw, s.D);
+    }
+    for (int i = grp; i < my_tiles; i += 2) {
+      const bool have_next = i + 2 < my_tiles;
+      const float* nxt = have_next ? row_ptr(i + 2, nb, npix) : cur;
+      const int lab = pix < s.HW ? (int)__ldg(prm.labels + b * s.HW + pix) : 0;
       const int st = i % L::NSTAGE;
       mbar_wait(bar(PB_ZEMPTY + st), ((i / L::NSTAGE) & 1) ^ 1);
       unsigned char* a0 = gbase + L::SM_Z + st * L::STAGE;
-      float v[64];
-#pragma unroll
-      for (int k = 0; k < 64; ++k) v[k] = (valid && k < s.D) ? __ldg(zs + (long long)k * s.HW) : 0.0f;
-      const int lab = valid ? (int)__ldg(prm.labels + b * s.HW + pix) : 0;
       float zn = 0.f;
-#pragma unroll
-      for (int gq = 0; gq < 8; ++gq) {
-        uint32_t hw[4], lw[4];
-#pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          const float v0 = v[gq * 8 + 2 * q], v1 = v[gq * 8 + 2 * q + 1];
-          hw[q] = Pack2<X>::pack(v0, v1);
-          float2 e = Pack2<X>::unpack(hw[q]);
-          if (NSPLIT == 3) {
-            lw[q] = Pack2<X>::pack(v0 - e.x, v1 - e.y);
-            const float2 el = Pack2<X>::unpack(lw[q]);
-            e.x += el.x;
-            e.y += el.y;
-          }
-          zn = fmaf(e.x, e.x, zn);
-          zn = fmaf(e.y, e.y, zn);
-        }
-        const uint32_t off = (uint32_t)m * 128u + ((((uint32_t)gq) ^ ((uint32_t)m & 7u)) << 4);
-        *reinterpret_cast<uint4*>(a0 + off) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
-        if (NSPLIT == 3) *reinterpret_cast<uint4*>(a0 + L::SOFF_LO + off) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+      zst.convert_half(0, m, a0, a0 + L::SOFF_LO, zn);
+      if (have_next) zst.issue_half(0, nxt, hw, s.D);
+      zst.convert_half(1, m, a0, a0 + L::SOFF_LO, zn);
+      if (MASKED) {
+        ZStage<X, NSPLIT>::store_norm_mask(m, a0 + L::SOFF_N, zn, lab);
+      } else {
+        ZStage<X, NSPLIT>::store_norm(m, a0 + L::SOFF_N, zn);
+        reinterpret_cast<int*>(gbase + L::SM_LAB)[(i % L::LAB_RING) * TILE_M + m] = lab;
       }
-      {
-        X h, mm, l;
-        split3<X>(zn, h, mm, l);
-        const uint32_t one = bits16(Fmt<X>::from(1.0f));
-        *reinterpret_cast<uint4*>(a0 + L::SOFF_N + norm_off(m, 0)) =
-            make_uint4(one | (one << 16), one | ((uint32_t)bits16(h) << 16), (uint32_t)bits16(mm) | ((uint32_t)bits16(l) << 16), 0u);
-        *reinterpret_cast<uint4*>(a0 + L::SOFF_N + norm_off(m, 8)) = make_uint4(0u, 0u, 0u, 0u);
-      }
-      reinterpret_cast<int*>(gbase + L::SM_LAB)[(i % L::LAB_RING) * TILE_M + m] = lab;
+      if (have_next) zst.issue_half(1, nxt, hw, s.D);
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(PB_ZFULL + st));
+      cur = nxt;
+      b = nb;
+      pix = npix;
     }
   }
   else if (warp < WARP_LOAD0) {
@@ -213,7 +227,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
     unsigned bidx = 0;
     long long cur_map = -1;
     auto flush = [&]() {
-      if (p >= 0 && cur_map >= 0 && best < 1.0e38f)
+      // MASKED: every differing label digit added MASK_BIG, so a minimum that large means "no position of this class"
+      if (p >= 0 && cur_map >= 0 && best < (MASKED ? 0.5f * MASK_BIG : 1.0e38f))
         atomicMin(prm.keys + cur_map * s.P + p, ((unsigned long long)__float_as_uint(best) << 32) | bidx);
     };
     for (int i = 0; i < my_tiles; ++i) {
@@ -229,7 +244,26 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       }
       mbar_wait(bar(PB_DFULL + db), (i >> 1) & 1);
       tc_fence_after();
-      if (live_warp) {
+      if (live_warp && MASKED) {
+#pragma unroll 1
+        for (int cb = 0; cb < 4; ++cb) {
+          uint32_t acc[32];
+          tmem_ld32(tmem + lane_base + db * 256 + mt * 128 + cb * 32, acc);
+          tmem_ld_wait();
+          float mn = __uint_as_float(acc[0]);
+#pragma unroll
+          for (int j = 1; j < 32; ++j) mn = fminf(mn, __uint_as_float(acc[j]));
+          mn = fmaxf(mn, 0.0f);                            // relu commutes with the minimum
+          if (mn < best) {                                 // strict <: an earlier batch keeps a tie
+            best = mn;
+            int jf = 31;                                   // first column whose clamped value is the minimum
+#pragma unroll
+            for (int j = 30; j >= 0; --j)
+              if (__uint_as_float(acc[j]) <= mn) jf = j;
+            bidx = pix0 + (unsigned)(cb * 32 + jf);
+          }
+        }
+      } else if (live_warp) {
         const int4* labs = reinterpret_cast<const int4*>(gbase + L::SM_LAB + (i % L::LAB_RING) * TILE_M * 4);
 #pragma unroll 1
         for (int cb = 0; cb < 4; ++cb) {
@@ -301,7 +335,7 @@ static int build_pgroups(const tc::ChunkTable& ct, long long n_tiles, int n_sm, 
   return next;
 }
 
-template <typename X, int NSPLIT>
+template <typename X, int NSPLIT, bool MASKED>
 static int launch_push_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const float* z, const int16_t* labels,
                             const int32_t* proto_class, unsigned long long* keys, const unsigned char* img, cudaStream_t st) {
   tcp::PushParams prm;
@@ -319,8 +353,8 @@ static int launch_push_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const 
   constexpr int SMEM = tcp::PLay<NSPLIT>::SM_TOTAL;
   static_assert(SMEM <= 227 * 1024 && tcp::PLay<NSPLIT>::NSTAGE >= 2 && tcp::PLay<NSPLIT>::NSTAGE + 2 <= tcp::PLay<NSPLIT>::LAB_RING,
                 "push kernel shared memory plan");
-  SPS_CUDA_TRY(cudaFuncSetAttribute(tcp::push_scan_tc_kernel<X, NSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-  tcp::push_scan_tc_kernel<X, NSPLIT><<<grid, tcp::NTHREADS, SMEM, st>>>(prm);
+  SPS_CUDA_TRY(cudaFuncSetAttribute(tcp::push_scan_tc_kernel<X, NSPLIT, MASKED>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  tcp::push_scan_tc_kernel<X, NSPLIT, MASKED><<<grid, tcp::NTHREADS, SMEM, st>>>(prm);
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;
@@ -338,12 +372,18 @@ int launch_push_scan_tc(const HeadShape& s, int math, const float* z, const floa
   unsigned char* img = reinterpret_cast<unsigned char*>(((uintptr_t)ws + 1023) & ~(uintptr_t)1023);
   rc = launch_proto_prep(s, math, ct, protos, nullptr, img, st);
   if (rc != SPS_OK) return rc;
+  // label values are class + 1 <= K; the in-GEMM class mask covers label values up to MASK_MAX_LABEL
+  const bool masked = s.K <= tc::MASK_MAX_LABEL;
+#define SPS_PUSH_CASE(X, NS)                                                                                  \
+  return masked ? launch_push_tc_t<X, NS, true>(s, ct, z, labels, proto_class, keys, img, st)                 \
+                : launch_push_tc_t<X, NS, false>(s, ct, z, labels, proto_class, keys, img, st)
   switch (math) {
-    case SPS_MATH_F16: return launch_push_tc_t<__half, 1>(s, ct, z, labels, proto_class, keys, img, st);
-    case SPS_MATH_F16X3: return launch_push_tc_t<__half, 3>(s, ct, z, labels, proto_class, keys, img, st);
-    case SPS_MATH_BF16: return launch_push_tc_t<__nv_bfloat16, 1>(s, ct, z, labels, proto_class, keys, img, st);
-    case SPS_MATH_BF16X3: return launch_push_tc_t<__nv_bfloat16, 3>(s, ct, z, labels, proto_class, keys, img, st);
+    case SPS_MATH_F16: SPS_PUSH_CASE(__half, 1);
+    case SPS_MATH_F16X3: SPS_PUSH_CASE(__half, 3);
+    case SPS_MATH_BF16: SPS_PUSH_CASE(__nv_bfloat16, 1);
+    case SPS_MATH_BF16X3: SPS_PUSH_CASE(__nv_bfloat16, 3);
   }
+#undef SPS_PUSH_CASE
   SPS_REQUIRE(false, SPS_ERR_BAD_ARG, "math=%d is not a tensor-core mode", math);
 }
 

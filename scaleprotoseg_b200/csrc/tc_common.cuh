@@ -241,6 +241,8 @@ template <typename X> __device__ __forceinline__ void split3(float v, X& h, X& m
 // The 64 values are staged in two halves of 32 so that the loads of the NEXT row can be issued while the current
 // half is still being converted (software pipeline across tiles; see the loader loops).
 // ---------------------------------------------------------------------------------------------
+constexpr float MASK_BIG = 32768.0f;   // added per differing label digit; exact in fp16 and bf16
+constexpr int MASK_MAX_LABEL = 35;      // 3 * 3 * 4 - 1
 template <typename X, int NSPLIT> struct ZStage {
   float v[64];
   // zs: channel 0 of this row (a VALID address: callers clamp out-of-range rows); hw: channel pitch in elements
@@ -286,6 +288,33 @@ template <typename X, int NSPLIT> struct ZStage {
     *reinterpret_cast<uint4*>(a_n + norm_off(m, 0)) = make_uint4(one | (one << 16), one | ((uint32_t)bits16(h) << 16),
                                                                  (uint32_t)bits16(mm) | ((uint32_t)bits16(l) << 16), 0u);
     *reinterpret_cast<uint4*>(a_n + norm_off(m, 8)) = make_uint4(0u, 0u, 0u, 0u);
+  }
+  // Push scan: the same K step also carries the class mask in its 10 free slots (k = 6..15).  The label value
+  // L = class + 1 (0 = void) is written in three digits (radix 3, 3, 4; L <= 35); the prototype side holds a 1 in the
+  // slot of each of ITS digits (write_proto_mask), the position side holds MASK_BIG in every slot that is NOT one of
+  // its digits.  The products add MASK_BIG once per differing digit, and every single product is exactly 0 for a
+  // matching pair, so the accumulator of a matching (prototype, position) pair is untouched.
+  static __device__ __forceinline__ void store_norm_mask(int m, unsigned char* a_n, float zn, int L) {
+    X h, mm, l;
+    split3<X>(zn, h, mm, l);
+    const uint32_t one = bits16(Fmt<X>::from(1.0f)), big = bits16(Fmt<X>::from(MASK_BIG));
+    if (L < 0 || L > MASK_MAX_LABEL) L = 0;
+    const uint32_t d0 = (uint32_t)L % 3u, d1 = ((uint32_t)L / 3u) % 3u, d2 = (uint32_t)L / 9u;
+    const uint32_t mk = 0x3FFu & ~((1u << d0) | (8u << d1) | (64u << d2));
+    auto sl = [&](int i) -> uint32_t { return ((mk >> i) & 1u) ? big : 0u; };
+    *reinterpret_cast<uint4*>(a_n + norm_off(m, 0)) =
+        make_uint4(one | (one << 16), one | ((uint32_t)bits16(h) << 16), (uint32_t)bits16(mm) | ((uint32_t)bits16(l) << 16),
+                   sl(0) | (sl(1) << 16));
+    *reinterpret_cast<uint4*>(a_n + norm_off(m, 8)) =
+        make_uint4(sl(2) | (sl(3) << 16), sl(4) | (sl(5) << 16), sl(6) | (sl(7) << 16), sl(8) | (sl(9) << 16));
+  }
+  // prototype side of the class mask: row r of a no-swizzle norm tile, label value L = class + 1 (1..35)
+  static __device__ __forceinline__ void write_proto_mask(unsigned char* b_n, int r, int L) {
+    const uint16_t one = bits16(Fmt<X>::from(1.0f));
+    const int d0 = L % 3, d1 = (L / 3) % 3, d2 = L / 9;
+    *reinterpret_cast<uint16_t*>(b_n + norm_off(r, 6 + d0)) = one;
+    *reinterpret_cast<uint16_t*>(b_n + norm_off(r, 9 + d1)) = one;
+    *reinterpret_cast<uint16_t*>(b_n + norm_off(r, 12 + d2)) = one;
   }
 };
 
