@@ -41,12 +41,13 @@ CPU_SAMPLE_B = 1                                            # maps per CPU step 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=200)
+    ap.add_argument("--warmup", type=int, default=20)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--math", default="f16x3", choices=["fp32", "bf16", "bf16x3", "f16", "f16x3"])
     ap.add_argument("--no-push", action="store_true", help="skip the secondary push measurement")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-c5", action="store_true", help="skip the secondary COCO-shape forward measurement")
     ap.add_argument("--push-maps", type=int, default=PUSH["n_maps"])
     return ap.parse_args()
 
@@ -61,39 +62,69 @@ def peaks():
 
 
 class ClockSampler:
-    """nvidia-smi clocks / throttle reasons sampled DURING the timed region (B200_PROFILING.md)."""
+    """SM clock / throttle reasons sampled DURING the timed region (B200_PROFILING.md).  NVML in-process (about 1 kHz);
+    falls back to polling nvidia-smi when pynvml is not importable."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+    NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+    BITS = [0x8, 0x40, 0x20, 0x4]   # nvmlClocksThrottleReason{HwSlowdown, HwThermalSlowdown, SwThermalSlowdown, SwPowerCap}
 
     def __init__(self, index):
-        self.index, self.rows, self.stop_flag, self.th = index, [], False, None
+        self.index, self.sm, self.mx, self.flags, self.stop_flag, self.th, self.nvml = index, [], [], set(), False, None, None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
+            phys = int(vis.split(",")[index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else index
+            self.nvml = (pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys))
+        except Exception:
+            self.nvml = None
 
-    def _run(self):
+    def _run_nvml(self):
+        nv, h = self.nvml
+        try:
+            self.mx.append(int(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)))
+        except Exception:
+            pass
+        while not self.stop_flag:
+            try:
+                self.sm.append(int(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
+                r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
+                for name, bit in zip(self.NAMES, self.BITS):
+                    if r & bit:
+                        self.flags.add(name)
+            except Exception:
+                pass
+            time.sleep(0.001)
+
+    def _run_smi(self):
         while not self.stop_flag:
             try:
                 out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
                                       "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
                 parts = [p.strip() for p in out.strip().split(",")]
-                if len(parts) >= 6:
-                    self.rows.append(parts)
+                if len(parts) >= 6 and parts[0].isdigit():
+                    self.sm.append(int(parts[0]))
+                    if parts[1].isdigit():
+                        self.mx.append(int(parts[1]))
+                    for i, name in enumerate(self.NAMES):
+                        if parts[2 + i].lower().startswith("active"):
+                            self.flags.add(name)
             except Exception:
                 pass
             time.sleep(0.05)
 
     def start(self):
-        self.th = threading.Thread(target=self._run, daemon=True)
+        self.th = threading.Thread(target=self._run_nvml if self.nvml else self._run_smi, daemon=True)
         self.th.start()
 
     def stop(self):
         self.stop_flag = True
         if self.th is not None:
             self.th.join(timeout=10)
-        sm = sorted(int(r[0]) for r in self.rows if r[0].isdigit())
-        mx = [int(r[1]) for r in self.rows if r[1].isdigit()]
-        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = [n for i, n in enumerate(names) if any(r[2 + i].lower().startswith("active") for r in self.rows)]
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(self.rows)}
+        sm = sorted(self.sm)
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
+                "reasons": sorted(self.flags), "samples": len(sm), "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
 MATH = {"fp32": 0, "bf16x3": 1, "bf16": 2, "f16": 3, "f16x3": 4}
@@ -284,6 +315,27 @@ def measure_push(ctx, args):
             "math": "fp32" if cfg.math == 0 else args.math}
 
 
+def measure_c5(ctx, args):
+    """Secondary: the COCO-Stuff head shape of BASELINE.json configs[4] (K=171, P=6840, B=32, 65x65), fused FORWARD
+    only (the tensor-core backward covers K <= 32; larger K runs the fp32 backward).  Tensor-bound shape."""
+    sps, ho, dev = ctx["sps"], ctx["ho"], ctx["dev"]
+    B, H, W, P, K, S, D = 32, 65, 65, 6840, 171, 4, 64
+    g = torch.Generator(device=dev).manual_seed(SEED + 5)
+    z = torch.sigmoid(torch.randn(B, S * D, H, W, device=dev, generator=g))
+    protos = torch.rand(P, D, device=dev, generator=g)
+    last_w = ho.make_last_layer(ho.make_identity(P, K, S)).contiguous().to(dev)
+    cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, S), K, math=ctx["cfg"].math)
+    iters = max(3, min(args.steps, 20))
+    ms = event_ms(lambda i: sps.head_forward_raw(z, protos, last_w, cfg, False, False), iters)   # 138 MB of z per pass > L2
+    units = B * H * W * P
+    flops = units * (2 * D + 2 * K)
+    pk = peaks()
+    return {"workload": f"COCO-Stuff head forward (configs[4] shape): B={B} maps 256x{H}x{W}, P={P}, K={K}, fused mode",
+            "ms": ms, "value": units / (ms * 1e-3), "unit": "positions*prototypes/s (forward only)",
+            "tflops_algorithmic": flops / (ms * 1e-3) / 1e12, "tensor_frac": flops / (ms * 1e-3) / 1e12 / pk["tensor_sustained"],
+            "math": args.math}
+
+
 def PUSH_TC(sps):
     return bool(getattr(sps, "HAS_TC_PUSH", False))
 
@@ -351,6 +403,7 @@ def main():
     ctx = run_ours(args)
     e2e = measure_e2e(ctx, args)
     push = None if args.no_push else measure_push(ctx, args)
+    c5 = None if (args.no_c5 or ctx["world"] > 1) else measure_c5(ctx, args)
     if ctx["world"] > 1:
         ctx["barrier"]()
     if rank != 0:
@@ -382,6 +435,8 @@ def main():
                 "clocks": ctx["clocks"], "e2e": e2e, "gpu_launches": ctx["launches"], "roofline": roof})
     if push is not None:
         out["push"] = push
+    if c5 is not None:
+        out["coco_forward"] = c5
     if not args.no_cpu and ctx["world"] == 1:
         out["cpu_baseline"] = measure_cpu(8, 2)
     if ctx["world"] > 1:

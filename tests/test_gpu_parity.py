@@ -267,3 +267,49 @@ def test_push_tensor_core_large_map(built_lib, math):
     best = spush.reduce_keys(keys, 0)
     win, _ = spush.decode_keys(best)
     check_push(keys, win, [z[i:i + 1] for i in range(n)], [labels[i] for i in range(n)], protos, ranges, ident, K, _tol(math))
+
+
+@pytest.mark.parametrize("K", [35, 40, 171])
+@pytest.mark.parametrize("math", [sps.MATH_F16X3, sps.MATH_BF16X3])
+def test_push_tensor_core_many_classes(built_lib, K, math):
+    """K = 35 is the largest class count whose mask rides in the GEMM (label values up to 35); K = 40 and the
+    COCO-Stuff count take the label-compare epilogue.  Both must give the same answers as the oracle."""
+    S, P = 4, 4 * 96
+    ranges = ho.uniform_ranges(P, S)
+    gen = torch.Generator().manual_seed(ho.SEED + K)
+    ident = torch.zeros(P, K)
+    ident[torch.arange(P), torch.randint(0, K, (P,), generator=gen)] = 1
+    protos = torch.rand(P, 64, 1, 1, generator=gen)
+    n, h, w = 3, 19, 27
+    z = torch.sigmoid(torch.randn(n, 256, h, w, generator=gen))
+    labels = torch.randint(0, K + 1, (n, h, w), generator=gen)          # 0 = void, per-pixel classes: many ties of class
+    labels[0, :4] = K                                                     # the top label value is present
+    cfg = sps.HeadConfig.from_ranges(ranges, K, math=math)
+    pc = spush.proto_class_of(ident)
+    keys = spush.scan_maps(z.to(DEV), labels.to(torch.int16).to(DEV), protos.to(DEV), pc, cfg)
+    best = spush.reduce_keys(keys, 0)
+    win, _ = spush.decode_keys(best)
+    check_push(keys, win, [z[i:i + 1] for i in range(n)], [labels[i] for i in range(n)], protos, ranges, ident, K, _tol(math))
+
+
+def test_push_label_values_outside_the_class_range_never_match(built_lib):
+    """Label values above K (or negative) belong to no prototype: they behave like void in both scan epilogues."""
+    K, S, P = 19, 4, 228
+    ranges = ho.uniform_ranges(P, S)
+    gen = torch.Generator().manual_seed(ho.SEED + 99)
+    ident = ho.make_identity(P, K, S)
+    protos = torch.rand(P, 64, 1, 1, generator=gen)
+    h, w = 17, 21
+    z = torch.sigmoid(torch.randn(2, 256, h, w, generator=gen))
+    labels = torch.stack([ho.make_labels(i, h, w, K, absent_class=3) for i in range(2)])
+    weird = labels.clone()
+    weird[0, :3] = 77          # beyond MASK_MAX_LABEL
+    weird[1, :3] = -5
+    as_void = labels.clone()
+    as_void[:, :3] = 0
+    pc = spush.proto_class_of(ident)
+    for math in (sps.MATH_F16X3, sps.MATH_FP32):
+        cfg = sps.HeadConfig.from_ranges(ranges, K, math=math)
+        k1 = spush.scan_maps(z.to(DEV), weird.to(torch.int16).to(DEV), protos.to(DEV), pc, cfg)
+        k0 = spush.scan_maps(z.to(DEV), as_void.to(torch.int16).to(DEV), protos.to(DEV), pc, cfg)
+        assert torch.equal(k1, k0)
