@@ -324,7 +324,10 @@ def measure_c5(ctx, args):
     z = torch.sigmoid(torch.randn(B, S * D, H, W, device=dev, generator=g))
     protos = torch.rand(P, D, device=dev, generator=g)
     last_w = ho.make_last_layer(ho.make_identity(P, K, S)).contiguous().to(dev)
-    cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, S), K, math=ctx["cfg"].math)
+    # 3-term products need hi + lo last-layer tiles that do not fit shared memory at K=171 (the library would route to
+    # the fp32 kernels), so this shape is timed with single fp16 products: logits within 1e-3 of fp32 (tests)
+    math_name = {"f16x3": "f16", "bf16x3": "bf16"}.get(args.math, args.math)
+    cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, S), K, math=MATH[math_name])
     iters = max(3, min(args.steps, 20))
     ms = event_ms(lambda i: sps.head_forward_raw(z, protos, last_w, cfg, False, False), iters)   # 138 MB of z per pass > L2
     units = B * H * W * P
@@ -333,7 +336,7 @@ def measure_c5(ctx, args):
     return {"workload": f"COCO-Stuff head forward (configs[4] shape): B={B} maps 256x{H}x{W}, P={P}, K={K}, fused mode",
             "ms": ms, "value": units / (ms * 1e-3), "unit": "positions*prototypes/s (forward only)",
             "tflops_algorithmic": flops / (ms * 1e-3) / 1e12, "tensor_frac": flops / (ms * 1e-3) / 1e12 / pk["tensor_sustained"],
-            "math": args.math}
+            "math": math_name}
 
 
 def PUSH_TC(sps):

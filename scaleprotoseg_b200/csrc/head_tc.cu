@@ -549,6 +549,19 @@ static int launch_fwd_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const f
   return SPS_OK;
 }
 
+// Shapes the tcgen05 forward covers in this math mode; api.cu routes everything else to the exact fp32 kernels
+// (e.g. K = 171 with 3-term products: the hi + lo last-layer tiles leave room for a single ring stage).
+bool head_fwd_tc_supported(const HeadShape& s, int math, bool with_last_layer) {
+  if (math == SPS_MATH_FP32 || s.D > 64 || s.D % 8 != 0 || s.K > 192) return false;
+  int nc = 0;
+  for (int sc = 0; sc < s.S; ++sc) nc += (s.scale_lo[sc + 1] - s.scale_lo[sc] + tc::CN - 1) / tc::CN;
+  if (nc > tc::MAX_CHUNKS) return false;
+  const int kp = with_last_layer ? (s.K + 15) / 16 * 16 : 0;
+  const bool split = math == SPS_MATH_F16X3 || math == SPS_MATH_BF16X3;
+  const tc::SmemPlan pl = split ? tc::smem_plan<3>(tc::chunk_img_bytes(kp)) : tc::smem_plan<1>(tc::chunk_img_bytes(kp));
+  return pl.nst >= 2 && pl.total <= 227 * 1024;
+}
+
 int launch_head_fwd_tc(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w,
                        float* logits, float* dist, float* act, void* ws, size_t ws_bytes, cudaStream_t st) {
   SPS_REQUIRE(s.D <= 64 && s.D % 8 == 0, SPS_ERR_UNSUPPORTED, "tensor-core head: D=%d must be a multiple of 8, <= 64", s.D);
