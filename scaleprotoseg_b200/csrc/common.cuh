@@ -1,5 +1,6 @@
 // Shared device/host helpers for libscaleproto_sm100.so (sm_100a only).
 #pragma once
+#include <utility>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -53,6 +54,26 @@ inline HeadShape make_shape(const SpsHeadDesc* d) {
 int validate_desc(const SpsHeadDesc* d);
 int sm_count();
 void count_launch(int n = 1);
+
+// Programmatic dependent launch: the kernel may start while the previous kernel of the stream is still running (that
+// kernel calls pdl_launch_dependents() early); every thread that reads what the previous kernel wrote calls
+// pdl_wait() first, which blocks until that kernel has completed and its writes are visible.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
 
 // distance -> similarity (model_multiscale.py:324-330) and its derivative.
 __device__ __forceinline__ float act_of(float d, int kind, float eps) {

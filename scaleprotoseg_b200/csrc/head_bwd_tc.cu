@@ -62,7 +62,29 @@ struct BwdParams {
 template <typename X, int NSPLIT>
 __global__ void __launch_bounds__(256) bwd_prep_kernel(const __grid_constant__ ChunkTable ct, int D, int P, int K,
                                                         const float* __restrict__ protos, const float* __restrict__ last_w,
-                                                        unsigned char* __restrict__ img_base) {
+                                                        unsigned char* __restrict__ img_base, const float* __restrict__ dlogits,
+                                                        long long dl_count, unsigned int* __restrict__ amax_out) {
+  pdl_launch_dependents();  // the main kernel may start its prologue and feature loads; its readers of our output wait
+  if ((int)blockIdx.x >= ct.n_chunks) {
+    // blocks past the chunk images: max |dlogits| (float4 loads when the base is 16-B aligned), one atomicMax per warp
+    const long long nb = (long long)gridDim.x - ct.n_chunks, b = (long long)blockIdx.x - ct.n_chunks;
+    float m = 0.f;
+    if ((reinterpret_cast<uintptr_t>(dlogits) & 15) == 0) {
+      const long long n4 = dl_count >> 2;
+      const float4* x4 = reinterpret_cast<const float4*>(dlogits);
+      for (long long i = b * blockDim.x + threadIdx.x; i < n4; i += nb * blockDim.x) {
+        const float4 v = __ldg(x4 + i);
+        m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+      }
+      for (long long i = (n4 << 2) + b * blockDim.x + threadIdx.x; i < dl_count; i += nb * blockDim.x) m = fmaxf(m, fabsf(__ldg(dlogits + i)));
+    } else {
+      for (long long i = b * blockDim.x + threadIdx.x; i < dl_count; i += nb * blockDim.x) m = fmaxf(m, fabsf(__ldg(dlogits + i)));
+    }
+#pragma unroll
+    for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
+    if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(amax_out, __float_as_uint(m));
+    return;
+  }
   const int c = blockIdx.x, t = threadIdx.x;
   const int p0 = ct.p0[c], n = ct.n[c];
   unsigned char* img = img_base + (size_t)c * BIMG;
@@ -106,15 +128,6 @@ __global__ void __launch_bounds__(256) bwd_prep_kernel(const __grid_constant__ C
     const float v = (k < K && j < n) ? __ldg(last_w + (size_t)k * P + p0 + j) : 0.0f;
     *reinterpret_cast<uint16_t*>(img + BOFF_W3 + sw64_off(j, k)) = bits16(Fmt<X>::from(v));
   }
-}
-
-__global__ void amax_kernel(const float* __restrict__ x, long long count, unsigned int* __restrict__ out) {
-  float m = 0.f;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (long long)gridDim.x * blockDim.x)
-    m = fmaxf(m, fabsf(__ldg(x + i)));
-#pragma unroll
-  for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-  if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(out, __float_as_uint(m));
 }
 
 // power-of-two scale that brings max|dlogits| to [2^-5, 2^-4)
@@ -194,6 +207,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
   constexpr uint32_t FM = Fmt<X>::id;
 
   if (warp == WARP_RES) {
+    pdl_wait();  // chunk images come from the pre-pass launched just before this kernel
     if (lane == 0) {
       mbar_arrive_expect_tx(bar(B_RES), (uint32_t)nch * RES);
       for (int j = 0; j < nch; ++j)
@@ -272,7 +286,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
     // ================= loaders: z_s tile (16-bit, K-major swizzled) + norms + scaled dlogits tile =================
     // Software pipeline: the feature loads of tile ti+1 are issued half by half while tile ti is converted.
     const int m = threadIdx.x - WARP_LOAD0 * 32;
-    const float G = grad_scale(__ldg(prm.amax_bits));
     const uint32_t hw = (uint32_t)s.HW;
     auto row_of = [&](int ti) -> long long { return ((long long)cta_local + (long long)ti * ncta) * TILE_M + m; };
     auto row_ptr = [&](int ti) -> const float* {
@@ -288,6 +301,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       zst.issue_half(0, cur, hw, s.D);
       zst.issue_half(1, cur, hw, s.D);
     }
+    pdl_wait();  // max |dlogits| comes from the pre-pass launched just before this kernel (the loads above are in flight)
+    const float G = grad_scale(*reinterpret_cast<const volatile unsigned int*>(prm.amax_bits));
     for (int ti = 0; ti < my_tiles; ++ti) {
       const long long n = row_of(ti);
       const bool valid = n < s.N;
@@ -326,7 +341,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
     const uint32_t lane_base = ((uint32_t)(q * 32)) << 16;
     const float eps = s.eps, ome = 1.0f - s.eps;
     const bool is_log = s.act_kind == SPS_ACT_LOG;
-    const float G = grad_scale(__ldg(prm.amax_bits)), invG = 1.0f / G;
+    pdl_wait();  // max |dlogits| comes from the pre-pass launched just before this kernel
+    const float G = grad_scale(*reinterpret_cast<const volatile unsigned int*>(prm.amax_bits)), invG = 1.0f / G;
     float* sgbuf = reinterpret_cast<float*>(gbase + SM_SG);
     // dz of (tile tj, this scale): acc + 2 z sum_p gamma.  Called one unit into the NEXT tile, so the epilogue never
     // sits waiting for the last dz GEMM of a tile (the issuer only needs the read-out before it overwrites T_DZ).
@@ -484,12 +500,29 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
   }
 }
 
-__global__ void bwd_reduce_kernel(const float* __restrict__ part, int nsplit, long long count, float* __restrict__ out) {
-  const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= count) return;
-  float a = 0.f;
-  for (int sp = 0; sp < nsplit; ++sp) a += part[(long long)sp * count + i];
-  out[i] = a;
+// out1[i] = sum over the CTA partials of part1 (i < count1); likewise out2 for the following count2 threads (either may
+// be empty).  Fixed order: deterministic.
+__global__ void bwd_reduce_kernel(const float* __restrict__ part1, long long count1, float* __restrict__ out1,
+                                  const float* __restrict__ part2, long long count2, float* __restrict__ out2, int nsplit) {
+  long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const float* part = part1;
+  float* out = out1;
+  long long count = count1;
+  if (i >= count1) {
+    i -= count1;
+    part = part2, out = out2, count = count2;
+    if (i >= count2) return;
+  }
+  float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+  int sp = 0;
+  for (; sp + 4 <= nsplit; sp += 4) {
+    a0 += part[(long long)sp * count + i];
+    a1 += part[(long long)(sp + 1) * count + i];
+    a2 += part[(long long)(sp + 2) * count + i];
+    a3 += part[(long long)(sp + 3) * count + i];
+  }
+  for (; sp < nsplit; ++sp) a0 += part[(long long)sp * count + i];
+  out[i] = (a0 + a1) + (a2 + a3);
 }
 
 }  // namespace tcb
@@ -577,9 +610,9 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   bool any_multi = false;
   for (int g = 0; g < prm.gt.n_groups; ++g) any_multi |= prm.gt.multi[g] != 0;
   if (dz != nullptr && any_multi) SPS_CUDA_TRY(cudaMemsetAsync(dz, 0, sizeof(float) * (size_t)s.B * s.C * s.HW, st));
-  tcb::amax_kernel<<<sm_count(), 256, 0, st>>>(dlogits, s.N * s.K, amax);
-  count_launch();
-  tcb::bwd_prep_kernel<X, NSPLIT><<<prm.ct.n_chunks, 256, 0, st>>>(prm.ct, s.D, s.P, s.K, protos, last_w, img);
+  // one launch: chunk images (n_chunks blocks) + max |dlogits| (the remaining blocks)
+  tcb::bwd_prep_kernel<X, NSPLIT><<<prm.ct.n_chunks + sm_count(), 256, 0, st>>>(prm.ct, s.D, s.P, s.K, protos, last_w, img, dlogits,
+                                                                               (long long)s.N * s.K, amax);
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   prm.s = s;
@@ -594,18 +627,14 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   constexpr int SMEM = tcb::Lay<NSPLIT>::SM_TOTAL;
   static_assert(SMEM <= 227 * 1024, "backward kernel shared memory");
   SPS_CUDA_TRY(cudaFuncSetAttribute(tcb::head_bwd_tc_kernel<X, NSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-  tcb::head_bwd_tc_kernel<X, NSPLIT><<<grid, tcb::NTHREADS, SMEM, st>>>(prm);
+  SPS_CUDA_TRY(launch_pdl(tcb::head_bwd_tc_kernel<X, NSPLIT>, dim3(grid), dim3(tcb::NTHREADS), (size_t)SMEM, st, prm));
   count_launch();
-  SPS_CUDA_TRY(cudaGetLastError());
-  if (dprotos != nullptr) {
-    const long long cnt = (long long)s.P * s.D;
-    tcb::bwd_reduce_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(part_dp, nsplit, cnt, dprotos);
-    count_launch();
-  }
-  if (dlast_w != nullptr) {
-    const long long cnt = (long long)s.K * s.P;
-    tcb::bwd_reduce_kernel<<<(unsigned)((cnt + 255) / 256), 256, 0, st>>>(part_dw, nsplit, cnt, dlast_w);
-    count_launch();
+  {
+    const long long c1 = dprotos != nullptr ? (long long)s.P * s.D : 0, c2 = dlast_w != nullptr ? (long long)s.K * s.P : 0;
+    if (c1 + c2 > 0) {
+      tcb::bwd_reduce_kernel<<<(unsigned)((c1 + c2 + 255) / 256), 256, 0, st>>>(part_dp, c1, dprotos, part_dw, c2, dlast_w, nsplit);
+      count_launch();
+    }
   }
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;

@@ -43,6 +43,7 @@ __global__ void __launch_bounds__(256) proto_prep_kernel(const __grid_constant__
                                                           int act_kind, const float* __restrict__ protos,
                                                           const float* __restrict__ last_w,
                                                           unsigned char* __restrict__ img_base) {
+  pdl_launch_dependents();  // the main kernel may start its prologue and feature loads; its producer warp waits for us
   const int c = blockIdx.x;
   const int p0 = ct.p0[c], n = ct.n[c];
   unsigned char* img = img_base + (size_t)c * ct.img_bytes;
@@ -274,6 +275,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
   } else if (warp == WARP_PROD) {
     // ================================ prototype-chunk producer ================================
     {
+      pdl_wait();  // the packed images come from the pre-pass launched just before this kernel
       const int U = my_tiles * NC;
       const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128, bytes_n = CN * 32, bytes_w = (NSPLIT == 3 ? 2 : 1) * KP * 128;
       for (int i = 0; i < U; ++i) {
@@ -543,8 +545,7 @@ static int launch_fwd_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const f
               pl.total, s.K);
   SPS_CUDA_TRY(cudaFuncSetAttribute(tc::head_fwd_tc_kernel<X, NSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
   const int grid = prm.n_tiles < sm_count() ? prm.n_tiles : sm_count();
-  tc::head_fwd_tc_kernel<X, NSPLIT><<<grid, tc::NTHREADS, pl.total, st>>>(prm);
-  SPS_CUDA_TRY(cudaGetLastError());
+  SPS_CUDA_TRY(launch_pdl(tc::head_fwd_tc_kernel<X, NSPLIT>, dim3(grid), dim3(tc::NTHREADS), (size_t)pl.total, st, prm));
   count_launch();
   return SPS_OK;
 }
