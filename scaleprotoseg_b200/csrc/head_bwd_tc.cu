@@ -26,6 +26,17 @@ namespace sps {
 namespace tcb {
 using namespace sps::tc;
 
+#ifdef SPS_TIMELINE
+// Debug build only: clock stamps of CTA 0 (role r, event e) -> g_tlb[r * 1024 + e]; read by sps_debug_timeline_bwd.
+__device__ long long g_tlb[8 * 1024];
+#define TLB(role, ev)                                                                      \
+  do {                                                                                     \
+    if (blockIdx.x == 0 && (ev) < 1024) g_tlb[(role) * 1024 + (ev)] = clock64();            \
+  } while (0)
+#else
+#define TLB(role, ev) do { } while (0)
+#endif
+
 constexpr int GROUP_CHUNKS = 3;   // chunks per CTA (TMEM budget)
 constexpr int MAX_GROUPS = 64;
 constexpr int KP_BWD = 32;        // classes padded (this kernel: K <= 32)
@@ -220,8 +231,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
     int j = 0, ti = 0;
     for (int u = 0; u < U; ++u) {
       const uint32_t ab = ti & 1, sb = u & 1;
+      if (lane == 0) TLB(0, 4 * u);
       if (j == 0) mbar_wait(bar(B_AFULL + ab), (ti >> 1) & 1);
       mbar_wait(bar(B_SEMPTY + sb), ((u >> 1) & 1) ^ 1);
+      if (lane == 0) TLB(0, 4 * u + 1);
       tc_fence_after();
       if (lane == 0) {
         const uint32_t ab0 = base + SM_A + ab * A_BUF, img = base + SM_RES + j * RES;
@@ -238,6 +251,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
 #pragma unroll
         for (int k = 0; k < 2; ++k) mma_f16(dA, desc_k_sw64(ab0 + AOFF_DL + 32 * k), desc_k_sw64(img + BOFF_W3 + 32 * k), ID, k);
         mma_commit(bar(B_SFULL + sb));
+        TLB(0, 4 * u + 2);
       }
       __syncwarp();
       if (++j == nch) { j = 0; ++ti; }
@@ -252,8 +266,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
     int j = 0, ti = 0;
     for (int u = 0; u < U; ++u) {
       const uint32_t ab = ti & 1, gb = u & 1;
+      if (lane == 0) TLB(1, 4 * u);
       mbar_wait(bar(B_GFULL + gb), (u >> 1) & 1);
       if (j == 0) mbar_wait(bar(B_DZEMPTY), (ti & 1) ^ 1);
+      if (lane == 0) TLB(1, 4 * u + 1);
       tc_fence_after();
       if (lane == 0) {
         const uint32_t ab0 = base + SM_A + ab * A_BUF, img = base + SM_RES + j * RES;
@@ -273,6 +289,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
                   ID5C, accum);
         }
         mma_commit(bar(B_GEMPTY + gb));
+        TLB(1, 4 * u + 2);
         if (j == nch - 1) {
           mma_commit(bar(B_DZFULL));
           mma_commit(bar(B_AEMPTY + ab));
@@ -284,54 +301,64 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
     }
   } else if (warp >= WARP_LOAD0 && warp < WARP_I1) {
     // ================= loaders: z_s tile (16-bit, K-major swizzled) + norms + scaled dlogits tile =================
-    // Software pipeline: the feature loads of tile ti+1 are issued half by half while tile ti is converted.
+    // Software pipeline: the feature loads of tile ti+1 are issued as soon as tile ti has been handed over, and fly
+    // while this warp waits for the next buffer.
     const int m = threadIdx.x - WARP_LOAD0 * 32;
     const uint32_t hw = (uint32_t)s.HW;
     auto row_of = [&](int ti) -> long long { return ((long long)cta_local + (long long)ti * ncta) * TILE_M + m; };
-    auto row_ptr = [&](int ti) -> const float* {
-      long long n = row_of(ti);
+    auto row_ptr = [&](long long n) -> const float* {
       if (n >= s.N) n = s.N - 1;  // rows past the end read a valid row; their dlogits are zero and nothing is stored
-      const long long b = n / s.HW, pix = n % s.HW;
-      return prm.z + (b * (long long)s.C + (long long)sc * s.D) * s.HW + pix;
+      const uint32_t b = (uint32_t)n / hw, pix = (uint32_t)n % hw;   // N < 2^31 (checked by head_bwd_tc_supported)
+      return prm.z + ((size_t)b * s.C + (size_t)sc * s.D) * s.HW + pix;
+    };
+    // raw dlogits row (zeros past the end / past K); scaled by G when it is packed
+    auto load_dl = [&](long long n, float (&dl)[KP_BWD]) {
+      const float* src = prm.dlogits + (n < s.N ? n : 0) * s.K;
+      const int kl = n < s.N ? s.K : 0;
+#pragma unroll
+      for (int k = 0; k < KP_BWD; ++k) dl[k] = k < kl ? __ldg(src + k) : 0.0f;
     };
     ZStage<X, NSPLIT> zst;
-    const float* cur = nullptr;
+    float dl[KP_BWD];
     if (my_tiles > 0) {
-      cur = row_ptr(0);
-      zst.issue_half(0, cur, hw, s.D);
-      zst.issue_half(1, cur, hw, s.D);
+      const long long n0 = row_of(0);
+      const float* p0 = row_ptr(n0);
+      zst.issue_half(0, p0, hw, s.D);
+      zst.issue_half(1, p0, hw, s.D);
+      load_dl(n0, dl);
     }
     pdl_wait();  // max |dlogits| comes from the pre-pass launched just before this kernel (the loads above are in flight)
     const float G = grad_scale(*reinterpret_cast<const volatile unsigned int*>(prm.amax_bits));
     for (int ti = 0; ti < my_tiles; ++ti) {
-      const long long n = row_of(ti);
-      const bool valid = n < s.N;
-      const bool have_next = ti + 1 < my_tiles;
-      const float* nxt = have_next ? row_ptr(ti + 1) : cur;
-      float dl[KP_BWD];
-#pragma unroll
-      for (int k = 0; k < KP_BWD; ++k) dl[k] = (valid && k < s.K) ? __ldg(prm.dlogits + n * s.K + k) * G : 0.0f;
       const uint32_t ab = ti & 1;
+      if (m == 0) TLB(2, 4 * ti);
       mbar_wait(bar(B_AEMPTY + ab), ((ti >> 1) & 1) ^ 1);
+      if (m == 0) TLB(2, 4 * ti + 1);
       unsigned char* a0 = gbase + SM_A + ab * A_BUF;
       float zn = 0.f;
       zst.convert_half(0, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
-      if (have_next) zst.issue_half(0, nxt, hw, s.D);
       zst.convert_half(1, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
       ZStage<X, NSPLIT>::store_norm(m, a0 + AOFF_N, zn);
-      if (have_next) zst.issue_half(1, nxt, hw, s.D);
 #pragma unroll
       for (int gq = 0; gq < 4; ++gq) {
         uint32_t w[4];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) w[q] = Pack2<X>::pack(dl[gq * 8 + 2 * q], dl[gq * 8 + 2 * q + 1]);
+        for (int q = 0; q < 4; ++q) w[q] = Pack2<X>::pack(dl[gq * 8 + 2 * q] * G, dl[gq * 8 + 2 * q + 1] * G);
         *reinterpret_cast<uint4*>(a0 + AOFF_DL + (uint32_t)m * 64u + ((((uint32_t)gq) ^ (((uint32_t)m >> 1) & 3u)) << 4)) =
             make_uint4(w[0], w[1], w[2], w[3]);
       }
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(B_AFULL + ab));
-      cur = nxt;
+      if (m == 0) TLB(2, 4 * ti + 2);
+      // the next tile's loads go out AFTER the arrive: mbarrier.arrive has release semantics and would wait for them
+      if (ti + 1 < my_tiles) {
+        const long long nn = row_of(ti + 1);
+        const float* pn = row_ptr(nn);
+        zst.issue_half(0, pn, hw, s.D);
+        zst.issue_half(1, pn, hw, s.D);
+        load_dl(nn, dl);
+      }
     }
   }
   else if (warp < WARP_LOAD0) {
@@ -356,7 +383,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       named_bar_sync(1, 256);
       const float tot = sgb[m] + sgb[128 + m];
       uint32_t rd[32];
+      if (threadIdx.x == 0) TLB(4, 4 * tj);
       mbar_wait(bar(B_DZFULL), ti & 1);
+      if (threadIdx.x == 0) TLB(4, 4 * tj + 1);
       tc_fence_after();
       tmem_ld32(tmem + lane_base + T_DZ + half * 32, rd);
       tmem_ld_wait();
@@ -364,7 +393,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(B_DZEMPTY));
       const unsigned char* zrow = gbase + SM_A + ab * A_BUF + AOFF_Z + (uint32_t)m * 128u;
-      float* dzp = prm.dz + b * (long long)s.C * s.HW + (long long)sc * s.D * s.HW + pix;
+      // values first (registers), then one tight store loop: the channel pointer advances by the map pitch
+      float dv[32];
+      const float tot2 = 2.0f * tot;
 #pragma unroll
       for (int gq = 0; gq < 4; ++gq) {
         const uint32_t zo = (((uint32_t)(half * 4 + gq)) ^ ((uint32_t)m & 7u)) << 4;
@@ -383,19 +414,34 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
             zf.x += zl2.x;
             zf.y += zl2.y;
           }
-          const int c = half * 32 + gq * 8 + 2 * e;
-          const float v0 = (__uint_as_float(rd[gq * 8 + 2 * e]) + 2.0f * zf.x * tot) * invG;
-          const float v1 = (__uint_as_float(rd[gq * 8 + 2 * e + 1]) + 2.0f * zf.y * tot) * invG;
-          if (prm.dz != nullptr && valid && c < s.D) {
-            if (multi) atomicAdd(dzp + (long long)c * s.HW, v0); else dzp[(long long)c * s.HW] = v0;
-          }
-          if (prm.dz != nullptr && valid && c + 1 < s.D) {
-            if (multi) atomicAdd(dzp + (long long)(c + 1) * s.HW, v1); else dzp[(long long)(c + 1) * s.HW] = v1;
-          }
+          dv[gq * 8 + 2 * e] = fmaf(zf.x, tot2, __uint_as_float(rd[gq * 8 + 2 * e])) * invG;
+          dv[gq * 8 + 2 * e + 1] = fmaf(zf.y, tot2, __uint_as_float(rd[gq * 8 + 2 * e + 1])) * invG;
         }
       }
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar(B_AEMPTY + ab));
+      if (lane == 0) mbar_arrive(bar(B_AEMPTY + ab));   // the shared-memory z tile has been read
+      if (prm.dz != nullptr && valid) {
+        const int ch0 = half * 32;
+        const int nlive = s.D - ch0 < 32 ? s.D - ch0 : 32;   // channels of this half that exist (D may be < 64)
+        float* dzp = prm.dz + (b * (long long)s.C + (long long)sc * s.D + ch0) * s.HW + pix;
+        const size_t pitch = (size_t)s.HW;
+        if (!multi && nlive == 32) {
+#pragma unroll
+          for (int k = 0; k < 32; ++k) {
+            *dzp = dv[k];
+            dzp += pitch;
+          }
+        } else {
+#pragma unroll
+          for (int k = 0; k < 32; ++k) {
+            if (k < nlive) {
+              if (multi) atomicAdd(dzp, dv[k]); else *dzp = dv[k];
+            }
+            dzp += pitch;
+          }
+        }
+      }
+      if (threadIdx.x == 0) TLB(4, 4 * tj + 2);
     };
     int u = 0;
     for (int ti = 0; ti < my_tiles; ++ti) {
@@ -403,7 +449,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       for (int j = 0; j < nch; ++j, ++u) {
         const uint32_t sb = u & 1, gb = u & 1;
         uint32_t rs[32], ra[32];
+        if (threadIdx.x == 0) TLB(3, 8 * u);
         mbar_wait(bar(B_SFULL + sb), (u >> 1) & 1);
+        if (threadIdx.x == 0) TLB(3, 8 * u + 1);
         tc_fence_after();
         tmem_ld32(tmem + lane_base + T_S + sb * CN + half * 32, rs);
         tmem_ld32(tmem + lane_base + T_DA + sb * CN + half * 32, ra);
@@ -411,6 +459,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
         tc_fence_before();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(B_SEMPTY + sb));
+        if (threadIdx.x == 0) TLB(3, 8 * u + 2);
         uint32_t gw[16], aw[16];
 #pragma unroll
         for (int e = 0; e < 16; ++e) {
@@ -435,7 +484,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
           gw[e] = Pack2<X>::pack(gm[0], gm[1]);
           aw[e] = Pack2<X>::pack(a2[0], a2[1]);
         }
+        if (threadIdx.x == 0) TLB(3, 8 * u + 3);
         mbar_wait(bar(B_GEMPTY + gb), ((u >> 1) & 1) ^ 1);
+        if (threadIdx.x == 0) TLB(3, 8 * u + 4);
         unsigned char* grow = gbase + SM_G + gb * G_BUF + (uint32_t)m * 128u;
 #pragma unroll
         for (int gq = 0; gq < 4; ++gq) {
@@ -446,6 +497,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(B_GFULL + gb));
+        if (threadIdx.x == 0) TLB(3, 8 * u + 5);
         if (j == 0 && ti > 0) dz_readout(ti - 1);
       }
       sgbuf[(ti & 1) * 256 + half * 128 + m] = sg;   // row sums of gamma of this tile (read after the named barrier in dz_readout)
@@ -527,6 +579,12 @@ __global__ void bwd_reduce_kernel(const float* __restrict__ part1, long long cou
 
 }  // namespace tcb
 
+#ifdef SPS_TIMELINE
+extern "C" int sps_debug_timeline_bwd(long long* host, int count) {
+  return (int)cudaMemcpyFromSymbol(host, tcb::g_tlb, sizeof(long long) * (size_t)count);
+}
+#endif
+
 // ---------------------------------------------------------------------------------------------
 // Host side
 // ---------------------------------------------------------------------------------------------
@@ -576,7 +634,7 @@ static int bwd_nsplit(const tcb::GroupTable& gt) {
 bool head_bwd_tc_supported(const HeadShape& s, int math, const float* last_w, const float* dlogits, const float* ddist,
                            const float* dact) {
   return math != SPS_MATH_FP32 && last_w != nullptr && dlogits != nullptr && ddist == nullptr && dact == nullptr &&
-         s.K <= tcb::KP_BWD && s.D <= 64 && s.D % 8 == 0 && s.N > 0 && s.P > 0;
+         s.K <= tcb::KP_BWD && s.D <= 64 && s.D % 8 == 0 && s.N > 0 && s.N < (1ll << 31) && s.P > 0;
 }
 
 size_t head_bwd_tc_workspace(const HeadShape& s) {

@@ -295,7 +295,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
   } else if (warp >= WARP_LOAD0 && warp < WARP_PROD) {
     // ================================ feature-tile loaders ================================
     // Work list: (tile, scale) pairs in the order the distance-GEMM issuer consumes them.  Software pipeline: the
-    // loads of pair i+1 are issued half by half while pair i is converted, and before the wait for its buffer.
+    // loads of pair i+1 are issued right after pair i has been handed over and fly during the wait for its buffer.
     const int m = threadIdx.x - WARP_LOAD0 * 32;  // row of the tile
     const uint32_t hw = (uint32_t)s.HW;
     auto row_ptr = [&](int ti, int c) -> const float* {
@@ -330,13 +330,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       unsigned char* a_n = a_hi + (NSPLIT == 3 ? 2 : 1) * A_HI;
       float zn = 0.f;
       zst.convert_half(0, m, a_hi, a_lo, zn);
-      if (have_next) zst.issue_half(0, nxt, hw, s.D);
       zst.convert_half(1, m, a_hi, a_lo, zn);
       ZStage<X, NSPLIT>::store_norm(m, a_n, zn);
-      if (have_next) zst.issue_half(1, nxt, hw, s.D);
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(BAR_AFULL + ab));
+      // the next pair's loads go out AFTER the arrive: mbarrier.arrive has release semantics and would wait for them
+      if (have_next) {
+        zst.issue_half(0, nxt, hw, s.D);
+        zst.issue_half(1, nxt, hw, s.D);
+      }
       ++acount;
       ti = nti;
       c = nc;

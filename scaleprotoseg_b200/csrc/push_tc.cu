@@ -166,8 +166,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
     }
   } else if (warp >= WARP_LOAD0 && warp < WARP_MMA) {
     // ================================ feature loaders (two groups of 4 warps, alternate tiles) ================================
-    // Software pipeline per group: the feature loads of the group's next tile are issued half by half while the
-    // current one is converted, and before the wait for its stage.
+    // Software pipeline per group: the feature loads of the group's next tile are issued right after the current one
+    // has been handed over and fly during the wait for its stage.
     const int lt = threadIdx.x - WARP_LOAD0 * 32, grp = lt >> 7, m = lt & 127;
     const uint32_t hw = (uint32_t)s.HW;
     auto row_ptr = [&](int i, long long& b, int& pix) -> const float* {
@@ -195,7 +195,6 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       unsigned char* a0 = gbase + L::SM_Z + st * L::STAGE;
       float zn = 0.f;
       zst.convert_half(0, m, a0, a0 + L::SOFF_LO, zn);
-      if (have_next) zst.issue_half(0, nxt, hw, s.D);
       zst.convert_half(1, m, a0, a0 + L::SOFF_LO, zn);
       if (MASKED) {
         ZStage<X, NSPLIT>::store_norm_mask(m, a0 + L::SOFF_N, zn, lab);
@@ -203,10 +202,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
         ZStage<X, NSPLIT>::store_norm(m, a0 + L::SOFF_N, zn);
         reinterpret_cast<int*>(gbase + L::SM_LAB)[(i % L::LAB_RING) * TILE_M + m] = lab;
       }
-      if (have_next) zst.issue_half(1, nxt, hw, s.D);
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(PB_ZFULL + st));
+      // the next tile's loads go out AFTER the arrive: mbarrier.arrive has release semantics and would wait for them
+      if (have_next) {
+        zst.issue_half(0, nxt, hw, s.D);
+        zst.issue_half(1, nxt, hw, s.D);
+      }
       cur = nxt;
       b = nb;
       pix = npix;
