@@ -123,25 +123,32 @@ constexpr int TMEM_S0 = 0, TMEM_L0 = 2 * CN; // S double buffer at columns [0,12
 
 template <int NSPLIT> __host__ __device__ constexpr int a_buf_bytes() { return (NSPLIT == 3 ? 2 : 1) * A_HI + A_NORM; }
 
-// shared memory plan: [A x2][P x2][B ring x nst][barriers]; offsets are computed, not tabulated, so that
-// a run-time buffer index never turns into a local-memory lookup
+// shared memory plan: [A x2][P x2][B ring x nst][W ring x NSTW][barriers]; offsets are computed, not tabulated, so
+// that a run-time buffer index never turns into a local-memory lookup.  The prototype operands (hi [lo] | norm) and the
+// last-layer tile of a chunk travel in SEPARATE rings: a B slot is free again as soon as the distance GEMM of its unit
+// has completed, a W slot only after the logits GEMM a unit later, so the B ring runs several units ahead.
+constexpr int NSTW = 2;
 struct SmemPlan {
-  int a_stride, p0, b0, b_stride, nst, bar_off, total;
+  int a_stride, p0, b0, b_stride, nst, w0, w_stride, bar_off, total;
   __host__ __device__ int a_off(int i) const { return i * a_stride; }
   int p_stride;
   __host__ __device__ int p_off(int i) const { return p0 + i * p_stride; }
   __host__ __device__ int b_off(int i) const { return b0 + i * b_stride; }
+  __host__ __device__ int w_off(int i) const { return w0 + i * w_stride; }
 };
-template <int NSPLIT> __host__ __device__ inline SmemPlan smem_plan(int img_bytes) {
+template <int NSPLIT> __host__ __device__ inline SmemPlan smem_plan(int kp) {
   SmemPlan pl;
   pl.a_stride = a_buf_bytes<NSPLIT>();
   pl.p0 = 2 * pl.a_stride;
   pl.p_stride = (NSPLIT == 3 ? 2 : 1) * P_BYTES;   // a tile (hi) [+ lo tile]
   pl.b0 = pl.p0 + 2 * pl.p_stride;
-  pl.b_stride = (img_bytes + 1023) / 1024 * 1024;
-  int nst = (227 * 1024 - 512 - 1024 - pl.b0) / pl.b_stride;
+  pl.b_stride = ((NSPLIT == 3 ? 2 : 1) * CN * 128 + CN * 32 + 1023) / 1024 * 1024;
+  pl.w_stride = ((NSPLIT == 3 ? 2 : 1) * kp * 128 + 1023) / 1024 * 1024;
+  const int w_total = kp > 0 ? NSTW * pl.w_stride : 0;
+  int nst = (227 * 1024 - 512 - 1024 - pl.b0 - w_total) / pl.b_stride;
   pl.nst = nst > MAX_NST ? MAX_NST : nst;
-  pl.bar_off = pl.b0 + pl.nst * pl.b_stride;
+  pl.w0 = pl.b0 + (pl.nst > 0 ? pl.nst : 0) * pl.b_stride;
+  pl.bar_off = pl.w0 + w_total;
   pl.total = pl.bar_off + 512 + 1024;  // barriers + slack to align the base to 1024
   return pl;
 }
@@ -149,7 +156,7 @@ template <int NSPLIT> __host__ __device__ inline SmemPlan smem_plan(int img_byte
 // barrier indices
 enum { BAR_AFULL = 0, BAR_AEMPTY = 2, BAR_BFULL = 4, BAR_BEMPTY = 4 + MAX_NST, BAR_SFULL = 4 + 2 * MAX_NST,
        BAR_SEMPTY = 6 + 2 * MAX_NST, BAR_PFULL = 8 + 2 * MAX_NST, BAR_PEMPTY = 10 + 2 * MAX_NST, BAR_LFULL = 12 + 2 * MAX_NST,
-       BAR_LEMPTY = 14 + 2 * MAX_NST, BAR_COUNT = 16 + 2 * MAX_NST };
+       BAR_LEMPTY = 14 + 2 * MAX_NST, BAR_WFULL = 16 + 2 * MAX_NST, BAR_WEMPTY = 18 + 2 * MAX_NST, BAR_COUNT = 20 + 2 * MAX_NST };
 
 template <typename X, int NSPLIT>
 __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_constant__ FwdParams prm) {
@@ -158,7 +165,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
   const ChunkTable& ct = prm.ct;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   unsigned char* gbase = smem_raw + (base - smem_u32(smem_raw));
-  const SmemPlan pl = smem_plan<NSPLIT>(ct.img_bytes);
+  const SmemPlan pl = smem_plan<NSPLIT>(ct.kp);
   const uint32_t bar0 = base + pl.bar_off;
   auto bar = [&](int i) { return bar0 + 8u * (uint32_t)i; };
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + pl.bar_off + 8 * BAR_COUNT);
@@ -178,7 +185,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       mbar_init(bar(BAR_PFULL + i), 4);
       mbar_init(bar(BAR_PEMPTY + i), 1);
       mbar_init(bar(BAR_LFULL + i), 1);
-      mbar_init(bar(BAR_LEMPTY + i), 4);   // epilogue warps 4..7 read the logits
+      mbar_init(bar(BAR_LEMPTY + i), 4);   // epilogue warps 0..3 read the logits
+      mbar_init(bar(BAR_WFULL + i), 1);
+      mbar_init(bar(BAR_WEMPTY + i), 1);
     }
     for (int i = 0; i < MAX_NST; ++i) {
       mbar_init(bar(BAR_BFULL + i), 1);
@@ -219,7 +228,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
         const uint32_t a_hi = base + pl.a_off(ab), a_lo = a_hi + A_HI;
         const uint32_t a_n = a_hi + (NSPLIT == 3 ? 2 : 1) * A_HI;
         const uint32_t b_hi = base + pl.b_off(st) + OFF_BHI, b_lo = base + pl.b_off(st) + OFF_BLO;
-        const uint32_t b_n = base + pl.b_off(st) + OFF_BN;
+        const uint32_t b_n = base + pl.b_off(st) + (NSPLIT == 3 ? 2 : 1) * CN * 128;
         const uint32_t d = tmem + TMEM_S0 + sb * CN;
         mma_f16(d, desc_noswz(a_n, NORM_LBO, NORM_SBO), desc_noswz(b_n, NORM_LBO, NORM_SBO), ID1, 0);
 #pragma unroll
@@ -232,7 +241,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
         }
         mma_commit(bar(BAR_SFULL + sb));
         if (last_of_scale) mma_commit(bar(BAR_AEMPTY + ab));
-        if (!has_w) mma_commit(bar(BAR_BEMPTY + st));
+        mma_commit(bar(BAR_BEMPTY + st));   // the B slot is free once this unit's distance GEMM has read it
         TL(0, i);
       }
       __syncwarp();
@@ -246,13 +255,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       const int U = my_tiles * NC;
       int c = 0, tl = 0;
       for (int u = 0; u < U; ++u) {
-        const uint32_t pb = u & 1, st = u % NST, lb = tl & 1;
+        const uint32_t pb = u & 1, sw = u % NSTW, lb = tl & 1;
         if (c == 0) mbar_wait(bar(BAR_LEMPTY + lb), ((tl >> 1) & 1) ^ 1);
+        mbar_wait(bar(BAR_WFULL + sw), (u / NSTW) & 1);
         mbar_wait(bar(BAR_PFULL + pb), (u >> 1) & 1);
         tc_fence_after();
         if (lane == 0) {
           TL(1, u);
-          const uint32_t pa = base + pl.p_off(pb), w2 = base + pl.b_off(st) + OFF_W2;
+          const uint32_t pa = base + pl.p_off(pb), w2 = base + pl.w_off(sw);
           const uint32_t d = tmem + TMEM_L0 + lb * KP;
 #pragma unroll
           for (int k = 0; k < 4; ++k)
@@ -264,7 +274,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
             for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pa + P_BYTES + 32 * k), desc_sw128(w2 + 32 * k), ID2, 1);
           }
           mma_commit(bar(BAR_PEMPTY + pb));
-          mma_commit(bar(BAR_BEMPTY + st));
+          mma_commit(bar(BAR_WEMPTY + sw));
           if (c == NC - 1) mma_commit(bar(BAR_LFULL + lb));
           TL(2, u);
         }
@@ -278,18 +288,33 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       pdl_wait();  // the packed images come from the pre-pass launched just before this kernel
       const int U = my_tiles * NC;
       const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128, bytes_n = CN * 32, bytes_w = (NSPLIT == 3 ? 2 : 1) * KP * 128;
-      for (int i = 0; i < U; ++i) {
+      // W(i) is fetched together with B(i + 1): the W slot frees a unit later than the B slot, and a producer that
+      // waited for it first would hold the B ring back
+      auto fetch_b = [&](int i) {
         const int c = i % NC, st = i % NST;
         mbar_wait(bar(BAR_BEMPTY + st), ((i / NST) & 1) ^ 1);
         if (lane == 0) {
-          mbar_arrive_expect_tx(bar(BAR_BFULL + st), bytes_b + bytes_n + bytes_w);
+          mbar_arrive_expect_tx(bar(BAR_BFULL + st), bytes_b + bytes_n);
           const unsigned char* src = prm.img + (size_t)c * ct.img_bytes;
           const uint32_t dst = base + pl.b_off(st);
           bulk_g2s(dst + OFF_BHI, src + OFF_BHI, bytes_b, bar(BAR_BFULL + st));
-          bulk_g2s(dst + OFF_BN, src + OFF_BN, bytes_n, bar(BAR_BFULL + st));
-          if (has_w) bulk_g2s(dst + OFF_W2, src + OFF_W2, bytes_w, bar(BAR_BFULL + st));
+          bulk_g2s(dst + (NSPLIT == 3 ? 2 : 1) * CN * 128, src + OFF_BN, bytes_n, bar(BAR_BFULL + st));
         }
         __syncwarp();
+      };
+      auto fetch_w = [&](int i) {
+        const int c = i % NC, sw = i % NSTW;
+        mbar_wait(bar(BAR_WEMPTY + sw), ((i / NSTW) & 1) ^ 1);
+        if (lane == 0) {
+          mbar_arrive_expect_tx(bar(BAR_WFULL + sw), bytes_w);
+          bulk_g2s(base + pl.w_off(sw), prm.img + (size_t)c * ct.img_bytes + OFF_W2, bytes_w, bar(BAR_WFULL + sw));
+        }
+        __syncwarp();
+      };
+      if (U > 0) fetch_b(0);
+      for (int i = 0; i < U; ++i) {
+        if (i + 1 < U) fetch_b(i + 1);
+        if (has_w) fetch_w(i);
       }
     }
   } else if (warp >= WARP_LOAD0 && warp < WARP_PROD) {
@@ -543,7 +568,7 @@ static int launch_fwd_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const f
   prm.dist = dist;
   prm.act = act;
   prm.n_tiles = (int)((s.N + tc::TILE_M - 1) / tc::TILE_M);
-  const tc::SmemPlan pl = tc::smem_plan<NSPLIT>(ct.img_bytes);
+  const tc::SmemPlan pl = tc::smem_plan<NSPLIT>(ct.kp);
   SPS_REQUIRE(pl.nst >= 2 && pl.total <= 227 * 1024, SPS_ERR_UNSUPPORTED, "tensor-core head: %d bytes of shared memory needed (K=%d)",
               pl.total, s.K);
   SPS_CUDA_TRY(cudaFuncSetAttribute(tc::head_fwd_tc_kernel<X, NSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
@@ -562,7 +587,7 @@ bool head_fwd_tc_supported(const HeadShape& s, int math, bool with_last_layer) {
   if (nc > tc::MAX_CHUNKS) return false;
   const int kp = with_last_layer ? (s.K + 15) / 16 * 16 : 0;
   const bool split = math == SPS_MATH_F16X3 || math == SPS_MATH_BF16X3;
-  const tc::SmemPlan pl = split ? tc::smem_plan<3>(tc::chunk_img_bytes(kp)) : tc::smem_plan<1>(tc::chunk_img_bytes(kp));
+  const tc::SmemPlan pl = split ? tc::smem_plan<3>(kp) : tc::smem_plan<1>(kp);
   return pl.nst >= 2 && pl.total <= 227 * 1024;
 }
 
