@@ -342,6 +342,29 @@ def measure_push(ctx, args):
             "math": "fp32" if cfg.math == 0 else args.math}
 
 
+def measure_dense(ctx, args):
+    """Secondary: the step as the UNCHANGED reference trainer drives it (API-exact 'dense' mode): forward returns logits
+    AND the dense (B,P,H,W) distance map, backward receives dlogits AND a gradient through the distance map (KLD loss)."""
+    sps, c, dev = ctx["sps"], C2, ctx["dev"]
+    n = c["B"] * c["H"] * c["W"]
+    g = torch.Generator(device=dev).manual_seed(SEED + 9)
+    dd = torch.randn(c["B"], c["P"], c["H"], c["W"], device=dev, generator=g) * (1e-3 / n)
+    zs, p2, w, dls, cfg = ctx["zs"], ctx["p2"], ctx["last_w"], ctx["dls"], ctx["cfg"]
+
+    def step(i):
+        sps.head_forward_raw(zs[i % N_SETS], p2, w, cfg, True, False)
+        sps.head_backward_raw(zs[i % N_SETS], p2, w, cfg, dls[i % N_SETS], dd, None, True, True, True)
+
+    iters = max(3, min(args.steps, 50))
+    for i in range(3):
+        step(i)
+    ms = event_ms(step, iters)
+    bytes_alg = n * (3 * c["S"] * c["D"] * 4 + 8 * c["K"]) + 2 * n * c["P"] * 4      # + distance map out, ddist in
+    return {"workload": "same shape, dense mode: distance map written by the forward (205 MB) and its gradient read by the backward",
+            "ms_per_step": ms, "value": ctx["units"] / (ms * 1e-3), "unit": "positions*prototypes/s",
+            "hbm_frac": bytes_alg / (ms * 1e-3) / 1e9 / peaks()["hbm"]}
+
+
 def measure_c5(ctx, args):
     """Secondary: the COCO-Stuff head shape of BASELINE.json configs[4] (K=171, P=6840, B=32, 65x65), fused FORWARD
     only (the tensor-core backward covers K <= 32; larger K runs the fp32 backward).  Tensor-bound shape."""
@@ -434,6 +457,7 @@ def main():
     e2e = measure_e2e(ctx, args)
     push = None if args.no_push else measure_push(ctx, args)
     c5 = None if (args.no_c5 or ctx["world"] > 1) else measure_c5(ctx, args)
+    dense = None if (args.no_c5 or ctx["world"] > 1) else measure_dense(ctx, args)
     if ctx["world"] > 1:
         ctx["barrier"]()
     if rank != 0:
@@ -467,6 +491,8 @@ def main():
         out["push"] = push
     if c5 is not None:
         out["coco_forward"] = c5
+    if dense is not None:
+        out["dense_mode"] = dense
     if not args.no_cpu and ctx["world"] == 1:
         out["cpu_baseline"] = measure_cpu(8, 2)
     if ctx["world"] > 1:

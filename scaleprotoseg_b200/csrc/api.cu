@@ -103,10 +103,11 @@ int sps_head_bwd(const SpsHeadDesc* desc, const float* z, const float* protos, c
   SPS_REQUIRE(z != nullptr && protos != nullptr, SPS_ERR_BAD_ARG, "z/protos NULL");
   SPS_REQUIRE(dlogits == nullptr || last_w != nullptr, SPS_ERR_BAD_ARG, "dlogits given without last_w");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  // fused-mode step (upstream gradient = dlogits only) in a tensor-core math mode: tcgen05 backward;
-  // gradients arriving through the dense maps (ddist / dact) or SPS_MATH_FP32: exact-operand CUDA-core kernels
+  // tensor-core math mode with a last layer (upstream gradient = dlogits, optionally + ddist from the KLD loss):
+  // tcgen05 backward; a gradient through the activation map (dact), no dlogits, or SPS_MATH_FP32: exact-operand
+  // CUDA-core kernels
   if (head_bwd_tc_supported(s, desc->math, last_w, dlogits, ddist, dact))
-    return launch_head_bwd_tc(s, desc->math, z, protos, last_w, dlogits, dz, dprotos, dlast_w, workspace, workspace_bytes, st);
+    return launch_head_bwd_tc(s, desc->math, z, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, workspace, workspace_bytes, st);
   return launch_head_bwd_simt(s, desc->flags, z, protos, last_w, dlogits, ddist, dact, dz, dprotos, dlast_w, workspace,
                               workspace_bytes, st);
 }

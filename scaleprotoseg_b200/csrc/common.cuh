@@ -98,8 +98,8 @@ bool head_bwd_tc_supported(const HeadShape& s, int math, const float* last_w, co
                            const float* dact);
 size_t head_bwd_tc_workspace(const HeadShape& s);
 int launch_head_bwd_tc(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w,
-                       const float* dlogits, float* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes,
-                       cudaStream_t st);
+                       const float* dlogits, const float* ddist, float* dz, float* dprotos, float* dlast_w, void* ws,
+                       size_t ws_bytes, cudaStream_t st);
 int launch_head_bwd_simt(const HeadShape& s, int flags, const float* z, const float* protos, const float* last_w,
                          const float* dlogits, const float* ddist, const float* dact, float* dz, float* dprotos,
                          float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st);

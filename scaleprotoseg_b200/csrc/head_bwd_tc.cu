@@ -62,6 +62,7 @@ struct BwdParams {
   const float* z;
   const float* protos;
   const float* dlogits;
+  const float* ddist;           // [B, P, H, W] gradient arriving through the distance map (KLD loss), or nullptr
   const unsigned char* img;     // packed chunk images (BIMG each)
   const unsigned int* amax_bits;  // max |dlogits| as float bits
   float* dz;
@@ -74,23 +75,30 @@ template <typename X, int NSPLIT>
 __global__ void __launch_bounds__(256) bwd_prep_kernel(const __grid_constant__ ChunkTable ct, int D, int P, int K,
                                                         const float* __restrict__ protos, const float* __restrict__ last_w,
                                                         unsigned char* __restrict__ img_base, const float* __restrict__ dlogits,
-                                                        long long dl_count, unsigned int* __restrict__ amax_out) {
+                                                        long long dl_count, const float* __restrict__ ddist, long long dd_count,
+                                                        unsigned int* __restrict__ amax_out) {
   pdl_launch_dependents();  // the main kernel may start its prologue and feature loads; its readers of our output wait
   if ((int)blockIdx.x >= ct.n_chunks) {
-    // blocks past the chunk images: max |dlogits| (float4 loads when the base is 16-B aligned), one atomicMax per warp
+    // blocks past the chunk images: max |dlogits| and max |ddist| (float4 loads when the base is 16-B aligned), one
+    // atomicMax per warp
     const long long nb = (long long)gridDim.x - ct.n_chunks, b = (long long)blockIdx.x - ct.n_chunks;
     float m = 0.f;
-    if ((reinterpret_cast<uintptr_t>(dlogits) & 15) == 0) {
-      const long long n4 = dl_count >> 2;
-      const float4* x4 = reinterpret_cast<const float4*>(dlogits);
-      for (long long i = b * blockDim.x + threadIdx.x; i < n4; i += nb * blockDim.x) {
-        const float4 v = __ldg(x4 + i);
-        m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+    auto scan = [&](const float* __restrict__ x, long long count) {
+      if (x == nullptr) return;
+      if ((reinterpret_cast<uintptr_t>(x) & 15) == 0) {
+        const long long n4 = count >> 2;
+        const float4* x4 = reinterpret_cast<const float4*>(x);
+        for (long long i = b * blockDim.x + threadIdx.x; i < n4; i += nb * blockDim.x) {
+          const float4 v = __ldg(x4 + i);
+          m = fmaxf(fmaxf(m, fmaxf(fabsf(v.x), fabsf(v.y))), fmaxf(fabsf(v.z), fabsf(v.w)));
+        }
+        for (long long i = (n4 << 2) + b * blockDim.x + threadIdx.x; i < count; i += nb * blockDim.x) m = fmaxf(m, fabsf(__ldg(x + i)));
+      } else {
+        for (long long i = b * blockDim.x + threadIdx.x; i < count; i += nb * blockDim.x) m = fmaxf(m, fabsf(__ldg(x + i)));
       }
-      for (long long i = (n4 << 2) + b * blockDim.x + threadIdx.x; i < dl_count; i += nb * blockDim.x) m = fmaxf(m, fabsf(__ldg(dlogits + i)));
-    } else {
-      for (long long i = b * blockDim.x + threadIdx.x; i < dl_count; i += nb * blockDim.x) m = fmaxf(m, fabsf(__ldg(dlogits + i)));
-    }
+    };
+    scan(dlogits, dl_count);
+    scan(ddist, dd_count);
 #pragma unroll
     for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
     if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(amax_out, __float_as_uint(m));
@@ -171,7 +179,8 @@ constexpr int T_S = 0, T_DA = 128, T_DZ = 256, T_ACC = 320;
 enum { B_AFULL = 0, B_AEMPTY = 2, B_SFULL = 4, B_SEMPTY = 6, B_GFULL = 8, B_GEMPTY = 10, B_DZFULL = 12, B_DZEMPTY = 13,
        B_RES = 14, B_ACC = 15, B_COUNT = 16 };
 
-template <typename X, int NSPLIT>
+// HAS_DD: a gradient also arrives through the dense distance map (prm.ddist; the KLD loss of stage-1 training).
+template <typename X, int NSPLIT, bool HAS_DD>
 __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_constant__ BwdParams prm) {
   using L = Lay<NSPLIT>;
   constexpr int A_BUF = L::A_BUF, RES = L::RES, SM_RES = L::SM_RES, SM_A = L::SM_A, SM_G = L::SM_G, SM_SG = L::SM_SG,
@@ -446,9 +455,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
     int u = 0;
     for (int ti = 0; ti < my_tiles; ++ti) {
       float sg = 0.f;
+      const long long n_row = ((long long)cta_local + (long long)ti * ncta) * TILE_M + m;
+      const bool row_valid = n_row < s.N;
+      const uint32_t row_b = row_valid ? (uint32_t)n_row / (uint32_t)s.HW : 0u, row_pix = row_valid ? (uint32_t)n_row % (uint32_t)s.HW : 0u;
       for (int j = 0; j < nch; ++j, ++u) {
         const uint32_t sb = u & 1, gb = u & 1;
         uint32_t rs[32], ra[32];
+        float dd[HAS_DD ? 32 : 1];
+        if (HAS_DD) {   // issued before the wait for the accumulators: the loads fly while the GEMMs finish
+          const int c = c0 + j, nlive = row_valid ? ct.n[c] - half * 32 : 0;
+          const float* src = prm.ddist + ((size_t)row_b * s.P + ct.p0[c] + half * 32) * s.HW + row_pix;
+#pragma unroll
+          for (int k = 0; k < 32; ++k) dd[k] = k < nlive ? __ldg(src + (size_t)k * s.HW) : 0.0f;
+        }
         if (threadIdx.x == 0) TLB(3, 8 * u);
         mbar_wait(bar(B_SFULL + sb), (u >> 1) & 1);
         if (threadIdx.x == 0) TLB(3, 8 * u + 1);
@@ -477,7 +496,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
               ap = -1.0f;
               av = -d;
             }
-            gm[h] = sv > 0.0f ? dav * ap : 0.0f;
+            gm[h] = sv > 0.0f ? (HAS_DD ? fmaf(dav, ap, dd[2 * e + h] * G) : dav * ap) : 0.0f;
             a2[h] = av;
             sg += gm[h];
           }
@@ -633,7 +652,7 @@ static int bwd_nsplit(const tcb::GroupTable& gt) {
 
 bool head_bwd_tc_supported(const HeadShape& s, int math, const float* last_w, const float* dlogits, const float* ddist,
                            const float* dact) {
-  return math != SPS_MATH_FP32 && last_w != nullptr && dlogits != nullptr && ddist == nullptr && dact == nullptr &&
+  return math != SPS_MATH_FP32 && last_w != nullptr && dlogits != nullptr && dact == nullptr &&
          s.K <= tcb::KP_BWD && s.D <= 64 && s.D % 8 == 0 && s.N > 0 && s.N < (1ll << 31) && s.P > 0;
 }
 
@@ -649,7 +668,7 @@ size_t head_bwd_tc_workspace(const HeadShape& s) {
 
 template <typename X, int NSPLIT>
 static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* protos, const float* last_w, const float* dlogits,
-                           float* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st) {
+                           const float* ddist, float* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st) {
   tcb::BwdParams prm;
   int rc = build_chunk_table(s, true, &prm.ct);
   if (rc != SPS_OK) return rc;
@@ -669,14 +688,18 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   for (int g = 0; g < prm.gt.n_groups; ++g) any_multi |= prm.gt.multi[g] != 0;
   if (dz != nullptr && any_multi) SPS_CUDA_TRY(cudaMemsetAsync(dz, 0, sizeof(float) * (size_t)s.B * s.C * s.HW, st));
   // one launch: chunk images (n_chunks blocks) + max |dlogits| (the remaining blocks)
-  tcb::bwd_prep_kernel<X, NSPLIT><<<prm.ct.n_chunks + sm_count(), 256, 0, st>>>(prm.ct, s.D, s.P, s.K, protos, last_w, img, dlogits,
-                                                                               (long long)s.N * s.K, amax);
+  // (the amax blocks also scan the dense ddist map when there is one: enough of them to stream it at HBM rate)
+  const int amax_blocks = sm_count() * (ddist != nullptr ? 16 : 1);
+  tcb::bwd_prep_kernel<X, NSPLIT><<<prm.ct.n_chunks + amax_blocks, 256, 0, st>>>(prm.ct, s.D, s.P, s.K, protos, last_w, img, dlogits,
+                                                                                (long long)s.N * s.K, ddist,
+                                                                                (long long)s.N * s.P, amax);
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   prm.s = s;
   prm.z = z;
   prm.protos = protos;
   prm.dlogits = dlogits;
+  prm.ddist = ddist;
   prm.img = img;
   prm.amax_bits = amax;
   prm.dz = dz;
@@ -684,8 +707,13 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   prm.part_dw = part_dw;
   constexpr int SMEM = tcb::Lay<NSPLIT>::SM_TOTAL;
   static_assert(SMEM <= 227 * 1024, "backward kernel shared memory");
-  SPS_CUDA_TRY(cudaFuncSetAttribute(tcb::head_bwd_tc_kernel<X, NSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-  SPS_CUDA_TRY(launch_pdl(tcb::head_bwd_tc_kernel<X, NSPLIT>, dim3(grid), dim3(tcb::NTHREADS), (size_t)SMEM, st, prm));
+  if (ddist != nullptr) {
+    SPS_CUDA_TRY(cudaFuncSetAttribute(tcb::head_bwd_tc_kernel<X, NSPLIT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    SPS_CUDA_TRY(launch_pdl(tcb::head_bwd_tc_kernel<X, NSPLIT, true>, dim3(grid), dim3(tcb::NTHREADS), (size_t)SMEM, st, prm));
+  } else {
+    SPS_CUDA_TRY(cudaFuncSetAttribute(tcb::head_bwd_tc_kernel<X, NSPLIT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+    SPS_CUDA_TRY(launch_pdl(tcb::head_bwd_tc_kernel<X, NSPLIT, false>, dim3(grid), dim3(tcb::NTHREADS), (size_t)SMEM, st, prm));
+  }
   count_launch();
   {
     const long long c1 = dprotos != nullptr ? (long long)s.P * s.D : 0, c2 = dlast_w != nullptr ? (long long)s.K * s.P : 0;
@@ -699,15 +727,15 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
 }
 
 int launch_head_bwd_tc(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w,
-                       const float* dlogits, float* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes,
-                       cudaStream_t st) {
+                       const float* dlogits, const float* ddist, float* dz, float* dprotos, float* dlast_w, void* ws,
+                       size_t ws_bytes, cudaStream_t st) {
   // the split modes recompute the distances with the 3-term product (a' = da/dd is as sensitive to d as a is);
   // the gradient GEMMs themselves run single-term 16-bit operands with fp32 accumulation
   switch (math) {
-    case SPS_MATH_BF16: return launch_bwd_tc_t<__nv_bfloat16, 1>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
-    case SPS_MATH_BF16X3: return launch_bwd_tc_t<__nv_bfloat16, 3>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
-    case SPS_MATH_F16X3: return launch_bwd_tc_t<__half, 3>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
-    default: return launch_bwd_tc_t<__half, 1>(s, z, protos, last_w, dlogits, dz, dprotos, dlast_w, ws, ws_bytes, st);
+    case SPS_MATH_BF16: return launch_bwd_tc_t<__nv_bfloat16, 1>(s, z, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
+    case SPS_MATH_BF16X3: return launch_bwd_tc_t<__nv_bfloat16, 3>(s, z, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
+    case SPS_MATH_F16X3: return launch_bwd_tc_t<__half, 3>(s, z, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
+    default: return launch_bwd_tc_t<__half, 1>(s, z, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
   }
 }
 

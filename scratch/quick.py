@@ -56,3 +56,9 @@ if "push" in what:
     i1, v1 = spush.decode_keys(k1); i0, v0 = spush.decode_keys(k0)
     same = (i1 == i0).float().mean().item()
     print(f"push {t:.1f} us per {nm} maps = {nm*h*w/t*1e6/1e9:.2f} Gpatch/s, {nm*h*w*1026/t*1e6/1e9:.0f} GB/s | idx agree {same:.4f} val err {rel(v1, v0):.2e}")
+if "train" in what:
+    # what stage-1 training really calls: dense distances out, gradient into distances (KLD) and logits
+    t1 = timeit(lambda i: sps.head_forward_raw(zs[i % 4], protos, W_, cfg, True, False))
+    dd = torch.randn(B, P, H, W, device=dev) * 1e-3 / N
+    t2 = timeit(lambda i: sps.head_backward_raw(zs[i % 4], protos, W_, cfg, dls[i % 4], dd, None, True, True, True), iters=5, warm=2)
+    print(f"train-style: fwd (logits + dense dist) {t1:.1f} us | bwd (dlogits + ddist) {t2:.1f} us")

@@ -313,3 +313,37 @@ def test_push_label_values_outside_the_class_range_never_match(built_lib):
         k1 = spush.scan_maps(z.to(DEV), weird.to(torch.int16).to(DEV), protos.to(DEV), pc, cfg)
         k0 = spush.scan_maps(z.to(DEV), as_void.to(torch.int16).to(DEV), protos.to(DEV), pc, cfg)
         assert torch.equal(k1, k0)
+
+
+@pytest.mark.parametrize("math", TC_MATHS)
+@pytest.mark.parametrize("shape", [(2, 9, 7, 228, 19, None), (1, 33, 40, 760, 19, None),
+                                   (2, 20, 20, 221, 19, [(0, 50), (50, 121), (121, 130), (130, 221)])])
+def test_tensor_core_backward_with_distance_gradient(built_lib, shape, math):
+    """Stage-1 training step as the reference runs it: the loss reads the logits AND the dense distance map (KLD loss,
+    segmentation/module_multiscale.py:242), so a gradient arrives through both.  The tcgen05 backward takes ddist
+    next to dlogits; compared with the CPU oracle's autograd."""
+    B, H, W, P, K, ranges = shape
+    gen = torch.Generator().manual_seed(ho.SEED + 7 * P)
+    z = torch.sigmoid(torch.randn(B, 256, H, W, generator=gen))
+    protos = torch.rand(P, 64, 1, 1, generator=gen)
+    last_w = ho.make_last_layer(ho.make_identity(P, K, 4)).contiguous() if ranges is None else torch.randn(K, P, generator=gen)
+    ranges = ranges or ho.uniform_ranges(P, 4)
+    N = B * H * W
+    dl = torch.randn(B, H, W, K, generator=gen) / N
+    dd = torch.randn(B, P, H, W, generator=gen) * (3.0 / (N * P))
+    dd[:, ::3] = 0                                     # the KLD loss touches only some (pixel, prototype) pairs
+    zr, pr, wr = z.clone().requires_grad_(True), protos.clone().requires_grad_(True), last_w.clone().requires_grad_(True)
+    lo, do, _ = ho.head_stage1(zr, pr, ranges, wr)
+    ((lo * dl).sum() + (do * dd).sum()).backward()
+    cfg = sps.HeadConfig.from_ranges(ranges, K, math=math)
+    zc, pc, wc = (t.to(DEV).requires_grad_(True) for t in (z, protos, last_w))
+    lg, dg, _ = sps.PrototypeHeadFn.apply(zc, pc, wc, cfg, True, False)
+    ((lg.view(B, H, W, K) * dl.to(DEV)).sum() + (dg * dd.to(DEV)).sum()).backward()
+    gt = _grad_tol(math)
+    assert_grad(zc.grad, zr.grad, gt, "dz"), assert_grad(pc.grad, pr.grad, gt, "dprotos"), assert_grad(wc.grad, wr.grad, gt, "dlast_w")
+    # same answer as the exact-operand kernels on the same inputs (they served this case before)
+    cfg32 = sps.HeadConfig.from_ranges(ranges, K, math=sps.MATH_FP32)
+    g_tc = sps.head_backward_raw(z.to(DEV), protos.to(DEV), last_w.to(DEV), cfg, dl.reshape(N, K).to(DEV), dd.to(DEV), None, True, True, True)
+    g_32 = sps.head_backward_raw(z.to(DEV), protos.to(DEV), last_w.to(DEV), cfg32, dl.reshape(N, K).to(DEV), dd.to(DEV), None, True, True, True)
+    for a, b_, name in zip(g_tc, g_32, ("dz", "dprotos", "dlast_w")):
+        assert_grad(a, b_.cpu(), gt, name + " vs fp32 kernels")
