@@ -89,7 +89,7 @@ int sps_head_fwd(const SpsHeadDesc* desc, const float* z, const float* protos, c
   SPS_REQUIRE((last_w == nullptr) == (logits == nullptr), SPS_ERR_BAD_ARG, "last_w and logits go together");
   SPS_REQUIRE(last_w != nullptr || dist != nullptr || act != nullptr, SPS_ERR_BAD_ARG, "no output requested");
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (desc->math == SPS_MATH_FP32 || !head_fwd_tc_supported(s, desc->math, last_w != nullptr))
+  if (desc->math == SPS_MATH_FP32 || !head_fwd_tc_supported(s, desc->math, last_w != nullptr, act != nullptr))
     return launch_head_fwd_simt(s, z, protos, last_w, logits, dist, act, st);
   return launch_head_fwd_tc(s, desc->math, z, protos, last_w, logits, dist, act, workspace, workspace_bytes, st);
 }

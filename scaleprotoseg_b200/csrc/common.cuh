@@ -91,7 +91,7 @@ __device__ __forceinline__ float dact_dd(float d, int kind, float eps) {
 int launch_head_fwd_simt(const HeadShape& s, const float* z, const float* protos, const float* last_w,
                          float* logits, float* dist, float* act, cudaStream_t st);
 size_t head_fwd_tc_workspace(const HeadShape& s);
-bool head_fwd_tc_supported(const HeadShape& s, int math, bool with_last_layer);
+bool head_fwd_tc_supported(const HeadShape& s, int math, bool with_last_layer, bool dense_act);
 int launch_head_fwd_tc(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w,
                        float* logits, float* dist, float* act, void* ws, size_t ws_bytes, cudaStream_t st);
 bool head_bwd_tc_supported(const HeadShape& s, int math, const float* last_w, const float* dlogits, const float* ddist,

@@ -122,20 +122,39 @@ __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGrou
   }
 }
 
-// dG_k'[j,q] += sum_n dpre[n, J k'+j] * act[n, members_k'[q]]  over this CTA's slice of n
-__global__ void group_bwd_dG_kernel(HeadShape s, SpsGroupDesc g, const float* __restrict__ act,
-                                    const float* __restrict__ ws_dpre, float* __restrict__ dG) {
-  const int kc = blockIdx.x;
+// dG_k'[j, col(p)] += sum_n dpre[n, J k'+j] * act[n, p]  over this CTA's slice of n.  One thread per prototype p
+// (blockIdx.x * 256 + threadIdx.x): the activation map is read along p, coalesced, exactly once.
+constexpr int GDR = 16;  // dpre rows staged per step
+__global__ void __launch_bounds__(256) group_bwd_dG_kernel(HeadShape s, SpsGroupDesc g, const float* __restrict__ act,
+                                                           const float* __restrict__ ws_dpre, float* __restrict__ dG) {
+  extern __shared__ __align__(16) float dps[];   // [GDR][Gt]
   const int Gt = g.J * g.Kc;
-  const int off = g.class_off[kc], nk = g.class_off[kc + 1] - off;
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  const int kc = p < s.P ? g.proto_slot[p] : -1;
   const long long per = (s.N + gridDim.y - 1) / gridDim.y;
   const long long lo = per * blockIdx.y, hi = min(s.N, lo + per);
-  for (int o = threadIdx.x; o < g.J * nk; o += blockDim.x) {
-    const int j = o / nk, q = o % nk;
-    const int p = g.members[off + q];
-    float a = 0.f;
-    for (long long n = lo; n < hi; ++n) a = fmaf(__ldg(ws_dpre + n * Gt + g.J * kc + j), __ldg(act + n * s.P + p), a);
-    atomicAdd(dG + (long long)g.J * off + o, a);
+  float acc[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+  for (long long r0 = lo; r0 < hi; r0 += GDR) {
+    const int rows = (int)min((long long)GDR, hi - r0);
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < rows * Gt; idx += blockDim.x) dps[idx] = __ldg(ws_dpre + r0 * Gt + idx);
+    __syncthreads();
+    if (kc >= 0) {
+      for (int m = 0; m < rows; ++m) {
+        const float a = __ldg(act + (r0 + m) * s.P + p);
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (j < g.J) acc[j] = fmaf(dps[m * Gt + g.J * kc + j], a, acc[j]);
+      }
+    }
+  }
+  if (kc >= 0) {
+    const int off = g.class_off[kc], nk = g.class_off[kc + 1] - off, col = g.proto_col[p];
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      if (j < g.J) atomicAdd(dG + (long long)g.J * off + j * nk + col, acc[j]);
   }
 }
 
@@ -174,8 +193,12 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
   if (split > 64) split = 64;
   if (split < 1) split = 1;
   if (dG != nullptr) {
-    dim3 grid(g.Kc, (unsigned)split);
-    group_bwd_dG_kernel<<<grid, 128, 0, st>>>(s, g, act, ws_dpre, dG);
+    long long rsplit = (s.N + 127) / 128;   // >= 128 rows per CTA; enough CTAs to fill the machine
+    const long long want = (long long)sm_count() * 8 / ((s.P + 255) / 256) + 1;
+    if (rsplit > want) rsplit = want;
+    if (rsplit < 1) rsplit = 1;
+    dim3 grid((s.P + 255) / 256, (unsigned)rsplit);
+    group_bwd_dG_kernel<<<grid, 256, sizeof(float) * GDR * Gt, st>>>(s, g, act, ws_dpre, dG);
     count_launch();
     SPS_CUDA_TRY(cudaGetLastError());
   }

@@ -129,14 +129,15 @@ template <int NSPLIT> __host__ __device__ constexpr int a_buf_bytes() { return (
 // has completed, a W slot only after the logits GEMM a unit later, so the B ring runs several units ahead.
 constexpr int NSTW = 2;
 struct SmemPlan {
-  int a_stride, p0, b0, b_stride, nst, w0, w_stride, bar_off, total;
+  int a_stride, p0, b0, b_stride, nst, w0, w_stride, scr0, bar_off, total;
   __host__ __device__ int a_off(int i) const { return i * a_stride; }
   int p_stride;
   __host__ __device__ int p_off(int i) const { return p0 + i * p_stride; }
   __host__ __device__ int b_off(int i) const { return b0 + i * b_stride; }
   __host__ __device__ int w_off(int i) const { return w0 + i * w_stride; }
 };
-template <int NSPLIT> __host__ __device__ inline SmemPlan smem_plan(int kp) {
+constexpr int ACT_SCRATCH = 32 * 33 * 4;   // per epilogue warp: a 32 x 32 fp32 block (padded) for the transposed activation store
+template <int NSPLIT> __host__ __device__ inline SmemPlan smem_plan(int kp, bool dense_act) {
   SmemPlan pl;
   pl.a_stride = a_buf_bytes<NSPLIT>();
   pl.p0 = 2 * pl.a_stride;
@@ -145,10 +146,12 @@ template <int NSPLIT> __host__ __device__ inline SmemPlan smem_plan(int kp) {
   pl.b_stride = ((NSPLIT == 3 ? 2 : 1) * CN * 128 + CN * 32 + 1023) / 1024 * 1024;
   pl.w_stride = ((NSPLIT == 3 ? 2 : 1) * kp * 128 + 1023) / 1024 * 1024;
   const int w_total = kp > 0 ? NSTW * pl.w_stride : 0;
-  int nst = (227 * 1024 - 512 - 1024 - pl.b0 - w_total) / pl.b_stride;
+  const int scr_total = dense_act ? 8 * ACT_SCRATCH : 0;
+  int nst = (227 * 1024 - 512 - 1024 - pl.b0 - w_total - scr_total) / pl.b_stride;
   pl.nst = nst > MAX_NST ? MAX_NST : nst;
   pl.w0 = pl.b0 + (pl.nst > 0 ? pl.nst : 0) * pl.b_stride;
-  pl.bar_off = pl.w0 + w_total;
+  pl.scr0 = pl.w0 + w_total;
+  pl.bar_off = pl.scr0 + scr_total;
   pl.total = pl.bar_off + 512 + 1024;  // barriers + slack to align the base to 1024
   return pl;
 }
@@ -165,7 +168,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
   const ChunkTable& ct = prm.ct;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   unsigned char* gbase = smem_raw + (base - smem_u32(smem_raw));
-  const SmemPlan pl = smem_plan<NSPLIT>(ct.kp);
+  const SmemPlan pl = smem_plan<NSPLIT>(ct.kp, prm.act != nullptr);
   const uint32_t bar0 = base + pl.bar_off;
   auto bar = [&](int i) { return bar0 + 8u * (uint32_t)i; };
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + pl.bar_off + 8 * BAR_COUNT);
@@ -448,11 +451,23 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
             av[j] = is_log ? lg2_approx(fmaf(ome, rcp_approx(d + eps), 1.0f)) : -d;
             if (drow != nullptr && valid && j < ncols) drow[(long long)(p0 + j) * s.HW] = d;
           }
-          if (arow != nullptr && valid) {
+          if (prm.act != nullptr) {
+            // (N x P) activation map: transpose the warp's 32 x 32 block through shared memory so that every store
+            // instruction writes 128 contiguous bytes of one row (a thread's own 32 values belong to ONE row)
             const float sc = is_log ? 0.69314718055994531f : 1.0f;
+            float* scr = reinterpret_cast<float*>(gbase + pl.scr0 + ew * ACT_SCRATCH);
+            __syncwarp();
 #pragma unroll
-            for (int j = 0; j < 32; ++j)
-              if (j < ncols) arow[p0 + j] = av[j] * sc;
+            for (int j = 0; j < 32; ++j) scr[lane * 33 + j] = av[j] * sc;
+            __syncwarp();
+            const long long n_first = n - lane;                    // row of lane 0 (the warp's rows are consecutive)
+            float* abase = prm.act + n_first * (long long)s.P + p0 + lane;
+            const int rows = s.N - n_first < 32 ? (int)(s.N - n_first) : 32;
+            if (lane < ncols) {
+#pragma unroll 8
+              for (int r = 0; r < 32; ++r)
+                if (r < rows) abase[(long long)r * s.P] = scr[r * 33 + lane];
+            }
           }
         }
         if (has_w) {
@@ -568,7 +583,7 @@ static int launch_fwd_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const f
   prm.dist = dist;
   prm.act = act;
   prm.n_tiles = (int)((s.N + tc::TILE_M - 1) / tc::TILE_M);
-  const tc::SmemPlan pl = tc::smem_plan<NSPLIT>(ct.kp);
+  const tc::SmemPlan pl = tc::smem_plan<NSPLIT>(ct.kp, act != nullptr);
   SPS_REQUIRE(pl.nst >= 2 && pl.total <= 227 * 1024, SPS_ERR_UNSUPPORTED, "tensor-core head: %d bytes of shared memory needed (K=%d)",
               pl.total, s.K);
   SPS_CUDA_TRY(cudaFuncSetAttribute(tc::head_fwd_tc_kernel<X, NSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
@@ -580,14 +595,14 @@ static int launch_fwd_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const f
 
 // Shapes the tcgen05 forward covers in this math mode; api.cu routes everything else to the exact fp32 kernels
 // (e.g. K = 171 with 3-term products: the hi + lo last-layer tiles leave room for a single ring stage).
-bool head_fwd_tc_supported(const HeadShape& s, int math, bool with_last_layer) {
+bool head_fwd_tc_supported(const HeadShape& s, int math, bool with_last_layer, bool dense_act) {
   if (math == SPS_MATH_FP32 || s.D > 64 || s.D % 8 != 0 || s.K > 192) return false;
   int nc = 0;
   for (int sc = 0; sc < s.S; ++sc) nc += (s.scale_lo[sc + 1] - s.scale_lo[sc] + tc::CN - 1) / tc::CN;
   if (nc > tc::MAX_CHUNKS) return false;
   const int kp = with_last_layer ? (s.K + 15) / 16 * 16 : 0;
   const bool split = math == SPS_MATH_F16X3 || math == SPS_MATH_BF16X3;
-  const tc::SmemPlan pl = split ? tc::smem_plan<3>(kp) : tc::smem_plan<1>(kp);
+  const tc::SmemPlan pl = split ? tc::smem_plan<3>(kp, dense_act) : tc::smem_plan<1>(kp, dense_act);
   return pl.nst >= 2 && pl.total <= 227 * 1024;
 }
 

@@ -62,3 +62,19 @@ if "train" in what:
     dd = torch.randn(B, P, H, W, device=dev) * 1e-3 / N
     t2 = timeit(lambda i: sps.head_backward_raw(zs[i % 4], protos, W_, cfg, dls[i % 4], dd, None, True, True, True), iters=5, warm=2)
     print(f"train-style: fwd (logits + dense dist) {t1:.1f} us | bwd (dlogits + ddist) {t2:.1f} us")
+if "stage2" in what:
+    from scaleprotoseg_b200 import head as sh
+    tables = sh.build_group_tables(ident, 3, dev)
+    Gp = torch.rand(3 * P, device=dev).requires_grad_(True)
+    Wg = torch.randn(K, 3 * tables.Kc, device=dev).requires_grad_(True)
+    def s2(i, train=True):
+        act = sps.head_forward_raw(zs[i % 4], protos, None, cfg, False, True)[2]
+        groups, lg = sh.GroupHeadFn.apply(act, Gp, Wg, cfg, tables, (B, H, W))
+        if train:
+            Gp.grad = Wg.grad = None
+            lg.backward(dls[i % 4])
+    tf = timeit(lambda i: sps.head_forward_raw(zs[i % 4], protos, None, cfg, False, True))
+    act0 = sps.head_forward_raw(zs[0], protos, None, cfg, False, True)[2]
+    tg = timeit(lambda i: sh.GroupHeadFn.apply(act0, Gp, Wg, cfg, tables, (B, H, W)))
+    tt = timeit(lambda i: s2(i))
+    print(f"stage2: head fwd (act only) {tf:.1f} us | group fwd {tg:.1f} us | fwd+bwd (frozen prototypes) {tt:.1f} us")
