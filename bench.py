@@ -365,6 +365,35 @@ def measure_dense(ctx, args):
             "hbm_frac": bytes_alg / (ms * 1e-3) / 1e9 / peaks()["hbm"]}
 
 
+def measure_stage2(ctx, args):
+    """Secondary: BASELINE.json configs[2], the stage-2 grouping finetune step on the same batch: head forward writing
+    the (N x P) activation map, group projection + exp + last_layer_group forward, backward to the projections and
+    the group last layer (prototypes and features frozen, as finetune_wandb_group trains)."""
+    sps, ho, dev, c = ctx["sps"], ctx["ho"], ctx["dev"], C2
+    from scaleprotoseg_b200 import head as sh
+    tables = sh.build_group_tables(ctx["ident"], 3, dev)
+    g = torch.Generator(device=dev).manual_seed(SEED + 3)
+    Gp = torch.rand(3 * c["P"], device=dev, generator=g).requires_grad_(True)
+    Wg = torch.randn(c["K"], 3 * tables.Kc, device=dev, generator=g).requires_grad_(True)
+    zs, p2, dls, cfg = ctx["zs"], ctx["p2"], ctx["dls"], ctx["cfg"]
+
+    def step(i):
+        act = sps.head_forward_raw(zs[i % N_SETS], p2, None, cfg, False, True)[2]
+        _, logits = sh.GroupHeadFn.apply(act, Gp, Wg, cfg, tables, (c["B"], c["H"], c["W"]))
+        Gp.grad = Wg.grad = None
+        logits.backward(dls[i % N_SETS])
+
+    iters = max(3, min(args.steps, 50))
+    for i in range(3):
+        step(i)
+    ms = event_ms(step, iters)
+    n = c["B"] * c["H"] * c["W"]
+    bytes_alg = n * c["S"] * c["D"] * 4 + 4 * n * c["P"] * 4      # z read; activation map written once, read 3 times
+    return {"workload": "stage-2 grouping head (3 groups per class), fwd + bwd to group projections and last_layer_group, same batch",
+            "ms_per_step": ms, "value": ctx["units"] / (ms * 1e-3), "unit": "positions*prototypes/s",
+            "hbm_frac": bytes_alg / (ms * 1e-3) / 1e9 / peaks()["hbm"]}
+
+
 def measure_c5(ctx, args):
     """Secondary: the COCO-Stuff head shape of BASELINE.json configs[4] (K=171, P=6840, B=32, 65x65), fused FORWARD
     only (the tensor-core backward covers K <= 32; larger K runs the fp32 backward).  Tensor-bound shape."""
@@ -458,6 +487,7 @@ def main():
     push = None if args.no_push else measure_push(ctx, args)
     c5 = None if (args.no_c5 or ctx["world"] > 1) else measure_c5(ctx, args)
     dense = None if (args.no_c5 or ctx["world"] > 1) else measure_dense(ctx, args)
+    stage2 = None if (args.no_c5 or ctx["world"] > 1) else measure_stage2(ctx, args)
     if ctx["world"] > 1:
         ctx["barrier"]()
     if rank != 0:
@@ -493,6 +523,8 @@ def main():
         out["coco_forward"] = c5
     if dense is not None:
         out["dense_mode"] = dense
+    if stage2 is not None:
+        out["stage2"] = stage2
     if not args.no_cpu and ctx["world"] == 1:
         out["cpu_baseline"] = measure_cpu(8, 2)
     if ctx["world"] > 1:
