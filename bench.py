@@ -463,8 +463,18 @@ def config_dict(args, world):
             "replicas": world, "l2": f"{N_SETS} rotating input sets ({N_SETS} x 69 MB z > 126 MB L2)", "math": args.math}
 
 
+def _claim_stdout():
+    """The contract is ONE JSON line on stdout.  Libraries write there too (NCCL prints its version banner at
+    communicator creation), so fd 1 is pointed at stderr for the whole run and the JSON line goes to the saved fd."""
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    return os.fdopen(saved, "w")
+
+
 def main():
     args = parse_args()
+    json_out = _claim_stdout()
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
     base = {"metric": "feature-positions x prototypes per second, prototype head fwd+bwd", "unit": "positions*prototypes/s",
@@ -479,7 +489,7 @@ def main():
         out.update({"impl": "reference", "value": cpu["value"], "ms_per_step": cpu["ms_per_step"], "dtype": "f32",
                     "steps": steps, "cpu_baseline": cpu, "gpu_launches": 0,
                     "e2e": {"value": cpu["value"], "unit": cpu["unit"], "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}})
-        print(json.dumps(out), flush=True)
+        print(json.dumps(out), file=json_out, flush=True)
         return
 
     ctx = run_ours(args)
@@ -529,7 +539,7 @@ def main():
         out["cpu_baseline"] = measure_cpu(8, 2)
     if ctx["world"] > 1:
         ctx["dist"].destroy_process_group()
-    print(json.dumps(out), flush=True)
+    print(json.dumps(out), file=json_out, flush=True)
 
 
 if __name__ == "__main__":
