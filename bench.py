@@ -23,7 +23,6 @@ import json
 import os
 import subprocess
 import sys
-import threading
 import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
@@ -62,69 +61,39 @@ def peaks():
 
 
 class ClockSampler:
-    """SM clock / throttle reasons sampled DURING the timed region (B200_PROFILING.md).  NVML in-process (about 1 kHz);
-    falls back to polling nvidia-smi when pynvml is not importable."""
+    """SM clock / throttle reasons sampled while the GPU is under load (B200_PROFILING.md): `nvidia-smi -lms 20` in a
+    child process (independent of this process's GIL), started before the warm-up and stopped after the end-to-end
+    measurement, so the window covers the timed region and the phase / e2e loops around it."""
     Q = "clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
-        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap,utilization.gpu"
     NAMES = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-    BITS = [0x8, 0x40, 0x20, 0x4]   # nvmlClocksThrottleReason{HwSlowdown, HwThermalSlowdown, SwThermalSlowdown, SwPowerCap}
 
     def __init__(self, index):
-        self.index, self.sm, self.mx, self.flags, self.stop_flag, self.th, self.nvml = index, [], [], set(), False, None, None
-        try:
-            import pynvml
-            pynvml.nvmlInit()
-            vis = os.environ.get("CUDA_VISIBLE_DEVICES")
-            phys = int(vis.split(",")[index]) if vis and all(v.strip().isdigit() for v in vis.split(",")) else index
-            self.nvml = (pynvml, pynvml.nvmlDeviceGetHandleByIndex(phys))
-        except Exception:
-            self.nvml = None
-
-    def _run_nvml(self):
-        nv, h = self.nvml
-        try:
-            self.mx.append(int(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)))
-        except Exception:
-            pass
-        while not self.stop_flag:
-            try:
-                self.sm.append(int(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)))
-                r = int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))
-                for name, bit in zip(self.NAMES, self.BITS):
-                    if r & bit:
-                        self.flags.add(name)
-            except Exception:
-                pass
-            time.sleep(0.001)
-
-    def _run_smi(self):
-        while not self.stop_flag:
-            try:
-                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
-                parts = [p.strip() for p in out.strip().split(",")]
-                if len(parts) >= 6 and parts[0].isdigit():
-                    self.sm.append(int(parts[0]))
-                    if parts[1].isdigit():
-                        self.mx.append(int(parts[1]))
-                    for i, name in enumerate(self.NAMES):
-                        if parts[2 + i].lower().startswith("active"):
-                            self.flags.add(name)
-            except Exception:
-                pass
-            time.sleep(0.05)
+        self.index, self.proc = index, None
 
     def start(self):
-        self.th = threading.Thread(target=self._run_nvml if self.nvml else self._run_smi, daemon=True)
-        self.th.start()
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:
+            self.proc = None
 
     def stop(self):
-        self.stop_flag = True
-        if self.th is not None:
-            self.th.join(timeout=10)
-        sm = sorted(self.sm)
-        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(self.mx) if self.mx else None,
-                "reasons": sorted(self.flags), "samples": len(sm), "source": "nvml" if self.nvml else "nvidia-smi"}
+        rows = []
+        if self.proc is not None:
+            try:
+                self.proc.terminate()
+                out, _ = self.proc.communicate(timeout=10)
+                rows = [[p.strip() for p in line.split(",")] for line in out.splitlines() if line.count(",") >= 6]
+            except Exception:
+                rows = []
+        busy = [r for r in rows if r[6].isdigit() and int(r[6]) > 0] or rows     # samples taken under load
+        sm = sorted(int(r[0]) for r in busy if r[0].isdigit())
+        mx = [int(r[1]) for r in rows if r[1].isdigit()]
+        reasons = [n for i, n in enumerate(self.NAMES) if any(r[2 + i].lower().startswith("active") for r in rows)]
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None, "reasons": reasons,
+                "samples": len(sm), "source": "nvidia-smi -lms 20, samples with utilization > 0, window = warm-up .. e2e"}
 
 
 MATH = {"fp32": 0, "bf16x3": 1, "bf16": 2, "f16": 3, "f16x3": 4}
@@ -199,12 +168,12 @@ def run_ours(args):
             dist.barrier()
         torch.cuda.synchronize()
 
-    for i in range(max(args.warmup, 3)):
-        step(i)
-    barrier()
     sampler = ClockSampler(local)
     if rank == 0:
         sampler.start()
+    for i in range(max(args.warmup, 3)):
+        step(i)
+    barrier()
     l0 = int(lib.sps_launch_count())
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
@@ -223,10 +192,9 @@ def run_ours(args):
     # per-phase device time (rank 0 reports): which kernel dominates, and its roofline
     t_fwd = event_ms(fwd, args.steps)
     t_bwd = event_ms(bwd, args.steps)
-    clocks = sampler.stop() if rank == 0 else None
     return dict(world=world, rank=rank, dev=dev, dist=dist, sps=sps, spush=spush, lib=lib, ho=ho, cfg=cfg, cfg_bwd=cfg_bwd,
                 zs=zs, protos=protos, p2=p2, last_w=last_w, dls=dls, ident=ident, units=units, ms_per_step=ms_per_step,
-                value=value, launches=launches, t_fwd=t_fwd, t_bwd=t_bwd, clocks=clocks, barrier=barrier)
+                value=value, launches=launches, t_fwd=t_fwd, t_bwd=t_bwd, sampler=sampler, barrier=barrier)
 
 
 def measure_e2e(ctx, args):
@@ -494,6 +462,7 @@ def main():
 
     ctx = run_ours(args)
     e2e = measure_e2e(ctx, args)
+    ctx["clocks"] = ctx["sampler"].stop() if rank == 0 else None
     push = None if args.no_push else measure_push(ctx, args)
     c5 = None if (args.no_c5 or ctx["world"] > 1) else measure_c5(ctx, args)
     dense = None if (args.no_c5 or ctx["world"] > 1) else measure_dense(ctx, args)
