@@ -20,6 +20,7 @@
 //
 // TMEM (512 columns): S x2 [0,128), dA x2 [128,256), dz [256,320), chunk j accumulators [320+64j, 384+64j):
 //   lanes 0-15 (+32q): dp^T 64 columns; lanes 16-31 (+32q): dW^T columns [0,32), csum columns [32,40).
+#include <type_traits>
 #include "tc_common.cuh"
 
 namespace sps {
@@ -33,8 +34,12 @@ __device__ long long g_tlb[8 * 1024];
   do {                                                                                     \
     if (blockIdx.x == 0 && (ev) < 1024) g_tlb[(role) * 1024 + (ev)] = clock64();            \
   } while (0)
+// every CTA: global-timer stamps (ns) of kernel entry / main loop end / exit -> roles 5, 6, 7 indexed by blockIdx.x
+__device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define TLB_CTA(role) do { if (blockIdx.x < 1024) g_tlb[(role) * 1024 + blockIdx.x] = gtimer(); } while (0)
 #else
 #define TLB(role, ev) do { } while (0)
+#define TLB_CTA(role) do { } while (0)
 #endif
 
 constexpr int GROUP_CHUNKS = 3;   // chunks per CTA (TMEM budget)
@@ -68,6 +73,7 @@ struct BwdParams {
   float* dz;
   float* part_dp;               // [nsplit][P*D]
   float* part_dw;               // [nsplit][K*P]
+  float* part_cs;               // [nsplit][P]   2/G * column sums of gamma (the 2 p csum term is applied by the reduce)
   int n_tiles;
 };
 
@@ -205,6 +211,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
   const int U = my_tiles * nch;
 
   if (threadIdx.x == 0) {
+    TLB_CTA(5);
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(B_AFULL + i), 4);
       mbar_init(bar(B_AEMPTY + i), 9);   // 8 epilogue warps (dz read z from smem) + 1 commit (dp GEMM read it)
@@ -245,7 +252,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       mbar_wait(bar(B_SEMPTY + sb), ((u >> 1) & 1) ^ 1);
       if (lane == 0) TLB(0, 4 * u + 1);
       tc_fence_after();
-      if (lane == 0) {
+      {
         const uint32_t ab0 = base + SM_A + ab * A_BUF, img = base + SM_RES + j * RES;
         const uint32_t dS = tmem + T_S + sb * CN, dA = tmem + T_DA + sb * CN;
         mma_f16(dS, desc_noswz(ab0 + AOFF_N, NORM_LBO, NORM_SBO), desc_noswz(img + BOFF_BN, NORM_LBO, NORM_SBO), ID, 0);
@@ -260,7 +267,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
 #pragma unroll
         for (int k = 0; k < 2; ++k) mma_f16(dA, desc_k_sw64(ab0 + AOFF_DL + 32 * k), desc_k_sw64(img + BOFF_W3 + 32 * k), ID, k);
         mma_commit(bar(B_SFULL + sb));
-        TLB(0, 4 * u + 2);
+        if (lane == 0) TLB(0, 4 * u + 2);
       }
       __syncwarp();
       if (++j == nch) { j = 0; ++ti; }
@@ -280,7 +287,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       if (j == 0) mbar_wait(bar(B_DZEMPTY), (ti & 1) ^ 1);
       if (lane == 0) TLB(1, 4 * u + 1);
       tc_fence_after();
-      if (lane == 0) {
+      {
         const uint32_t ab0 = base + SM_A + ab * A_BUF, img = base + SM_RES + j * RES;
         const uint32_t gam = base + SM_G + gb * G_BUF, act = gam + TILE_M * 128;
         const uint32_t acc = tmem + T_ACC + 64 * j;
@@ -298,7 +305,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
                   ID5C, accum);
         }
         mma_commit(bar(B_GEMPTY + gb));
-        TLB(1, 4 * u + 2);
+        if (lane == 0) TLB(1, 4 * u + 2);
         if (j == nch - 1) {
           mma_commit(bar(B_DZFULL));
           mma_commit(bar(B_AEMPTY + ab));
@@ -344,10 +351,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       mbar_wait(bar(B_AEMPTY + ab), ((ti >> 1) & 1) ^ 1);
       if (m == 0) TLB(2, 4 * ti + 1);
       unsigned char* a0 = gbase + SM_A + ab * A_BUF;
-      float zn = 0.f;
-      zst.convert_half(0, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
-      zst.convert_half(1, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
-      ZStage<X, NSPLIT>::store_norm(m, a0 + AOFF_N, zn);
+      // dlogits first: its 32 registers are dead while the feature row is converted
 #pragma unroll
       for (int gq = 0; gq < 4; ++gq) {
         uint32_t w[4];
@@ -356,6 +360,13 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
         *reinterpret_cast<uint4*>(a0 + AOFF_DL + (uint32_t)m * 64u + ((((uint32_t)gq) ^ (((uint32_t)m >> 1) & 3u)) << 4)) =
             make_uint4(w[0], w[1], w[2], w[3]);
       }
+      float zn = 0.f;
+      zst.template convert_half<4>(0, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
+      if (m == 0) TLB(6, 512 + 2 * ti);
+      zst.template convert_half<4>(1, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
+      if (m == 0) TLB(6, 513 + 2 * ti);
+      ZStage<X, NSPLIT>::store_norm(m, a0 + AOFF_N, zn);
+      if (m == 0) TLB(2, 4 * ti + 3);
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(B_AFULL + ab));
@@ -480,29 +491,35 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
         if (lane == 0) mbar_arrive(bar(B_SEMPTY + sb));
         if (threadIdx.x == 0) TLB(3, 8 * u + 2);
         uint32_t gw[16], aw[16];
+        // the activation kind is resolved per unit, not per element: as a run-time select inside the loop both
+        // formulas were evaluated for every element (20 instructions per element instead of 12)
+        auto gamma_act = [&](auto log_t) {
+          constexpr bool LOG = decltype(log_t)::value;
 #pragma unroll
-        for (int e = 0; e < 16; ++e) {
-          float gm[2], a2[2];
+          for (int e = 0; e < 16; ++e) {
+            float gm[2], a2[2];
 #pragma unroll
-          for (int h = 0; h < 2; ++h) {
-            const float sv = __uint_as_float(rs[2 * e + h]), dav = __uint_as_float(ra[2 * e + h]);
-            const float d = fmaxf(sv, 0.0f);
-            float ap, av;
-            if (is_log) {
-              const float s1 = d + 1.0f, ru = rcp_approx(s1 * (d + eps));
-              ap = -ome * ru;
-              av = lg2_approx(s1 * s1 * ru);
-            } else {
-              ap = -1.0f;
-              av = -d;
+            for (int h = 0; h < 2; ++h) {
+              const float sv = __uint_as_float(rs[2 * e + h]), dav = __uint_as_float(ra[2 * e + h]);
+              const float d = fmaxf(sv, 0.0f);
+              float ap, av;
+              if (LOG) {
+                const float s1 = d + 1.0f, ru = rcp_approx(s1 * (d + eps));
+                ap = -ome * ru;
+                av = lg2_approx(s1 * s1 * ru);
+              } else {
+                ap = -1.0f;
+                av = -d;
+              }
+              gm[h] = sv > 0.0f ? (HAS_DD ? fmaf(dav, ap, dd[2 * e + h] * G) : dav * ap) : 0.0f;
+              a2[h] = av;
+              sg += gm[h];
             }
-            gm[h] = sv > 0.0f ? (HAS_DD ? fmaf(dav, ap, dd[2 * e + h] * G) : dav * ap) : 0.0f;
-            a2[h] = av;
-            sg += gm[h];
+            gw[e] = Pack2<X>::pack(gm[0], gm[1]);
+            aw[e] = Pack2<X>::pack(a2[0], a2[1]);
           }
-          gw[e] = Pack2<X>::pack(gm[0], gm[1]);
-          aw[e] = Pack2<X>::pack(a2[0], a2[1]);
-        }
+        };
+        if (is_log) gamma_act(std::true_type{}); else gamma_act(std::false_type{});
         if (threadIdx.x == 0) TLB(3, 8 * u + 3);
         mbar_wait(bar(B_GEMPTY + gb), ((u >> 1) & 1) ^ 1);
         if (threadIdx.x == 0) TLB(3, 8 * u + 4);
@@ -522,66 +539,84 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       sgbuf[(ti & 1) * 256 + half * 128 + m] = sg;   // row sums of gamma of this tile (read after the named barrier in dz_readout)
     }
     if (my_tiles > 0) dz_readout(my_tiles - 1);
+    if (threadIdx.x == 0) TLB_CTA(6);
     // ---- partial dp / dW of this CTA ----
     if (U > 0) {
+      if (threadIdx.x == 0) TLB(4, 960);
       mbar_wait(bar(B_ACC), 0);
+      if (threadIdx.x == 0) TLB(4, 961);
       tc_fence_after();
-      float* cs = sgbuf;  // csum exchange [3][64]
-      named_bar_sync(1, 256);
-      uint32_t racc[GROUP_CHUNKS][32];
-      for (int j = 0; j < nch; ++j) {
-        tmem_ld32(tmem + lane_base + T_ACC + 64 * j + half * 32, racc[j]);
-        tmem_ld_wait();
-        if (half == 1 && lane >= 16) cs[j * 64 + q * 16 + lane - 16] = __uint_as_float(racc[j][0]);
-      }
-      named_bar_sync(1, 256);
+      // M = 64 accumulators: prototype row pl = q*16 + l sits in TMEM lane q*32 + l (dp^T, 64 channels) and lane
+      // q*32 + 16 + l (dW^T in columns 0..31, the column sum of gamma in column 32).  Lanes 0-15 write -2/G * acc as
+      // 16-byte pieces; lanes 16-31 write the dW columns (first warp set) or the column sums (second set) - the
+      // 2 p csum term of dp is added by the reduce kernel, which reads the prototypes coalesced.  An earlier version
+      // fetched them here, one dependent load per scalar store, and spent 25 us (20 % of the kernel) in this tail.
       const float wsc = (is_log ? 0.69314718055994531f : 1.0f) * invG;
-      for (int j = 0; j < nch; ++j) {
-        const int c = c0 + j, p0 = ct.p0[c], nc = ct.n[c];
-        if (lane < 16) {
-          const int pl = q * 16 + lane;
-          if (pl < nc) {
-            const float csum = cs[j * 64 + pl];
-            const float* prow = prm.protos + (size_t)(p0 + pl) * s.D;
-            float* out = prm.part_dp + (size_t)cta_local * s.P * s.D + (size_t)(p0 + pl) * s.D;
+      const int nlive = s.D - half * 32 < 32 ? s.D - half * 32 : 32;   // channels of this half that exist
+      const float m2 = -2.0f * invG;
 #pragma unroll
-            for (int e = 0; e < 32; ++e) {
-              const int cc = half * 32 + e;
-              if (cc < s.D) out[cc] = (2.0f * __ldg(prow + cc) * csum - 2.0f * __uint_as_float(racc[j][e])) * invG;
+      for (int j = 0; j < GROUP_CHUNKS; ++j) {
+        if (j < nch) {
+          uint32_t racc[32];
+          tmem_ld32(tmem + lane_base + T_ACC + 64 * j + half * 32, racc);
+          tmem_ld_wait();
+          const int c = c0 + j, p0 = ct.p0[c], nc = ct.n[c];
+          if (lane < 16) {
+            const int pl = q * 16 + lane;
+            if (pl < nc) {
+              float* out = prm.part_dp + (size_t)cta_local * s.P * s.D + (size_t)(p0 + pl) * s.D + half * 32;
+#pragma unroll
+              for (int e4 = 0; e4 < 8; ++e4)
+                if (4 * e4 < nlive)   // D is a multiple of 8
+                  *reinterpret_cast<float4*>(out + 4 * e4) =
+                      make_float4(__uint_as_float(racc[4 * e4]) * m2, __uint_as_float(racc[4 * e4 + 1]) * m2,
+                                  __uint_as_float(racc[4 * e4 + 2]) * m2, __uint_as_float(racc[4 * e4 + 3]) * m2);
             }
-          }
-        } else if (half == 0) {
-          const int pl = q * 16 + lane - 16;
-          if (pl < nc) {
-            float* out = prm.part_dw + (size_t)cta_local * s.K * s.P + p0 + pl;
+          } else {
+            const int pl = q * 16 + lane - 16;
+            if (pl < nc) {
+              if (half == 0) {
+                float* out = prm.part_dw + (size_t)cta_local * s.K * s.P + p0 + pl;
 #pragma unroll
-            for (int e = 0; e < 32; ++e)
-              if (e < s.K) out[(size_t)e * s.P] = __uint_as_float(racc[j][e]) * wsc;
+                for (int e = 0; e < 32; ++e)
+                  if (e < s.K) out[(size_t)e * s.P] = __uint_as_float(racc[e]) * wsc;
+              } else {
+                prm.part_cs[(size_t)cta_local * s.P + p0 + pl] = -__uint_as_float(racc[0]) * m2;
+              }
+            }
           }
         }
       }
+      if (threadIdx.x == 0) TLB(4, 963);
     }
   }
 
+  if (lane == 0) TLB(4, 900 + warp);
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) TLB(4, 964);
+  if (threadIdx.x == 0) TLB_CTA(7);
   if (warp == WARP_I1) {
     tc_fence_after();
     tmem_dealloc(tmem, 512);
   }
 }
 
-// out1[i] = sum over the CTA partials of part1 (i < count1); likewise out2 for the following count2 threads (either may
-// be empty).  Fixed order: deterministic.
+// out1[i] = sum over the CTA partials of part1 (i < count1) + protos[i] * sum of the column-sum partials of its
+// prototype (the 2 p csum term of dp); out2 likewise (plain sum) for the following count2 threads.  Either may be empty.
+// Fixed order: deterministic.
 __global__ void bwd_reduce_kernel(const float* __restrict__ part1, long long count1, float* __restrict__ out1,
-                                  const float* __restrict__ part2, long long count2, float* __restrict__ out2, int nsplit) {
+                                  const float* __restrict__ part2, long long count2, float* __restrict__ out2, int nsplit,
+                                  const float* __restrict__ part_cs, const float* __restrict__ protos, int D, int P) {
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const float* part = part1;
   float* out = out1;
   long long count = count1;
+  bool is_dp = true;
   if (i >= count1) {
     i -= count1;
     part = part2, out = out2, count = count2;
+    is_dp = false;
     if (i >= count2) return;
   }
   float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
@@ -593,8 +628,20 @@ __global__ void bwd_reduce_kernel(const float* __restrict__ part1, long long cou
     a3 += part[(long long)(sp + 3) * count + i];
   }
   for (; sp < nsplit; ++sp) a0 += part[(long long)sp * count + i];
-  out[i] = (a0 + a1) + (a2 + a3);
+  float r = (a0 + a1) + (a2 + a3);
+  if (is_dp) {
+    const long long p = i / D;
+    float c0 = 0.f, c1 = 0.f;
+    for (sp = 0; sp + 2 <= nsplit; sp += 2) {
+      c0 += part_cs[(long long)sp * P + p];
+      c1 += part_cs[(long long)(sp + 1) * P + p];
+    }
+    for (; sp < nsplit; ++sp) c0 += part_cs[(long long)sp * P + p];
+    r = fmaf(protos[i], c0 + c1, r);
+  }
+  out[i] = r;
 }
+
 
 }  // namespace tcb
 
@@ -663,7 +710,7 @@ size_t head_bwd_tc_workspace(const HeadShape& s) {
   const int n_tiles = (int)((s.N + tc::TILE_M - 1) / tc::TILE_M);
   if (build_group_table(ct, n_tiles > 0 ? n_tiles : 1, sm_count(), &gt) <= 0) return 0;
   const size_t nsplit = (size_t)bwd_nsplit(gt);
-  return 1024 + (size_t)ct.n_chunks * tcb::BIMG + 256 + sizeof(float) * nsplit * ((size_t)s.P * s.D + (size_t)s.K * s.P);
+  return 1024 + (size_t)ct.n_chunks * tcb::BIMG + 256 + sizeof(float) * nsplit * ((size_t)s.P * s.D + (size_t)s.K * s.P + (size_t)s.P);
 }
 
 template <typename X, int NSPLIT>
@@ -682,7 +729,8 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   unsigned int* amax = reinterpret_cast<unsigned int*>(img + (size_t)prm.ct.n_chunks * tcb::BIMG);
   float* part_dp = reinterpret_cast<float*>(reinterpret_cast<unsigned char*>(amax) + 256);
   float* part_dw = part_dp + (size_t)nsplit * s.P * s.D;
-  const size_t part_bytes = sizeof(float) * (size_t)nsplit * ((size_t)s.P * s.D + (size_t)s.K * s.P);
+  float* part_cs = part_dw + (size_t)nsplit * s.K * s.P;
+  const size_t part_bytes = sizeof(float) * (size_t)nsplit * ((size_t)s.P * s.D + (size_t)s.K * s.P + (size_t)s.P);
   SPS_CUDA_TRY(cudaMemsetAsync(amax, 0, 256 + part_bytes, st));
   bool any_multi = false;
   for (int g = 0; g < prm.gt.n_groups; ++g) any_multi |= prm.gt.multi[g] != 0;
@@ -705,6 +753,7 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   prm.dz = dz;
   prm.part_dp = part_dp;
   prm.part_dw = part_dw;
+  prm.part_cs = part_cs;
   constexpr int SMEM = tcb::Lay<NSPLIT>::SM_TOTAL;
   static_assert(SMEM <= 227 * 1024, "backward kernel shared memory");
   if (ddist != nullptr) {
@@ -718,7 +767,8 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   {
     const long long c1 = dprotos != nullptr ? (long long)s.P * s.D : 0, c2 = dlast_w != nullptr ? (long long)s.K * s.P : 0;
     if (c1 + c2 > 0) {
-      tcb::bwd_reduce_kernel<<<(unsigned)((c1 + c2 + 255) / 256), 256, 0, st>>>(part_dp, c1, dprotos, part_dw, c2, dlast_w, nsplit);
+      tcb::bwd_reduce_kernel<<<(unsigned)((c1 + c2 + 255) / 256), 256, 0, st>>>(part_dp, c1, dprotos, part_dw, c2, dlast_w, nsplit,
+                                                                                       part_cs, protos, s.D, s.P);
       count_launch();
     }
   }

@@ -161,7 +161,9 @@ enum { BAR_AFULL = 0, BAR_AEMPTY = 2, BAR_BFULL = 4, BAR_BEMPTY = 4 + MAX_NST, B
        BAR_SEMPTY = 6 + 2 * MAX_NST, BAR_PFULL = 8 + 2 * MAX_NST, BAR_PEMPTY = 10 + 2 * MAX_NST, BAR_LFULL = 12 + 2 * MAX_NST,
        BAR_LEMPTY = 14 + 2 * MAX_NST, BAR_WFULL = 16 + 2 * MAX_NST, BAR_WEMPTY = 18 + 2 * MAX_NST, BAR_COUNT = 20 + 2 * MAX_NST };
 
-template <typename X, int NSPLIT>
+// DENSE: the distance and / or activation maps leave the SM as well.  A compile-time switch: as a run-time test the
+// compiler merged both paths and the fused epilogue carried the (predicated-off) address arithmetic of the dense stores.
+template <typename X, int NSPLIT, bool DENSE>
 __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_constant__ FwdParams prm) {
   extern __shared__ unsigned char smem_raw[];
   const HeadShape& s = prm.s;
@@ -227,7 +229,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       mbar_wait(bar(BAR_SEMPTY + sb), ((i >> 1) & 1) ^ 1);
       if (lane == 0) TL(7, i);
       tc_fence_after();
-      if (lane == 0) {
+      {
         const uint32_t a_hi = base + pl.a_off(ab), a_lo = a_hi + A_HI;
         const uint32_t a_n = a_hi + (NSPLIT == 3 ? 2 : 1) * A_HI;
         const uint32_t b_hi = base + pl.b_off(st) + OFF_BHI, b_lo = base + pl.b_off(st) + OFF_BLO;
@@ -245,7 +247,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
         mma_commit(bar(BAR_SFULL + sb));
         if (last_of_scale) mma_commit(bar(BAR_AEMPTY + ab));
         mma_commit(bar(BAR_BEMPTY + st));   // the B slot is free once this unit's distance GEMM has read it
-        TL(0, i);
+        if (lane == 0) TL(0, i);
       }
       __syncwarp();
       if (last_of_scale) ++acount;
@@ -263,8 +265,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
         mbar_wait(bar(BAR_WFULL + sw), (u / NSTW) & 1);
         mbar_wait(bar(BAR_PFULL + pb), (u >> 1) & 1);
         tc_fence_after();
-        if (lane == 0) {
-          TL(1, u);
+        {
+          if (lane == 0) TL(1, u);
           const uint32_t pa = base + pl.p_off(pb), w2 = base + pl.w_off(sw);
           const uint32_t d = tmem + TMEM_L0 + lb * KP;
 #pragma unroll
@@ -279,7 +281,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
           mma_commit(bar(BAR_PEMPTY + pb));
           mma_commit(bar(BAR_WEMPTY + sw));
           if (c == NC - 1) mma_commit(bar(BAR_LFULL + lb));
-          TL(2, u);
+          if (lane == 0) TL(2, u);
         }
         __syncwarp();
         if (++c == NC) { c = 0; ++tl; }
@@ -416,8 +418,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
     for (int u = set; u < U; u += 2) {
       const bool valid = n < s.N;
       const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
-      float* drow = prm.dist != nullptr ? prm.dist + b * (long long)s.P * s.HW + pix : nullptr;
-      float* arow = prm.act != nullptr ? prm.act + n * (long long)s.P : nullptr;
+      float* drow = DENSE && prm.dist != nullptr ? prm.dist + b * (long long)s.P * s.HW + pix : nullptr;
       const uint32_t sb = u & 1, pb = u & 1, ph = (u >> 1) & 1;
       if (lane == 0 && q == 0) TL(3, 8 * u + 0);
       mbar_wait(bar(BAR_SFULL + sb), ph);
@@ -438,18 +439,31 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
         const int col0 = hf * 32, ncols = ct.n[c] - col0;  // live columns of this half: [0, ncols)
         const int p0 = ct.p0[c] + col0;
         float av[32];  // log2 of the similarity ratio ('log'), or -d ('linear')
-        if (drow == nullptr && arow == nullptr) {  // fused mode: nothing but the logits leaves the SM
+        // activation kind resolved per half-unit, not per element (a run-time select evaluates both formulas)
+        if (is_log) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             const float d = fmaxf(__uint_as_float(r[j]), 0.0f);
-            av[j] = is_log ? lg2_approx(fmaf(ome, rcp_approx(d + eps), 1.0f)) : -d;
+            av[j] = lg2_approx(fmaf(ome, rcp_approx(d + eps), 1.0f));
+            if (DENSE) r[j] = __float_as_uint(d);
           }
         } else {
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             const float d = fmaxf(__uint_as_float(r[j]), 0.0f);
-            av[j] = is_log ? lg2_approx(fmaf(ome, rcp_approx(d + eps), 1.0f)) : -d;
-            if (drow != nullptr && valid && j < ncols) drow[(long long)(p0 + j) * s.HW] = d;
+            av[j] = -d;
+            if (DENSE) r[j] = __float_as_uint(d);
+          }
+        }
+        if (DENSE) {
+          if (drow != nullptr && valid) {
+            float* dp = drow + (long long)p0 * s.HW;
+            const size_t pitch = (size_t)s.HW;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (j < ncols) *dp = __uint_as_float(r[j]);
+              dp += pitch;
+            }
           }
           if (prm.act != nullptr) {
             // (N x P) activation map: transpose the warp's 32 x 32 block through shared memory so that every store
@@ -586,9 +600,14 @@ static int launch_fwd_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const f
   const tc::SmemPlan pl = tc::smem_plan<NSPLIT>(ct.kp, act != nullptr);
   SPS_REQUIRE(pl.nst >= 2 && pl.total <= 227 * 1024, SPS_ERR_UNSUPPORTED, "tensor-core head: %d bytes of shared memory needed (K=%d)",
               pl.total, s.K);
-  SPS_CUDA_TRY(cudaFuncSetAttribute(tc::head_fwd_tc_kernel<X, NSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
   const int grid = prm.n_tiles < sm_count() ? prm.n_tiles : sm_count();
-  SPS_CUDA_TRY(launch_pdl(tc::head_fwd_tc_kernel<X, NSPLIT>, dim3(grid), dim3(tc::NTHREADS), (size_t)pl.total, st, prm));
+  if (dist != nullptr || act != nullptr) {
+    SPS_CUDA_TRY(cudaFuncSetAttribute(tc::head_fwd_tc_kernel<X, NSPLIT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+    SPS_CUDA_TRY(launch_pdl(tc::head_fwd_tc_kernel<X, NSPLIT, true>, dim3(grid), dim3(tc::NTHREADS), (size_t)pl.total, st, prm));
+  } else {
+    SPS_CUDA_TRY(cudaFuncSetAttribute(tc::head_fwd_tc_kernel<X, NSPLIT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+    SPS_CUDA_TRY(launch_pdl(tc::head_fwd_tc_kernel<X, NSPLIT, false>, dim3(grid), dim3(tc::NTHREADS), (size_t)pl.total, st, prm));
+  }
   count_launch();
   return SPS_OK;
 }

@@ -145,7 +145,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       mbar_wait(bar(PB_ZFULL + st), (i / L::NSTAGE) & 1);
       mbar_wait(bar(PB_DEMPTY + db), ((i >> 1) & 1) ^ 1);
       tc_fence_after();
-      if (lane == 0) {
+      {
         const uint32_t zt = base + L::SM_Z + st * L::STAGE;
         for (int t = 0; t < n_mt; ++t) {
           const uint32_t pt = base + L::SM_RES + t * L::RES_T, d = tmem + db * 256 + t * 128;

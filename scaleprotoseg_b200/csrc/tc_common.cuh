@@ -85,18 +85,26 @@ __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence:
 __device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
 
 // D[tmem] (+)= A[smem] * B[smem]^T, kind::f16 (fp16 or bf16 operands, fp32 accumulate). One thread issues.
+// tcgen05.mma / tcgen05.commit are called by EVERY lane of a converged issuer warp on warp-uniform operands; the
+// instruction itself is predicated on elect.sync (the same lane every time for the full mask, so the commit tracks
+// the MMAs).  Issuing under `if (lane == 0)` instead makes the compiler wrap each MMA in an elect / branch loop that
+// costs ~80 clk per instruction (measured, scratch/mma_rate.cu) against 28-50 clk for the shapes used here.
 __device__ __forceinline__ void mma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(
-      "{\n\t.reg .pred p;\n\t"
+      "{\n\t.reg .pred p, q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
       "setp.ne.b32 p, %4, 0;\n\t"
-      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}"
       ::"r"(tmem_d), "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
       : "memory");
 }
-// Arrives on the mbarrier when every tcgen05 op issued so far by this thread has completed.
+// Arrives on the mbarrier when every tcgen05 op issued so far by the elected lane has completed.
 // (implies tcgen05.fence::before_thread_sync)
 __device__ __forceinline__ void mma_commit(uint32_t bar) {
-  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+  asm volatile(
+      "{\n\t.reg .pred q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "@q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n\t}" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void tmem_ld_wait() { asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory"); }
 
@@ -256,7 +264,14 @@ template <typename X, int NSPLIT> struct ZStage {
     }
   }
   // converts channels [32h, 32h+32) of row m into a_hi (and a_lo); accumulates the squared norm
+  // NACC partial sums for the norm (1, 2 or 4): a single FFMA chain serialises the row when the caller has registers
+  // to spare (backward: 128 -> 122 us with 4); the push loaders do not (4 sums: 220 -> 284 us per 16 maps)
+  template <int NACC = 1>
   __device__ __forceinline__ void convert_half(int h, int m, unsigned char* a_hi, unsigned char* a_lo, float& zn) {
+    float zq[NACC];
+    zq[0] = zn;
+#pragma unroll
+    for (int i = 1; i < NACC; ++i) zq[i] = 0.f;
 #pragma unroll
     for (int g4 = 0; g4 < 4; ++g4) {
       const int g = h * 4 + g4;
@@ -272,13 +287,16 @@ template <typename X, int NSPLIT> struct ZStage {
           e.x += el.x;
           e.y += el.y;
         }
-        zn = fmaf(e.x, e.x, zn);
-        zn = fmaf(e.y, e.y, zn);
+        zq[q % NACC] = fmaf(e.x, e.x, zq[q % NACC]);
+        zq[q % NACC] = fmaf(e.y, e.y, zq[q % NACC]);
       }
       const uint32_t off = (uint32_t)m * 128u + ((((uint32_t)g) ^ ((uint32_t)m & 7u)) << 4);
       *reinterpret_cast<uint4*>(a_hi + off) = make_uint4(hw_[0], hw_[1], hw_[2], hw_[3]);
       if (NSPLIT == 3) *reinterpret_cast<uint4*>(a_lo + off) = make_uint4(lw_[0], lw_[1], lw_[2], lw_[3]);
     }
+    if (NACC == 4) zn = (zq[0] + zq[1]) + (zq[2] + zq[3]);
+    else if (NACC == 2) zn = zq[0] + zq[1];
+    else zn = zq[0];
   }
   // the extra K step of row m: [1, 1, 1, zn_hi, zn_mid, zn_lo, 0 ...]
   static __device__ __forceinline__ void store_norm(int m, unsigned char* a_n, float zn) {

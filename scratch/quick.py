@@ -1,6 +1,6 @@
 """Quick GPU iteration: time fwd / bwd / push kernels (CUDA events, rotating inputs) and check them vs the fp32 kernels.
 usage: python scratch/quick.py [math=4] [what=fwd,bwd,push]"""
-import sys, torch
+import os, sys, torch
 sys.path.insert(0, "/root/repo")
 import scaleprotoseg_b200 as sps
 from scaleprotoseg_b200 import push as spush
@@ -16,8 +16,9 @@ ident = ho.make_identity(P, K, 4)
 W_ = ho.make_last_layer(ident).contiguous().to(dev)
 N = B * H * W
 dls = [torch.randn(N, K, device=dev) / N for _ in range(4)]
-cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, 4), K, math=math)
-cfg32 = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, 4), K, math=sps.MATH_FP32)
+ACT = os.environ.get("ACT", "log")
+cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, 4), K, act=ACT, math=math)
+cfg32 = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, 4), K, act=ACT, math=sps.MATH_FP32)
 
 def timeit(fn, iters=20, warm=5):
     for i in range(warm): fn(i)

@@ -27,4 +27,4 @@ for u in range(12, 30):
     print(u, "I1 top/waited/issued", f(g(0, 4*u)), f(g(0, 4*u+1)), f(g(0, 4*u+2)), "| I2 top/waited/issued", f(g(1, 4*u)), f(g(1, 4*u+1)), f(g(1, 4*u+2)),
           "| epi top/sfull/ld/math/gempty/gfull", " ".join(f(g(3, 8*u+k)) for k in range(6)))
     if u % 3 == 2:
-        print("   tile", ti, "loader wait/got/done", f(g(2, 4*ti)), f(g(2, 4*ti+1)), f(g(2, 4*ti+2)), "| dz readout start/dzfull/done", f(g(4, 4*ti)), f(g(4, 4*ti+1)), f(g(4, 4*ti+2)))
+        print("   tile", ti, "loader wait/got/done", f(g(2, 4*ti)), f(g(2, 4*ti+1)), f(g(2, 4*ti+2)), "[half0", f(g(6, 512+2*ti)), "half1", f(g(6, 513+2*ti)), "norm", f(g(2, 4*ti+3)), "] | dz readout start/dzfull/done", f(g(4, 4*ti)), f(g(4, 4*ti+1)), f(g(4, 4*ti+2)))
