@@ -540,6 +540,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
     }
     if (my_tiles > 0) dz_readout(my_tiles - 1);
     if (threadIdx.x == 0) TLB_CTA(6);
+    pdl_launch_dependents();   // the reduce kernel may be scheduled as the CTAs drain (it waits for the whole grid)
     // ---- partial dp / dW of this CTA ----
     if (U > 0) {
       if (threadIdx.x == 0) TLB(4, 960);
@@ -608,6 +609,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
 __global__ void bwd_reduce_kernel(const float* __restrict__ part1, long long count1, float* __restrict__ out1,
                                   const float* __restrict__ part2, long long count2, float* __restrict__ out2, int nsplit,
                                   const float* __restrict__ part_cs, const float* __restrict__ protos, int D, int P) {
+  pdl_wait();   // launched while the main kernel drains: its partials are complete (and visible) after this
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const float* part = part1;
   float* out = out1;
@@ -731,7 +733,11 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   float* part_dw = part_dp + (size_t)nsplit * s.P * s.D;
   float* part_cs = part_dw + (size_t)nsplit * s.K * s.P;
   const size_t part_bytes = sizeof(float) * (size_t)nsplit * ((size_t)s.P * s.D + (size_t)s.K * s.P + (size_t)s.P);
-  SPS_CUDA_TRY(cudaMemsetAsync(amax, 0, 256 + part_bytes, st));
+  // every partial slot is written by exactly one CTA when all groups run the same number of CTAs and each CTA owns at
+  // least one tile (the usual case); only then can the 9 MB clear of the partial buffers be skipped
+  bool all_written = true;
+  for (int g = 0; g < prm.gt.n_groups; ++g) all_written &= prm.gt.ncta[g] == nsplit && prm.n_tiles >= prm.gt.ncta[g];
+  SPS_CUDA_TRY(cudaMemsetAsync(amax, 0, all_written ? 256 : 256 + part_bytes, st));
   bool any_multi = false;
   for (int g = 0; g < prm.gt.n_groups; ++g) any_multi |= prm.gt.multi[g] != 0;
   if (dz != nullptr && any_multi) SPS_CUDA_TRY(cudaMemsetAsync(dz, 0, sizeof(float) * (size_t)s.B * s.C * s.HW, st));
@@ -767,8 +773,9 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   {
     const long long c1 = dprotos != nullptr ? (long long)s.P * s.D : 0, c2 = dlast_w != nullptr ? (long long)s.K * s.P : 0;
     if (c1 + c2 > 0) {
-      tcb::bwd_reduce_kernel<<<(unsigned)((c1 + c2 + 255) / 256), 256, 0, st>>>(part_dp, c1, dprotos, part_dw, c2, dlast_w, nsplit,
-                                                                                       part_cs, protos, s.D, s.P);
+      SPS_CUDA_TRY(launch_pdl(tcb::bwd_reduce_kernel, dim3((unsigned)((c1 + c2 + 255) / 256)), dim3(256), (size_t)0, st,
+                              (const float*)part_dp, c1, dprotos, (const float*)part_dw, c2, dlast_w, nsplit,
+                              (const float*)part_cs, protos, s.D, s.P));
       count_launch();
     }
   }

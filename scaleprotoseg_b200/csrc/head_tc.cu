@@ -31,8 +31,12 @@ __device__ long long g_tl[8 * 1024];
   do {                                                                                  \
     if (blockIdx.x == 0 && (ev) < 1024) g_tl[(role) * 1024 + (ev)] = clock64();          \
   } while (0)
+// every CTA: global-timer stamps (ns) of kernel entry / epilogue loop end / exit -> roles 5, 6, 7 at [512 + blockIdx.x]
+__device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); return t; }
+#define TL_CTA(role) do { if (blockIdx.x < 512) g_tl[(role) * 1024 + 512 + blockIdx.x] = gtimer(); } while (0)
 #else
 #define TL(role, ev) do { } while (0)
+#define TL_CTA(role) do { } while (0)
 #endif
 
 // ---------------------------------------------------------------------------------------------
@@ -182,6 +186,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
   while ((int)tmem_cols < TMEM_L0 + 2 * KP) tmem_cols <<= 1;
 
   if (threadIdx.x == 0) {
+    TL_CTA(5);
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(BAR_AFULL + i), 4);    // one arrive per loader warp
       mbar_init(bar(BAR_AEMPTY + i), 1);   // tcgen05.commit
@@ -519,6 +524,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       c += 2;
       while (c >= NC) { c -= NC; ++ti; n += (long long)gridDim.x * TILE_M; }
     }
+    if (threadIdx.x == 0) TL_CTA(6);
     if (has_w && set == 0)
       while (next_store < my_tiles) store_logits(next_store++);
   }
@@ -526,6 +532,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
   // ================================ teardown ================================
   tc_fence_before();
   __syncthreads();
+  if (threadIdx.x == 0) TL_CTA(7);
   if (warp == WARP_MMA) {
     tc_fence_after();
     tmem_dealloc(tmem, tmem_cols);
