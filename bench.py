@@ -423,6 +423,27 @@ def measure_cpu(steps, warmup):
                       f"{steps} steps after {warmup} warm-up", "ms_per_step": dt * 1e3}
 
 
+def measure_torch_gpu(ctx, args):
+    """The same op sequence as the reference head (oracle port: model_multiscale.py:256-388 restated in stock PyTorch
+    ops, fp32, autograd backward) run on this GPU: the GPU baseline of SURVEY 8(d).  A baseline leg like cpu_baseline:
+    the oracle is the thing compared against, never the thing shipped."""
+    from oracle import head_oracle as ho
+    dev, c = ctx["dev"], C2
+    g = torch.Generator(device=dev).manual_seed(SEED + 5)
+    z = torch.sigmoid(torch.randn(c["B"], c["S"] * c["D"], c["H"], c["W"], device=dev, generator=g))
+    protos = torch.rand(c["P"], c["D"], 1, 1, device=dev, generator=g)
+    last_w = ho.make_last_layer(ho.make_identity(c["P"], c["K"], c["S"])).contiguous().to(dev)
+    ranges = ho.uniform_ranges(c["P"], c["S"])
+    n = c["B"] * c["H"] * c["W"]
+    dl = (torch.randn(n, c["K"], device=dev, generator=g) / n).view(c["B"], c["H"], c["W"], c["K"])
+    for _ in range(3):
+        cpu_head_step(ho, z, protos, last_w, ranges, dl)
+    ms = event_ms(lambda i: cpu_head_step(ho, z, protos, last_w, ranges, dl), 10)
+    return {"ms_per_step": ms, "value": n * c["P"] / (ms * 1e-3), "unit": "positions*prototypes/s",
+            "note": "oracle port of the reference head in stock PyTorch ops (2 convs + elementwise chain + linear, autograd "
+                    "backward), fp32, on the same GPU; 10 steps after warm-up"}
+
+
 def config_dict(args, world):
     c = C2
     return {"workload": f"ScaleProtoSeg Cityscapes head fwd+bwd (BASELINE.json configs[1]): B={c['B']} maps 256x{c['H']}x{c['W']} "
@@ -467,6 +488,7 @@ def main():
     c5 = None if (args.no_c5 or ctx["world"] > 1) else measure_c5(ctx, args)
     dense = None if (args.no_c5 or ctx["world"] > 1) else measure_dense(ctx, args)
     stage2 = None if (args.no_c5 or ctx["world"] > 1) else measure_stage2(ctx, args)
+    torch_gpu = None if (args.no_c5 or ctx["world"] > 1) else measure_torch_gpu(ctx, args)
     if ctx["world"] > 1:
         ctx["barrier"]()
     if rank != 0:
@@ -504,6 +526,8 @@ def main():
         out["dense_mode"] = dense
     if stage2 is not None:
         out["stage2"] = stage2
+    if torch_gpu is not None:
+        out["torch_gpu_baseline"] = torch_gpu
     if not args.no_cpu and ctx["world"] == 1:
         out["cpu_baseline"] = measure_cpu(8, 2)
     if ctx["world"] > 1:

@@ -116,38 +116,13 @@ __global__ void __launch_bounds__(256) bwd_prep_kernel(const __grid_constant__ C
   __shared__ float pn[CN];
   {
     const int j = t >> 2, kq = (t & 3) * 16;
-    float part = 0.f;
-#pragma unroll
-    for (int kk = 0; kk < 16; ++kk) {
-      const int k = kq + kk;
-      const float v = (j < n && k < D) ? -2.0f * __ldg(protos + (size_t)(p0 + j) * D + k) : 0.0f;
-      const X hi = Fmt<X>::from(v);
-      float eff = Fmt<X>::to(hi);
-      X lo = Fmt<X>::from(0.0f);
-      if (NSPLIT == 3) {
-        lo = Fmt<X>::from(v - eff);
-        eff += Fmt<X>::to(lo);
-      }
-      *reinterpret_cast<uint16_t*>(img + BOFF_BH + sw128_off(j, k)) = bits16(hi);
-      *reinterpret_cast<uint16_t*>(img + BOFF_BL + sw128_off(j, k)) = bits16(lo);
-      part = fmaf(0.5f * eff, 0.5f * eff, part);
-    }
+    float part = pack_row16<X, NSPLIT>(protos + (size_t)(p0 + (j < n ? j : 0)) * D, j < n, D, -2.0f, img + BOFF_BH, img + BOFF_BL, j, kq);
     part += __shfl_xor_sync(0xffffffffu, part, 1);
     part += __shfl_xor_sync(0xffffffffu, part, 2);
     if ((t & 3) == 0) pn[j] = part;
   }
   __syncthreads();
-  if (t < CN) {
-    X h, m, l;
-    split3<X>(pn[t], h, m, l);
-    const X one = Fmt<X>::from(1.0f), zero = Fmt<X>::from(0.0f);
-    const bool live = t < n;
-    for (int k = 0; k < 16; ++k) {
-      X v = zero;
-      if (live) v = k == 0 ? h : k == 1 ? m : k == 2 ? l : k < 6 ? one : zero;
-      *reinterpret_cast<uint16_t*>(img + BOFF_BN + norm_off(t, k)) = bits16(v);
-    }
-  }
+  if (t < CN) store_proto_norm<X>(img + BOFF_BN, t, pn[t], t < n);
   for (int idx = t; idx < CN * KP_BWD; idx += blockDim.x) {
     const int j = idx / KP_BWD, k = idx % KP_BWD;
     const float v = (k < K && j < n) ? __ldg(last_w + (size_t)k * P + p0 + j) : 0.0f;

@@ -336,6 +336,53 @@ template <typename X, int NSPLIT> struct ZStage {
   }
 };
 
+// Pre-pass helper: 16 consecutive channels [kq, kq+16) of operand row j, value scale * src[k] (zero where !live or
+// k >= D), into the SW128 K-major tiles t_hi / t_lo as 16-byte pieces (2-byte stores cost one L2 sector write each and
+// made the 12-block pre-pass take 5 us).  Returns sum of (0.5 * p_eff)^2 over the 16 channels, p_eff = the value the
+// MMA really sees (hi + lo).
+template <typename X, int NSPLIT>
+__device__ __forceinline__ float pack_row16(const float* __restrict__ src, bool live, int D, float scale, unsigned char* t_hi,
+                                            unsigned char* t_lo, int j, int kq) {
+  float v[16];
+#pragma unroll
+  for (int kk = 0; kk < 16; ++kk) v[kk] = (live && kq + kk < D) ? scale * __ldg(src + kq + kk) : 0.0f;
+  float part = 0.f;
+#pragma unroll
+  for (int g = 0; g < 2; ++g) {
+    uint32_t hw[4], lw[4];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const float v0 = v[g * 8 + 2 * q], v1 = v[g * 8 + 2 * q + 1];
+      hw[q] = Pack2<X>::pack(v0, v1);
+      float2 e = Pack2<X>::unpack(hw[q]);
+      lw[q] = 0u;
+      if (NSPLIT == 3) {
+        lw[q] = Pack2<X>::pack(v0 - e.x, v1 - e.y);
+        const float2 el = Pack2<X>::unpack(lw[q]);
+        e.x += el.x;
+        e.y += el.y;
+      }
+      part = fmaf(0.5f * e.x, 0.5f * e.x, part);
+      part = fmaf(0.5f * e.y, 0.5f * e.y, part);
+    }
+    const uint32_t off = sw128_off(j, kq + 8 * g);
+    *reinterpret_cast<uint4*>(t_hi + off) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+    *reinterpret_cast<uint4*>(t_lo + off) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+  }
+  return part;
+}
+// norm K step of prototype row t: [|p|^2 hi, mid, lo, 1, 1, 1, 0 ...] (zeros for a dead row), two 16-byte pieces
+template <typename X>
+__device__ __forceinline__ void store_proto_norm(unsigned char* t_n, int t, float pn, bool live) {
+  X h, m, l;
+  split3<X>(pn, h, m, l);
+  const uint32_t one = bits16(Fmt<X>::from(1.0f));
+  uint4 a = make_uint4(0u, 0u, 0u, 0u);
+  if (live) a = make_uint4((uint32_t)bits16(h) | ((uint32_t)bits16(m) << 16), (uint32_t)bits16(l) | (one << 16), one | (one << 16), 0u);
+  *reinterpret_cast<uint4*>(t_n + norm_off(t, 0)) = a;
+  *reinterpret_cast<uint4*>(t_n + norm_off(t, 8)) = make_uint4(0u, 0u, 0u, 0u);
+}
+
 // ---------------------------------------------------------------------------------------------
 // Prototype chunks.  The prototypes of every scale are cut into chunks of <= CN rows; the pre-pass writes
 // one packed image per chunk that the main kernels bulk-copy straight into shared memory:
