@@ -513,7 +513,13 @@ def main():
         roof = {"bound": "tensor", "achieved": ph["flops"] / t / 1e12, "peak": pk["tensor_sustained"], "unit": "TFLOP/s", "frac": tensor_frac}
     else:
         roof = {"bound": "hbm", "achieved": ph["bytes"] / t / 1e9, "peak": pk["hbm"], "unit": "GB/s", "frac": hbm_frac}
-    roof.update({"kernel": name, "ms_per_launch": ph["ms"], "peak_source": pk["source"] + " (sustained bf16 / copy)", "traffic": None,
+    traffic = None   # DRAM bytes per launch of the dominant kernel, from the committed ncu --set full capture
+    try:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")) as f:
+            traffic = json.load(f).get("backward" if "backward" in name else "forward")
+    except (OSError, ValueError):
+        pass
+    roof.update({"kernel": name, "ms_per_launch": ph["ms"], "peak_source": pk["source"] + " (sustained bf16 / copy)", "traffic": traffic,
                  "phases_ms": {k: v["ms"] for k, v in phases.items()}, "tensor_frac": tensor_frac, "hbm_frac": hbm_frac})
     out = dict(base)
     out.update({"value": ctx["value"], "ms_per_step": ctx["ms_per_step"], "dtype": args.math + " operands, f32 accumulate",
