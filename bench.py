@@ -363,8 +363,8 @@ def measure_stage2(ctx, args):
 
 
 def measure_c5(ctx, args):
-    """Secondary: the COCO-Stuff head shape of BASELINE.json configs[4] (K=171, P=6840, B=32, 65x65), fused FORWARD
-    only (the tensor-core backward covers K <= 32; larger K runs the fp32 backward).  Tensor-bound shape."""
+    """Secondary: the COCO-Stuff head shape of BASELINE.json configs[4] (K=171, P=6840, B=32, 65x65), fused forward
+    (the headline of this object, tensor-bound) and the backward (class slabs)."""
     sps, ho, dev = ctx["sps"], ctx["ho"], ctx["dev"]
     B, H, W, P, K, S, D = 32, 65, 65, 6840, 171, 4, 64
     g = torch.Generator(device=dev).manual_seed(SEED + 5)
@@ -380,10 +380,23 @@ def measure_c5(ctx, args):
     units = B * H * W * P
     flops = units * (2 * D + 2 * K)
     pk = peaks()
-    return {"workload": f"COCO-Stuff head forward (configs[4] shape): B={B} maps 256x{H}x{W}, P={P}, K={K}, fused mode",
-            "ms": ms, "value": units / (ms * 1e-3), "unit": "positions*prototypes/s (forward only)",
-            "tflops_algorithmic": flops / (ms * 1e-3) / 1e12, "tensor_frac": flops / (ms * 1e-3) / 1e12 / pk["tensor_sustained"],
-            "math": math_name}
+    out = {"workload": f"COCO-Stuff head forward (configs[4] shape): B={B} maps 256x{H}x{W}, P={P}, K={K}, fused mode",
+           "ms": ms, "value": units / (ms * 1e-3), "unit": "positions*prototypes/s (forward only)",
+           "tflops_algorithmic": flops / (ms * 1e-3) / 1e12, "tensor_frac": flops / (ms * 1e-3) / 1e12 / pk["tensor_sustained"],
+           "math": math_name}
+    # the backward of this shape: K = 171 runs the tcgen05 backward as six slabs of <= 32 classes (gamma, dz, dprototypes are
+    # linear in dlogits), each recomputing the distances; reported so the cost is visible
+    try:
+        dl = torch.randn(B * H * W, K, device=dev, generator=g) / (B * H * W)
+        run_b = lambda i: sps.head_backward_raw(z, protos, last_w, cfg, dl, None, None, True, True, True)
+        run_b(0)
+        ms_b = event_ms(run_b, 3)
+        out["backward_ms"] = ms_b
+        out["backward_note"] = "tcgen05 backward in 6 class slabs of <= 32 classes (distances recomputed per slab), dz by atomics"
+        out["fwd_bwd_value"] = units / ((ms + ms_b) * 1e-3)
+    except RuntimeError as e:   # report, do not hide
+        out["backward_error"] = str(e)[:200]
+    return out
 
 
 def PUSH_TC(sps):

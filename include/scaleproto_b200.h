@@ -112,8 +112,9 @@ int sps_head_fwd(const SpsHeadDesc* desc, const float* z, const float* protos, c
  *   module_multiscale.py:242), dact [N,P] or NULL.
  *   dz [B,S*D,H,W] or NULL, dprotos [P,D] or NULL, dlast_w [K,P] or NULL: OVERWRITTEN.
  *   workspace: >= sps_workspace_bytes(desc) bytes, contents undefined on entry and exit.
- * Routing: a tensor-core math mode with last_w, dlogits (and optionally ddist) runs the tcgen05 backward; a gradient
- * through act, a call without last_w/dlogits, or SPS_MATH_FP32 runs the exact-operand CUDA-core kernels. */
+ * Routing: a tensor-core math mode with last_w, dlogits (and optionally ddist) runs the tcgen05 backward (K <= 256; more
+ * than 32 classes run as slabs of 32, the gradients being linear in dlogits); a gradient through act, a call without
+ * last_w/dlogits, K > 256, or SPS_MATH_FP32 runs the exact-operand CUDA-core kernels. */
 int sps_head_bwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w,
                  const float* dlogits, const float* ddist, const float* dact, float* dz, float* dprotos,
                  float* dlast_w, void* workspace, size_t workspace_bytes, void* stream);

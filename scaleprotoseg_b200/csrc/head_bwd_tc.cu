@@ -44,7 +44,7 @@ __device__ __forceinline__ long long gtimer() { long long t; asm volatile("mov.u
 
 constexpr int GROUP_CHUNKS = 3;   // chunks per CTA (TMEM budget)
 constexpr int MAX_GROUPS = 64;
-constexpr int KP_BWD = 32;        // classes padded (this kernel: K <= 32)
+constexpr int KP_BWD = 32;        // classes per launch, padded (wider last layers run as slabs of 32 classes)
 // per chunk: BH 8 KB | BN 2 KB | W3 4 KB | BL 8 KB (lo part of -2p; copied to shared memory only in the split mode)
 constexpr int BIMG = CN * 128 + CN * 32 + CN * 64 + CN * 128;
 constexpr int BOFF_BH = 0, BOFF_BN = CN * 128, BOFF_W3 = CN * 128 + CN * 32, BOFF_BL = CN * 128 + CN * 32 + CN * 64;
@@ -73,6 +73,8 @@ struct BwdParams {
   float* dz;
   float* part_dp;               // [nsplit][P*D]
   float* part_dw;               // [nsplit][K*P]
+  int dl_stride;                // floats between dlogits rows (the launch may cover a slab of <= 32 of the K classes)
+  int dz_acc;                   // 1: dz is accumulated with atomics (several class slabs add into it)
   float* part_cs;               // [nsplit][P]   2/G * column sums of gamma (the 2 p csum term is applied by the reduce)
   int n_tiles;
 };
@@ -181,7 +183,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
   while (g + 1 < gt.n_groups && (int)blockIdx.x >= gt.cta0[g + 1]) ++g;
   const int cta_local = (int)blockIdx.x - gt.cta0[g], ncta = gt.ncta[g];
   const int nch = gt.nch[g], c0 = gt.c0[g], sc = gt.scale[g];
-  const bool multi = gt.multi[g] != 0;
+  const bool multi = gt.multi[g] != 0 || prm.dz_acc != 0;
   const int my_tiles = prm.n_tiles > cta_local ? (prm.n_tiles - 1 - cta_local) / ncta + 1 : 0;
   const int U = my_tiles * nch;
 
@@ -304,7 +306,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
     };
     // raw dlogits row (zeros past the end / past K); scaled by G when it is packed
     auto load_dl = [&](long long n, float (&dl)[KP_BWD]) {
-      const float* src = prm.dlogits + (n < s.N ? n : 0) * s.K;
+      const float* src = prm.dlogits + (n < s.N ? n : 0) * prm.dl_stride;
       const int kl = n < s.N ? s.K : 0;
 #pragma unroll
       for (int k = 0; k < KP_BWD; ++k) dl[k] = k < kl ? __ldg(src + k) : 0.0f;
@@ -583,7 +585,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
 // Fixed order: deterministic.
 __global__ void bwd_reduce_kernel(const float* __restrict__ part1, long long count1, float* __restrict__ out1,
                                   const float* __restrict__ part2, long long count2, float* __restrict__ out2, int nsplit,
-                                  const float* __restrict__ part_cs, const float* __restrict__ protos, int D, int P) {
+                                  const float* __restrict__ part_cs, const float* __restrict__ protos, int D, int P,
+                                  int accumulate_dp) {
   pdl_wait();   // launched while the main kernel drains: its partials are complete (and visible) after this
   long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const float* part = part1;
@@ -615,6 +618,7 @@ __global__ void bwd_reduce_kernel(const float* __restrict__ part1, long long cou
     }
     for (; sp < nsplit; ++sp) c0 += part_cs[(long long)sp * P + p];
     r = fmaf(protos[i], c0 + c1, r);
+    if (accumulate_dp) r += out[i];   // a later class slab adds to the prototypes' gradient of the earlier ones
   }
   out[i] = r;
 }
@@ -677,7 +681,7 @@ static int bwd_nsplit(const tcb::GroupTable& gt) {
 bool head_bwd_tc_supported(const HeadShape& s, int math, const float* last_w, const float* dlogits, const float* ddist,
                            const float* dact) {
   return math != SPS_MATH_FP32 && last_w != nullptr && dlogits != nullptr && dact == nullptr &&
-         s.K <= tcb::KP_BWD && s.D <= 64 && s.D % 8 == 0 && s.N > 0 && s.N < (1ll << 31) && s.P > 0;
+         s.K <= 8 * tcb::KP_BWD && s.D <= 64 && s.D % 8 == 0 && s.N > 0 && s.N < (1ll << 31) && s.P > 0;
 }
 
 size_t head_bwd_tc_workspace(const HeadShape& s) {
@@ -690,9 +694,18 @@ size_t head_bwd_tc_workspace(const HeadShape& s) {
   return 1024 + (size_t)ct.n_chunks * tcb::BIMG + 256 + sizeof(float) * nsplit * ((size_t)s.P * s.D + (size_t)s.K * s.P + (size_t)s.P);
 }
 
+// One launch sequence (pre-pass, main kernel, reduce) over a SLAB of <= KP_BWD classes [k0, k0 + s.K) of the caller's
+// K_total: gamma, dz and dprototypes are linear in dlogits, so a wider last layer is the sum of its slabs (dz by
+// atomics, dprototypes by the reduce kernel's accumulate flag); every dW row belongs to exactly one slab.
+//   s        : the head shape with K = the slab width
+//   last_w   : row k0 of the (K_total x P) last layer;   dlast_w: row k0 of its gradient (or null)
+//   dlogits  : column k0 of the (N x K_total) upstream gradient, rows dl_stride = K_total floats apart
+//   dl_all / dl_all_count : the whole dlogits buffer (scanned for max |.|)
 template <typename X, int NSPLIT>
-static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* protos, const float* last_w, const float* dlogits,
-                           const float* ddist, float* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st) {
+static int launch_bwd_slab(const HeadShape& s, const float* z, const float* protos, const float* last_w, const float* dlogits,
+                           int dl_stride, const float* dl_all, long long dl_all_count, const float* ddist, float* dz,
+                           float* dprotos, float* dlast_w, bool first_slab, bool several_slabs, void* ws, size_t ws_bytes,
+                           cudaStream_t st) {
   tcb::BwdParams prm;
   int rc = build_chunk_table(s, true, &prm.ct);
   if (rc != SPS_OK) return rc;
@@ -715,12 +728,13 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   SPS_CUDA_TRY(cudaMemsetAsync(amax, 0, all_written ? 256 : 256 + part_bytes, st));
   bool any_multi = false;
   for (int g = 0; g < prm.gt.n_groups; ++g) any_multi |= prm.gt.multi[g] != 0;
-  if (dz != nullptr && any_multi) SPS_CUDA_TRY(cudaMemsetAsync(dz, 0, sizeof(float) * (size_t)s.B * s.C * s.HW, st));
+  if (dz != nullptr && first_slab && (any_multi || several_slabs))
+    SPS_CUDA_TRY(cudaMemsetAsync(dz, 0, sizeof(float) * (size_t)s.B * s.C * s.HW, st));
   // one launch: chunk images (n_chunks blocks) + max |dlogits| (the remaining blocks)
   // (the amax blocks also scan the dense ddist map when there is one: enough of them to stream it at HBM rate)
   const int amax_blocks = sm_count() * (ddist != nullptr ? 16 : 1);
-  tcb::bwd_prep_kernel<X, NSPLIT><<<prm.ct.n_chunks + amax_blocks, 256, 0, st>>>(prm.ct, s.D, s.P, s.K, protos, last_w, img, dlogits,
-                                                                                (long long)s.N * s.K, ddist,
+  tcb::bwd_prep_kernel<X, NSPLIT><<<prm.ct.n_chunks + amax_blocks, 256, 0, st>>>(prm.ct, s.D, s.P, s.K, protos, last_w, img, dl_all,
+                                                                                dl_all_count, ddist,
                                                                                 (long long)s.N * s.P, amax);
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
@@ -728,6 +742,8 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
   prm.z = z;
   prm.protos = protos;
   prm.dlogits = dlogits;
+  prm.dl_stride = dl_stride;
+  prm.dz_acc = several_slabs ? 1 : 0;
   prm.ddist = ddist;
   prm.img = img;
   prm.amax_bits = amax;
@@ -750,11 +766,27 @@ static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* prot
     if (c1 + c2 > 0) {
       SPS_CUDA_TRY(launch_pdl(tcb::bwd_reduce_kernel, dim3((unsigned)((c1 + c2 + 255) / 256)), dim3(256), (size_t)0, st,
                               (const float*)part_dp, c1, dprotos, (const float*)part_dw, c2, dlast_w, nsplit,
-                              (const float*)part_cs, protos, s.D, s.P));
+                              (const float*)part_cs, protos, s.D, s.P, first_slab ? 0 : 1));
       count_launch();
     }
   }
   SPS_CUDA_TRY(cudaGetLastError());
+  return SPS_OK;
+}
+
+template <typename X, int NSPLIT>
+static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* protos, const float* last_w, const float* dlogits,
+                           const float* ddist, float* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st) {
+  const int n_slabs = (s.K + tcb::KP_BWD - 1) / tcb::KP_BWD;
+  for (int sl = 0; sl < n_slabs; ++sl) {
+    const int k0 = sl * tcb::KP_BWD;
+    HeadShape ss = s;
+    ss.K = s.K - k0 < tcb::KP_BWD ? s.K - k0 : tcb::KP_BWD;
+    const int rc = launch_bwd_slab<X, NSPLIT>(ss, z, protos, last_w + (size_t)k0 * s.P, dlogits + k0, s.K, dlogits, (long long)s.N * s.K,
+                                              sl == 0 ? ddist : nullptr, dz, dprotos, dlast_w != nullptr ? dlast_w + (size_t)k0 * s.P : nullptr,
+                                              sl == 0, n_slabs > 1, ws, ws_bytes, st);
+    if (rc != SPS_OK) return rc;
+  }
   return SPS_OK;
 }
 

@@ -195,6 +195,8 @@ def test_stage1_golden_tensor_core(built_lib, golden_dir, name, math):
 @pytest.mark.parametrize("math", TC_MATHS)
 @pytest.mark.parametrize("shape", [(2, 9, 7, 228, 19, None), (1, 33, 40, 760, 19, None),
                                    (4, 65, 65, 760, 19, None),   # more tiles than CTAs per scale: every partial slot written
+                                   (1, 12, 11, 320, 40, None),   # 40 classes: two class slabs of the tensor-core backward
+                                   (1, 9, 10, 684, 171, None),   # COCO-Stuff class count: six slabs
                                    (2, 20, 20, 221, 19, [(0, 50), (50, 121), (121, 130), (130, 221)]),
                                    (1, 12, 11, 1100, 7, [(0, 500), (500, 700), (700, 900), (900, 1100)])])
 def test_tensor_core_fwd_bwd_vs_oracle(built_lib, shape, math):
@@ -346,6 +348,7 @@ def test_push_label_values_outside_the_class_range_never_match(built_lib):
 
 @pytest.mark.parametrize("math", TC_MATHS)
 @pytest.mark.parametrize("shape", [(2, 9, 7, 228, 19, None), (1, 33, 40, 760, 19, None),
+                                   (1, 12, 11, 320, 40, None),   # two class slabs: the distance gradient enters once
                                    (2, 20, 20, 221, 19, [(0, 50), (50, 121), (121, 130), (130, 221)])])
 def test_tensor_core_backward_with_distance_gradient(built_lib, shape, math):
     """Stage-1 training step as the reference runs it: the loss reads the logits AND the dense distance map (KLD loss,
