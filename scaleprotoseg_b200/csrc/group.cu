@@ -15,18 +15,53 @@ constexpr int GNT = 512;  // max threads per CTA (the launch uses the (row, clas
 // G_k'[j,q] / members_k'[q] (class blocks J*n_k' / n_k' words apart) collide in a few banks — as global loads they
 // cost one L1 wavefront per lane and dominated the kernel.
 __device__ __forceinline__ int gpad_floats(const HeadShape& s, const SpsGroupDesc& g) { return g.J * s.P + g.Kc; }
+// The thread block is cut into Kc teams (one per class, >= 1 thread each) that copy their class's block of G and of the
+// member list in parallel: no search, no division per element, and the loads of a thread are independent.  (A loop
+// per class with the whole block made 2*Kc dependent round trips to L2 per CTA - 38 at Kc = 19 - and that latency,
+// not the activation traffic, set the kernel time.)
 __device__ __forceinline__ void stage_tables(const HeadShape& s, const SpsGroupDesc& g, float* Gs, int* Ms) {
-  for (int kc = 0; kc < g.Kc; ++kc) {
-    const int off = g.class_off[kc], nk = g.class_off[kc + 1] - off;
-    for (int i = threadIdx.x; i < g.J * nk; i += blockDim.x) Gs[g.J * off + kc + i] = __ldg(g.G + (long long)g.J * off + i);
-    for (int i = threadIdx.x; i < nk; i += blockDim.x) Ms[off + kc + i] = __ldg(g.members + off + i);
+  const int team = blockDim.x / g.Kc > 0 ? blockDim.x / g.Kc : 1;   // threads per class
+  for (int kc = threadIdx.x / team; kc < g.Kc; kc += (blockDim.x + team - 1) / team) {
+    const int off = g.class_off[kc], nk = g.class_off[kc + 1] - off, t = threadIdx.x % team;
+    const float* src = g.G + (long long)g.J * off;
+    float* dst = Gs + g.J * off + kc;
+    for (int i = t; i < g.J * nk; i += team) dst[i] = __ldg(src + i);
+    for (int i = t; i < nk; i += team) Ms[off + kc + i] = __ldg(g.members + off + i);
   }
   __syncthreads();
 }
 
-// gs[m][J*k'+j] for the tile starting at n0 (zero rows beyond N)
-__device__ __forceinline__ void group_tile(const HeadShape& s, const SpsGroupDesc& g, const float* __restrict__ act,
-                                           long long n0, float* gs, const float* Gs, const int* Ms, int Gt) {
+// Rows [n0, n0 + GTM) of the activation map into shared memory As[GTM][P] with 16-byte asynchronous copies (issued
+// before the tables are staged, waited for after).  Gathering the members straight from global memory cost one L1
+// wavefront per lane: the lanes of a warp sit on different classes, i.e. on different sectors of the row.
+__device__ __forceinline__ void stage_rows(const HeadShape& s, const float* __restrict__ act, long long n0, float* As) {
+  const long long left = s.N - n0;
+  const int rows = left < GTM ? (int)left : GTM;
+  if ((s.P & 3) == 0 && (reinterpret_cast<uintptr_t>(act) & 15) == 0) {
+    const int per_row = s.P >> 2, warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nwarp = blockDim.x >> 5;
+    for (int m = warp; m < rows; m += nwarp) {          // one warp per row: consecutive lanes, consecutive 16-byte pieces
+      const float* src = act + (n0 + m) * s.P;
+      const uint32_t dst = (uint32_t)__cvta_generic_to_shared(As + m * s.P);
+      for (int c = lane; c < per_row; c += 32)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst + 16u * c), "l"(src + 4 * c) : "memory");
+    }
+  } else {
+    for (int idx = threadIdx.x; idx < rows * s.P; idx += blockDim.x) As[idx] = __ldg(act + n0 * s.P + idx);
+  }
+  asm volatile("cp.async.commit_group;" ::: "memory");
+}
+__device__ __forceinline__ void wait_rows() {
+  asm volatile("cp.async.wait_all;" ::: "memory");
+  __syncthreads();
+}
+
+// gs[m][J*k'+j] for the tile starting at n0 (zero rows beyond N).  STAGED: the rows are in As (stage_rows).
+// JT: groups per class as a compile-time constant (3 = the reference's num_groups), or 0 = read g.J at run time: with a
+// run-time J the 8-wide unrolled inner loops issue 8 predicated LDS + FFMA per member instead of J.
+template <bool STAGED, int JT>
+__device__ __forceinline__ void group_tile_j(const HeadShape& s, const SpsGroupDesc& g, const float* __restrict__ act,
+                                             long long n0, float* gs, const float* Gs, const int* Ms, int Gt, const float* As) {
+  const int J = JT ? JT : g.J;
   for (int idx = threadIdx.x; idx < GTM * g.Kc; idx += blockDim.x) {
     const int m = idx / g.Kc, kc = idx % g.Kc;
     const long long n = n0 + m;
@@ -35,44 +70,60 @@ __device__ __forceinline__ void group_tile(const HeadShape& s, const SpsGroupDes
 #pragma unroll
     for (int j = 0; j < 8; ++j) sum[j] = 0.f;
     if (n < s.N) {
-      const float* arow = act + n * s.P;
-      const float* Gk = Gs + g.J * off + kc;
+      const float* arow = STAGED ? As + m * s.P : act + n * s.P;
+      const float* Gk = Gs + J * off + kc;
       const int* Mk = Ms + off + kc;
       // batches of 8 members: the 8 activation loads (the only ones that go to DRAM) are in flight together
       int q = 0;
       for (; q + 8 <= nk; q += 8) {
         float a[8];
 #pragma unroll
-        for (int u = 0; u < 8; ++u) a[u] = __ldg(arow + Mk[q + u]);
+        for (int u = 0; u < 8; ++u) a[u] = STAGED ? arow[Mk[q + u]] : __ldg(arow + Mk[q + u]);
 #pragma unroll
         for (int u = 0; u < 8; ++u) {
 #pragma unroll
           for (int j = 0; j < 8; ++j)
-            if (j < g.J) sum[j] = fmaf(a[u], Gk[j * nk + q + u], sum[j]);
+            if (j < J) sum[j] = fmaf(a[u], Gk[j * nk + q + u], sum[j]);
         }
       }
       for (; q < nk; ++q) {
-        const float a = __ldg(arow + Mk[q]);
+        const float a = STAGED ? arow[Mk[q]] : __ldg(arow + Mk[q]);
 #pragma unroll
         for (int j = 0; j < 8; ++j)
-          if (j < g.J) sum[j] = fmaf(a, Gk[j * nk + q], sum[j]);
+          if (j < J) sum[j] = fmaf(a, Gk[j * nk + q], sum[j]);
       }
     }
 #pragma unroll
     for (int j = 0; j < 8; ++j)
-      if (j < g.J) gs[m * Gt + g.J * kc + j] = n < s.N ? expf(sum[j]) : 0.f;
+      if (j < J) gs[m * Gt + J * kc + j] = n < s.N ? expf(sum[j]) : 0.f;
   }
 }
 
+template <bool STAGED>
+__device__ __forceinline__ void group_tile(const HeadShape& s, const SpsGroupDesc& g, const float* __restrict__ act,
+                                           long long n0, float* gs, const float* Gs, const int* Ms, int Gt, const float* As) {
+  if (g.J == 3) group_tile_j<STAGED, 3>(s, g, act, n0, gs, Gs, Ms, Gt, As);
+  else group_tile_j<STAGED, 0>(s, g, act, n0, gs, Gs, Ms, Gt, As);
+}
+
+// shared memory: [rows As: GTM*P floats, 16-byte aligned, STAGED only][gs][Gs][Ms]
+template <bool STAGED>
 __global__ void __launch_bounds__(GNT) group_fwd_kernel(HeadShape s, SpsGroupDesc g, const float* __restrict__ act,
                                                          float* __restrict__ groups, float* __restrict__ logits) {
-  extern __shared__ __align__(16) float gs[];
+  extern __shared__ __align__(16) float smem_f[];
   const int Gt = g.J * g.Kc;
+  float* As = smem_f;
+  float* gs = smem_f + (STAGED ? GTM * s.P : 0);
   float* Gs = gs + GTM * Gt;
   int* Ms = reinterpret_cast<int*>(Gs + gpad_floats(s, g));
-  stage_tables(s, g, Gs, Ms);
+  float* Ws = reinterpret_cast<float*>(Ms + s.P + g.Kc);   // last_layer_group [K][Gt]
   const long long n0 = (long long)blockIdx.x * GTM;
-  group_tile(s, g, act, n0, gs, Gs, Ms, Gt);
+  if (STAGED) stage_rows(s, act, n0, As);
+  if (logits != nullptr)
+    for (int i = threadIdx.x; i < s.K * Gt; i += blockDim.x) Ws[i] = __ldg(g.Wg + i);
+  stage_tables(s, g, Gs, Ms);
+  if (STAGED) wait_rows();
+  group_tile<STAGED>(s, g, act, n0, gs, Gs, Ms, Gt, As);
   __syncthreads();
   if (groups != nullptr) {
     for (int idx = threadIdx.x; idx < GTM * Gt; idx += blockDim.x) {
@@ -85,13 +136,21 @@ __global__ void __launch_bounds__(GNT) group_fwd_kernel(HeadShape s, SpsGroupDes
       const int m = idx / s.K, k = idx % s.K;
       const long long n = n0 + m;
       if (n >= s.N) continue;
-      const float* w = g.Wg + (long long)k * Gt;
-      float a = 0.f;
-      for (int gg = 0; gg < Gt; ++gg) a = fmaf(gs[m * Gt + gg], __ldg(w + gg), a);
-      logits[n * s.K + k] = a;
+      const float* w = Ws + k * Gt;
+      const float* grow = gs + m * Gt;
+      float a0 = 0.f, a1 = 0.f;
+      int gg = 0;
+      for (; gg + 2 <= Gt; gg += 2) {
+        a0 = fmaf(grow[gg], w[gg], a0);
+        a1 = fmaf(grow[gg + 1], w[gg + 1], a1);
+      }
+      if (gg < Gt) a0 = fmaf(grow[gg], w[gg], a0);
+      logits[n * s.K + k] = a0 + a1;
     }
   }
 }
+
+constexpr size_t kGroupStagedMax = 75 * 1024;   // staged rows only while three CTAs per SM fit (227 KB / 3)
 
 static int group_threads(const SpsGroupDesc& g) {
   int t = (GTM * g.Kc + 31) / 32 * 32;   // one (row, class) pair per thread in a single round
@@ -102,11 +161,19 @@ int launch_group_fwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
                      cudaStream_t st) {
   if (s.N == 0 || g.Kc == 0) return SPS_OK;
   const int Gt = g.J * g.Kc;
-  size_t smem = sizeof(float) * ((size_t)GTM * Gt + (size_t)g.J * s.P + g.Kc + s.P + g.Kc);
+  size_t smem = sizeof(float) * ((size_t)GTM * Gt + (size_t)g.J * s.P + g.Kc + s.P + g.Kc + (size_t)s.K * Gt);
   SPS_REQUIRE(smem <= 200 * 1024, SPS_ERR_UNSUPPORTED, "group head: J*Kc=%d, J*P=%d need %zu bytes of shared memory", Gt, g.J * s.P, smem);
-  SPS_CUDA_TRY(cudaFuncSetAttribute(group_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  const size_t rows_bytes = sizeof(float) * (size_t)GTM * s.P;
+  const bool staged = smem + rows_bytes <= kGroupStagedMax;   // three CTAs per SM still fit
   long long tiles = (s.N + GTM - 1) / GTM;
-  group_fwd_kernel<<<(unsigned)tiles, group_threads(g), smem, st>>>(s, g, act, groups, logits);
+  if (staged) {
+    smem += rows_bytes;
+    SPS_CUDA_TRY(cudaFuncSetAttribute(group_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    group_fwd_kernel<true><<<(unsigned)tiles, group_threads(g), smem, st>>>(s, g, act, groups, logits);
+  } else {
+    SPS_CUDA_TRY(cudaFuncSetAttribute(group_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    group_fwd_kernel<false><<<(unsigned)tiles, group_threads(g), smem, st>>>(s, g, act, groups, logits);
+  }
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;
@@ -114,6 +181,7 @@ int launch_group_fwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
 
 // Backward pass 1: recompute groups, dpre = (dlogits Wg + dgroups) * groups, dact; spill groups and
 // dpre to the workspace for the two reductions over n.
+template <bool STAGED>
 __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGroupDesc g, const float* __restrict__ act,
                                                              const float* __restrict__ dlogits,
                                                              const float* __restrict__ dgroups,
@@ -121,13 +189,22 @@ __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGrou
                                                              float* __restrict__ ws_dpre) {
   extern __shared__ __align__(16) float smem[];
   const int Gt = g.J * g.Kc;
-  float* gs = smem;
-  float* dps = smem + GTM * Gt;
-  float* Gs = smem + 2 * GTM * Gt;
+  float* As = smem;
+  float* gs = smem + (STAGED ? GTM * s.P : 0);
+  float* dps = gs + GTM * Gt;
+  float* Gs = gs + 2 * GTM * Gt;
   int* Ms = reinterpret_cast<int*>(Gs + gpad_floats(s, g));
-  stage_tables(s, g, Gs, Ms);
+  float* Ws = reinterpret_cast<float*>(Ms + s.P + g.Kc);   // last_layer_group [K][Gt]
+  float* dls = Ws + s.K * Gt;                              // dlogits rows of the tile [GTM][K]
   const long long n0 = (long long)blockIdx.x * GTM;
-  group_tile(s, g, act, n0, gs, Gs, Ms, Gt);
+  if (STAGED) stage_rows(s, act, n0, As);
+  if (dlogits != nullptr) {
+    for (int i = threadIdx.x; i < s.K * Gt; i += blockDim.x) Ws[i] = __ldg(g.Wg + i);
+    for (int i = threadIdx.x; i < GTM * s.K; i += blockDim.x) dls[i] = n0 * s.K + i < s.N * s.K ? __ldg(dlogits + n0 * s.K + i) : 0.f;
+  }
+  stage_tables(s, g, Gs, Ms);
+  if (STAGED) wait_rows();
+  group_tile<STAGED>(s, g, act, n0, gs, Gs, Ms, Gt, As);
   __syncthreads();
   for (int idx = threadIdx.x; idx < GTM * Gt; idx += blockDim.x) {
     const int m = idx / Gt, gg = idx % Gt;
@@ -136,7 +213,7 @@ __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGrou
     if (n < s.N) {
       float up = dgroups != nullptr ? __ldg(dgroups + n * Gt + gg) : 0.f;
       if (dlogits != nullptr)
-        for (int k = 0; k < s.K; ++k) up = fmaf(__ldg(dlogits + n * s.K + k), __ldg(g.Wg + (long long)k * Gt + gg), up);
+        for (int k = 0; k < s.K; ++k) up = fmaf(dls[m * s.K + k], Ws[k * Gt + gg], up);
       v = up * gs[idx];
       ws_groups[n * Gt + gg] = gs[idx];
       ws_dpre[n * Gt + gg] = v;
@@ -145,18 +222,29 @@ __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGrou
   }
   __syncthreads();
   if (dact != nullptr) {
-    for (int idx = threadIdx.x; idx < GTM * s.P; idx += blockDim.x) {
-      const int m = idx / s.P, p = idx % s.P;
-      const long long n = n0 + m;
-      if (n >= s.N) continue;
-      const int kc = g.proto_slot[p], col = g.proto_col[p];
-      float a = 0.f;
+    // a thread owns prototypes p = tid, tid + blockDim, ...: its class slot and its J projection weights are fetched
+    // once and reused for the 16 rows (a flat (row, prototype) loop paid a division, four index loads and J weight
+    // loads per ELEMENT)
+    for (int p = threadIdx.x; p < s.P; p += blockDim.x) {
+      const int kc = g.proto_slot[p];
+      float w[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j) w[j] = 0.f;
       if (kc >= 0) {
-        const int off = g.class_off[kc], nk = g.class_off[kc + 1] - off;
-        const float* Gk = g.G + (long long)g.J * off;
-        for (int j = 0; j < g.J; ++j) a = fmaf(dps[m * Gt + g.J * kc + j], __ldg(Gk + j * nk + col), a);
+        const int off = g.class_off[kc], nk = g.class_off[kc + 1] - off, col = g.proto_col[p];
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (j < g.J) w[j] = Gs[g.J * off + kc + j * nk + col];
       }
-      dact[n * s.P + p] = a;
+      const float* dp = dps + (kc >= 0 ? g.J * kc : 0);
+      for (int m = 0; m < GTM; ++m) {
+        if (n0 + m >= s.N) break;
+        float a = 0.f;
+#pragma unroll
+        for (int j = 0; j < 8; ++j)
+          if (j < g.J) a = fmaf(dp[m * Gt + j], w[j], a);
+        dact[(n0 + m) * s.P + p] = kc >= 0 ? a : 0.f;
+      }
     }
   }
 }
@@ -244,13 +332,20 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
     if (dact != nullptr && s.N > 0) SPS_CUDA_TRY(cudaMemsetAsync(dact, 0, sizeof(float) * (size_t)s.N * s.P, st));
     return SPS_OK;
   }
-  size_t smem = sizeof(float) * (2 * (size_t)GTM * Gt + (size_t)g.J * s.P + g.Kc + s.P + g.Kc);
+  size_t smem = sizeof(float) * (2 * (size_t)GTM * Gt + (size_t)g.J * s.P + g.Kc + s.P + g.Kc + (size_t)s.K * Gt + (size_t)GTM * s.K);
   SPS_REQUIRE(smem <= 200 * 1024, SPS_ERR_UNSUPPORTED, "group head: J*Kc=%d, J*P=%d need %zu bytes of shared memory", Gt, g.J * s.P, smem);
   float* ws_groups = ws;
   float* ws_dpre = ws + (size_t)s.N * Gt;
-  SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_pos_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
   long long tiles = (s.N + GTM - 1) / GTM;
-  group_bwd_pos_kernel<<<(unsigned)tiles, group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre);
+  const size_t rows_bytes = sizeof(float) * (size_t)GTM * s.P;
+  if (smem + rows_bytes <= kGroupStagedMax) {
+    smem += rows_bytes;
+    SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_pos_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    group_bwd_pos_kernel<true><<<(unsigned)tiles, group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre);
+  } else {
+    SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_pos_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    group_bwd_pos_kernel<false><<<(unsigned)tiles, group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre);
+  }
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   if (dG != nullptr) {
