@@ -287,39 +287,59 @@ __global__ void __launch_bounds__(256) group_bwd_dG_kernel(HeadShape s, SpsGroup
 
 // dWg[k,g] += sum_n dlogits[n,k] * groups[n,g] over this CTA's slice of rows.  The two row tiles are staged in shared
 // memory (coalesced), every thread accumulates its (k,g) outputs over the slice, one atomicAdd per output and CTA.
-constexpr int GWR = 64;  // rows per staging step
-__global__ void __launch_bounds__(256) group_bwd_dWg_kernel(HeadShape s, int Gt, const float* __restrict__ dlogits,
+constexpr int GWR = 64;   // rows per staging step
+constexpr int GWT = 256;  // threads = (4 classes x 2 groups) output tiles per CTA
+// Each thread keeps a 4 (classes) x 2 (groups) tile of dWg in registers: per staged row one 16-byte and one 8-byte
+// shared-memory read feed 8 FMAs (one output per thread needed two reads per FMA and the kernel sat on the LSU).
+// Rows are staged zero-padded to Kp = 4*ceil(K/4) and Gp = 2*ceil(Gt/2) floats.
+__global__ void __launch_bounds__(GWT) group_bwd_dWg_kernel(HeadShape s, int Gt, int gwr, const float* __restrict__ dlogits,
                                                             const float* __restrict__ ws_groups, float* __restrict__ dWg) {
-  extern __shared__ __align__(16) float sm[];   // dl [GWR][K] | groups [GWR][Gt]
+  extern __shared__ __align__(16) float sm[];   // dl [gwr][Kp] | groups [gwr][Gp]   (gwr <= GWR rows per staging step)
+  const int Kt = (s.K + 3) >> 2, Gh = (Gt + 1) >> 1, Kp = Kt << 2, Gp = Gh << 1;
   float* dls = sm;
-  float* grs = sm + GWR * s.K;
+  float* grs = sm + gwr * Kp;
   const long long per = (s.N + gridDim.x - 1) / gridDim.x;
   const long long lo = per * blockIdx.x, hi = min(s.N, lo + per);
-  const int n_out = s.K * Gt;
-  float acc[8];
+  const int tile = blockIdx.y * GWT + threadIdx.x;
+  const bool live = tile < Kt * Gh;
+  const int kt = live ? tile / Gh : 0, g2 = live ? tile - kt * Gh : 0;
+  float acc[4][2];
 #pragma unroll
-  for (int i = 0; i < 8; ++i) acc[i] = 0.f;
-  for (long long r0 = lo; r0 < hi; r0 += GWR) {
-    const int rows = (int)min((long long)GWR, hi - r0);
+  for (int i = 0; i < 4; ++i) acc[i][0] = acc[i][1] = 0.f;
+  for (long long r0 = lo; r0 < hi; r0 += gwr) {
+    const int rows = (int)min((long long)gwr, hi - r0);
     __syncthreads();
-    for (int i = threadIdx.x; i < rows * s.K; i += blockDim.x) dls[i] = __ldg(dlogits + r0 * s.K + i);
-    for (int i = threadIdx.x; i < rows * Gt; i += blockDim.x) grs[i] = __ldg(ws_groups + r0 * Gt + i);
+    for (int i = threadIdx.x; i < rows * Kp; i += blockDim.x) {
+      const int m = i / Kp, k = i - m * Kp;
+      dls[i] = k < s.K ? __ldg(dlogits + (r0 + m) * s.K + k) : 0.f;
+    }
+    for (int i = threadIdx.x; i < rows * Gp; i += blockDim.x) {
+      const int m = i / Gp, gg = i - m * Gp;
+      grs[i] = gg < Gt ? __ldg(ws_groups + (r0 + m) * Gt + gg) : 0.f;
+    }
     __syncthreads();
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int o = (blockIdx.y * 8 + i) * blockDim.x + threadIdx.x;
-      if (o < n_out) {
-        const int k = o / Gt, gg = o - k * Gt;
-        float a = acc[i];
-        for (int m = 0; m < rows; ++m) a = fmaf(dls[m * s.K + k], grs[m * Gt + gg], a);
-        acc[i] = a;
+    if (live) {
+      const float4* dp = reinterpret_cast<const float4*>(dls) + kt;
+      const float2* gp = reinterpret_cast<const float2*>(grs) + g2;
+#pragma unroll 4
+      for (int m = 0; m < rows; ++m) {
+        const float4 d = dp[m * Kt];
+        const float2 gv = gp[m * Gh];
+        acc[0][0] = fmaf(d.x, gv.x, acc[0][0]), acc[0][1] = fmaf(d.x, gv.y, acc[0][1]);
+        acc[1][0] = fmaf(d.y, gv.x, acc[1][0]), acc[1][1] = fmaf(d.y, gv.y, acc[1][1]);
+        acc[2][0] = fmaf(d.z, gv.x, acc[2][0]), acc[2][1] = fmaf(d.z, gv.y, acc[2][1]);
+        acc[3][0] = fmaf(d.w, gv.x, acc[3][0]), acc[3][1] = fmaf(d.w, gv.y, acc[3][1]);
       }
     }
   }
+  if (live && lo < hi) {
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int o = (blockIdx.y * 8 + i) * blockDim.x + threadIdx.x;
-    if (o < n_out && lo < hi) atomicAdd(dWg + o, acc[i]);
+    for (int i = 0; i < 4; ++i)
+#pragma unroll
+      for (int j = 0; j < 2; ++j) {
+        const int k = 4 * kt + i, gg = 2 * g2 + j;
+        if (k < s.K && gg < Gt) atomicAdd(dWg + (long long)k * Gt + gg, acc[i][j]);
+      }
   }
 }
 
@@ -359,11 +379,18 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
     SPS_CUDA_TRY(cudaGetLastError());
   }
   if (dWg != nullptr && dlogits != nullptr) {
-    long long wsplit = (s.N + 4 * GWR - 1) / (4 * GWR);     // >= 256 rows per CTA
-    if (wsplit > 4LL * sm_count()) wsplit = 4LL * sm_count();
+    const int Kt = (s.K + 3) / 4, Gh = (Gt + 1) / 2;
+    const unsigned ny = (unsigned)((Kt * Gh + GWT - 1) / GWT);              // y: chunks of 256 output tiles
+    long long wsplit = (s.N + 2 * GWR - 1) / (2 * GWR);                      // >= 128 rows per CTA
+    const long long cap = (4LL * sm_count() + ny - 1) / ny;                  // about four CTAs per SM in all
+    if (wsplit > cap) wsplit = cap;
     if (wsplit < 1) wsplit = 1;
-    dim3 grid((unsigned)wsplit, (unsigned)((s.K * Gt + 8 * 256 - 1) / (8 * 256)));   // y: chunks of 2048 outputs
-    group_bwd_dWg_kernel<<<grid, 256, sizeof(float) * GWR * (s.K + Gt), st>>>(s, Gt, dlogits, ws_groups, dWg);
+    dim3 grid((unsigned)wsplit, ny);
+    const size_t row_bytes = sizeof(float) * (size_t)(4 * Kt + 2 * Gh);
+    int gwr = GWR;                                                           // fewer rows per step for wide heads (COCO-Stuff)
+    while (gwr > 8 && gwr * row_bytes > 96 * 1024) gwr >>= 1;
+    SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_dWg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(gwr * row_bytes)));
+    group_bwd_dWg_kernel<<<grid, GWT, gwr * row_bytes, st>>>(s, Gt, gwr, dlogits, ws_groups, dWg);
     count_launch();
     SPS_CUDA_TRY(cudaGetLastError());
   }

@@ -8,3 +8,5 @@ ncu --set full --clock-control none --import-source on -k regex:head_bwd_tc_kern
 ncu --set full --clock-control none --import-source on -k regex:head_fwd_tc_kernel -s 3 -c 1 -f -o gpurun_out/r1f_fwd_full python scratch/quick.py 4 fwd > gpurun_out/r1f_ncufwd.log 2>&1
 ncu --set full --clock-control none --import-source on -k regex:push_scan_tc_kernel -s 3 -c 1 -f -o gpurun_out/r1f_push_full python scratch/quick.py 4 push > gpurun_out/r1f_ncupush.log 2>&1
 tail -2 gpurun_out/r1f_tests.log; tail -2 gpurun_out/r1f_smoke.log; ls -la gpurun_out/*.ncu-rep
+timeout 60 scratch/mma_rate > gpurun_out/r1f_probe_mma_rate.txt 2>&1
+timeout 60 scratch/xu_probe > gpurun_out/r1f_probe_xu.txt 2>&1
