@@ -8,6 +8,10 @@
 namespace sps {
 
 constexpr int GTM = 16;   // positions per CTA
+#ifndef SPS_GROUP_TPB
+#define SPS_GROUP_TPB 2
+#endif
+constexpr int GTPB = SPS_GROUP_TPB;   // consecutive 16-position tiles per CTA (tables staged once per CTA)
 constexpr int GNT = 512;  // max threads per CTA (the launch uses the (row, class) pair count rounded up to a warp)
 
 // Per-CTA shared copies of the packed projections and of the member lists, each class block padded by one word:
@@ -117,36 +121,43 @@ __global__ void __launch_bounds__(GNT) group_fwd_kernel(HeadShape s, SpsGroupDes
   float* Gs = gs + GTM * Gt;
   int* Ms = reinterpret_cast<int*>(Gs + gpad_floats(s, g));
   float* Ws = reinterpret_cast<float*>(Ms + s.P + g.Kc);   // last_layer_group [K][Gt]
-  const long long n0 = (long long)blockIdx.x * GTM;
+  // a CTA walks GTPB consecutive tiles: the tables are staged once, the rows of the first tile fly meanwhile
+  long long n0 = (long long)blockIdx.x * GTPB * GTM;
   if (STAGED) stage_rows(s, act, n0, As);
   if (logits != nullptr)
     for (int i = threadIdx.x; i < s.K * Gt; i += blockDim.x) Ws[i] = __ldg(g.Wg + i);
   stage_tables(s, g, Gs, Ms);
-  if (STAGED) wait_rows();
-  group_tile<STAGED>(s, g, act, n0, gs, Gs, Ms, Gt, As);
-  __syncthreads();
-  if (groups != nullptr) {
-    for (int idx = threadIdx.x; idx < GTM * Gt; idx += blockDim.x) {
-      const long long n = n0 + idx / Gt;
-      if (n < s.N) groups[n * Gt + idx % Gt] = gs[idx];
+  for (int t = 0; t < GTPB && n0 < s.N; ++t, n0 += GTM) {
+    if (STAGED) {
+      if (t > 0) stage_rows(s, act, n0, As);
+      wait_rows();
     }
-  }
-  if (logits != nullptr) {
-    for (int idx = threadIdx.x; idx < GTM * s.K; idx += blockDim.x) {
-      const int m = idx / s.K, k = idx % s.K;
-      const long long n = n0 + m;
-      if (n >= s.N) continue;
-      const float* w = Ws + k * Gt;
-      const float* grow = gs + m * Gt;
-      float a0 = 0.f, a1 = 0.f;
-      int gg = 0;
-      for (; gg + 2 <= Gt; gg += 2) {
-        a0 = fmaf(grow[gg], w[gg], a0);
-        a1 = fmaf(grow[gg + 1], w[gg + 1], a1);
+    group_tile<STAGED>(s, g, act, n0, gs, Gs, Ms, Gt, As);
+    __syncthreads();
+    if (groups != nullptr) {
+      for (int idx = threadIdx.x; idx < GTM * Gt; idx += blockDim.x) {
+        const long long n = n0 + idx / Gt;
+        if (n < s.N) groups[n * Gt + idx % Gt] = gs[idx];
       }
-      if (gg < Gt) a0 = fmaf(grow[gg], w[gg], a0);
-      logits[n * s.K + k] = a0 + a1;
     }
+    if (logits != nullptr) {
+      for (int idx = threadIdx.x; idx < GTM * s.K; idx += blockDim.x) {
+        const int m = idx / s.K, k = idx % s.K;
+        const long long n = n0 + m;
+        if (n >= s.N) continue;
+        const float* w = Ws + k * Gt;
+        const float* grow = gs + m * Gt;
+        float a0 = 0.f, a1 = 0.f;
+        int gg = 0;
+        for (; gg + 2 <= Gt; gg += 2) {
+          a0 = fmaf(grow[gg], w[gg], a0);
+          a1 = fmaf(grow[gg + 1], w[gg + 1], a1);
+        }
+        if (gg < Gt) a0 = fmaf(grow[gg], w[gg], a0);
+        logits[n * s.K + k] = a0 + a1;
+      }
+    }
+    __syncthreads();   // gs and As are rewritten by the next tile
   }
 }
 
@@ -169,10 +180,10 @@ int launch_group_fwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
   if (staged) {
     smem += rows_bytes;
     SPS_CUDA_TRY(cudaFuncSetAttribute(group_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    group_fwd_kernel<true><<<(unsigned)tiles, group_threads(g), smem, st>>>(s, g, act, groups, logits);
+    group_fwd_kernel<true><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, groups, logits);
   } else {
     SPS_CUDA_TRY(cudaFuncSetAttribute(group_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    group_fwd_kernel<false><<<(unsigned)tiles, group_threads(g), smem, st>>>(s, g, act, groups, logits);
+    group_fwd_kernel<false><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, groups, logits);
   }
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
@@ -196,56 +207,62 @@ __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGrou
   int* Ms = reinterpret_cast<int*>(Gs + gpad_floats(s, g));
   float* Ws = reinterpret_cast<float*>(Ms + s.P + g.Kc);   // last_layer_group [K][Gt]
   float* dls = Ws + s.K * Gt;                              // dlogits rows of the tile [GTM][K]
-  const long long n0 = (long long)blockIdx.x * GTM;
+  long long n0 = (long long)blockIdx.x * GTPB * GTM;
   if (STAGED) stage_rows(s, act, n0, As);
-  if (dlogits != nullptr) {
+  if (dlogits != nullptr)
     for (int i = threadIdx.x; i < s.K * Gt; i += blockDim.x) Ws[i] = __ldg(g.Wg + i);
-    for (int i = threadIdx.x; i < GTM * s.K; i += blockDim.x) dls[i] = n0 * s.K + i < s.N * s.K ? __ldg(dlogits + n0 * s.K + i) : 0.f;
-  }
   stage_tables(s, g, Gs, Ms);
-  if (STAGED) wait_rows();
-  group_tile<STAGED>(s, g, act, n0, gs, Gs, Ms, Gt, As);
-  __syncthreads();
-  for (int idx = threadIdx.x; idx < GTM * Gt; idx += blockDim.x) {
-    const int m = idx / Gt, gg = idx % Gt;
-    const long long n = n0 + m;
-    float v = 0.f;
-    if (n < s.N) {
-      float up = dgroups != nullptr ? __ldg(dgroups + n * Gt + gg) : 0.f;
-      if (dlogits != nullptr)
-        for (int k = 0; k < s.K; ++k) up = fmaf(dls[m * s.K + k], Ws[k * Gt + gg], up);
-      v = up * gs[idx];
-      ws_groups[n * Gt + gg] = gs[idx];
-      ws_dpre[n * Gt + gg] = v;
+  for (int t = 0; t < GTPB && n0 < s.N; ++t, n0 += GTM) {
+    if (dlogits != nullptr)
+      for (int i = threadIdx.x; i < GTM * s.K; i += blockDim.x) dls[i] = n0 * s.K + i < s.N * s.K ? __ldg(dlogits + n0 * s.K + i) : 0.f;
+    if (STAGED) {
+      if (t > 0) stage_rows(s, act, n0, As);
+      wait_rows();
     }
-    dps[idx] = v;
-  }
-  __syncthreads();
-  if (dact != nullptr) {
-    // a thread owns prototypes p = tid, tid + blockDim, ...: its class slot and its J projection weights are fetched
-    // once and reused for the 16 rows (a flat (row, prototype) loop paid a division, four index loads and J weight
-    // loads per ELEMENT)
-    for (int p = threadIdx.x; p < s.P; p += blockDim.x) {
-      const int kc = g.proto_slot[p];
-      float w[8];
-#pragma unroll
-      for (int j = 0; j < 8; ++j) w[j] = 0.f;
-      if (kc >= 0) {
-        const int off = g.class_off[kc], nk = g.class_off[kc + 1] - off, col = g.proto_col[p];
-#pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (j < g.J) w[j] = Gs[g.J * off + kc + j * nk + col];
+    group_tile<STAGED>(s, g, act, n0, gs, Gs, Ms, Gt, As);
+    __syncthreads();
+    for (int idx = threadIdx.x; idx < GTM * Gt; idx += blockDim.x) {
+      const int m = idx / Gt, gg = idx % Gt;
+      const long long n = n0 + m;
+      float v = 0.f;
+      if (n < s.N) {
+        float up = dgroups != nullptr ? __ldg(dgroups + n * Gt + gg) : 0.f;
+        if (dlogits != nullptr)
+          for (int k = 0; k < s.K; ++k) up = fmaf(dls[m * s.K + k], Ws[k * Gt + gg], up);
+        v = up * gs[idx];
+        ws_groups[n * Gt + gg] = gs[idx];
+        ws_dpre[n * Gt + gg] = v;
       }
-      const float* dp = dps + (kc >= 0 ? g.J * kc : 0);
-      for (int m = 0; m < GTM; ++m) {
-        if (n0 + m >= s.N) break;
-        float a = 0.f;
+      dps[idx] = v;
+    }
+    __syncthreads();
+    if (dact != nullptr) {
+      // a thread owns prototypes p = tid, tid + blockDim, ...: its class slot and its J projection weights are fetched
+      // once and reused for the 16 rows (a flat (row, prototype) loop paid a division, four index loads and J weight
+      // loads per ELEMENT)
+      for (int p = threadIdx.x; p < s.P; p += blockDim.x) {
+        const int kc = g.proto_slot[p];
+        float w[8];
 #pragma unroll
-        for (int j = 0; j < 8; ++j)
-          if (j < g.J) a = fmaf(dp[m * Gt + j], w[j], a);
-        dact[(n0 + m) * s.P + p] = kc >= 0 ? a : 0.f;
+        for (int j = 0; j < 8; ++j) w[j] = 0.f;
+        if (kc >= 0) {
+          const int off = g.class_off[kc], nk = g.class_off[kc + 1] - off, col = g.proto_col[p];
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (j < g.J) w[j] = Gs[g.J * off + kc + j * nk + col];
+        }
+        const float* dp = dps + (kc >= 0 ? g.J * kc : 0);
+        for (int m = 0; m < GTM; ++m) {
+          if (n0 + m >= s.N) break;
+          float a = 0.f;
+#pragma unroll
+          for (int j = 0; j < 8; ++j)
+            if (j < g.J) a = fmaf(dp[m * Gt + j], w[j], a);
+          dact[(n0 + m) * s.P + p] = kc >= 0 ? a : 0.f;
+        }
       }
     }
+    __syncthreads();   // gs, dps, dls and As are rewritten by the next tile
   }
 }
 
@@ -361,10 +378,10 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
   if (smem + rows_bytes <= kGroupStagedMax) {
     smem += rows_bytes;
     SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_pos_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    group_bwd_pos_kernel<true><<<(unsigned)tiles, group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre);
+    group_bwd_pos_kernel<true><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre);
   } else {
     SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_pos_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    group_bwd_pos_kernel<false><<<(unsigned)tiles, group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre);
+    group_bwd_pos_kernel<false><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre);
   }
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
