@@ -29,10 +29,14 @@ __device__ __forceinline__ void stage_tables(const HeadShape& s, const SpsGroupD
     const int off = g.class_off[kc], nk = g.class_off[kc + 1] - off, t = threadIdx.x % team;
     const float* src = g.G + (long long)g.J * off;
     float* dst = Gs + g.J * off + kc;
-    for (int i = t; i < g.J * nk; i += team) dst[i] = __ldg(src + i);
-    for (int i = t; i < nk; i += team) Ms[off + kc + i] = __ldg(g.members + off + i);
+    // 4-byte asynchronous copies (the padded destination is not 16-byte aligned): no register staging, and they
+    // complete together with the activation rows (wait_rows)
+    for (int i = t; i < g.J * nk; i += team)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(dst + i)), "l"(src + i) : "memory");
+    for (int i = t; i < nk; i += team)
+      asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((uint32_t)__cvta_generic_to_shared(Ms + off + kc + i)),
+                   "l"(g.members + off + i) : "memory");
   }
-  __syncthreads();
 }
 
 // Rows [n0, n0 + GTM) of the activation map into shared memory As[GTM][P] with 16-byte asynchronous copies (issued
@@ -128,17 +132,15 @@ __global__ void __launch_bounds__(GNT) group_fwd_kernel(HeadShape s, SpsGroupDes
     for (int i = threadIdx.x; i < s.K * Gt; i += blockDim.x) Ws[i] = __ldg(g.Wg + i);
   stage_tables(s, g, Gs, Ms);
   for (int t = 0; t < GTPB && n0 < s.N; ++t, n0 += GTM) {
-    if (STAGED) {
-      if (t > 0) stage_rows(s, act, n0, As);
-      wait_rows();
-    }
+    if (STAGED && t > 0) stage_rows(s, act, n0, As);
+    if (STAGED || t == 0) wait_rows();
     group_tile<STAGED>(s, g, act, n0, gs, Gs, Ms, Gt, As);
     __syncthreads();
-    if (groups != nullptr) {
-      for (int idx = threadIdx.x; idx < GTM * Gt; idx += blockDim.x) {
-        const long long n = n0 + idx / Gt;
-        if (n < s.N) groups[n * Gt + idx % Gt] = gs[idx];
-      }
+    if (groups != nullptr) {   // the tile's rows are one contiguous range of the (N x Gt) output
+      const long long left = s.N - n0;
+      const int cnt = (left < GTM ? (int)left : GTM) * Gt;
+      float* dst = groups + n0 * Gt;
+      for (int idx = threadIdx.x; idx < cnt; idx += blockDim.x) dst[idx] = gs[idx];
     }
     if (logits != nullptr) {
       for (int idx = threadIdx.x; idx < GTM * s.K; idx += blockDim.x) {
@@ -215,10 +217,9 @@ __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGrou
   for (int t = 0; t < GTPB && n0 < s.N; ++t, n0 += GTM) {
     if (dlogits != nullptr)
       for (int i = threadIdx.x; i < GTM * s.K; i += blockDim.x) dls[i] = n0 * s.K + i < s.N * s.K ? __ldg(dlogits + n0 * s.K + i) : 0.f;
-    if (STAGED) {
-      if (t > 0) stage_rows(s, act, n0, As);
-      wait_rows();
-    }
+    if (STAGED && t > 0) stage_rows(s, act, n0, As);
+    __syncthreads();           // the dlogits tile
+    if (STAGED || t == 0) wait_rows();
     group_tile<STAGED>(s, g, act, n0, gs, Gs, Ms, Gt, As);
     __syncthreads();
     for (int idx = threadIdx.x; idx < GTM * Gt; idx += blockDim.x) {
