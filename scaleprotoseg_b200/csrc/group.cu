@@ -117,18 +117,19 @@ __device__ __forceinline__ void group_tile(const HeadShape& s, const SpsGroupDes
 // shared memory: [rows As: GTM*P floats, 16-byte aligned, STAGED only][gs][Gs][Ms]
 template <bool STAGED>
 __global__ void __launch_bounds__(GNT) group_fwd_kernel(HeadShape s, SpsGroupDesc g, const float* __restrict__ act,
-                                                         float* __restrict__ groups, float* __restrict__ logits) {
+                                                         float* __restrict__ groups, float* __restrict__ logits, int ws_smem) {
   extern __shared__ __align__(16) float smem_f[];
   const int Gt = g.J * g.Kc;
   float* As = smem_f;
   float* gs = smem_f + (STAGED ? GTM * s.P : 0);
   float* Gs = gs + GTM * Gt;
   int* Ms = reinterpret_cast<int*>(Gs + gpad_floats(s, g));
-  float* Ws = reinterpret_cast<float*>(Ms + s.P + g.Kc);   // last_layer_group [K][Gt]
+  float* Ws = reinterpret_cast<float*>(Ms + s.P + g.Kc);   // last_layer_group [K][Gt] (when it fits: ws_smem)
+  const float* Wp = ws_smem ? Ws : g.Wg;
   // a CTA walks GTPB consecutive tiles: the tables are staged once, the rows of the first tile fly meanwhile
   long long n0 = (long long)blockIdx.x * GTPB * GTM;
   if (STAGED) stage_rows(s, act, n0, As);
-  if (logits != nullptr)
+  if (logits != nullptr && ws_smem)
     for (int i = threadIdx.x; i < s.K * Gt; i += blockDim.x) Ws[i] = __ldg(g.Wg + i);
   stage_tables(s, g, Gs, Ms);
   for (int t = 0; t < GTPB && n0 < s.N; ++t, n0 += GTM) {
@@ -147,7 +148,7 @@ __global__ void __launch_bounds__(GNT) group_fwd_kernel(HeadShape s, SpsGroupDes
         const int m = idx / s.K, k = idx % s.K;
         const long long n = n0 + m;
         if (n >= s.N) continue;
-        const float* w = Ws + k * Gt;
+        const float* w = Wp + (long long)k * Gt;
         const float* grow = gs + m * Gt;
         float a0 = 0.f, a1 = 0.f;
         int gg = 0;
@@ -174,18 +175,21 @@ int launch_group_fwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
                      cudaStream_t st) {
   if (s.N == 0 || g.Kc == 0) return SPS_OK;
   const int Gt = g.J * g.Kc;
-  size_t smem = sizeof(float) * ((size_t)GTM * Gt + (size_t)g.J * s.P + g.Kc + s.P + g.Kc + (size_t)s.K * Gt);
+  size_t smem = sizeof(float) * ((size_t)GTM * Gt + (size_t)g.J * s.P + g.Kc + s.P + g.Kc);
   SPS_REQUIRE(smem <= 200 * 1024, SPS_ERR_UNSUPPORTED, "group head: J*Kc=%d, J*P=%d need %zu bytes of shared memory", Gt, g.J * s.P, smem);
+  const size_t ws_bytes = sizeof(float) * (size_t)s.K * Gt;    // last_layer_group in shared memory only when it is small
+  const int ws_smem = smem + ws_bytes <= 32 * 1024 ? 1 : 0;
+  if (ws_smem) smem += ws_bytes;
   const size_t rows_bytes = sizeof(float) * (size_t)GTM * s.P;
   const bool staged = smem + rows_bytes <= kGroupStagedMax;   // three CTAs per SM still fit
   long long tiles = (s.N + GTM - 1) / GTM;
   if (staged) {
     smem += rows_bytes;
     SPS_CUDA_TRY(cudaFuncSetAttribute(group_fwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    group_fwd_kernel<true><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, groups, logits);
+    group_fwd_kernel<true><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, groups, logits, ws_smem);
   } else {
     SPS_CUDA_TRY(cudaFuncSetAttribute(group_fwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    group_fwd_kernel<false><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, groups, logits);
+    group_fwd_kernel<false><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, groups, logits, ws_smem);
   }
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
@@ -199,7 +203,7 @@ __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGrou
                                                              const float* __restrict__ dlogits,
                                                              const float* __restrict__ dgroups,
                                                              float* __restrict__ dact, float* __restrict__ ws_groups,
-                                                             float* __restrict__ ws_dpre) {
+                                                             float* __restrict__ ws_dpre, int ws_smem) {
   extern __shared__ __align__(16) float smem[];
   const int Gt = g.J * g.Kc;
   float* As = smem;
@@ -207,11 +211,12 @@ __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGrou
   float* dps = gs + GTM * Gt;
   float* Gs = gs + 2 * GTM * Gt;
   int* Ms = reinterpret_cast<int*>(Gs + gpad_floats(s, g));
-  float* Ws = reinterpret_cast<float*>(Ms + s.P + g.Kc);   // last_layer_group [K][Gt]
-  float* dls = Ws + s.K * Gt;                              // dlogits rows of the tile [GTM][K]
+  float* Ws = reinterpret_cast<float*>(Ms + s.P + g.Kc);   // last_layer_group [K][Gt] (when it fits: ws_smem)
+  float* dls = Ws + (ws_smem ? s.K * Gt : 0);              // dlogits rows of the tile [GTM][K]
+  const float* Wp = ws_smem ? Ws : g.Wg;
   long long n0 = (long long)blockIdx.x * GTPB * GTM;
   if (STAGED) stage_rows(s, act, n0, As);
-  if (dlogits != nullptr)
+  if (dlogits != nullptr && ws_smem)
     for (int i = threadIdx.x; i < s.K * Gt; i += blockDim.x) Ws[i] = __ldg(g.Wg + i);
   stage_tables(s, g, Gs, Ms);
   for (int t = 0; t < GTPB && n0 < s.N; ++t, n0 += GTM) {
@@ -229,7 +234,7 @@ __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGrou
       if (n < s.N) {
         float up = dgroups != nullptr ? __ldg(dgroups + n * Gt + gg) : 0.f;
         if (dlogits != nullptr)
-          for (int k = 0; k < s.K; ++k) up = fmaf(dls[m * s.K + k], Ws[k * Gt + gg], up);
+          for (int k = 0; k < s.K; ++k) up = fmaf(dls[m * s.K + k], Wp[(long long)k * Gt + gg], up);
         v = up * gs[idx];
         ws_groups[n * Gt + gg] = gs[idx];
         ws_dpre[n * Gt + gg] = v;
@@ -370,7 +375,10 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
     if (dact != nullptr && s.N > 0) SPS_CUDA_TRY(cudaMemsetAsync(dact, 0, sizeof(float) * (size_t)s.N * s.P, st));
     return SPS_OK;
   }
-  size_t smem = sizeof(float) * (2 * (size_t)GTM * Gt + (size_t)g.J * s.P + g.Kc + s.P + g.Kc + (size_t)s.K * Gt + (size_t)GTM * s.K);
+  size_t smem = sizeof(float) * (2 * (size_t)GTM * Gt + (size_t)g.J * s.P + g.Kc + s.P + g.Kc + (size_t)GTM * s.K);
+  const size_t ws_bytes = sizeof(float) * (size_t)s.K * Gt;    // last_layer_group in shared memory only when it is small
+  const int ws_smem = smem + ws_bytes <= 32 * 1024 ? 1 : 0;
+  if (ws_smem) smem += ws_bytes;
   SPS_REQUIRE(smem <= 200 * 1024, SPS_ERR_UNSUPPORTED, "group head: J*Kc=%d, J*P=%d need %zu bytes of shared memory", Gt, g.J * s.P, smem);
   float* ws_groups = ws;
   float* ws_dpre = ws + (size_t)s.N * Gt;
@@ -379,10 +387,10 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
   if (smem + rows_bytes <= kGroupStagedMax) {
     smem += rows_bytes;
     SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_pos_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    group_bwd_pos_kernel<true><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre);
+    group_bwd_pos_kernel<true><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre, ws_smem);
   } else {
     SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_pos_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    group_bwd_pos_kernel<false><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre);
+    group_bwd_pos_kernel<false><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre, ws_smem);
   }
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());

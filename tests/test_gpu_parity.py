@@ -109,6 +109,39 @@ def test_stage2_golden(built_lib, golden_dir, name, math):
     assert_grad(allgot, allref, gt, "dgroup_w")
 
 
+@pytest.mark.parametrize("K,per", [(171, 1), (40, 2)])
+def test_stage2_many_classes_vs_oracle(built_lib, K, per):
+    """Stage-2 grouping head with a wide last_layer_group (COCO-Stuff class count: it does not fit shared memory and
+    is read from global memory; the dWg kernel stages fewer rows per step) against the oracle's autograd."""
+    B, H, W, S, D, J = 1, 7, 6, 4, 64, 3
+    P = K * per * S
+    gen = torch.Generator().manual_seed(ho.SEED + K)
+    z = torch.sigmoid(torch.randn(B, S * D, H, W, generator=gen))
+    protos = torch.rand(P, D, 1, 1, generator=gen)
+    ident = ho.make_identity(P, K, S)
+    ranges = ho.uniform_ranges(P, S)
+    members = ho.class_members(ident)
+    gws = [torch.softmax(torch.randn(J, len(m), generator=gen), dim=1) for m in members]
+    wg = torch.randn(K, J * len(members), generator=gen) * 0.1
+    N = B * H * W
+    dlog = torch.randn(B, H, W, K, generator=gen) / N
+    dgr = torch.randn(N, J * len(members), generator=gen) / N
+    gr = [w.clone().requires_grad_(True) for w in gws]
+    wr = wg.clone().requires_grad_(True)
+    lo, _, ao, go = ho.head_stage2(z, protos, ranges, ident, gr, wr)
+    ((lo * dlog).sum() + (go * dgr).sum()).backward()
+    cfg = sps.HeadConfig.from_ranges(ranges, K, math=sps.MATH_FP32)
+    tables = sps.build_group_tables(ident, J, DEV)
+    _, _, a = sps.PrototypeHeadFn.apply(z.to(DEV), protos.to(DEV), None, cfg, False, True)
+    Gc = torch.cat([w.reshape(-1) for w in gws]).to(DEV).requires_grad_(True)
+    wc = wg.to(DEV).requires_grad_(True)
+    groups, logits = sps.GroupHeadFn.apply(a, Gc, wc, cfg, tables, (B, H, W))
+    assert_rel(groups, go, 4e-4, "groups"), assert_rel(logits.view(B, H, W, K), lo, 4e-4, "logits")
+    ((logits.view(B, H, W, K) * dlog.to(DEV)).sum() + (groups * dgr.to(DEV)).sum()).backward()
+    assert_grad(wc.grad, wr.grad, 1e-3, "dlast_group_w")
+    assert_grad(Gc.grad, torch.cat([w.grad.reshape(-1) for w in gr]), 1e-3, "dgroup_w")
+
+
 def check_push(keys, win_map, z_maps, labels, protos, ranges, ident, K, tol):
     """keys (n,P) int64 from the kernel, win_map (P,) global winners."""
     n = len(z_maps)
