@@ -125,10 +125,21 @@ __global__ void __launch_bounds__(256) bwd_prep_kernel(const __grid_constant__ C
   }
   __syncthreads();
   if (t < CN) store_proto_norm<X>(img + BOFF_BN, t, pn[t], t < n);
-  for (int idx = t; idx < CN * KP_BWD; idx += blockDim.x) {
-    const int j = idx / KP_BWD, k = idx % KP_BWD;
-    const float v = (k < K && j < n) ? __ldg(last_w + (size_t)k * P + p0 + j) : 0.0f;
-    *reinterpret_cast<uint16_t*>(img + BOFF_W3 + sw64_off(j, k)) = bits16(Fmt<X>::from(v));
+  // all loads of a thread first, then the stores (a load -> store round per iteration was a chain of 8 dependent L2
+  // round trips); prototype index fastest across threads so the loads are coalesced along the last-layer rows
+  {
+    constexpr int PER = CN * KP_BWD / 256;
+    float v[PER];
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+      const int idx = t + u * 256, k = idx / CN, j = idx % CN;
+      v[u] = (k < K && j < n) ? __ldg(last_w + (size_t)k * P + p0 + j) : 0.0f;
+    }
+#pragma unroll
+    for (int u = 0; u < PER; ++u) {
+      const int idx = t + u * 256, k = idx / CN, j = idx % CN;
+      *reinterpret_cast<uint16_t*>(img + BOFF_W3 + sw64_off(j, k)) = bits16(Fmt<X>::from(v[u]));
+    }
   }
 }
 

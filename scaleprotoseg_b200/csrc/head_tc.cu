@@ -67,13 +67,25 @@ __global__ void __launch_bounds__(256) proto_prep_kernel(const __grid_constant__
   if (t < CN) store_proto_norm<X>(img + OFF_BN, t, pn[t], t < n);
   if (last_w != nullptr) {
     const float sc = act_kind == SPS_ACT_LOG ? 0.69314718055994531f : 1.0f;  // the epilogue produces log2
-    for (int idx = t; idx < ct.kp * CN; idx += blockDim.x) {
-      const int k = idx / CN, j = idx % CN;
-      const float v = (k < K && j < n) ? sc * __ldg(last_w + (size_t)k * P + p0 + j) : 0.0f;
-      const X hi = Fmt<X>::from(v);
-      *reinterpret_cast<uint16_t*>(img + OFF_W2 + sw128_off(k, j)) = bits16(hi);
-      *reinterpret_cast<uint16_t*>(img + OFF_W2 + ct.kp * 128 + sw128_off(k, j)) =
-          bits16(Fmt<X>::from(NSPLIT == 3 ? v - Fmt<X>::to(hi) : 0.0f));
+    // batches of 8 loads per thread, then the stores: one load -> store round per iteration made this loop a chain of
+    // kp/4 dependent L2 round trips (most of the pre-pass time)
+    const int total = ct.kp * CN;
+    for (int i0 = t; i0 < total; i0 += 8 * blockDim.x) {
+      float v[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int idx = i0 + u * blockDim.x, k = idx / CN, j = idx % CN;
+        v[u] = (idx < total && k < K && j < n) ? sc * __ldg(last_w + (size_t)k * P + p0 + j) : 0.0f;
+      }
+#pragma unroll
+      for (int u = 0; u < 8; ++u) {
+        const int idx = i0 + u * blockDim.x, k = idx / CN, j = idx % CN;
+        if (idx >= total) break;
+        const X hi = Fmt<X>::from(v[u]);
+        *reinterpret_cast<uint16_t*>(img + OFF_W2 + sw128_off(k, j)) = bits16(hi);
+        *reinterpret_cast<uint16_t*>(img + OFF_W2 + ct.kp * 128 + sw128_off(k, j)) =
+            bits16(Fmt<X>::from(NSPLIT == 3 ? v[u] - Fmt<X>::to(hi) : 0.0f));
+      }
     }
   }
 }
