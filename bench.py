@@ -362,6 +362,48 @@ def measure_stage2(ctx, args):
             "hbm_frac": bytes_alg / (ms * 1e-3) / 1e9 / peaks()["hbm"]}
 
 
+def measure_kld(ctx, args):
+    """Secondary: the KLD loss between same-class prototypes on the dense distance map of the same
+    batch — sps_kld_fwd + sps_kld_bwd through the autograd Function, next to the CPU oracle's restatement of the
+    reference loop (segmentation/model/loss.py:66-146) on one image."""
+    sps, ho, dev, c = ctx["sps"], ctx["ho"], ctx["dev"], C2
+    from scaleprotoseg_b200.kld import KldTables, kld_loss
+    ranges = ho.uniform_ranges(c["P"], c["S"])
+    tables = KldTables(ctx["ident"], ranges, dev)
+    labels = torch.stack([ho.make_labels(i, c["H"], c["W"], c["K"]) for i in range(c["B"])])
+    lab_dev = labels.to(dev)
+    dist = sps.head_forward_raw(ctx["zs"][0], ctx["p2"], None, ctx["cfg"], True, False)[1].requires_grad_(True)
+
+    def fwd(i):
+        return kld_loss(dist, lab_dev, tables)
+
+    def step(i):
+        dist.grad = None
+        kld_loss(dist, lab_dev, tables).backward()
+
+    iters = max(3, min(args.steps, 50))
+    for i in range(3):
+        step(i)
+    ms_fwd, ms = event_ms(fwd, iters), event_ms(step, iters)
+    n = c["B"] * c["H"] * c["W"]
+    per_cs = c["P"] // c["K"] // c["S"]
+    touched = n * c["S"] * per_cs                      # (pixel, prototype) pairs whose classes agree
+    out = {"workload": "KLD loss between same-class prototypes on the dense distance map of the same batch "
+                       "(B=%d, P=%d: %d pairs per image, %d class-matched (pixel, prototype) pairs)" % (c["B"], c["P"], tables.Q, touched),
+           "ms_fwd": ms_fwd, "ms_fwd_bwd": ms, "loss": float(fwd(0).detach()),
+           "note": "backward includes the zero fill of the 205 MB gradient map the head backward then reads"}
+    if not args.no_cpu:
+        import time
+        d1 = dist.detach()[:1].cpu()
+        t0 = time.perf_counter()
+        d1r = d1.clone().requires_grad_(True)
+        ho.kld_loss(d1r, labels[:1], ctx["ident"].cpu(), ranges).backward()
+        cpu_ms = (time.perf_counter() - t0) * 1e3
+        out["cpu_port_ms_per_image_fwd_bwd"] = cpu_ms
+        out["cpu_port_note"] = "oracle port (one matrix per image x class x scale, already far fewer ops than the reference's per-pair loop), 1 image, all host threads"
+    return out
+
+
 def measure_c5(ctx, args):
     """Secondary: the COCO-Stuff head shape of BASELINE.json configs[4] (K=171, P=6840, B=32, 65x65), fused forward
     (the headline of this object, tensor-bound) and the backward (class slabs)."""
@@ -502,6 +544,7 @@ def main():
     dense = None if (args.no_c5 or ctx["world"] > 1) else measure_dense(ctx, args)
     stage2 = None if (args.no_c5 or ctx["world"] > 1) else measure_stage2(ctx, args)
     torch_gpu = None if (args.no_c5 or ctx["world"] > 1) else measure_torch_gpu(ctx, args)
+    kld = None if (args.no_c5 or ctx["world"] > 1) else measure_kld(ctx, args)
     if ctx["world"] > 1:
         ctx["barrier"]()
     if rank != 0:
@@ -545,6 +588,8 @@ def main():
         out["dense_mode"] = dense
     if stage2 is not None:
         out["stage2"] = stage2
+    if kld is not None:
+        out["kld"] = kld
     if torch_gpu is not None:
         out["torch_gpu_baseline"] = torch_gpu
     if not args.no_cpu and ctx["world"] == 1:

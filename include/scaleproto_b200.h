@@ -81,6 +81,22 @@ typedef struct SpsGroupDesc {
   const float* Wg;           /* [K x J*Kc] last_layer_group.weight, row major */
 } SpsGroupDesc;
 
+/* Tables of the KLD loss between same-class prototypes (segmentation/model/loss.py:53-146).
+ * A group is one (class, scale) with its prototypes in ascending order; groups are numbered class-major.
+ * Pairs are the unordered prototype pairs (a < b) inside a group, numbered group by group, a-major. */
+typedef struct SpsKldDesc {
+  int32_t G;                  /* groups = K * S (empty groups allowed) */
+  int32_t Q;                  /* pairs over all groups */
+  const int32_t* proto_class; /* [P] class of prototype p (argmax of prototype_class_identity) */
+  const int32_t* proto_group; /* [P] group of p */
+  const int32_t* proto_local; /* [P] rank of p inside its group */
+  const int32_t* group_moff;  /* [G+1] prefix sum of group sizes (into members) */
+  const int32_t* group_poff;  /* [G+1] prefix sum of pairs per group (into pair_a / pair_b) */
+  const int32_t* members;     /* [P] prototype ids ordered by group */
+  const int32_t* pair_a;      /* [Q] first prototype of pair q */
+  const int32_t* pair_b;      /* [Q] second prototype of pair q */
+} SpsKldDesc;
+
 int sps_version(void);
 const char* sps_last_error(void);
 /* Number of kernels this library has launched in this process (bench.py reports it as gpu_launches). */
@@ -133,6 +149,21 @@ size_t sps_group_workspace_bytes(const SpsHeadDesc* desc, const SpsGroupDesc* g)
 int sps_group_bwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* act, const float* dlogits,
                   const float* dgroups, float* dact, float* dG, float* dWg, void* workspace,
                   size_t workspace_bytes, void* stream);
+
+/* KLD loss between the same-class prototypes of every scale.  Replaces KLDLoss.forward
+ * (segmentation/model/loss.py:66-146: the image x class x scale x pair loop of masked_select / log_softmax /
+ * kl_div calls) called from segmentation/model/module_multiscale.py:242.
+ *   dist    [B, P, H, W] fp32 distances (the head's dense output)
+ *   labels  [B, H, W] int16, 0 = void, c+1 = class c (the loss subtracts 1, loss.py:77)
+ *   loss    [2] fp32: mean of exp(-kld) over the contributing pairs (0 when none), and their number
+ *   workspace >= sps_kld_workspace_bytes bytes; sps_kld_bwd reads what sps_kld_fwd left in it. */
+size_t sps_kld_workspace_bytes(const SpsHeadDesc* desc, const SpsKldDesc* k);
+int sps_kld_fwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* dist, const int16_t* labels,
+                void* workspace, size_t workspace_bytes, float* loss, void* stream);
+/* Gradient of the loss into the distance map.  dloss [1] fp32 (device) upstream gradient of the scalar;
+ * ddist [B, P, H, W] OVERWRITTEN (zero wherever the pixel's class differs from the prototype's). */
+int sps_kld_bwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* dist, void* workspace,
+                size_t workspace_bytes, const float* dloss, float* ddist, void* stream);
 
 /* Push scan: per map and per prototype, the nearest position among those labelled with the
  * prototype's class.  Replaces compute_distances lines 68-91 of

@@ -179,6 +179,40 @@ def push_case(mm, pm, name, n_img, h, w, P, K, absent_class, dup=False, seed=0):
     print(name, "absent->1e10:", int((torch.cat(list_val).min(0).values >= 1e10).sum()))
 
 
+def kld_case(name, B, H, W, P, K, S=4, prune=(), absent_class=None, void_only=False, seed=0):
+    """Reference KLDLoss (segmentation/model/loss.py:53-146) on a random distance map; value and gradient."""
+    from segmentation.model.loss import KLDLoss
+    g = torch.Generator().manual_seed(ho.SEED + 31 * seed)
+    ident = ho.make_identity(P, K, S)
+    ranges = ho.uniform_ranges(P, S)
+    if prune:
+        keep = [p for p in range(P) if p not in set(prune)]
+        ident = ident[keep]
+        new, lo = [], 0
+        for a, b in ranges:
+            n = sum(1 for p in keep if a <= p < b)
+            new.append((lo, lo + n))
+            lo += n
+        ranges, P = new, len(keep)
+    dist = (torch.rand(B, P, H, W, generator=g) * 6.0).requires_grad_(True)
+    labels = torch.stack([ho.make_labels(seed * 100 + i, H, W, K, absent_class=absent_class, block=3) for i in range(B)])
+    if void_only:
+        labels[0] = 0
+    ref = KLDLoss(ident, len(ranges), {s: tuple(r) for s, r in enumerate(ranges)})
+    loss = ref(dist, labels)
+    if loss.requires_grad:
+        (ddist,) = torch.autograd.grad(loss * 3.0, dist)
+    else:
+        ddist = torch.zeros_like(dist)
+    mine = ho.kld_loss(dist.detach(), labels, ident, ranges)
+    lv = float(loss.detach())
+    assert abs(float(mine) - lv) <= 1e-5 * max(1.0, abs(lv)), (name, float(mine), lv)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", name + ".npz"), dist=dist.detach().numpy(),
+                        labels=labels.numpy(), identity=ident.numpy(), ranges=np.array(ranges, dtype=np.int64),
+                        loss=np.float32(loss.detach().item()), ddist=ddist.numpy(), upstream=np.float32(3.0))
+    print(name, "loss", lv)
+
+
 def main():
     mm, mg, pm = import_reference()
     torch.manual_seed(ho.SEED)
@@ -193,6 +227,9 @@ def main():
     stage2_case(mm, mg, "stage2_city228_ragged", B=1, H=4, W=5, P=228, K=19, prune=(0, 5, 100, 227), drop_class=4, seed=1)
     push_case(mm, pm, "push_small", n_img=5, h=9, w=11, P=40, K=5, absent_class=3, dup=True)
     push_case(mm, pm, "push_city228", n_img=3, h=17, w=9, P=228, K=19, absent_class=7, seed=5)
+    kld_case("kld_em", B=2, H=9, W=7, P=24, K=2)
+    kld_case("kld_small_ragged", B=2, H=7, W=8, P=40, K=5, prune=(0, 1, 11, 39), absent_class=3, void_only=True, seed=1)
+    kld_case("kld_city228", B=1, H=12, W=10, P=228, K=19, seed=2)
 
 
 if __name__ == "__main__":

@@ -18,6 +18,7 @@ Reference lines followed (relative to /root/reference):
   push_image_min            segmentation/push_multiscale_optimization.py:68-91
   push_dataset_argmin       segmentation/push_multiscale_optimization.py:135-137
   push_gather               segmentation/push_multiscale_optimization.py:161-188
+  kld_loss                  segmentation/model/loss.py:53-146 (KLDLoss.forward)
 """
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -176,6 +177,45 @@ def push_full(z_maps: Sequence[torch.Tensor], labels: Sequence[torch.Tensor], pr
 # Synthetic inputs.  Counter-based so every rank / GPU count sees the same data.
 # --------------------------------------------------------------------------------------------
 SEED = 20220227  # configs/scaleproto_cityscapes.gin:15
+
+
+def kld_loss(dist: torch.Tensor, target: torch.Tensor, identity: torch.Tensor,
+             scale_ranges: Sequence[Tuple[int, int]]) -> torch.Tensor:
+    """KLDLoss.forward (segmentation/model/loss.py:66-146) restated with one matrix per (image, class, scale).
+
+    dist (B,P,H,W) distances; target (B,H,W) integer labels, 0 = void, c+1 = class c (loss.py:77);
+    identity (P,K) prototype_class_identity.  For every image, every class present in it (loss.py:88-91)
+    and every scale (loss.py:103), the class's prototypes of that scale give one distribution each over the
+    class's pixels: log_softmax of the DISTANCES along the pixels (loss.py:112-115).  Every unordered pair
+    with at least two pixels contributes kld = (KL(a||b) + KL(b||a)) / 2 (loss.py:121-140); the loss is the
+    mean of exp(-kld) over all contributions (loss.py:142-146), 0 when there are none."""
+    B, P = dist.shape[0], dist.shape[1]
+    K = identity.shape[1]
+    lab = target.reshape(B, -1).long() - 1
+    d = dist.permute(0, 2, 3, 1).reshape(B, -1, P)
+    terms = []
+    for b in range(B):
+        for c in sorted(set(lab[b].tolist())):
+            if c < 0 or c >= K:
+                continue
+            members = torch.nonzero(identity[:, c]).flatten()
+            mask = lab[b] == c
+            if members.numel() == 0 or int(mask.sum()) < 2:
+                continue
+            for lo, hi in scale_ranges:
+                ms = members[(members >= lo) & (members < hi)]
+                if ms.numel() < 2:
+                    continue
+                logp = torch.log_softmax(d[b][mask][:, ms], dim=0)            # (n, m)
+                prob = logp.exp()
+                cross = prob.t() @ logp                                        # cross[a, b] = sum_x p_a log p_b
+                kl = cross.diagonal().unsqueeze(1) - cross                     # kl[a, b] = KL(a || b)
+                sym = 0.5 * (kl + kl.t())
+                iu = torch.triu_indices(ms.numel(), ms.numel(), offset=1)
+                terms.append(sym[iu[0], iu[1]])
+    if not terms:
+        return torch.zeros((), dtype=dist.dtype)
+    return torch.exp(-torch.cat(terms)).mean()
 
 
 def uniform_ranges(P: int, S: int):

@@ -36,6 +36,15 @@ class SpsGroupDesc(C.Structure):
     ]
 
 
+class SpsKldDesc(C.Structure):
+    _fields_ = [
+        ("G", C.c_int32), ("Q", C.c_int32),
+        ("proto_class", C.c_void_p), ("proto_group", C.c_void_p), ("proto_local", C.c_void_p),
+        ("group_moff", C.c_void_p), ("group_poff", C.c_void_p), ("members", C.c_void_p),
+        ("pair_a", C.c_void_p), ("pair_b", C.c_void_p),
+    ]
+
+
 _P = C.c_void_p
 _SIGNATURES = {
     "sps_version": (C.c_int, []),
@@ -49,6 +58,9 @@ _SIGNATURES = {
     "sps_group_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc)]),
     "sps_group_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc), _P, _P, _P, _P, _P, _P, _P,
                                 C.c_size_t, _P]),
+    "sps_kld_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc)]),
+    "sps_kld_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc), _P, _P, _P, C.c_size_t, _P, _P]),
+    "sps_kld_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc), _P, _P, C.c_size_t, _P, _P, _P]),
     "sps_push_scan": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "sps_push_reduce": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint32, _P, _P]),
     "sps_push_gather": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, C.c_int32, C.c_uint32, _P, _P, _P]),

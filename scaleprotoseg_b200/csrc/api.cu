@@ -152,6 +152,55 @@ int sps_group_bwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* a
                           reinterpret_cast<cudaStream_t>(stream));
 }
 
+static int check_kld(const SpsKldDesc* k) {
+  SPS_REQUIRE(k != nullptr, SPS_ERR_BAD_ARG, "kld desc NULL");
+  SPS_REQUIRE(k->G >= 0 && k->Q >= 0, SPS_ERR_BAD_ARG, "kld desc G=%d Q=%d", k->G, k->Q);
+  SPS_REQUIRE(k->proto_class && k->proto_group && k->proto_local && k->group_moff && k->group_poff && k->members,
+              SPS_ERR_BAD_ARG, "kld desc has NULL tables");
+  SPS_REQUIRE(k->Q == 0 || (k->pair_a && k->pair_b), SPS_ERR_BAD_ARG, "kld desc has NULL pair tables");
+  return SPS_OK;
+}
+
+size_t sps_kld_workspace_bytes(const SpsHeadDesc* desc, const SpsKldDesc* k) {
+  if (validate_desc(desc) != SPS_OK || k == nullptr || k->Q < 0) return 0;
+  return kld_workspace(make_shape(desc), k->Q);
+}
+
+int sps_kld_fwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* dist, const int16_t* labels,
+                void* workspace, size_t workspace_bytes, float* loss, void* stream) {
+  int rc = validate_desc(desc);
+  if (rc != SPS_OK) return rc;
+  rc = check_kld(k);
+  if (rc != SPS_OK) return rc;
+  SPS_REQUIRE(loss != nullptr, SPS_ERR_BAD_ARG, "kld_fwd: loss NULL");
+  HeadShape s = make_shape(desc);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (s.N == 0 || s.P == 0) {
+    SPS_CUDA_TRY(cudaMemsetAsync(loss, 0, 2 * sizeof(float), st));
+    return SPS_OK;
+  }
+  SPS_REQUIRE(dist && labels, SPS_ERR_BAD_ARG, "kld_fwd: dist/labels NULL");
+  size_t need = kld_workspace(s, k->Q);
+  SPS_REQUIRE(workspace != nullptr && workspace_bytes >= need, SPS_ERR_WORKSPACE,
+              "kld workspace: need %zu bytes, got %zu", need, workspace_bytes);
+  return launch_kld_fwd(s, *k, dist, labels, workspace, loss, st);
+}
+
+int sps_kld_bwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* dist, void* workspace,
+                size_t workspace_bytes, const float* dloss, float* ddist, void* stream) {
+  int rc = validate_desc(desc);
+  if (rc != SPS_OK) return rc;
+  rc = check_kld(k);
+  if (rc != SPS_OK) return rc;
+  HeadShape s = make_shape(desc);
+  if (s.N == 0 || s.P == 0) return SPS_OK;
+  SPS_REQUIRE(dist && dloss && ddist, SPS_ERR_BAD_ARG, "kld_bwd: NULL argument");
+  size_t need = kld_workspace(s, k->Q);
+  SPS_REQUIRE(workspace != nullptr && workspace_bytes >= need, SPS_ERR_WORKSPACE,
+              "kld workspace: need %zu bytes, got %zu", need, workspace_bytes);
+  return launch_kld_bwd(s, *k, dist, workspace, dloss, ddist, reinterpret_cast<cudaStream_t>(stream));
+}
+
 int sps_push_scan(const SpsHeadDesc* desc, const float* z, const float* protos, const int16_t* labels,
                   const int32_t* proto_class, uint64_t* keys, void* workspace, size_t workspace_bytes, void* stream) {
   int rc = validate_desc(desc);

@@ -119,4 +119,10 @@ int launch_push_gather(const HeadShape& s, const float* z, const unsigned long l
                        const unsigned long long* best, int n_maps, uint32_t map_base, const int32_t* proto_scale,
                        float* out, cudaStream_t st);
 
+size_t kld_workspace(const HeadShape& s, int Q);
+int launch_kld_fwd(const HeadShape& s, const SpsKldDesc& k, const float* dist, const int16_t* labels, void* ws,
+                   float* loss, cudaStream_t st);
+int launch_kld_bwd(const HeadShape& s, const SpsKldDesc& k, const float* dist, void* ws, const float* dloss,
+                   float* ddist, cudaStream_t st);
+
 }  // namespace sps

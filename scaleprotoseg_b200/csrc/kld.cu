@@ -1,0 +1,300 @@
+// Fused KLD loss between same-class prototypes (segmentation/model/loss.py:53-146).
+//
+// The reference walks image x class x scale x prototype-pair in Python, masking the distance map and calling
+// log_softmax / kl_div per pair (about 6 small kernels and one host sync per pair).  Here the labels of an image are
+// bucketed by class once (pixel index lists), and everything after that touches only the (pixel, prototype) pairs
+// whose classes agree — 1/K of the distance map:
+//   kld_hist     per image: pixels per class and their exclusive offsets
+//   kld_bucket   per (class, image): ordered list of the class's pixels (ballot + prefix: the order is the pixel
+//                order, so every later sum has a fixed order)
+//   kld_lse      one warp per (image, prototype): log-sum-exp of the prototype's distances over its class's pixels
+//   kld_pairs    one warp per (image, pair): KL(a||b) and KL(b||a) over the class's pixels, term = exp(-kld)
+//   kld_finish   one CTA: mean of the terms in a fixed order
+//   kld_bwd      one warp per (image, prototype): gradient into the distance map at the class's pixels
+// All sums are fp32 in a fixed order; exp/log are the full-precision library versions (the work is tiny).
+#include "common.cuh"
+
+namespace sps {
+
+namespace {
+
+constexpr int KLD_THREADS = 256;
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+
+// cnt[b][c], off[b][c] for c in [0, K): pixels of image b labelled c+1 (0 = void and labels above K are dropped).
+__global__ void kld_hist_kernel(const int16_t* __restrict__ labels, int HW, int K, int* __restrict__ cnt,
+                                int* __restrict__ off) {
+  extern __shared__ int hist[];  // K
+  const int b = blockIdx.x;
+  for (int c = threadIdx.x; c < K; c += blockDim.x) hist[c] = 0;
+  __syncthreads();
+  const int16_t* lab = labels + (size_t)b * HW;
+  for (int x = threadIdx.x; x < HW; x += blockDim.x) {
+    int c = (int)lab[x] - 1;
+    if (c >= 0 && c < K) atomicAdd(&hist[c], 1);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    int run = 0;
+    for (int c = 0; c < K; ++c) {
+      cnt[b * K + c] = hist[c];
+      off[b * K + c] = run;
+      run += hist[c];
+    }
+  }
+}
+
+// idx[b*HW + off[b][c] + r] = r-th pixel (ascending) of image b labelled c+1.
+__global__ void kld_bucket_kernel(const int16_t* __restrict__ labels, int HW, int K, const int* __restrict__ cnt,
+                                  const int* __restrict__ off, int* __restrict__ idx) {
+  __shared__ int warp_cnt[KLD_THREADS / 32];
+  __shared__ int base;
+  const int c = blockIdx.x, b = blockIdx.y;
+  if (cnt[b * K + c] == 0) return;
+  const int16_t* lab = labels + (size_t)b * HW;
+  int* out = idx + (size_t)b * HW + off[b * K + c];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (threadIdx.x == 0) base = 0;
+  __syncthreads();
+  for (int x0 = 0; x0 < HW; x0 += KLD_THREADS) {
+    const int x = x0 + threadIdx.x;
+    const bool hit = x < HW && (int)lab[x] == c + 1;
+    const unsigned m = __ballot_sync(0xffffffffu, hit);
+    if (lane == 0) warp_cnt[warp] = __popc(m);
+    __syncthreads();
+    int before = base;
+    for (int w = 0; w < warp; ++w) before += warp_cnt[w];
+    if (hit) out[before + __popc(m & ((1u << lane) - 1u))] = x;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      int t = 0;
+      for (int w = 0; w < KLD_THREADS / 32; ++w) t += warp_cnt[w];
+      base += t;
+    }
+    __syncthreads();
+  }
+}
+
+// lse[b*P + p] = log sum_x exp(d[b,p,x]) over the pixels of p's class (loss.py:112-115 log_softmax denominator).
+__global__ void kld_lse_kernel(const float* __restrict__ dist, int B, int P, int HW, int K,
+                               const int* __restrict__ proto_class, const int* __restrict__ cnt,
+                               const int* __restrict__ off, const int* __restrict__ idx, float* __restrict__ lse) {
+  const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (wid >= (long long)B * P) return;
+  const int b = (int)(wid / P), p = (int)(wid % P);
+  const int c = proto_class[p];
+  const int n = (c >= 0 && c < K) ? cnt[b * K + c] : 0;
+  if (n == 0) {
+    if (lane == 0) lse[wid] = 0.0f;
+    return;
+  }
+  const int* ix = idx + (size_t)b * HW + off[b * K + c];
+  const float* row = dist + ((size_t)b * P + p) * HW;
+  float mx = -INFINITY;
+  for (int i = lane; i < n; i += 32) mx = fmaxf(mx, row[ix[i]]);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) mx = fmaxf(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+  float s = 0.0f;
+  for (int i = lane; i < n; i += 32) s += expf(row[ix[i]] - mx);
+  s = warp_sum(s);
+  if (lane == 0) lse[wid] = mx + logf(s);
+}
+
+// One warp per (image, pair q): kl[b*Q+q] = (KL(a||b), KL(b||a)), term[b*Q+q] = exp(-(sum)/2), or -1 when the pair
+// does not contribute (class absent from the image or fewer than two pixels, loss.py:117-135).
+__global__ void kld_pairs_kernel(const float* __restrict__ dist, int B, int P, int HW, int K, int Q,
+                                 const int* __restrict__ pair_a, const int* __restrict__ pair_b,
+                                 const int* __restrict__ proto_class, const int* __restrict__ cnt,
+                                 const int* __restrict__ off, const int* __restrict__ idx,
+                                 const float* __restrict__ lse, float2* __restrict__ kl, float* __restrict__ term) {
+  const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (wid >= (long long)B * Q) return;
+  const int b = (int)(wid / Q), q = (int)(wid % Q);
+  const int pa = pair_a[q], pb = pair_b[q];
+  const int c = proto_class[pa];
+  const int n = (c >= 0 && c < K) ? cnt[b * K + c] : 0;
+  if (n < 2) {
+    if (lane == 0) {
+      kl[wid] = make_float2(0.0f, 0.0f);
+      term[wid] = -1.0f;  // marks "no contribution" (a real term is exp(-kld) >= 0)
+    }
+    return;
+  }
+  const int* ix = idx + (size_t)b * HW + off[b * K + c];
+  const float* ra = dist + ((size_t)b * P + pa) * HW;
+  const float* rb = dist + ((size_t)b * P + pb) * HW;
+  const float la = lse[(size_t)b * P + pa], lb = lse[(size_t)b * P + pb];
+  float kab = 0.0f, kba = 0.0f;
+  for (int i = lane; i < n; i += 32) {
+    const int x = ix[i];
+    const float a = ra[x] - la, bb = rb[x] - lb;
+    const float diff = a - bb;
+    kab += expf(a) * diff;
+    kba -= expf(bb) * diff;
+  }
+  kab = warp_sum(kab);
+  kba = warp_sum(kba);
+  if (lane == 0) {
+    kl[wid] = make_float2(kab, kba);
+    term[wid] = expf(-0.5f * (kab + kba));
+  }
+}
+
+// out[0] = mean of the contributing terms (0 when none, loss.py:142-146), out[1] = their number.
+__global__ void kld_finish_kernel(const float* __restrict__ term, long long total, float* __restrict__ out) {
+  __shared__ float ssum[32];
+  __shared__ float scnt[32];
+  float s = 0.0f, m = 0.0f;
+  for (long long i = threadIdx.x; i < total; i += blockDim.x) {
+    const float t = term[i];
+    if (t >= 0.0f) {
+      s += t;
+      m += 1.0f;
+    }
+  }
+  s = warp_sum(s);
+  m = warp_sum(m);
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  if (lane == 0) {
+    ssum[warp] = s;
+    scnt[warp] = m;
+  }
+  __syncthreads();
+  if (warp == 0) {
+    const int nw = blockDim.x >> 5;
+    s = lane < nw ? ssum[lane] : 0.0f;
+    m = lane < nw ? scnt[lane] : 0.0f;
+    s = warp_sum(s);
+    m = warp_sum(m);
+    if (lane == 0) {
+      out[0] = m > 0.0f ? s / m : 0.0f;
+      out[1] = m;
+    }
+  }
+}
+
+// One warp per (image, prototype a): for every pixel y of a's class,
+//   ddist[b,a,y] = dloss * sum_{b' != a in group} (-term_ab'/M) * 1/2 * p_a(y) * (l_a(y) - l_b'(y) + 1 - KL(a||b')) - p_b'(y)
+// (derivative of exp(-kld) through the two log_softmax; the rest of ddist was zeroed by the caller).
+__global__ void kld_bwd_kernel(const float* __restrict__ dist, int B, int P, int HW, int K, int Q,
+                               const int* __restrict__ proto_class, const int* __restrict__ proto_group,
+                               const int* __restrict__ proto_local, const int* __restrict__ group_moff,
+                               const int* __restrict__ group_poff, const int* __restrict__ members,
+                               const int* __restrict__ cnt, const int* __restrict__ off, const int* __restrict__ idx,
+                               const float* __restrict__ lse, const float2* __restrict__ kl,
+                               const float* __restrict__ term, const float* __restrict__ fin,
+                               const float* __restrict__ dloss, float* __restrict__ ddist) {
+  const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int lane = threadIdx.x & 31;
+  if (wid >= (long long)B * P) return;
+  const int b = (int)(wid / P), p = (int)(wid % P);
+  const int c = proto_class[p];
+  const int n = (c >= 0 && c < K) ? cnt[b * K + c] : 0;
+  const float M = fin[1];
+  if (n < 2 || M <= 0.0f) return;
+  const int g = proto_group[p], a = proto_local[p];
+  const int m0 = group_moff[g], m = group_moff[g + 1] - m0;
+  if (m < 2) return;
+  const int q0 = group_poff[g];
+  const float scale = -0.5f * dloss[0] / M;
+  const int* ix = idx + (size_t)b * HW + off[b * K + c];
+  const float* ra = dist + ((size_t)b * P + p) * HW;
+  float* ga = ddist + ((size_t)b * P + p) * HW;
+  const float la = lse[(size_t)b * P + p];
+  for (int i = lane; i < n; i += 32) {
+    const int x = ix[i];
+    const float l_a = ra[x] - la;
+    const float p_a = expf(l_a);
+    float acc = 0.0f;
+    for (int o = 0; o < m; ++o) {
+      if (o == a) continue;
+      const int lo = o < a ? o : a, hi = o < a ? a : o;
+      const int q = q0 + lo * (2 * m - lo - 1) / 2 + (hi - lo - 1);
+      const float2 k2 = kl[(size_t)b * Q + q];
+      const float w = term[(size_t)b * Q + q];
+      const float k_ab = a < o ? k2.x : k2.y;  // KL(a || o)
+      const int po = members[m0 + o];
+      const float l_o = dist[((size_t)b * P + po) * HW + x] - lse[(size_t)b * P + po];
+      acc += w * (p_a * (l_a - l_o + 1.0f - k_ab) - expf(l_o));
+    }
+    ga[x] = scale * acc;
+  }
+}
+
+inline size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
+
+struct KldCarve {
+  int *cnt, *off, *idx;
+  float *lse, *term, *fin;
+  float2* kl;
+  size_t bytes;
+};
+
+KldCarve carve(const HeadShape& s, int Q, void* ws) {
+  char* base = reinterpret_cast<char*>(ws);
+  size_t o = 0;
+  KldCarve k;
+  auto take = [&](size_t bytes) {
+    char* p = base ? base + o : nullptr;
+    o += align16(bytes);
+    return p;
+  };
+  k.fin = reinterpret_cast<float*>(take(4 * sizeof(float)));
+  k.cnt = reinterpret_cast<int*>(take(sizeof(int) * (size_t)s.B * s.K));
+  k.off = reinterpret_cast<int*>(take(sizeof(int) * (size_t)s.B * s.K));
+  k.idx = reinterpret_cast<int*>(take(sizeof(int) * (size_t)s.N));
+  k.lse = reinterpret_cast<float*>(take(sizeof(float) * (size_t)s.B * s.P));
+  k.term = reinterpret_cast<float*>(take(sizeof(float) * (size_t)s.B * Q));
+  k.kl = reinterpret_cast<float2*>(take(sizeof(float2) * (size_t)s.B * Q));
+  k.bytes = o;
+  return k;
+}
+
+inline unsigned warps_grid(long long warps) { return (unsigned)((warps * 32 + KLD_THREADS - 1) / KLD_THREADS); }
+
+}  // namespace
+
+size_t kld_workspace(const HeadShape& s, int Q) { return carve(s, Q, nullptr).bytes; }
+
+int launch_kld_fwd(const HeadShape& s, const SpsKldDesc& k, const float* dist, const int16_t* labels, void* ws,
+                   float* loss, cudaStream_t st) {
+  KldCarve w = carve(s, k.Q, ws);
+  kld_hist_kernel<<<s.B, KLD_THREADS, sizeof(int) * s.K, st>>>(labels, s.HW, s.K, w.cnt, w.off);
+  kld_bucket_kernel<<<dim3(s.K, s.B), KLD_THREADS, 0, st>>>(labels, s.HW, s.K, w.cnt, w.off, w.idx);
+  kld_lse_kernel<<<warps_grid((long long)s.B * s.P), KLD_THREADS, 0, st>>>(dist, s.B, s.P, s.HW, s.K, k.proto_class,
+                                                                          w.cnt, w.off, w.idx, w.lse);
+  int launched = 3;
+  if (k.Q > 0) {
+    kld_pairs_kernel<<<warps_grid((long long)s.B * k.Q), KLD_THREADS, 0, st>>>(
+        dist, s.B, s.P, s.HW, s.K, k.Q, k.pair_a, k.pair_b, k.proto_class, w.cnt, w.off, w.idx, w.lse, w.kl, w.term);
+    ++launched;
+  }
+  kld_finish_kernel<<<1, 1024, 0, st>>>(w.term, (long long)s.B * k.Q, w.fin);
+  count_launch(launched + 1);
+  SPS_CUDA_TRY(cudaMemcpyAsync(loss, w.fin, 2 * sizeof(float), cudaMemcpyDeviceToDevice, st));
+  SPS_CUDA_TRY(cudaGetLastError());
+  return SPS_OK;
+}
+
+int launch_kld_bwd(const HeadShape& s, const SpsKldDesc& k, const float* dist, void* ws, const float* dloss,
+                   float* ddist, cudaStream_t st) {
+  KldCarve w = carve(s, k.Q, ws);
+  SPS_CUDA_TRY(cudaMemsetAsync(ddist, 0, sizeof(float) * (size_t)s.N * s.P, st));
+  if (k.Q > 0) {
+    kld_bwd_kernel<<<warps_grid((long long)s.B * s.P), KLD_THREADS, 0, st>>>(
+        dist, s.B, s.P, s.HW, s.K, k.Q, k.proto_class, k.proto_group, k.proto_local, k.group_moff, k.group_poff,
+        k.members, w.cnt, w.off, w.idx, w.lse, w.kl, w.term, w.fin, dloss, ddist);
+    count_launch(1);
+  }
+  SPS_CUDA_TRY(cudaGetLastError());
+  return SPS_OK;
+}
+
+}  // namespace sps

@@ -11,6 +11,8 @@ What is patched (reference file:line of what each replaces):
       push_forward :454
   segmentation.push_multiscale_optimization (module globals, looked up at call time :286,:291)
       compute_distances :35, min_across_dataset :94, global_min :141
+  segmentation.model.loss.KLDLoss
+      forward :66 (the image x class x scale x pair loop; CPU inputs keep the reference's loop)
 Configurations the kernels do not cover (scale_head set, callable activation, non-1x1 prototypes)
 keep the reference's original method.  CPU tensors raise: there is no CPU fallback.
 """
@@ -22,6 +24,7 @@ import numpy as np
 import torch
 
 from . import _lib, model_api
+from . import kld as _kld
 from . import push as _push
 
 _installed = {}
@@ -165,6 +168,25 @@ def install_push(pm):
         setattr(pm, name, fn)
 
 
+def install_kld(kld_cls):
+    """Bind the fused KLD loss over `kld_cls.forward` (the reference's KLDLoss or any module with its three
+    attributes).  Distances on the CPU keep the original loop."""
+    _lib.load()
+    old = getattr(kld_cls, "forward")
+    if hasattr(old, "__sps_original__"):
+        return
+
+    @functools.wraps(old)
+    def forward(self, prototype_distances, target_labels):
+        if not prototype_distances.is_cuda:
+            return old(self, prototype_distances, target_labels)
+        return _kld.kld_forward(self, prototype_distances, target_labels)
+
+    forward.__sps_original__ = old
+    setattr(kld_cls, "forward", forward)
+    _installed[(kld_cls, "forward")] = old
+
+
 def install():
     """Patch the reference (must be importable: `segmentation` on sys.path)."""
     from segmentation.model import model_multiscale as mm
@@ -174,3 +196,6 @@ def install():
     import segmentation.push_multiscale_optimization as pm
 
     install_push(pm)
+    from segmentation.model import loss as ml
+
+    install_kld(ml.KLDLoss)

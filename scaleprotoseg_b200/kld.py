@@ -1,0 +1,149 @@
+"""Host side of the fused KLD loss between same-class prototypes.
+
+Drop-in for `KLDLoss.forward(prototype_distances, target_labels)` (segmentation/model/loss.py:66-146, called from
+segmentation/model/module_multiscale.py:242).  The reference walks image x class x scale x prototype-pair in Python
+(one host sync per class, about six small kernels per pair); here one autograd Function calls `sps_kld_fwd` /
+`sps_kld_bwd` of libscaleproto_sm100.so.  CUDA tensors only; there is no CPU path.
+"""
+import ctypes as C
+from typing import Dict, Optional, Sequence, Tuple
+
+import torch
+
+from . import _lib
+from ._lib import SpsHeadDesc, SpsKldDesc
+from .head import _check_cuda_f32, _ptr, _stream
+
+
+class KldTables:
+    """(class, scale) groups and their prototype pairs, derived once from prototype_class_identity (P x K) and
+    scale_num_prototypes — what loss.py:92-109 recomputes per image and class."""
+
+    def __init__(self, identity: torch.Tensor, scale_ranges: Sequence[Tuple[int, int]], device):
+        ident = identity.detach().to("cpu")
+        P, K = ident.shape
+        ranges = [(int(a), int(b)) for a, b in scale_ranges]
+        S = len(ranges)
+        if (ident != 0).sum(dim=1).max().item() > 1 if P else False:
+            raise RuntimeError("prototype_class_identity must give every prototype at most one class")
+        pclass = torch.where((ident != 0).any(dim=1), (ident != 0).float().argmax(dim=1), torch.full((P,), -1)).to(torch.int32) \
+            if P else torch.zeros(0, dtype=torch.int32)
+        pgroup = torch.full((P,), -1, dtype=torch.int32)
+        plocal = torch.zeros((P,), dtype=torch.int32)
+        moff, poff, members, pa, pb = [0], [0], [], [], []
+        for c in range(K):
+            cls = torch.nonzero(ident[:, c]).flatten().tolist()
+            for s, (lo, hi) in enumerate(ranges):
+                ms = [p for p in cls if lo <= p < hi]          # loss.py:105-110
+                g = c * S + s
+                for r, p in enumerate(ms):
+                    pgroup[p], plocal[p] = g, r
+                members += ms
+                for i in range(len(ms)):                       # loss.py:121-127: j, then k > j
+                    for j in range(i + 1, len(ms)):
+                        pa.append(ms[i]), pb.append(ms[j])
+                moff.append(len(members))
+                poff.append(len(pa))
+        # prototypes outside every scale range or without a class never take part; park them in an extra group of size 1
+        self.P, self.K, self.S = P, K, S
+        self.G, self.Q = K * S, len(pa)
+        i32 = dict(dtype=torch.int32, device=device)
+        self.proto_class = pclass.to(device)
+        pgroup = torch.where(pgroup < 0, torch.full_like(pgroup, self.G), pgroup)
+        moff.append(moff[-1]), poff.append(poff[-1])           # the parking group: no members listed, no pairs
+        self.proto_group, self.proto_local = pgroup.to(device), plocal.to(device)
+        self.group_moff, self.group_poff = torch.tensor(moff, **i32), torch.tensor(poff, **i32)
+        self.members = torch.tensor(members + [0] * max(0, 1 - len(members)), **i32)
+        self.pair_a = torch.tensor(pa + [0] * max(0, 1 - len(pa)), **i32)
+        self.pair_b = torch.tensor(pb + [0] * max(0, 1 - len(pb)), **i32)
+
+    def desc(self) -> SpsKldDesc:
+        k = SpsKldDesc()
+        k.G, k.Q = self.G, self.Q
+        k.proto_class, k.proto_group, k.proto_local = (self.proto_class.data_ptr(), self.proto_group.data_ptr(),
+                                                       self.proto_local.data_ptr())
+        k.group_moff, k.group_poff, k.members = (self.group_moff.data_ptr(), self.group_poff.data_ptr(),
+                                                 self.members.data_ptr())
+        k.pair_a, k.pair_b = self.pair_a.data_ptr(), self.pair_b.data_ptr()
+        return k
+
+
+def _desc(B: int, P: int, H: int, W: int, K: int) -> SpsHeadDesc:
+    d = SpsHeadDesc()
+    d.B, d.H, d.W, d.S, d.D, d.P, d.K = B, H, W, 1, 1, P, K
+    d.scale_lo[0] = 0
+    for i in range(1, _lib.SPS_MAX_SCALES + 1):
+        d.scale_lo[i] = P
+    d.act_kind, d.eps, d.math, d.flags = _lib.ACT_LOG, 1e-4, _lib.MATH_FP32, 0
+    return d
+
+
+def labels_int16(target_labels: torch.Tensor, num_classes: int) -> torch.Tensor:
+    """loss.py:77 subtracts 1 and skips what falls outside [0, K) (:90-91): 0 = void stays 0, values above K never
+    match.  Clamped before the 16-bit cast so that e.g. 255 / 65535 cannot wrap into a class id."""
+    t = target_labels.to(torch.int64)
+    return torch.where((t >= 1) & (t <= num_classes), t, torch.zeros_like(t)).to(torch.int16).contiguous()
+
+
+class KldLossFn(torch.autograd.Function):
+    """(distances (B,P,H,W), labels int16 (B,H,W)) -> scalar mean of exp(-kld) over the contributing pairs."""
+
+    @staticmethod
+    def forward(ctx, dist, labels, tables: KldTables):
+        lib = _lib.load()
+        _check_cuda_f32("prototype_distances", dist)
+        if dist.dim() != 4 or dist.shape[1] != tables.P:
+            raise RuntimeError(f"prototype_distances must be (B,{tables.P},H,W), got {tuple(dist.shape)}")
+        if labels.dtype != torch.int16 or not labels.is_cuda or labels.numel() != dist.shape[0] * dist.shape[2] * dist.shape[3]:
+            raise RuntimeError("labels must be CUDA int16 of shape (B,H,W) matching the distance map")
+        dist, labels = dist.contiguous(), labels.contiguous()
+        B, P, H, W = dist.shape
+        desc, kd = _desc(B, P, H, W, tables.K), tables.desc()
+        nbytes = int(lib.sps_kld_workspace_bytes(C.byref(desc), C.byref(kd)))
+        ws = torch.empty(max(nbytes, 16), device=dist.device, dtype=torch.uint8)
+        out = torch.empty(2, device=dist.device, dtype=torch.float32)
+        with torch.cuda.device(dist.device):
+            _lib.check(lib.sps_kld_fwd(C.byref(desc), C.byref(kd), _ptr(dist), _ptr(labels), _ptr(ws), nbytes, _ptr(out),
+                                       _stream()), "sps_kld_fwd")
+        ctx.tables, ctx.nbytes = tables, nbytes
+        ctx.save_for_backward(dist, ws)
+        ctx.mark_non_differentiable(labels)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, dloss):
+        lib = _lib.load()
+        dist, ws = ctx.saved_tensors
+        if not ctx.needs_input_grad[0]:
+            return None, None, None
+        B, P, H, W = dist.shape
+        desc, kd = _desc(B, P, H, W, ctx.tables.K), ctx.tables.desc()
+        g = dloss.to(torch.float32).reshape(1).contiguous()
+        ddist = torch.empty_like(dist, memory_format=torch.contiguous_format)
+        with torch.cuda.device(dist.device):
+            _lib.check(lib.sps_kld_bwd(C.byref(desc), C.byref(kd), _ptr(dist), _ptr(ws), ctx.nbytes, _ptr(g), _ptr(ddist),
+                                       _stream()), "sps_kld_bwd")
+        return ddist, None, None
+
+
+def kld_loss(dist: torch.Tensor, target_labels: torch.Tensor, tables: KldTables) -> torch.Tensor:
+    """Same value as KLDLoss(...)(prototype_distances=dist, target_labels=target_labels) of the reference."""
+    return KldLossFn.apply(dist, labels_int16(target_labels, tables.K).to(dist.device), tables)
+
+
+_TABLE_CACHE: Dict[int, Tuple[tuple, KldTables]] = {}
+
+
+def kld_forward(self, prototype_distances: torch.Tensor, target_labels: torch.Tensor) -> torch.Tensor:
+    """Bound over KLDLoss.forward by install(): `self` is the reference's KLDLoss module (attributes
+    prototype_class_identity, num_scales, scale_num_prototypes; loss.py:56-64)."""
+    if not prototype_distances.is_cuda:
+        raise RuntimeError("scaleprotoseg_b200 KLD loss runs on CUDA only: there is no CPU path")
+    ranges = tuple(tuple(int(v) for v in self.scale_num_prototypes[s]) for s in range(self.num_scales))
+    ident = self.prototype_class_identity
+    sig = (ranges, tuple(ident.shape), int(ident.data_ptr()), int(ident._version), str(prototype_distances.device))
+    hit: Optional[Tuple[tuple, KldTables]] = _TABLE_CACHE.get(id(self))
+    if hit is None or hit[0] != sig:
+        hit = (sig, KldTables(ident, ranges, prototype_distances.device))
+        _TABLE_CACHE[id(self)] = hit
+    return kld_loss(prototype_distances.float(), target_labels, hit[1])

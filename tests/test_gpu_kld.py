@@ -1,0 +1,166 @@
+"""GPU parity of the fused KLD loss (sps_kld_fwd / sps_kld_bwd through the C ABI) against (i) golden vectors produced
+by the reference's KLDLoss (segmentation/model/loss.py:53-146, oracle/gen_golden.py) and (ii) the CPU oracle on
+seeded inputs.
+
+Tolerances: loss |err| <= 1e-4 * max(|ref|, 1e-3) (fp32 sums in a different order than the reference's);
+gradient |err| <= 1e-3 * max|ref| per tensor (the north_star's gradient bound).
+"""
+import os
+
+import numpy as np
+import pytest
+import torch
+import torch.nn as nn
+
+import scaleprotoseg_b200 as sps
+from oracle import head_oracle as ho
+from scaleprotoseg_b200.kld import KldTables, kld_loss
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def _load(golden_dir, name):
+    return {k: v for k, v in np.load(os.path.join(golden_dir, name + ".npz")).items()}
+
+
+def _close_loss(got, ref):
+    got, ref = float(torch.as_tensor(got).detach()), float(torch.as_tensor(ref).detach())
+    assert abs(got - ref) <= 1e-4 * max(abs(ref), 1e-3), f"loss {got} vs {ref}"
+
+
+def _close_grad(got, ref, tol=1e-3):
+    got, ref = got.detach().cpu().double(), torch.as_tensor(ref).double()
+    scale = ref.abs().max().clamp_min(1e-30)
+    err = ((got - ref).abs() / scale).max().item()
+    assert err <= tol, f"ddist: max err {err:.3e} of the largest entry"
+
+
+@pytest.mark.parametrize("name", ["kld_em", "kld_small_ragged", "kld_city228"])
+def test_kld_golden(built_lib, golden_dir, name):
+    g = _load(golden_dir, name)
+    ranges = [tuple(int(v) for v in r) for r in g["ranges"]]
+    tables = KldTables(torch.from_numpy(g["identity"]), ranges, DEV)
+    dist = torch.from_numpy(g["dist"]).to(DEV).requires_grad_(True)
+    loss = kld_loss(dist, torch.from_numpy(g["labels"]).to(DEV), tables)
+    _close_loss(loss, g["loss"])
+    (ddist,) = torch.autograd.grad(loss * float(g["upstream"]), dist)
+    _close_grad(ddist, g["ddist"])
+    # zero exactly where the pixel's class is not the prototype's
+    lab = torch.from_numpy(g["labels"]).reshape(dist.shape[0], 1, -1) - 1
+    pc = torch.from_numpy(g["identity"]).argmax(dim=1).reshape(1, -1, 1)
+    off_class = (lab != pc).reshape(ddist.shape)
+    assert float(ddist.cpu()[off_class].abs().max()) == 0.0
+
+
+def _seeded(B, H, W, P, K, S, seed, block=8, spread=6.0, absent=None):
+    g = torch.Generator().manual_seed(ho.SEED + seed)
+    dist = torch.rand(B, P, H, W, generator=g) * spread
+    labels = torch.stack([ho.make_labels(1000 * seed + i, H, W, K, absent_class=absent, block=block) for i in range(B)])
+    return dist, labels, ho.make_identity(P, K, S), ho.uniform_ranges(P, S)
+
+
+@pytest.mark.parametrize("shape", [(2, 65, 65, 760, 19, 4), (1, 33, 41, 228, 19, 4), (3, 17, 9, 40, 5, 4), (1, 21, 21, 684, 171, 2)])
+def test_kld_vs_oracle(built_lib, shape):
+    B, H, W, P, K, S = shape
+    dist, labels, ident, ranges = _seeded(B, H, W, P, K, S, seed=P + H, absent=2)
+    dref = dist.clone().requires_grad_(True)
+    lref = ho.kld_loss(dref, labels, ident, ranges)
+    (gref,) = torch.autograd.grad(lref * 0.7, dref)
+    d = dist.to(DEV).requires_grad_(True)
+    loss = kld_loss(d, labels.to(DEV), KldTables(ident, ranges, DEV))
+    _close_loss(loss, lref.detach())
+    (gd,) = torch.autograd.grad(loss * 0.7, d)
+    _close_grad(gd, gref)
+
+
+def test_kld_large_distances_do_not_overflow(built_lib):
+    """log_softmax of distances in the hundreds (exp would overflow without the running maximum)."""
+    dist, labels, ident, ranges = _seeded(1, 16, 16, 40, 5, 4, seed=3, spread=300.0)
+    lref = ho.kld_loss(dist.double(), labels, ident, ranges)
+    loss = kld_loss(dist.to(DEV), labels.to(DEV), KldTables(ident, ranges, DEV))
+    assert torch.isfinite(loss).item()
+    _close_loss(loss, lref)
+
+
+def test_kld_no_contribution(built_lib):
+    """Void-only labels and labels above K: loss 0, gradient 0 (loss.py:90-91, 142-146)."""
+    dist, labels, ident, ranges = _seeded(2, 8, 8, 40, 5, 4, seed=4)
+    labels[0] = 0
+    labels[1] = 200
+    d = dist.to(DEV).requires_grad_(True)
+    loss = kld_loss(d, labels.to(DEV), KldTables(ident, ranges, DEV))
+    assert float(loss) == 0.0
+    (gd,) = torch.autograd.grad(loss, d)
+    assert float(gd.abs().max()) == 0.0
+
+
+def test_kld_full_size_properties(built_lib):
+    """BASELINE.json configs[1] size (B=16, 65x65, P=760, K=19), where the oracle would take minutes:
+    (i) log_softmax is shift-invariant: adding a constant per (image, prototype) row leaves the loss unchanged;
+    (ii) the gradient of every row sums to zero over the map (softmax Jacobian), and is zero off-class;
+    (iii) identical distance rows inside a group give kld = 0 for its pairs, i.e. loss exactly 1 when all rows agree."""
+    B, H, W, P, K, S = 16, 65, 65, 760, 19, 4
+    dist, labels, ident, ranges = _seeded(B, H, W, P, K, S, seed=9)
+    tables = KldTables(ident, ranges, DEV)
+    d = dist.to(DEV).requires_grad_(True)
+    lab = labels.to(DEV)
+    loss = kld_loss(d, lab, tables)
+    shift = torch.rand(B, P, 1, 1, device=DEV) * 3.0
+    loss_shift = kld_loss(d.detach() + shift, lab, tables)
+    assert abs(float(loss) - float(loss_shift)) <= 1e-4 * max(float(loss), 1e-3)
+    (gd,) = torch.autograd.grad(loss, d)
+    rows = gd.reshape(B, P, -1)
+    assert float(rows.sum(dim=2).abs().max()) <= 1e-3 * float(rows.abs().sum(dim=2).max())
+    pc = ident.argmax(dim=1).to(DEV).reshape(1, P, 1)
+    off_class = (lab.reshape(B, 1, -1) - 1) != pc
+    assert float(rows[off_class].abs().max()) == 0.0
+    same = torch.rand(B, 1, H, W, device=DEV).expand(B, P, H, W).contiguous()
+    assert abs(float(kld_loss(same, lab, tables)) - 1.0) <= 1e-5
+
+
+class _KLDLossStandin(nn.Module):
+    """Same attributes as the reference's KLDLoss (loss.py:56-64); its own forward is the CPU oracle."""
+
+    def __init__(self, prototype_class_identity, num_scales, scale_num_prototypes):
+        super().__init__()
+        self.prototype_class_identity = prototype_class_identity
+        self.num_scales = num_scales
+        self.scale_num_prototypes = scale_num_prototypes
+
+    def forward(self, prototype_distances, target_labels):
+        ranges = [self.scale_num_prototypes[s] for s in range(self.num_scales)]
+        return ho.kld_loss(prototype_distances, target_labels, self.prototype_class_identity, ranges)
+
+
+def test_kld_dropin_through_install(built_lib):
+    """install_kld binds the kernels over KLDLoss.forward: CUDA distances run the fused path, CPU distances keep the
+    original loop; a stage-1 style step (head forward in dense mode -> KLD -> backward into z and prototypes) matches."""
+    B, H, W, P, K, S, D = 2, 13, 11, 228, 19, 4, 64
+    ident, ranges = ho.make_identity(P, K, S), ho.uniform_ranges(P, S)
+    labels = torch.stack([ho.make_labels(50 + i, H, W, K, block=4) for i in range(B)])
+    torch.manual_seed(ho.SEED)
+    z = torch.sigmoid(torch.randn(B, S * D, H, W))
+    protos = torch.rand(P, D, 1, 1)
+    last_w = ho.make_last_layer(ident)
+    mod = _KLDLossStandin(ident, S, {s: r for s, r in enumerate(ranges)})
+    zr, pr = z.clone().requires_grad_(True), protos.clone().requires_grad_(True)
+    _, dist_ref, _ = ho.head_stage1(zr, pr, ranges, last_w)
+    loss_ref = mod(prototype_distances=dist_ref, target_labels=labels)
+    loss_ref.backward()
+    sps.install_kld(_KLDLossStandin)
+    try:
+        assert hasattr(_KLDLossStandin.forward, "__sps_original__")
+        _close_loss(mod(prototype_distances=dist_ref.detach(), target_labels=labels), loss_ref.detach())   # CPU: original
+        cfg = sps.HeadConfig.from_ranges(ranges, K, math=sps.MATH_FP32)
+        zc, pc = z.to(DEV).requires_grad_(True), protos.to(DEV).requires_grad_(True)
+        _, dist, _ = sps.PrototypeHeadFn.apply(zc, pc, last_w.to(DEV), cfg, True, True)
+        loss = mod(prototype_distances=dist, target_labels=labels.to(DEV))
+        assert loss.is_cuda
+        _close_loss(loss, loss_ref.detach())
+        loss.backward()
+        _close_grad(zc.grad, zr.grad, tol=2e-3)
+        _close_grad(pc.grad, pr.grad, tol=2e-3)
+    finally:
+        sps.uninstall()
+    assert not hasattr(_KLDLossStandin.forward, "__sps_original__")

@@ -103,3 +103,27 @@ def test_push_two_rank_exchange_gloo(tmp_path):
     port = 29500 + (os.getpid() % 2000)
     mp.spawn(_rank_main, args=(2, port, out), nprocs=2, join=True)
     assert open(out).read() == "ok"
+
+
+def test_kld_tables_follow_the_reference_pair_order():
+    """Groups = (class, scale) in class-major order, members ascending, pairs (j, k > j) as loss.py:105-127."""
+    from scaleprotoseg_b200.kld import KldTables, labels_int16
+    ident = ho.make_identity(24, 2, 4)
+    keep = [p for p in range(24) if p not in (1, 7, 8)]          # ragged: class 0 keeps one prototype in scale 1
+    ranges = [(0, 5), (5, 9), (9, 15), (15, 21)]
+    t = KldTables(ident[keep], ranges, "cpu")
+    assert t.G == 8 and t.P == 21
+    sizes = (t.group_moff[1:] - t.group_moff[:-1]).tolist()
+    assert sizes == [2, 1, 3, 3, 3, 3, 3, 3, 0]                  # last = parking group for unassigned prototypes
+    assert t.Q == sum(m * (m - 1) // 2 for m in sizes)
+    for g in range(t.G):
+        ms = t.members[t.group_moff[g]:t.group_moff[g + 1]].tolist()
+        assert ms == sorted(ms)
+        want = [(ms[i], ms[j]) for i in range(len(ms)) for j in range(i + 1, len(ms))]
+        got = list(zip(t.pair_a[t.group_poff[g]:t.group_poff[g + 1]].tolist(),
+                       t.pair_b[t.group_poff[g]:t.group_poff[g + 1]].tolist()))
+        assert got == want
+        for r, p in enumerate(ms):
+            assert int(t.proto_group[p]) == g and int(t.proto_local[p]) == r
+    lab = labels_int16(torch.tensor([[0, 1, 2, 3, 255, 65537, -1]]), 2)
+    assert lab.tolist() == [[0, 1, 2, 0, 0, 0, 0]]

@@ -77,3 +77,28 @@ def test_push(golden_dir, name):
 
 def test_golden_files_present(golden_dir):
     assert len(glob.glob(os.path.join(golden_dir, "*.npz"))) >= 8
+
+
+KLD_CASES = ["kld_em", "kld_small_ragged", "kld_city228"]
+
+
+@pytest.mark.parametrize("name", KLD_CASES)
+def test_kld_loss_and_gradient(golden_dir, name):
+    """ho.kld_loss against KLDLoss.forward of the reference (segmentation/model/loss.py:66-146): value, and the
+    gradient autograd takes through the reference's masked_select / log_softmax / kl_div chain."""
+    g = _load(golden_dir, name)
+    dist = torch.from_numpy(g["dist"]).requires_grad_(True)
+    loss = ho.kld_loss(dist, torch.from_numpy(g["labels"]), torch.from_numpy(g["identity"]), _ranges(g))
+    np.testing.assert_allclose(loss.detach().numpy(), g["loss"], rtol=1e-5, atol=1e-7)
+    (ddist,) = torch.autograd.grad(loss * float(g["upstream"]), dist)
+    np.testing.assert_allclose(ddist.numpy(), g["ddist"], rtol=1e-4, atol=1e-7)
+
+
+def test_kld_no_contribution_is_zero():
+    """Void-only labels, or one pixel per class: no pair contributes and the loss is 0 (loss.py:142-146)."""
+    ident, ranges = ho.make_identity(24, 2, 4), ho.uniform_ranges(24, 4)
+    dist = torch.rand(1, 24, 3, 3)
+    assert float(ho.kld_loss(dist, torch.zeros(1, 3, 3, dtype=torch.int64), ident, ranges)) == 0.0
+    one_each = torch.zeros(1, 3, 3, dtype=torch.int64)
+    one_each[0, 0, 0], one_each[0, 2, 2] = 1, 2
+    assert float(ho.kld_loss(dist, one_each, ident, ranges)) == 0.0
