@@ -385,13 +385,42 @@ def measure_kld(ctx, args):
     for i in range(3):
         step(i)
     ms_fwd, ms = event_ms(fwd, iters), event_ms(step, iters)
+    # feature mode: the same loss from z and the prototypes, no (B,P,H,W) map; and the whole stage-1 style step on it
+    # (fused head fwd + bwd on dlogits, plus this loss's own dz / dprototypes)
+    z0 = ctx["zs"][0].detach().requires_grad_(True)
+    pv = ctx["protos"].detach().requires_grad_(True)
+    cfg32 = sps.HeadConfig.from_ranges(ranges, c["K"], math=sps.MATH_FP32)
+
+    def feat_step(i):
+        z0.grad = pv.grad = None
+        sps.kld_loss_from_features(z0, pv, lab_dev, tables, cfg32).backward()
+
+    def train_step(i):
+        z0.grad = pv.grad = None
+        logits = sps.PrototypeHeadFn.apply(z0, pv, ctx["last_w"], ctx["cfg"], False, False)[0]
+        loss = sps.kld_loss_from_features(z0, pv, lab_dev, tables, cfg32)
+        torch.autograd.backward([logits, loss], [ctx["dls"][0].reshape(logits.shape), torch.ones_like(loss)])
+
+    def train_step_dense(i):
+        z0.grad = pv.grad = None
+        logits, dmap, _ = sps.PrototypeHeadFn.apply(z0, pv, ctx["last_w"], ctx["cfg"], True, False)
+        loss = kld_loss(dmap, lab_dev, tables)
+        torch.autograd.backward([logits, loss], [ctx["dls"][0].reshape(logits.shape), torch.ones_like(loss)])
+
+    for i in range(3):
+        feat_step(i), train_step(i), train_step_dense(i)
+    ms_feat, ms_train, ms_train_dense = event_ms(feat_step, iters), event_ms(train_step, iters), event_ms(train_step_dense, iters)
     n = c["B"] * c["H"] * c["W"]
     per_cs = c["P"] // c["K"] // c["S"]
     touched = n * c["S"] * per_cs                      # (pixel, prototype) pairs whose classes agree
     out = {"workload": "KLD loss between same-class prototypes on the dense distance map of the same batch "
                        "(B=%d, P=%d: %d pairs per image, %d class-matched (pixel, prototype) pairs)" % (c["B"], c["P"], tables.Q, touched),
            "ms_fwd": ms_fwd, "ms_fwd_bwd": ms, "loss": float(fwd(0).detach()),
-           "note": "backward includes the zero fill of the 205 MB gradient map the head backward then reads"}
+           "note": "backward includes the zero fill of the 205 MB gradient map the head backward then reads",
+           "feature_mode_ms_fwd_bwd": ms_feat,
+           "train_step_ms": {"fused head + feature-mode KLD (no distance map)": ms_train,
+                             "dense head + KLD on the map + head backward through ddist": ms_train_dense},
+           "train_step_note": "autograd step incl. Python dispatch: head forward, loss, head backward, gradients accumulated"}
     if not args.no_cpu:
         import time
         d1 = dist.detach()[:1].cpu()

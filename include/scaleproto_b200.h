@@ -87,6 +87,8 @@ typedef struct SpsGroupDesc {
 typedef struct SpsKldDesc {
   int32_t G;                  /* groups = K * S (empty groups allowed) */
   int32_t Q;                  /* pairs over all groups */
+  int32_t mmax;               /* largest group size (rows per scale of the compact distance block, feature mode) */
+  int32_t reserved;           /* 0 */
   const int32_t* proto_class; /* [P] class of prototype p (argmax of prototype_class_identity) */
   const int32_t* proto_group; /* [P] group of p */
   const int32_t* proto_local; /* [P] rank of p inside its group */
@@ -164,6 +166,21 @@ int sps_kld_fwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* dist,
  * ddist [B, P, H, W] OVERWRITTEN (zero wherever the pixel's class differs from the prototype's). */
 int sps_kld_bwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* dist, void* workspace,
                 size_t workspace_bytes, const float* dloss, float* ddist, void* stream);
+
+/* The same loss straight from the feature maps ("feature mode"): the distances the loss needs are only those between a
+ * pixel and the prototypes of the pixel's own class (1/K of the map), so they are computed here from z and the
+ * prototypes into a compact block inside the workspace and the (B,P,H,W) map is never needed — the head can run in
+ * fused mode (dist = NULL) during stage-1 training.  desc carries the head's S, D and scale_lo; every group must
+ * lie inside one scale (it does by construction) and hold at most 32 prototypes.
+ *   z [B,S*D,H,W], protos [P,D], labels as above; loss [2] as sps_kld_fwd.
+ *   sps_kld_feat_bwd: dz [B,S*D,H,W] and dprotos [P,D] (either may be NULL) are OVERWRITTEN with the loss's own
+ *   gradient (the caller adds them to the head's); workspace as left by sps_kld_feat_fwd. */
+size_t sps_kld_feat_workspace_bytes(const SpsHeadDesc* desc, const SpsKldDesc* k);
+int sps_kld_feat_fwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* z, const float* protos,
+                     const int16_t* labels, void* workspace, size_t workspace_bytes, float* loss, void* stream);
+int sps_kld_feat_bwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* z, const float* protos,
+                     const int16_t* labels, void* workspace, size_t workspace_bytes, const float* dloss, float* dz,
+                     float* dprotos, void* stream);
 
 /* Push scan: per map and per prototype, the nearest position among those labelled with the
  * prototype's class.  Replaces compute_distances lines 68-91 of

@@ -38,7 +38,7 @@ class SpsGroupDesc(C.Structure):
 
 class SpsKldDesc(C.Structure):
     _fields_ = [
-        ("G", C.c_int32), ("Q", C.c_int32),
+        ("G", C.c_int32), ("Q", C.c_int32), ("mmax", C.c_int32), ("reserved", C.c_int32),
         ("proto_class", C.c_void_p), ("proto_group", C.c_void_p), ("proto_local", C.c_void_p),
         ("group_moff", C.c_void_p), ("group_poff", C.c_void_p), ("members", C.c_void_p),
         ("pair_a", C.c_void_p), ("pair_b", C.c_void_p),
@@ -61,6 +61,10 @@ _SIGNATURES = {
     "sps_kld_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc)]),
     "sps_kld_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc), _P, _P, _P, C.c_size_t, _P, _P]),
     "sps_kld_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc), _P, _P, C.c_size_t, _P, _P, _P]),
+    "sps_kld_feat_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc)]),
+    "sps_kld_feat_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc), _P, _P, _P, _P, C.c_size_t, _P, _P]),
+    "sps_kld_feat_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc), _P, _P, _P, _P, C.c_size_t, _P, _P, _P,
+                                   _P]),
     "sps_push_scan": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "sps_push_reduce": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint32, _P, _P]),
     "sps_push_gather": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, C.c_int32, C.c_uint32, _P, _P, _P]),

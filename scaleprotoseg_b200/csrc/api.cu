@@ -201,6 +201,56 @@ int sps_kld_bwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* dist,
   return launch_kld_bwd(s, *k, dist, workspace, dloss, ddist, reinterpret_cast<cudaStream_t>(stream));
 }
 
+static int check_kld_feat(const SpsHeadDesc* desc, const SpsKldDesc* k) {
+  int rc = validate_desc(desc);
+  if (rc != SPS_OK) return rc;
+  rc = check_kld(k);
+  if (rc != SPS_OK) return rc;
+  SPS_REQUIRE(k->mmax >= 1 && k->mmax <= 32, SPS_ERR_UNSUPPORTED, "kld feature mode: largest group %d outside [1,32]",
+              k->mmax);
+  SPS_REQUIRE(k->G == desc->K * desc->S, SPS_ERR_BAD_ARG, "kld feature mode: G=%d must be K*S=%d", k->G,
+              desc->K * desc->S);
+  return SPS_OK;
+}
+
+size_t sps_kld_feat_workspace_bytes(const SpsHeadDesc* desc, const SpsKldDesc* k) {
+  if (validate_desc(desc) != SPS_OK || k == nullptr || k->Q < 0 || k->mmax < 1) return 0;
+  return kld_feat_workspace(make_shape(desc), *k);
+}
+
+int sps_kld_feat_fwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* z, const float* protos,
+                     const int16_t* labels, void* workspace, size_t workspace_bytes, float* loss, void* stream) {
+  int rc = check_kld_feat(desc, k);
+  if (rc != SPS_OK) return rc;
+  SPS_REQUIRE(loss != nullptr, SPS_ERR_BAD_ARG, "kld_feat_fwd: loss NULL");
+  HeadShape s = make_shape(desc);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (s.N == 0 || s.P == 0) {
+    SPS_CUDA_TRY(cudaMemsetAsync(loss, 0, 2 * sizeof(float), st));
+    return SPS_OK;
+  }
+  SPS_REQUIRE(z && protos && labels, SPS_ERR_BAD_ARG, "kld_feat_fwd: NULL argument");
+  size_t need = kld_feat_workspace(s, *k);
+  SPS_REQUIRE(workspace != nullptr && workspace_bytes >= need, SPS_ERR_WORKSPACE,
+              "kld feature workspace: need %zu bytes, got %zu", need, workspace_bytes);
+  return launch_kld_feat_fwd(s, *k, z, protos, labels, workspace, loss, st);
+}
+
+int sps_kld_feat_bwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* z, const float* protos,
+                     const int16_t* labels, void* workspace, size_t workspace_bytes, const float* dloss, float* dz,
+                     float* dprotos, void* stream) {
+  int rc = check_kld_feat(desc, k);
+  if (rc != SPS_OK) return rc;
+  HeadShape s = make_shape(desc);
+  if (s.N == 0 || s.P == 0) return SPS_OK;
+  SPS_REQUIRE(z && protos && labels && dloss, SPS_ERR_BAD_ARG, "kld_feat_bwd: NULL argument");
+  size_t need = kld_feat_workspace(s, *k);
+  SPS_REQUIRE(workspace != nullptr && workspace_bytes >= need, SPS_ERR_WORKSPACE,
+              "kld feature workspace: need %zu bytes, got %zu", need, workspace_bytes);
+  return launch_kld_feat_bwd(s, *k, z, protos, labels, workspace, dloss, dz, dprotos,
+                             reinterpret_cast<cudaStream_t>(stream));
+}
+
 int sps_push_scan(const SpsHeadDesc* desc, const float* z, const float* protos, const int16_t* labels,
                   const int32_t* proto_class, uint64_t* keys, void* workspace, size_t workspace_bytes, void* stream) {
   int rc = validate_desc(desc);

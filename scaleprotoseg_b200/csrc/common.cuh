@@ -125,4 +125,11 @@ int launch_kld_fwd(const HeadShape& s, const SpsKldDesc& k, const float* dist, c
 int launch_kld_bwd(const HeadShape& s, const SpsKldDesc& k, const float* dist, void* ws, const float* dloss,
                    float* ddist, cudaStream_t st);
 
+size_t kld_feat_workspace(const HeadShape& s, const SpsKldDesc& k);
+int launch_kld_feat_fwd(const HeadShape& s, const SpsKldDesc& k, const float* z, const float* protos,
+                        const int16_t* labels, void* ws, float* loss, cudaStream_t st);
+int launch_kld_feat_bwd(const HeadShape& s, const SpsKldDesc& k, const float* z, const float* protos,
+                        const int16_t* labels, void* ws, const float* dloss, float* dz, float* dprotos,
+                        cudaStream_t st);
+
 }  // namespace sps

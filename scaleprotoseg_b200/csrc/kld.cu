@@ -80,8 +80,20 @@ __global__ void kld_bucket_kernel(const int16_t* __restrict__ labels, int HW, in
   }
 }
 
+// Row of prototype p inside one image's distance block.  Dense map: the prototype itself (rows = P).  Compact map
+// (feature mode): row (scale, rank inside the (class, scale) group) of rows = S * mmax, where the entry at pixel x
+// belongs to the group of x's own class — the only prototypes the loss ever pairs with that pixel.
+struct RowMap {
+  int compact, rows, S, mmax;
+  const int* proto_group;
+  const int* proto_local;
+  __device__ __forceinline__ int operator()(int p) const {
+    return compact ? (proto_group[p] % S) * mmax + proto_local[p] : p;
+  }
+};
+
 // lse[b*P + p] = log sum_x exp(d[b,p,x]) over the pixels of p's class (loss.py:112-115 log_softmax denominator).
-__global__ void kld_lse_kernel(const float* __restrict__ dist, int B, int P, int HW, int K,
+__global__ void kld_lse_kernel(const float* __restrict__ dist, RowMap rm, int B, int P, int HW, int K,
                                const int* __restrict__ proto_class, const int* __restrict__ cnt,
                                const int* __restrict__ off, const int* __restrict__ idx, float* __restrict__ lse) {
   const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -95,7 +107,7 @@ __global__ void kld_lse_kernel(const float* __restrict__ dist, int B, int P, int
     return;
   }
   const int* ix = idx + (size_t)b * HW + off[b * K + c];
-  const float* row = dist + ((size_t)b * P + p) * HW;
+  const float* row = dist + ((size_t)b * rm.rows + rm(p)) * HW;
   float mx = -INFINITY;
   for (int i = lane; i < n; i += 32) mx = fmaxf(mx, row[ix[i]]);
 #pragma unroll
@@ -108,7 +120,7 @@ __global__ void kld_lse_kernel(const float* __restrict__ dist, int B, int P, int
 
 // One warp per (image, pair q): kl[b*Q+q] = (KL(a||b), KL(b||a)), term[b*Q+q] = exp(-(sum)/2), or -1 when the pair
 // does not contribute (class absent from the image or fewer than two pixels, loss.py:117-135).
-__global__ void kld_pairs_kernel(const float* __restrict__ dist, int B, int P, int HW, int K, int Q,
+__global__ void kld_pairs_kernel(const float* __restrict__ dist, RowMap rm, int B, int P, int HW, int K, int Q,
                                  const int* __restrict__ pair_a, const int* __restrict__ pair_b,
                                  const int* __restrict__ proto_class, const int* __restrict__ cnt,
                                  const int* __restrict__ off, const int* __restrict__ idx,
@@ -128,8 +140,8 @@ __global__ void kld_pairs_kernel(const float* __restrict__ dist, int B, int P, i
     return;
   }
   const int* ix = idx + (size_t)b * HW + off[b * K + c];
-  const float* ra = dist + ((size_t)b * P + pa) * HW;
-  const float* rb = dist + ((size_t)b * P + pb) * HW;
+  const float* ra = dist + ((size_t)b * rm.rows + rm(pa)) * HW;
+  const float* rb = dist + ((size_t)b * rm.rows + rm(pb)) * HW;
   const float la = lse[(size_t)b * P + pa], lb = lse[(size_t)b * P + pb];
   float kab = 0.0f, kba = 0.0f;
   for (int i = lane; i < n; i += 32) {
@@ -183,7 +195,7 @@ __global__ void kld_finish_kernel(const float* __restrict__ term, long long tota
 // One warp per (image, prototype a): for every pixel y of a's class,
 //   ddist[b,a,y] = dloss * sum_{b' != a in group} (-term_ab'/M) * 1/2 * p_a(y) * (l_a(y) - l_b'(y) + 1 - KL(a||b')) - p_b'(y)
 // (derivative of exp(-kld) through the two log_softmax; the rest of ddist was zeroed by the caller).
-__global__ void kld_bwd_kernel(const float* __restrict__ dist, int B, int P, int HW, int K, int Q,
+__global__ void kld_bwd_kernel(const float* __restrict__ dist, RowMap rm, int B, int P, int HW, int K, int Q,
                                const int* __restrict__ proto_class, const int* __restrict__ proto_group,
                                const int* __restrict__ proto_local, const int* __restrict__ group_moff,
                                const int* __restrict__ group_poff, const int* __restrict__ members,
@@ -205,8 +217,8 @@ __global__ void kld_bwd_kernel(const float* __restrict__ dist, int B, int P, int
   const int q0 = group_poff[g];
   const float scale = -0.5f * dloss[0] / M;
   const int* ix = idx + (size_t)b * HW + off[b * K + c];
-  const float* ra = dist + ((size_t)b * P + p) * HW;
-  float* ga = ddist + ((size_t)b * P + p) * HW;
+  const float* ra = dist + ((size_t)b * rm.rows + rm(p)) * HW;
+  float* ga = ddist + ((size_t)b * rm.rows + rm(p)) * HW;
   const float la = lse[(size_t)b * P + p];
   for (int i = lane; i < n; i += 32) {
     const int x = ix[i];
@@ -221,11 +233,141 @@ __global__ void kld_bwd_kernel(const float* __restrict__ dist, int B, int P, int
       const float w = term[(size_t)b * Q + q];
       const float k_ab = a < o ? k2.x : k2.y;  // KL(a || o)
       const int po = members[m0 + o];
-      const float l_o = dist[((size_t)b * P + po) * HW + x] - lse[(size_t)b * P + po];
+      const float l_o = dist[((size_t)b * rm.rows + rm(po)) * HW + x] - lse[(size_t)b * P + po];
       acc += w * (p_a * (l_a - l_o + 1.0f - k_ab) - expf(l_o));
     }
     ga[x] = scale * acc;
   }
+}
+
+
+// ---- feature mode: the class-matched distances straight from z, no (B,P,H,W) map --------------------------------
+constexpr int FEAT_THREADS = 128;
+constexpr int FEAT_MMAX = 32;  // largest (class, scale) group the shared-memory gradient tile holds
+
+// dc[b][s*mmax + j][x] = |z_s(x) - p_j|^2 for the j-th prototype of group (class(x), s)  (the value
+// _l2_convolution gives, model_multiscale.py:256-281, in its difference form: never negative, so no clamp).
+__global__ void kld_feat_dist_kernel(const float* __restrict__ z, const float* __restrict__ protos,
+                                     const int16_t* __restrict__ labels, int HW, int K, int S, int D, int mmax,
+                                     const int* __restrict__ group_moff, const int* __restrict__ members,
+                                     float* __restrict__ dc) {
+  const int x = blockIdx.x * FEAT_THREADS + threadIdx.x, s = blockIdx.y, b = blockIdx.z;
+  if (x >= HW) return;
+  const int c = (int)labels[(size_t)b * HW + x] - 1;
+  if (c < 0 || c >= K) return;
+  const int g = c * S + s, m0 = group_moff[g], m = group_moff[g + 1] - m0;
+  const float* zp = z + ((size_t)b * S * D + (size_t)s * D) * HW + x;
+  float* out = dc + ((size_t)b * S * mmax + (size_t)s * mmax) * HW + x;
+  for (int j = 0; j < m; ++j) {
+    const float* pv = protos + (size_t)members[m0 + j] * D;
+    float a0 = 0.0f, a1 = 0.0f;
+    int ch = 0;
+    for (; ch + 1 < D; ch += 2) {
+      const float d0 = zp[(size_t)ch * HW] - pv[ch], d1 = zp[(size_t)(ch + 1) * HW] - pv[ch + 1];
+      a0 = fmaf(d0, d0, a0);
+      a1 = fmaf(d1, d1, a1);
+    }
+    if (ch < D) {
+      const float d0 = zp[(size_t)ch * HW] - pv[ch];
+      a0 = fmaf(d0, d0, a0);
+    }
+    out[(size_t)j * HW] = a0 + a1;
+  }
+}
+
+// dz[b, s*D + ch, x] = 2 * sum_j g_j(x) * (z - p_j)[ch] over the group of x's class; 0 for void pixels.
+__global__ void kld_feat_dz_kernel(const float* __restrict__ z, const float* __restrict__ protos,
+                                   const int16_t* __restrict__ labels, int HW, int K, int S, int D, int mmax,
+                                   const int* __restrict__ group_moff, const int* __restrict__ members,
+                                   const float* __restrict__ gc, float* __restrict__ dz) {
+  __shared__ float gs[FEAT_MMAX][FEAT_THREADS];
+  const int x = blockIdx.x * FEAT_THREADS + threadIdx.x, s = blockIdx.y, b = blockIdx.z;
+  if (x >= HW) return;
+  const int c = (int)labels[(size_t)b * HW + x] - 1;
+  float* dzp = dz + ((size_t)b * S * D + (size_t)s * D) * HW + x;
+  int m0 = 0, m = 0;
+  if (c >= 0 && c < K) {
+    m0 = group_moff[c * S + s];
+    m = group_moff[c * S + s + 1] - m0;
+  }
+  float gsum = 0.0f;
+  const float* gp = gc + ((size_t)b * S * mmax + (size_t)s * mmax) * HW + x;
+  for (int j = 0; j < m; ++j) {
+    const float g = gp[(size_t)j * HW];
+    gs[j][threadIdx.x] = g;
+    gsum += g;
+  }
+  const float* zp = z + ((size_t)b * S * D + (size_t)s * D) * HW + x;
+  for (int ch = 0; ch < D; ++ch) {
+    float acc = 0.0f;
+    if (m > 0) {
+      acc = gsum * zp[(size_t)ch * HW];
+      for (int j = 0; j < m; ++j) acc = fmaf(-gs[j][threadIdx.x], protos[(size_t)members[m0 + j] * D + ch], acc);
+    }
+    dzp[(size_t)ch * HW] = 2.0f * acc;
+  }
+}
+
+// part[b][p][ch] = 2 * sum_x g_p(x) * (p - z_s(x))[ch] over the pixels of p's class in image b.  One CTA per
+// (group, image): tiles of 32 bucketed pixels staged in shared memory (z tile D x 32, gradient tile m x 32).
+__global__ void kld_feat_dp_kernel(const float* __restrict__ z, const float* __restrict__ protos, int HW, int K, int S,
+                                   int D, int P, int mmax, const int* __restrict__ group_moff,
+                                   const int* __restrict__ members, const int* __restrict__ cnt,
+                                   const int* __restrict__ off, const int* __restrict__ idx,
+                                   const float* __restrict__ gc, float* __restrict__ part) {
+  extern __shared__ float sm[];  // zt[D][33], gt[mmax][33]
+  const int g = blockIdx.x, b = blockIdx.y;
+  const int c = g / S, s = g % S;
+  const int m0 = group_moff[g], m = group_moff[g + 1] - m0;
+  if (m == 0) return;
+  float* zt = sm;
+  float* gt = sm + (size_t)D * 33;
+  const int n = cnt[b * K + c];
+  const int* ix = idx + (size_t)b * HW + off[b * K + c];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
+  // thread t owns output elements e = t, t + blockDim, ... of the m x D block (e = j*D + ch)
+  constexpr int MAXE = 8;
+  float acc[MAXE];
+#pragma unroll
+  for (int e = 0; e < MAXE; ++e) acc[e] = 0.0f;
+  const float* zb = z + ((size_t)b * S * D + (size_t)s * D) * HW;
+  const float* gb = gc + ((size_t)b * S * mmax + (size_t)s * mmax) * HW;
+  for (int i0 = 0; i0 < n; i0 += 32) {
+    const int i = i0 + lane;
+    const int x = i < n ? ix[i] : -1;
+    for (int ch = warp; ch < D; ch += nw) zt[ch * 33 + lane] = x >= 0 ? zb[(size_t)ch * HW + x] : 0.0f;
+    for (int j = warp; j < m; j += nw) gt[j * 33 + lane] = x >= 0 ? gb[(size_t)j * HW + x] : 0.0f;
+    __syncthreads();
+#pragma unroll
+    for (int e = 0; e < MAXE; ++e) {
+      const int el = threadIdx.x + e * blockDim.x;
+      if (el < m * D) {
+        const int j = el / D, ch = el % D;
+        const float pv = protos[(size_t)members[m0 + j] * D + ch];
+        float a = acc[e];
+#pragma unroll 8
+        for (int t = 0; t < 32; ++t) a = fmaf(gt[j * 33 + t], pv - zt[ch * 33 + t], a);
+        acc[e] = a;
+      }
+    }
+    __syncthreads();
+  }
+#pragma unroll
+  for (int e = 0; e < MAXE; ++e) {
+    const int el = threadIdx.x + e * blockDim.x;
+    if (el < m * D) part[((size_t)b * P + members[m0 + el / D]) * D + el % D] = 2.0f * acc[e];
+  }
+}
+
+// dprotos[p][ch] = sum_b part[b][p][ch] (fixed order); prototypes outside every group get 0.
+__global__ void kld_feat_dp_reduce_kernel(const float* __restrict__ part, int B, long long PD,
+                                          const int* __restrict__ proto_class, int D, float* __restrict__ dprotos) {
+  const long long e = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (e >= PD) return;
+  float a = 0.0f;
+  if (proto_class[e / D] >= 0)
+    for (int b = 0; b < B; ++b) a += part[(size_t)b * PD + e];
+  dprotos[e] = a;
 }
 
 inline size_t align16(size_t v) { return (v + 15) & ~(size_t)15; }
@@ -234,10 +376,11 @@ struct KldCarve {
   int *cnt, *off, *idx;
   float *lse, *term, *fin;
   float2* kl;
+  float *dc, *gc, *part;  // feature mode only
   size_t bytes;
 };
 
-KldCarve carve(const HeadShape& s, int Q, void* ws) {
+KldCarve carve(const HeadShape& s, int Q, void* ws, int feat_rows = 0) {
   char* base = reinterpret_cast<char*>(ws);
   size_t o = 0;
   KldCarve k;
@@ -253,6 +396,12 @@ KldCarve carve(const HeadShape& s, int Q, void* ws) {
   k.lse = reinterpret_cast<float*>(take(sizeof(float) * (size_t)s.B * s.P));
   k.term = reinterpret_cast<float*>(take(sizeof(float) * (size_t)s.B * Q));
   k.kl = reinterpret_cast<float2*>(take(sizeof(float2) * (size_t)s.B * Q));
+  k.dc = k.gc = k.part = nullptr;
+  if (feat_rows > 0) {
+    k.dc = reinterpret_cast<float*>(take(sizeof(float) * (size_t)s.B * feat_rows * s.HW));
+    k.gc = reinterpret_cast<float*>(take(sizeof(float) * (size_t)s.B * feat_rows * s.HW));
+    k.part = reinterpret_cast<float*>(take(sizeof(float) * (size_t)s.B * s.P * s.D));
+  }
   k.bytes = o;
   return k;
 }
@@ -263,17 +412,29 @@ inline unsigned warps_grid(long long warps) { return (unsigned)((warps * 32 + KL
 
 size_t kld_workspace(const HeadShape& s, int Q) { return carve(s, Q, nullptr).bytes; }
 
-int launch_kld_fwd(const HeadShape& s, const SpsKldDesc& k, const float* dist, const int16_t* labels, void* ws,
-                   float* loss, cudaStream_t st) {
-  KldCarve w = carve(s, k.Q, ws);
+namespace {
+
+RowMap dense_rows(const HeadShape& s) { return RowMap{0, s.P, 1, 1, nullptr, nullptr}; }
+RowMap compact_rows(const HeadShape& s, const SpsKldDesc& k) {
+  return RowMap{1, s.S * k.mmax, s.S, k.mmax, k.proto_group, k.proto_local};
+}
+
+void launch_buckets(const HeadShape& s, const int16_t* labels, const KldCarve& w, cudaStream_t st) {
   kld_hist_kernel<<<s.B, KLD_THREADS, sizeof(int) * s.K, st>>>(labels, s.HW, s.K, w.cnt, w.off);
   kld_bucket_kernel<<<dim3(s.K, s.B), KLD_THREADS, 0, st>>>(labels, s.HW, s.K, w.cnt, w.off, w.idx);
-  kld_lse_kernel<<<warps_grid((long long)s.B * s.P), KLD_THREADS, 0, st>>>(dist, s.B, s.P, s.HW, s.K, k.proto_class,
-                                                                          w.cnt, w.off, w.idx, w.lse);
-  int launched = 3;
+  count_launch(2);
+}
+
+// lse -> pairs -> mean over a dense or compact distance block; copies (loss, count) out
+int launch_stats(const HeadShape& s, const SpsKldDesc& k, const float* dist, RowMap rm, const KldCarve& w, float* loss,
+                 cudaStream_t st) {
+  kld_lse_kernel<<<warps_grid((long long)s.B * s.P), KLD_THREADS, 0, st>>>(dist, rm, s.B, s.P, s.HW, s.K,
+                                                                          k.proto_class, w.cnt, w.off, w.idx, w.lse);
+  int launched = 1;
   if (k.Q > 0) {
-    kld_pairs_kernel<<<warps_grid((long long)s.B * k.Q), KLD_THREADS, 0, st>>>(
-        dist, s.B, s.P, s.HW, s.K, k.Q, k.pair_a, k.pair_b, k.proto_class, w.cnt, w.off, w.idx, w.lse, w.kl, w.term);
+    kld_pairs_kernel<<<warps_grid((long long)s.B * k.Q), KLD_THREADS, 0, st>>>(dist, rm, s.B, s.P, s.HW, s.K, k.Q,
+                                                                              k.pair_a, k.pair_b, k.proto_class, w.cnt,
+                                                                              w.off, w.idx, w.lse, w.kl, w.term);
     ++launched;
   }
   kld_finish_kernel<<<1, 1024, 0, st>>>(w.term, (long long)s.B * k.Q, w.fin);
@@ -283,15 +444,71 @@ int launch_kld_fwd(const HeadShape& s, const SpsKldDesc& k, const float* dist, c
   return SPS_OK;
 }
 
+}  // namespace
+
+int launch_kld_fwd(const HeadShape& s, const SpsKldDesc& k, const float* dist, const int16_t* labels, void* ws,
+                   float* loss, cudaStream_t st) {
+  KldCarve w = carve(s, k.Q, ws);
+  launch_buckets(s, labels, w, st);
+  return launch_stats(s, k, dist, dense_rows(s), w, loss, st);
+}
+
 int launch_kld_bwd(const HeadShape& s, const SpsKldDesc& k, const float* dist, void* ws, const float* dloss,
                    float* ddist, cudaStream_t st) {
   KldCarve w = carve(s, k.Q, ws);
   SPS_CUDA_TRY(cudaMemsetAsync(ddist, 0, sizeof(float) * (size_t)s.N * s.P, st));
   if (k.Q > 0) {
     kld_bwd_kernel<<<warps_grid((long long)s.B * s.P), KLD_THREADS, 0, st>>>(
-        dist, s.B, s.P, s.HW, s.K, k.Q, k.proto_class, k.proto_group, k.proto_local, k.group_moff, k.group_poff,
+        dist, dense_rows(s), s.B, s.P, s.HW, s.K, k.Q, k.proto_class, k.proto_group, k.proto_local, k.group_moff, k.group_poff,
         k.members, w.cnt, w.off, w.idx, w.lse, w.kl, w.term, w.fin, dloss, ddist);
     count_launch(1);
+  }
+  SPS_CUDA_TRY(cudaGetLastError());
+  return SPS_OK;
+}
+
+size_t kld_feat_workspace(const HeadShape& s, const SpsKldDesc& k) { return carve(s, k.Q, nullptr, s.S * k.mmax).bytes; }
+
+int launch_kld_feat_fwd(const HeadShape& s, const SpsKldDesc& k, const float* z, const float* protos,
+                        const int16_t* labels, void* ws, float* loss, cudaStream_t st) {
+  KldCarve w = carve(s, k.Q, ws, s.S * k.mmax);
+  launch_buckets(s, labels, w, st);
+  dim3 grid((s.HW + FEAT_THREADS - 1) / FEAT_THREADS, s.S, s.B);
+  kld_feat_dist_kernel<<<grid, FEAT_THREADS, 0, st>>>(z, protos, labels, s.HW, s.K, s.S, s.D, k.mmax, k.group_moff,
+                                                      k.members, w.dc);
+  count_launch(1);
+  return launch_stats(s, k, w.dc, compact_rows(s, k), w, loss, st);
+}
+
+int launch_kld_feat_bwd(const HeadShape& s, const SpsKldDesc& k, const float* z, const float* protos,
+                        const int16_t* labels, void* ws, const float* dloss, float* dz, float* dprotos,
+                        cudaStream_t st) {
+  const int rows = s.S * k.mmax;
+  KldCarve w = carve(s, k.Q, ws, rows);
+  SPS_CUDA_TRY(cudaMemsetAsync(w.gc, 0, sizeof(float) * (size_t)s.B * rows * s.HW, st));
+  if (k.Q > 0) {
+    kld_bwd_kernel<<<warps_grid((long long)s.B * s.P), KLD_THREADS, 0, st>>>(
+        w.dc, compact_rows(s, k), s.B, s.P, s.HW, s.K, k.Q, k.proto_class, k.proto_group, k.proto_local, k.group_moff,
+        k.group_poff, k.members, w.cnt, w.off, w.idx, w.lse, w.kl, w.term, w.fin, dloss, w.gc);
+    count_launch(1);
+  }
+  if (dz != nullptr) {
+    dim3 grid((s.HW + FEAT_THREADS - 1) / FEAT_THREADS, s.S, s.B);
+    kld_feat_dz_kernel<<<grid, FEAT_THREADS, 0, st>>>(z, protos, labels, s.HW, s.K, s.S, s.D, k.mmax, k.group_moff,
+                                                      k.members, w.gc, dz);
+    count_launch(1);
+  }
+  if (dprotos != nullptr) {
+    SPS_CUDA_TRY(cudaMemsetAsync(w.part, 0, sizeof(float) * (size_t)s.B * s.P * s.D, st));
+    const int threads = 256;
+    SPS_REQUIRE(k.mmax * s.D <= 8 * threads, SPS_ERR_UNSUPPORTED, "kld feature mode: group size %d x depth %d > %d",
+                k.mmax, s.D, 8 * threads);
+    const size_t smem = sizeof(float) * 33 * (size_t)(s.D + k.mmax);
+    kld_feat_dp_kernel<<<dim3(k.G, s.B), threads, smem, st>>>(z, protos, s.HW, s.K, s.S, s.D, s.P, k.mmax, k.group_moff,
+                                                              k.members, w.cnt, w.off, w.idx, w.gc, w.part);
+    const long long PD = (long long)s.P * s.D;
+    kld_feat_dp_reduce_kernel<<<(unsigned)((PD + 255) / 256), 256, 0, st>>>(w.part, s.B, PD, k.proto_class, s.D, dprotos);
+    count_launch(2);
   }
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;

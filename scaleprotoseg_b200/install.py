@@ -9,6 +9,8 @@ What is patched (reference file:line of what each replaces):
   segmentation.model.model_multiscale_group.PPNetMultiScale
       _scale_l2_convolution :347, compute_group :283, run_last_layer :305, forward_from_conv_features :404,
       push_forward :454
+  segmentation.model.model.PPNet (single-scale ProtoSeg baseline = one scale owning every prototype)
+      _l2_convolution :250, prototype_distances :270, forward_from_conv_features :306 (patch branch), push_forward :345
   segmentation.push_multiscale_optimization (module globals, looked up at call time :286,:291)
       compute_distances :35, min_across_dataset :94, global_min :141
   segmentation.model.loss.KLDLoss
@@ -49,9 +51,14 @@ def _patch(cls, name, new_fn):
     _installed[(cls, name)] = old
 
 
-def install_on_classes(stage1_cls=None, stage2_cls=None):
+def install_on_classes(stage1_cls=None, stage2_cls=None, single_cls=None):
     """Patch the given classes (any class with the reference's attribute names works)."""
     _lib.load()  # fail now, loudly, if the CUDA library has not been built
+    if single_cls is not None:
+        _patch(single_cls, "_l2_convolution", model_api._l2_convolution_single)
+        _patch(single_cls, "prototype_distances", model_api.prototype_distances_single)
+        _patch(single_cls, "push_forward", model_api.push_forward_single)
+        _patch(single_cls, "forward_from_conv_features", model_api.forward_from_conv_features_single)
     if stage1_cls is not None:
         _patch(stage1_cls, "_scale_l2_convolution", model_api._scale_l2_convolution)
         _patch(stage1_cls, "prototype_distances", model_api.prototype_distances)
@@ -192,7 +199,9 @@ def install():
     from segmentation.model import model_multiscale as mm
     from segmentation.model import model_multiscale_group as mg
 
-    install_on_classes(mm.PPNetMultiScale, mg.PPNetMultiScale)
+    from segmentation.model import model as m1
+
+    install_on_classes(mm.PPNetMultiScale, mg.PPNetMultiScale, m1.PPNet)
     import segmentation.push_multiscale_optimization as pm
 
     install_push(pm)

@@ -49,8 +49,11 @@ class KldTables:
         self.G, self.Q = K * S, len(pa)
         i32 = dict(dtype=torch.int32, device=device)
         self.proto_class = pclass.to(device)
+        self.mmax = max([b - a for a, b in zip(moff[:-1], moff[1:])] + [1])
+        pclass = torch.where(pgroup < 0, torch.full_like(pclass, -1), pclass)   # outside every scale range: never used
         pgroup = torch.where(pgroup < 0, torch.full_like(pgroup, self.G), pgroup)
         moff.append(moff[-1]), poff.append(poff[-1])           # the parking group: no members listed, no pairs
+        self.proto_class = pclass.to(device)
         self.proto_group, self.proto_local = pgroup.to(device), plocal.to(device)
         self.group_moff, self.group_poff = torch.tensor(moff, **i32), torch.tensor(poff, **i32)
         self.members = torch.tensor(members + [0] * max(0, 1 - len(members)), **i32)
@@ -59,7 +62,7 @@ class KldTables:
 
     def desc(self) -> SpsKldDesc:
         k = SpsKldDesc()
-        k.G, k.Q = self.G, self.Q
+        k.G, k.Q, k.mmax, k.reserved = self.G, self.Q, self.mmax, 0
         k.proto_class, k.proto_group, k.proto_local = (self.proto_class.data_ptr(), self.proto_group.data_ptr(),
                                                        self.proto_local.data_ptr())
         k.group_moff, k.group_poff, k.members = (self.group_moff.data_ptr(), self.group_poff.data_ptr(),
@@ -129,6 +132,61 @@ class KldLossFn(torch.autograd.Function):
 def kld_loss(dist: torch.Tensor, target_labels: torch.Tensor, tables: KldTables) -> torch.Tensor:
     """Same value as KLDLoss(...)(prototype_distances=dist, target_labels=target_labels) of the reference."""
     return KldLossFn.apply(dist, labels_int16(target_labels, tables.K).to(dist.device), tables)
+
+
+class KldFeatureLossFn(torch.autograd.Function):
+    """(z (B,S*D,H,W), prototype_vectors (P,D,1,1), labels int16) -> the same scalar as KldLossFn on the head's distance
+    map, without that map: sps_kld_feat_fwd / sps_kld_feat_bwd ("feature mode").  The gradient flows into z and the
+    prototypes directly, so the head itself can run in fused mode (no (B,P,H,W) tensor in HBM) during training."""
+
+    @staticmethod
+    def forward(ctx, z, protos, labels, tables: KldTables, cfg):
+        from .head import make_desc, _shape_of
+        lib = _lib.load()
+        _check_cuda_f32("z", z), _check_cuda_f32("prototype_vectors", protos)
+        z = z.contiguous()
+        p2 = protos.reshape(protos.shape[0], -1).contiguous()
+        B, H, W, S, D, P = _shape_of(z, p2, cfg)
+        if P != tables.P or S != tables.S or cfg.num_classes != tables.K:
+            raise RuntimeError("KLD tables do not match the head configuration")
+        if labels.dtype != torch.int16 or not labels.is_cuda or labels.numel() != B * H * W:
+            raise RuntimeError("labels must be CUDA int16 of shape (B,H,W) matching the feature map")
+        labels = labels.contiguous()
+        desc, kd = make_desc(cfg, B, H, W, D, P), tables.desc()
+        nbytes = int(lib.sps_kld_feat_workspace_bytes(C.byref(desc), C.byref(kd)))
+        ws = torch.empty(max(nbytes, 16), device=z.device, dtype=torch.uint8)
+        out = torch.empty(2, device=z.device, dtype=torch.float32)
+        with torch.cuda.device(z.device):
+            _lib.check(lib.sps_kld_feat_fwd(C.byref(desc), C.byref(kd), _ptr(z), _ptr(p2), _ptr(labels), _ptr(ws), nbytes,
+                                            _ptr(out), _stream()), "sps_kld_feat_fwd")
+        ctx.tables, ctx.cfg, ctx.nbytes, ctx.proto_shape = tables, cfg, nbytes, protos.shape
+        ctx.save_for_backward(z, p2, labels, ws)
+        return out[0]
+
+    @staticmethod
+    def backward(ctx, dloss):
+        from .head import make_desc
+        lib = _lib.load()
+        z, p2, labels, ws = ctx.saved_tensors
+        need_dz, need_dp = ctx.needs_input_grad[0], ctx.needs_input_grad[1]
+        if not (need_dz or need_dp):
+            return None, None, None, None, None
+        B, _, H, W = z.shape
+        P, D = p2.shape
+        desc, kd = make_desc(ctx.cfg, B, H, W, D, P), ctx.tables.desc()
+        g = dloss.to(torch.float32).reshape(1).contiguous()
+        dz = torch.empty_like(z) if need_dz else None
+        dp = torch.empty_like(p2) if need_dp else None
+        with torch.cuda.device(z.device):
+            _lib.check(lib.sps_kld_feat_bwd(C.byref(desc), C.byref(kd), _ptr(z), _ptr(p2), _ptr(labels), _ptr(ws), ctx.nbytes,
+                                            _ptr(g), _ptr(dz), _ptr(dp), _stream()), "sps_kld_feat_bwd")
+        return dz, (dp.view(ctx.proto_shape) if dp is not None else None), None, None, None
+
+
+def kld_loss_from_features(z: torch.Tensor, protos: torch.Tensor, target_labels: torch.Tensor, tables: KldTables,
+                           cfg) -> torch.Tensor:
+    """KLDLoss(...)(prototype_distances=head(z), target_labels) without materialising prototype_distances."""
+    return KldFeatureLossFn.apply(z, protos, labels_int16(target_labels, tables.K).to(z.device), tables, cfg)
 
 
 _TABLE_CACHE: Dict[int, Tuple[tuple, KldTables]] = {}

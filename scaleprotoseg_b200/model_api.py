@@ -17,7 +17,10 @@ _group_cache: "weakref.WeakKeyDictionary" = weakref.WeakKeyDictionary()
 
 
 def head_config(m, math=None) -> HeadConfig:
-    ranges = [tuple(m.scale_num_prototypes[s]) for s in range(m.num_scales)]
+    if hasattr(m, "scale_num_prototypes"):
+        ranges = [tuple(m.scale_num_prototypes[s]) for s in range(m.num_scales)]
+    else:   # single-scale ProtoSeg baseline (segmentation/model/model.py:74): one scale owning every prototype
+        ranges = [(0, int(m.prototype_vectors.shape[0]))]
     return HeadConfig.from_ranges(ranges, m.num_classes, m.prototype_activation_function, m.epsilon,
                                   default_math() if math is None else math)
 
@@ -129,3 +132,41 @@ def forward_from_conv_features_stage2(self, conv_features: Union[torch.Tensor, L
     (_, logits), _ = _group_apply(self, act, (B, H, W))
     logits = logits.reshape(B, H, W, -1)
     return _returns(logits, dist, act, return_activations, return_distances)
+
+
+# ---- single-scale ProtoSeg baseline (segmentation/model/model.py, class PPNet) --------------------
+def _l2_convolution_single(self, x: torch.Tensor) -> torch.Tensor:
+    """model.py:250-268: the S = 1 case of the same kernels (C = D)."""
+    _require_cuda(x)
+    _, dist, _ = PrototypeHeadFn.apply(x.float(), self.prototype_vectors, None, head_config(self), True, False)
+    return dist
+
+
+def prototype_distances_single(self, x: torch.Tensor) -> torch.Tensor:
+    return self._l2_convolution(self.conv_features(x))          # model.py:270-276
+
+
+def push_forward_single(self, x: torch.Tensor) -> Any:
+    conv_output = self.conv_features(x)                          # model.py:345-354
+    if isinstance(conv_output, list):
+        return [(c, self._l2_convolution(c)) for c in conv_output]
+    return conv_output, self._l2_convolution(conv_output)
+
+
+def forward_from_conv_features_single(self, conv_features: Union[torch.Tensor, List[torch.Tensor]],
+                                      return_activations: bool = False, return_distances: bool = False) -> Any:
+    """model.py:306-343.  The patch-classification branch runs fused; the image-level branch (global min pooling, the
+    original ProtoPNet head) keeps the reference's code."""
+    if isinstance(conv_features, list):
+        return [self.forward_from_conv_features(c) for c in conv_features]
+    if not (hasattr(self, "patch_classification") and self.patch_classification):
+        original = type(self).forward_from_conv_features.__sps_original__
+        return original(self, conv_features, return_activations=return_activations, return_distances=return_distances)
+    _require_cuda(conv_features)
+    B, _, H, W = conv_features.shape
+    logits, dist, act = PrototypeHeadFn.apply(conv_features.float(), self.prototype_vectors, self.last_layer.weight,
+                                              head_config(self), not return_activations, bool(return_activations))
+    logits = logits.reshape(B, H, W, -1)
+    if return_activations:
+        return logits, act                                       # model.py:327-328
+    return logits, dist

@@ -114,3 +114,71 @@ class Stage2Standin(Stage1Standin):
 
     def run_last_layer(self, a):
         return self.last_layer_group(torch.cat(self.compute_group(a), dim=-1))
+
+
+class SingleScaleStandin(nn.Module):
+    """Attribute and method names of the single-scale ProtoSeg `PPNet` (segmentation/model/model.py:74-354): no
+    num_scales / scale_num_prototypes, `_l2_convolution` instead of `_scale_l2_convolution`, and the two-way return
+    convention of its forward_from_conv_features (:327-330)."""
+
+    def __init__(self, P, K, D=64, act="log", patch_classification=True):
+        super().__init__()
+        self.epsilon = 1e-4
+        self.patch_classification = patch_classification
+        self.prototype_activation_function = act
+        self.prototype_vectors = nn.Parameter(torch.rand(P, D, 1, 1))
+        self.ones = nn.Parameter(torch.ones(P, D, 1, 1), requires_grad=False)
+        self.prototype_class_identity = ho.make_identity(P, K, 1)
+        self.last_layer = nn.Linear(P, K, bias=False)
+        self.last_layer.weight.data.copy_(ho.make_last_layer(self.prototype_class_identity))
+        self.features = nn.Identity()
+        self.add_on_layers = nn.Sequential(nn.Sigmoid())
+
+    @property
+    def num_prototypes(self):
+        return self.prototype_vectors.shape[0]
+
+    @property
+    def num_classes(self):
+        return self.prototype_class_identity.shape[1]
+
+    def conv_features(self, x):
+        x = self.features(x)
+        if isinstance(x, list):
+            return [self.add_on_layers(v) for v in x]
+        return self.add_on_layers(x)
+
+    def _l2_convolution(self, x):
+        return ho.l2_convolution(x, self.prototype_vectors)
+
+    def prototype_distances(self, x):
+        return self._l2_convolution(self.conv_features(x))
+
+    def distance_2_similarity(self, d):
+        return ho.distance_2_similarity(d, self.prototype_activation_function, self.epsilon)
+
+    def run_last_layer(self, a):
+        return self.last_layer(a)
+
+    def forward(self, x, **kw):
+        c = self.conv_features(x)
+        if isinstance(c, list):
+            return [self.forward_from_conv_features(v, **kw) for v in c]
+        return self.forward_from_conv_features(c, **kw)
+
+    def forward_from_conv_features(self, conv_features, return_activations=False, return_distances=False):
+        if isinstance(conv_features, list):
+            return [self.forward_from_conv_features(c) for c in conv_features]
+        d = self._l2_convolution(conv_features)
+        B, P, H, W = d.shape
+        if self.patch_classification:
+            a = self.distance_2_similarity(d.permute(0, 2, 3, 1).contiguous().reshape(-1, P))
+            logits = self.run_last_layer(a).reshape(B, H, W, -1)
+            return (logits, a) if return_activations else (logits, d)
+        mins = d.reshape(B, P, -1).min(dim=2).values          # model.py:331-343, global min pooling
+        logits = self.run_last_layer(self.distance_2_similarity(mins))
+        return (logits, mins, d) if return_distances else (logits, mins)
+
+    def push_forward(self, x):
+        c = self.conv_features(x)
+        return c, self._l2_convolution(c)

@@ -30,8 +30,8 @@ def _patched(cls):
     """A patched subclass so the un-patched class keeps serving as the CPU oracle."""
     sub = type(cls.__name__ + "Patched", (cls,), {})
     # copy the methods onto the subclass so install_on_classes wraps them there
-    for name in ("_scale_l2_convolution", "prototype_distances", "push_forward", "forward_from_conv_features",
-                 "compute_group", "run_last_layer"):
+    for name in ("_scale_l2_convolution", "_l2_convolution", "prototype_distances", "push_forward",
+                 "forward_from_conv_features", "compute_group", "run_last_layer"):
         if hasattr(cls, name):
             setattr(sub, name, getattr(cls, name))
     return sub
@@ -204,3 +204,56 @@ def test_default_math_is_tensor_core_and_training_step_matches(patched_classes):
     torch.nn.functional.cross_entropy(lg.permute(0, 3, 1, 2), target.to(DEV)).backward()
     assert_grad(got.prototype_vectors.grad, ref.prototype_vectors.grad, 1e-3, "dprotos")
     assert_grad(got.last_layer.weight.grad, ref.last_layer.weight.grad, 1e-3, "dlast")
+
+
+# ---- single-scale ProtoSeg baseline (segmentation/model/model.py:74) ------------------------------
+@pytest.fixture(scope="module")
+def patched_single(built_lib):
+    from standin_model import SingleScaleStandin
+    sub = _patched(SingleScaleStandin)
+    sps.install_on_classes(single_cls=sub)
+    return SingleScaleStandin, sub
+
+
+@pytest.mark.parametrize("return_activations", [False, True])
+def test_single_scale_forward_and_step(patched_single, return_activations):
+    """PPNet.forward_from_conv_features (model.py:306-330): (logits, distances) or (logits, activations), and the
+    gradients of one CE-like step into the features, the prototypes and the last layer."""
+    base, sub = patched_single
+    ref, got = _pair(base, sub, 57, 19)
+    x = torch.randn(2, 64, 9, 6)
+    xr, xg = x.clone().requires_grad_(True), x.to(DEV).requires_grad_(True)
+    o_ref = ref.forward(xr, return_activations=return_activations)
+    o_got = got.forward(xg, return_activations=return_activations)
+    assert len(o_ref) == len(o_got) == 2
+    for a, b in zip(o_got, o_ref):
+        assert a.is_cuda and a.shape == b.shape
+        assert_rel(a, b, TOL, "output")
+    w = torch.randn(o_ref[0].shape) / o_ref[0].numel()
+    (o_ref[0] * w).sum().backward()
+    (o_got[0] * w.to(DEV)).sum().backward()
+    for a, b, name in [(xg.grad, xr.grad, "dx"), (got.prototype_vectors.grad, ref.prototype_vectors.grad, "dprotos"),
+                       (got.last_layer.weight.grad, ref.last_layer.weight.grad, "dW")]:
+        scale = b.abs().max().clamp_min(1e-30)
+        assert_rel(a.cpu() / scale, b / scale, 20 * TOL, name)
+
+
+def test_single_scale_list_push_forward_and_image_level_branch(patched_single):
+    base, sub = patched_single
+    ref, got = _pair(base, sub, 40, 5)
+    maps = [torch.randn(1, 64, 5, 4), torch.randn(1, 64, 3, 7)]
+    for (lr, dr), (lg, dg) in zip(ref.forward_from_conv_features([torch.sigmoid(m) for m in maps]),
+                                  got.forward_from_conv_features([torch.sigmoid(m).to(DEV) for m in maps])):
+        assert_rel(lg, lr, TOL, "list logits"), assert_rel(dg, dr, TOL, "list distances")
+    cr, dr = ref.push_forward(maps[0])
+    cg, dg = got.push_forward(maps[0].to(DEV))
+    assert_rel(cg, cr, TOL, "conv_output"), assert_rel(dg, dr, TOL, "push distances")
+    assert_rel(got.prototype_distances(maps[1].to(DEV)), ref.prototype_distances(maps[1]), TOL, "prototype_distances")
+    # image-level (original ProtoPNet) head: not covered by the kernels' fused path, keeps the class's own code,
+    # which still gets its distances from the patched _l2_convolution
+    ref2, got2 = _pair(base, sub, 40, 5, patch_classification=False)
+    o_ref = ref2.forward(maps[0], return_distances=True)
+    o_got = got2.forward(maps[0].to(DEV), return_distances=True)
+    assert len(o_got) == 3
+    for a, b in zip(o_got, o_ref):
+        assert_rel(a, b, TOL, "image-level output")

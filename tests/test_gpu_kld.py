@@ -164,3 +164,63 @@ def test_kld_dropin_through_install(built_lib):
     finally:
         sps.uninstall()
     assert not hasattr(_KLDLossStandin.forward, "__sps_original__")
+
+
+# ---- feature mode: the loss straight from z and the prototypes (no distance map) --------------------------------
+def _feature_case(B, H, W, P, K, S, D, seed, prune=(), block=4):
+    gen = torch.Generator().manual_seed(ho.SEED + seed)
+    z = torch.sigmoid(torch.randn(B, S * D, H, W, generator=gen))
+    protos = torch.rand(P, D, 1, 1, generator=gen)
+    ident, ranges = ho.make_identity(P, K, S), ho.uniform_ranges(P, S)
+    if prune:
+        keep = [p for p in range(P) if p not in set(prune)]
+        new, lo = [], 0
+        for a, b in ranges:
+            n = sum(1 for p in keep if a <= p < b)
+            new.append((lo, lo + n))
+            lo += n
+        ident, protos, ranges = ident[keep], protos[keep].contiguous(), new
+    labels = torch.stack([ho.make_labels(77 * seed + i, H, W, K, absent_class=1, block=block) for i in range(B)])
+    return z, protos, ident, ranges, labels
+
+
+@pytest.mark.parametrize("case", [dict(B=2, H=13, W=11, P=228, K=19, S=4, D=64, seed=1),
+                                  dict(B=1, H=33, W=20, P=760, K=19, S=4, D=64, seed=2, block=8),
+                                  dict(B=3, H=9, W=10, P=40, K=5, S=4, D=64, seed=3, prune=(0, 1, 11, 39)),
+                                  dict(B=2, H=8, W=9, P=48, K=4, S=2, D=24, seed=4),
+                                  dict(B=1, H=12, W=12, P=190, K=19, S=1, D=64, seed=5)])
+def test_kld_from_features_vs_oracle(built_lib, case):
+    """kld_loss_from_features(z, prototypes, labels) against the oracle's head distances fed to the oracle's KLD loss,
+    with the gradients autograd takes back into z and the prototypes (ragged groups, S = 1 and 2, D = 24)."""
+    z, protos, ident, ranges, labels = _feature_case(**case)
+    K = ident.shape[1]
+    zr, pr = z.clone().requires_grad_(True), protos.clone().requires_grad_(True)
+    lref = ho.kld_loss(ho.scale_l2_convolution(zr, pr, ranges), labels, ident, ranges)
+    lref.backward()
+    cfg = sps.HeadConfig.from_ranges(ranges, K, math=sps.MATH_FP32)
+    tables = KldTables(ident, ranges, DEV)
+    zc, pc = z.to(DEV).requires_grad_(True), protos.to(DEV).requires_grad_(True)
+    loss = sps.kld_loss_from_features(zc, pc, labels.to(DEV), tables, cfg)
+    _close_loss(loss, lref.detach())
+    (loss * 1.0).backward()
+    _close_grad(zc.grad, zr.grad), _close_grad(pc.grad, pr.grad)
+
+
+def test_kld_from_features_matches_dense_path_at_full_size(built_lib):
+    """configs[1] size: feature mode against the dense path of this library (head distances -> sps_kld_fwd/bwd ->
+    head backward through ddist), loss and both gradients; fused-mode training step = head (no map) + this loss."""
+    z, protos, ident, ranges, labels = _feature_case(16, 65, 65, 760, 19, 4, 64, seed=6, block=8)
+    cfg = sps.HeadConfig.from_ranges(ranges, 19, math=sps.MATH_FP32)
+    tables = KldTables(ident, ranges, DEV)
+    lab = labels.to(DEV)
+    z1, p1 = z.to(DEV).requires_grad_(True), protos.to(DEV).requires_grad_(True)
+    _, dist, _ = sps.PrototypeHeadFn.apply(z1, p1, None, cfg, True, False)
+    l1 = kld_loss(dist, lab, tables)
+    l1.backward()
+    z2, p2 = z.to(DEV).requires_grad_(True), protos.to(DEV).requires_grad_(True)
+    l2 = sps.kld_loss_from_features(z2, p2, lab, tables, cfg)
+    l2.backward()
+    _close_loss(l2, l1.detach())
+    _close_grad(z2.grad, z1.grad.cpu()), _close_grad(p2.grad, p1.grad.cpu())
+    void = (labels == 0).unsqueeze(1).expand_as(z)
+    assert float(z2.grad.cpu()[void].abs().max()) == 0.0

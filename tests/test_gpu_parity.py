@@ -412,3 +412,34 @@ def test_tensor_core_backward_with_distance_gradient(built_lib, shape, math):
     g_32 = sps.head_backward_raw(z.to(DEV), protos.to(DEV), last_w.to(DEV), cfg32, dl.reshape(N, K).to(DEV), dd.to(DEV), None, True, True, True)
     for a, b_, name in zip(g_tc, g_32, ("dz", "dprotos", "dlast_w")):
         assert_grad(a, b_.cpu(), gt, name + " vs fp32 kernels")
+
+
+@pytest.mark.parametrize("math", [sps.MATH_FP32, sps.MATH_F16X3, sps.MATH_BF16X3])
+@pytest.mark.parametrize("shape", [(2, 17, 13, 190, 19), (1, 65, 65, 210, 21)])
+def test_single_scale_head_and_push(built_lib, shape, math):
+    """S = 1 (the single-scale ProtoSeg baseline, segmentation/model/model.py:250-268: C = D = 64, one range owning every
+    prototype; the second shape is its Pascal head, 21 classes x 10): fused step and push scan against the oracle."""
+    B, H, W, P, K = shape
+    gen = torch.Generator().manual_seed(ho.SEED + P + H)
+    z = torch.sigmoid(torch.randn(B, 64, H, W, generator=gen))
+    protos = torch.rand(P, 64, 1, 1, generator=gen)
+    ident = ho.make_identity(P, K, 1)
+    last_w = ho.make_last_layer(ident).contiguous()
+    ranges = [(0, P)]
+    dl = torch.randn(B, H, W, K, generator=gen) / (B * H * W)
+    zr, pr, wr = z.clone().requires_grad_(True), protos.clone().requires_grad_(True), last_w.clone().requires_grad_(True)
+    lo, do, _ = ho.head_stage1(zr, pr, ranges, wr)
+    lo.backward(dl)
+    cfg = sps.HeadConfig.from_ranges(ranges, K, math=math)
+    zc, pc, wc = (t.to(DEV).requires_grad_(True) for t in (z, protos, last_w))
+    lg, dg, _ = sps.PrototypeHeadFn.apply(zc, pc, wc, cfg, True, False)
+    assert_rel(dg, do, _tol(math), "distances"), assert_rel(lg.view(B, H, W, K), lo, _tol(math), "logits")
+    lg.view(B, H, W, K).backward(dl.to(DEV))
+    gt = 1e-3
+    assert_grad(zc.grad, zr.grad, gt, "dz"), assert_grad(pc.grad, pr.grad, gt, "dprotos"), assert_grad(wc.grad, wr.grad, gt, "dlast_w")
+    labels = [ho.make_labels(i, H, W, K, absent_class=3) for i in range(B)]
+    z_maps = [z[i:i + 1] for i in range(B)]
+    pcl = spush.proto_class_of(ident).to(DEV)
+    keys = spush.scan_maps(z.to(DEV), torch.stack(labels).to(torch.int16).to(DEV), protos.view(P, 64).to(DEV), pcl, cfg)
+    best = spush.reduce_keys(keys, 0)
+    check_push(keys, (best & 0xFFFFFFFF).cpu(), z_maps, labels, protos, ranges, ident, K, max(_tol(math), 1e-4))
