@@ -195,6 +195,7 @@ _TABLE_CACHE: Dict[int, Tuple[tuple, KldTables]] = {}
 def kld_forward(self, prototype_distances: torch.Tensor, target_labels: torch.Tensor) -> torch.Tensor:
     """Bound over KLDLoss.forward by install(): `self` is the reference's KLDLoss module (attributes
     prototype_class_identity, num_scales, scale_num_prototypes; loss.py:56-64)."""
+    from .model_api import DeferredDistances
     if not prototype_distances.is_cuda:
         raise RuntimeError("scaleprotoseg_b200 KLD loss runs on CUDA only: there is no CPU path")
     ranges = tuple(tuple(int(v) for v in self.scale_num_prototypes[s]) for s in range(self.num_scales))
@@ -204,4 +205,7 @@ def kld_forward(self, prototype_distances: torch.Tensor, target_labels: torch.Te
     if hit is None or hit[0] != sig:
         hit = (sig, KldTables(ident, ranges, prototype_distances.device))
         _TABLE_CACHE[id(self)] = hit
+    if isinstance(prototype_distances, DeferredDistances):     # fused-mode training: no (B,P,H,W) map exists
+        d = prototype_distances
+        return kld_loss_from_features(d.z, d.protos, target_labels, hit[1], d.cfg)
     return kld_loss(prototype_distances.float(), target_labels, hit[1])

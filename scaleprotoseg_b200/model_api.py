@@ -33,6 +33,51 @@ def is_supported(m) -> bool:
             and len(shape) == 4 and shape[2] == 1 and shape[3] == 1)
 
 
+_DEFER_DISTANCES = False
+
+
+def set_deferred_distances(on: bool):
+    """Opt in: while training, the stage-1 `forward_from_conv_features(x)` (the call of module_multiscale.py:209, whose
+    distances go nowhere but into KLDLoss, :242) returns a DeferredDistances handle instead of the (B,P,H,W) map, the
+    head runs in fused mode, and the patched KLDLoss.forward computes the loss straight from the features."""
+    global _DEFER_DISTANCES
+    _DEFER_DISTANCES = bool(on)
+
+
+class DeferredDistances:
+    """Stands in for the dense distance map of one head call.  Carries what is needed to compute any part of it
+    (features, prototypes, head configuration).  The patched KLDLoss.forward consumes it without materialising it;
+    any other use (an attribute or method of a tensor) materialises the map through the head kernels and delegates,
+    so callers that really want the tensor still get it, with autograd intact."""
+
+    def __init__(self, z: torch.Tensor, protos: torch.Tensor, cfg: HeadConfig):
+        self.z, self.protos, self.cfg = z, protos, cfg
+        self._dense = None
+
+    @property
+    def shape(self):
+        B, _, H, W = self.z.shape
+        return torch.Size((B, self.protos.shape[0], H, W))
+
+    @property
+    def is_cuda(self):
+        return self.z.is_cuda
+
+    @property
+    def device(self):
+        return self.z.device
+
+    def materialize(self) -> torch.Tensor:
+        if self._dense is None:
+            _, self._dense, _ = PrototypeHeadFn.apply(self.z, self.protos, None, self.cfg, True, False)
+        return self._dense
+
+    def __getattr__(self, name):
+        if name.startswith("__"):
+            raise AttributeError(name)
+        return getattr(self.materialize(), name)
+
+
 def _require_cuda(x: torch.Tensor):
     if not x.is_cuda:
         raise RuntimeError("scaleprotoseg_b200 is installed: the prototype head runs on CUDA only "
@@ -88,8 +133,14 @@ def forward_from_conv_features_stage1(self, conv_features: Union[torch.Tensor, L
     _require_cuda(conv_features)
     B, _, H, W = conv_features.shape
     want_dist = return_distances or not return_activations
+    cfg = head_config(self)
+    if (_DEFER_DISTANCES and self.training and torch.is_grad_enabled() and not return_activations
+            and not return_distances):
+        z = conv_features.float()
+        logits, _, _ = PrototypeHeadFn.apply(z, self.prototype_vectors, self.last_layer.weight, cfg, False, False)
+        return logits.reshape(B, H, W, -1), DeferredDistances(z, self.prototype_vectors, cfg)
     logits, dist, act = PrototypeHeadFn.apply(conv_features.float(), self.prototype_vectors, self.last_layer.weight,
-                                              head_config(self), want_dist, bool(return_activations))
+                                              cfg, want_dist, bool(return_activations))
     logits = logits.reshape(B, H, W, -1)
     return _returns(logits, dist, act, return_activations, return_distances)
 

@@ -224,3 +224,60 @@ def test_kld_from_features_matches_dense_path_at_full_size(built_lib):
     _close_grad(z2.grad, z1.grad.cpu()), _close_grad(p2.grad, p1.grad.cpu())
     void = (labels == 0).unsqueeze(1).expand_as(z)
     assert float(z2.grad.cpu()[void].abs().max()) == 0.0
+
+
+def test_unchanged_trainer_step_in_fused_mode(built_lib):
+    """The lines of the reference's training step that touch the head (module_multiscale.py:209-242, shipped config:
+    entropy and norm weights 0): outputs = ppnet.forward(image, return_activations=False); cross entropy on
+    outputs[0]; kld_loss_func(prototype_distances=outputs[1], target_labels=target).  With set_deferred_distances
+    the same lines run without a (B,P,H,W) tensor and give the same loss and gradients as the CPU classes."""
+    import torch.nn.functional as F
+    from standin_model import Stage1Standin
+    from test_gpu_dropin import _patched
+    sub = _patched(Stage1Standin)
+    sps.install_on_classes(sub)
+    sps.install_kld(_KLDLossStandin)
+    old_math = sps.default_math()
+    sps.set_default_math(sps.MATH_F16X3)
+    sps.set_deferred_distances(True)
+    try:
+        P, K, S = 228, 19, 4
+        torch.manual_seed(11)
+        ref = Stage1Standin(P, K)
+        got = sub(P, K)
+        got.load_state_dict(ref.state_dict())
+        got = got.to(DEV).train()
+        ref.train()
+        x = torch.randn(2, 256, 14, 9)
+        target = torch.stack([ho.make_labels(300 + i, 14, 9, K, block=4) for i in range(2)])
+
+        def step(model, kld_mod, x, target):
+            outputs = model.forward(x, return_activations=False)
+            output, prototype_distances = outputs[0], outputs[1]
+            ce = F.cross_entropy(output.reshape(-1, K), (target.reshape(-1) - 1).clamp_min(0))
+            kld = kld_mod(prototype_distances=prototype_distances, target_labels=target)
+            (ce + 0.25 * kld).backward()
+            return ce.detach(), kld.detach(), prototype_distances
+
+        kld_ref = _KLDLossStandin(ref.prototype_class_identity, S, ref.scale_num_prototypes)
+        xr = x.clone().requires_grad_(True)
+        ce_r, kld_r, _ = step(ref, kld_ref, xr, target)
+        xg = x.to(DEV).requires_grad_(True)
+        ce_g, kld_g, handle = step(got, kld_ref, xg, target.to(DEV))
+        assert isinstance(handle, sps.DeferredDistances) and handle._dense is None      # never materialised
+        assert tuple(handle.shape) == (2, P, 14, 9)
+        _close_loss(kld_g, kld_r)
+        assert abs(float(ce_g) - float(ce_r)) <= 1e-3 * max(abs(float(ce_r)), 1.0)
+        _close_grad(xg.grad, xr.grad, tol=2e-3)
+        _close_grad(got.prototype_vectors.grad, ref.prototype_vectors.grad, tol=2e-3)
+        _close_grad(got.last_layer.weight.grad, ref.last_layer.weight.grad, tol=2e-3)
+        # any other use of the handle still behaves like the tensor
+        got.eval()
+        with torch.no_grad():
+            dense = got.forward(x.to(DEV))[1]
+        assert isinstance(dense, torch.Tensor)
+        assert torch.allclose(handle.detach().cpu(), dense.cpu(), rtol=1e-3, atol=1e-3)
+    finally:
+        sps.set_deferred_distances(False)
+        sps.set_default_math(old_math)
+        sps.uninstall()
