@@ -87,7 +87,7 @@ typedef struct SpsGroupDesc {
 typedef struct SpsKldDesc {
   int32_t G;                  /* groups = K * S (empty groups allowed) */
   int32_t Q;                  /* pairs over all groups */
-  int32_t mmax;               /* largest group size (rows per scale of the compact distance block, feature mode) */
+  int32_t mmax;               /* largest group size, 1..32 (also: rows per scale of the compact block, feature mode) */
   int32_t reserved;           /* 0 */
   const int32_t* proto_class; /* [P] class of prototype p (argmax of prototype_class_identity) */
   const int32_t* proto_group; /* [P] group of p */
@@ -171,7 +171,7 @@ int sps_kld_bwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* dist,
  * pixel and the prototypes of the pixel's own class (1/K of the map), so they are computed here from z and the
  * prototypes into a compact block inside the workspace and the (B,P,H,W) map is never needed — the head can run in
  * fused mode (dist = NULL) during stage-1 training.  desc carries the head's S, D and scale_lo; every group must
- * lie inside one scale (it does by construction) and hold at most 32 prototypes.
+ * lie inside one scale (it does by construction); D <= 64.
  *   z [B,S*D,H,W], protos [P,D], labels as above; loss [2] as sps_kld_fwd.
  *   sps_kld_feat_bwd: dz [B,S*D,H,W] and dprotos [P,D] (either may be NULL) are OVERWRITTEN with the loss's own
  *   gradient (the caller adds them to the head's); workspace as left by sps_kld_feat_fwd. */
@@ -181,6 +181,15 @@ int sps_kld_feat_fwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* 
 int sps_kld_feat_bwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* z, const float* protos,
                      const int16_t* labels, void* workspace, size_t workspace_bytes, const float* dloss, float* dz,
                      float* dprotos, void* stream);
+
+/* Evaluation epilogue: bilinear upsampling (align_corners = False) of a low-resolution map to the annotation size and
+ * argmax (logits -> predicted class) or argmin (distances -> nearest prototype) over the channel axis, without
+ * materialising the upsampled map.  Replaces F.interpolate + torch.argmax / torch.argmin of
+ * segmentation/eval_valid_multiscale.py:229-234.
+ *   maps    [B, C, h, w] fp32 (logits permuted to channels-first as :221 does, or the head's distances)
+ *   out_idx [B, H, W] int32 winning channel (first one on ties);  out_val [B, H, W] fp32 its value, or NULL */
+int sps_upsample_argext(const float* maps, int32_t B, int32_t C, int32_t h, int32_t w, int32_t H, int32_t W,
+                        int32_t argmin, int32_t* out_idx, float* out_val, void* stream);
 
 /* Push scan: per map and per prototype, the nearest position among those labelled with the
  * prototype's class.  Replaces compute_distances lines 68-91 of

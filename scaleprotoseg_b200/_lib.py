@@ -65,6 +65,8 @@ _SIGNATURES = {
     "sps_kld_feat_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc), _P, _P, _P, _P, C.c_size_t, _P, _P]),
     "sps_kld_feat_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc), _P, _P, _P, _P, C.c_size_t, _P, _P, _P,
                                    _P]),
+    "sps_upsample_argext": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32, C.c_int32,
+                                      _P, _P, _P]),
     "sps_push_scan": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "sps_push_reduce": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint32, _P, _P]),
     "sps_push_gather": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, C.c_int32, C.c_uint32, _P, _P, _P]),

