@@ -318,13 +318,18 @@ kld_feat_dist_kernel(const float* __restrict__ z, const float* __restrict__ prot
   }
 }
 
-// dz[b, s*D + ch, x] = 2 * sum_j g_j(x) * (z - p_j)[ch] over the group of x's class; 0 for void pixels.  Same thread
-// layout; the D partial sums -sum_j g_j p_j[ch] sit in registers.
+// dz[b, s*D + ch, x] = 2 * sum_j g_j(x) * (z - p_j)[ch] over the group of x's class; 0 for void pixels.  One thread
+// per (pixel, 16-channel slice, scale, image): 16 partial sums -sum_j g_j p_j[ch] in registers (a 64-register tile
+// per thread left 20 warps per SM waiting on dependent loads: 154 us; the slices quadruple the warps in flight).
+constexpr int DZ_SLICE = 16;
+
 __global__ void __launch_bounds__(FEAT_THREADS)
 kld_feat_dz_kernel(const float* __restrict__ z, const float* __restrict__ protos, const int16_t* __restrict__ labels,
                    int HW, int K, int S, int D, int mmax, const int* __restrict__ group_moff,
                    const int* __restrict__ members, const float* __restrict__ gc, float* __restrict__ dz) {
-  const int x = blockIdx.x * FEAT_THREADS + threadIdx.x, s = blockIdx.y, b = blockIdx.z;
+  const int nsl = (D + DZ_SLICE - 1) / DZ_SLICE;
+  const int x = blockIdx.x * FEAT_THREADS + threadIdx.x, s = blockIdx.y / nsl, c0 = (blockIdx.y % nsl) * DZ_SLICE;
+  const int b = blockIdx.z;
   if (x >= HW) return;
   const int c = (int)labels[(size_t)b * HW + x] - 1;
   float* dzp = dz + ((size_t)b * S * D + (size_t)s * D) * HW + x;
@@ -333,41 +338,48 @@ kld_feat_dz_kernel(const float* __restrict__ z, const float* __restrict__ protos
     m0 = group_moff[c * S + s];
     m = group_moff[c * S + s + 1] - m0;
   }
-  float acc[FEAT_D];
+  float acc[DZ_SLICE];
 #pragma unroll
-  for (int ch = 0; ch < FEAT_D; ++ch) acc[ch] = 0.0f;
+  for (int i = 0; i < DZ_SLICE; ++i) acc[i] = 0.0f;
   float gsum = 0.0f;
   const float* gp = gc + ((size_t)b * S * mmax + (size_t)s * mmax) * HW + x;
   const bool vec = (D & 3) == 0;
-  const int nq = (D + 3) >> 2;
   for (int j = 0; j < m; ++j) {
     const float g = gp[(size_t)j * HW];
     gsum += g;
     const float* pv = protos + (size_t)members[m0 + j] * D;
 #pragma unroll
-    for (int c4 = 0; c4 < FEAT_D / 4; ++c4) {
-      if (c4 < nq) {
-        const float4 p = proto_quad(pv, c4, D, vec);
-        acc[4 * c4 + 0] = fmaf(-g, p.x, acc[4 * c4 + 0]);
-        acc[4 * c4 + 1] = fmaf(-g, p.y, acc[4 * c4 + 1]);
-        acc[4 * c4 + 2] = fmaf(-g, p.z, acc[4 * c4 + 2]);
-        acc[4 * c4 + 3] = fmaf(-g, p.w, acc[4 * c4 + 3]);
+    for (int i4 = 0; i4 < DZ_SLICE / 4; ++i4) {
+      if (c0 + 4 * i4 < D) {
+        const float4 p = proto_quad(pv, c0 / 4 + i4, D, vec);
+        acc[4 * i4 + 0] = fmaf(-g, p.x, acc[4 * i4 + 0]);
+        acc[4 * i4 + 1] = fmaf(-g, p.y, acc[4 * i4 + 1]);
+        acc[4 * i4 + 2] = fmaf(-g, p.z, acc[4 * i4 + 2]);
+        acc[4 * i4 + 3] = fmaf(-g, p.w, acc[4 * i4 + 3]);
       }
     }
   }
   const float* zp = z + ((size_t)b * S * D + (size_t)s * D) * HW + x;
 #pragma unroll
-  for (int ch = 0; ch < FEAT_D; ++ch)
-    if (ch < D) dzp[(size_t)ch * HW] = m > 0 ? 2.0f * fmaf(gsum, zp[(size_t)ch * HW], acc[ch]) : 0.0f;
+  for (int i = 0; i < DZ_SLICE; ++i) {
+    const int ch = c0 + i;
+    if (ch < D) dzp[(size_t)ch * HW] = m > 0 ? 2.0f * fmaf(gsum, zp[(size_t)ch * HW], acc[i]) : 0.0f;
+  }
 }
 
 // part[b][p][ch] = 2 * sum_x g_p(x) * (p - z_s(x))[ch] over the pixels of p's class in image b.  One CTA per
-// (group, image): tiles of 32 bucketed pixels staged in shared memory (z tile D x 32, gradient tile m x 32).
-__global__ void kld_feat_dp_kernel(const float* __restrict__ z, const float* __restrict__ protos, int HW, int K, int S,
-                                   int D, int P, int mmax, const int* __restrict__ group_moff,
-                                   const int* __restrict__ members, const int* __restrict__ cnt,
-                                   const int* __restrict__ off, const int* __restrict__ idx,
-                                   const float* __restrict__ gc, float* __restrict__ part) {
+// (group, image): tiles of 32 bucketed pixels staged in shared memory (z tile D x 32, gradient tile m x 32).  Thread
+// (ch = t mod 64, jq = t / 64) owns channel ch of members jq, jq+4, ...: one z read from shared memory feeds all of
+// them, and p * sum g - sum g z needs one FMA per (pixel, member) instead of a subtract and an FMA.
+constexpr int DP_THREADS = 256;
+constexpr int DP_JQ = DP_THREADS / FEAT_D;   // 4 member lanes
+constexpr int DP_MAXE = 8;                   // members per thread: covers groups of up to 32
+
+__global__ void __launch_bounds__(DP_THREADS)
+kld_feat_dp_kernel(const float* __restrict__ z, const float* __restrict__ protos, int HW, int K, int S, int D, int P,
+                   int mmax, const int* __restrict__ group_moff, const int* __restrict__ members,
+                   const int* __restrict__ cnt, const int* __restrict__ off, const int* __restrict__ idx,
+                   const float* __restrict__ gc, float* __restrict__ part) {
   extern __shared__ float sm[];  // zt[D][33], gt[mmax][33]
   const int g = blockIdx.x, b = blockIdx.y;
   const int c = g / S, s = g % S;
@@ -377,38 +389,45 @@ __global__ void kld_feat_dp_kernel(const float* __restrict__ z, const float* __r
   float* gt = sm + (size_t)D * 33;
   const int n = cnt[b * K + c];
   const int* ix = idx + (size_t)b * HW + off[b * K + c];
-  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = blockDim.x >> 5;
-  // thread t owns output elements e = t, t + blockDim, ... of the m x D block (e = j*D + ch)
-  constexpr int MAXE = 8;
-  float acc[MAXE];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = DP_THREADS >> 5;
+  const int ch = threadIdx.x % FEAT_D, jq = threadIdx.x / FEAT_D;
+  float sgz[DP_MAXE], sg[DP_MAXE];
 #pragma unroll
-  for (int e = 0; e < MAXE; ++e) acc[e] = 0.0f;
+  for (int e = 0; e < DP_MAXE; ++e) sgz[e] = sg[e] = 0.0f;
   const float* zb = z + ((size_t)b * S * D + (size_t)s * D) * HW;
   const float* gb = gc + ((size_t)b * S * mmax + (size_t)s * mmax) * HW;
   for (int i0 = 0; i0 < n; i0 += 32) {
     const int i = i0 + lane;
     const int x = i < n ? ix[i] : -1;
-    for (int ch = warp; ch < D; ch += nw) zt[ch * 33 + lane] = x >= 0 ? zb[(size_t)ch * HW + x] : 0.0f;
+    for (int cc = warp; cc < D; cc += nw) zt[cc * 33 + lane] = x >= 0 ? zb[(size_t)cc * HW + x] : 0.0f;
     for (int j = warp; j < m; j += nw) gt[j * 33 + lane] = x >= 0 ? gb[(size_t)j * HW + x] : 0.0f;
     __syncthreads();
+    if (ch < D) {
+#pragma unroll 4
+      for (int t = 0; t < 32; ++t) {
+        const float zv = zt[ch * 33 + t];
 #pragma unroll
-    for (int e = 0; e < MAXE; ++e) {
-      const int el = threadIdx.x + e * blockDim.x;
-      if (el < m * D) {
-        const int j = el / D, ch = el % D;
-        const float pv = protos[(size_t)members[m0 + j] * D + ch];
-        float a = acc[e];
-#pragma unroll 8
-        for (int t = 0; t < 32; ++t) a = fmaf(gt[j * 33 + t], pv - zt[ch * 33 + t], a);
-        acc[e] = a;
+        for (int e = 0; e < DP_MAXE; ++e) {
+          const int j = jq + DP_JQ * e;
+          if (j < m) {
+            const float gv = gt[j * 33 + t];
+            sgz[e] = fmaf(gv, zv, sgz[e]);
+            sg[e] += gv;
+          }
+        }
       }
     }
     __syncthreads();
   }
+  if (ch < D) {
 #pragma unroll
-  for (int e = 0; e < MAXE; ++e) {
-    const int el = threadIdx.x + e * blockDim.x;
-    if (el < m * D) part[((size_t)b * P + members[m0 + el / D]) * D + el % D] = 2.0f * acc[e];
+    for (int e = 0; e < DP_MAXE; ++e) {
+      const int j = jq + DP_JQ * e;
+      if (j < m) {
+        const int p = members[m0 + j];
+        part[((size_t)b * P + p) * D + ch] = 2.0f * (protos[(size_t)p * D + ch] * sg[e] - sgz[e]);
+      }
+    }
   }
 }
 
@@ -546,18 +565,17 @@ int launch_kld_feat_bwd(const HeadShape& s, const SpsKldDesc& k, const float* z,
     count_launch(1);
   }
   if (dz != nullptr) {
-    dim3 grid((s.HW + FEAT_THREADS - 1) / FEAT_THREADS, s.S, s.B);
+    dim3 grid((s.HW + FEAT_THREADS - 1) / FEAT_THREADS, s.S * ((s.D + DZ_SLICE - 1) / DZ_SLICE), s.B);
     kld_feat_dz_kernel<<<grid, FEAT_THREADS, 0, st>>>(z, protos, labels, s.HW, s.K, s.S, s.D, k.mmax, k.group_moff,
                                                       k.members, w.gc, dz);
     count_launch(1);
   }
   if (dprotos != nullptr) {
     SPS_CUDA_TRY(cudaMemsetAsync(w.part, 0, sizeof(float) * (size_t)s.B * s.P * s.D, st));
-    const int threads = 256;
-    SPS_REQUIRE(k.mmax * s.D <= 8 * threads, SPS_ERR_UNSUPPORTED, "kld feature mode: group size %d x depth %d > %d",
-                k.mmax, s.D, 8 * threads);
+    SPS_REQUIRE(k.mmax <= DP_JQ * DP_MAXE && s.D <= FEAT_D, SPS_ERR_UNSUPPORTED,
+                "kld feature mode: group size %d > %d or depth %d > %d", k.mmax, DP_JQ * DP_MAXE, s.D, FEAT_D);
     const size_t smem = sizeof(float) * 33 * (size_t)(s.D + k.mmax);
-    kld_feat_dp_kernel<<<dim3(k.G, s.B), threads, smem, st>>>(z, protos, s.HW, s.K, s.S, s.D, s.P, k.mmax, k.group_moff,
+    kld_feat_dp_kernel<<<dim3(k.G, s.B), DP_THREADS, smem, st>>>(z, protos, s.HW, s.K, s.S, s.D, s.P, k.mmax, k.group_moff,
                                                               k.members, w.cnt, w.off, w.idx, w.gc, w.part);
     const long long PD = (long long)s.P * s.D;
     kld_feat_dp_reduce_kernel<<<(unsigned)((PD + 255) / 256), 256, 0, st>>>(w.part, s.B, PD, k.proto_class, s.D, dprotos);
