@@ -299,6 +299,7 @@ kld_feat_dist_kernel(const float* __restrict__ z, const float* __restrict__ prot
   float* out = dc + ((size_t)b * S * mmax + (size_t)s * mmax) * HW + x;
   const bool vec = (D & 3) == 0;
   const int nq = (D + 3) >> 2;
+#pragma unroll 2   // two members' prototype rows in flight
   for (int j = 0; j < m; ++j) {
     const float* pv = protos + (size_t)members[m0 + j] * D;
     float a0 = 0.0f, a1 = 0.0f;
@@ -338,32 +339,44 @@ kld_feat_dz_kernel(const float* __restrict__ z, const float* __restrict__ protos
     m0 = group_moff[c * S + s];
     m = group_moff[c * S + s + 1] - m0;
   }
+  // the slice's own z values first: their DRAM latency overlaps the member loop (read one by one next to the stores
+  // they were 60 % of the kernel's stall samples)
+  const float* zp = z + ((size_t)b * S * D + (size_t)s * D) * HW + x;
+  float zr[DZ_SLICE];
+#pragma unroll
+  for (int i = 0; i < DZ_SLICE; ++i) zr[i] = (m > 0 && c0 + i < D) ? zp[(size_t)(c0 + i) * HW] : 0.0f;
   float acc[DZ_SLICE];
 #pragma unroll
   for (int i = 0; i < DZ_SLICE; ++i) acc[i] = 0.0f;
   float gsum = 0.0f;
   const float* gp = gc + ((size_t)b * S * mmax + (size_t)s * mmax) * HW + x;
   const bool vec = (D & 3) == 0;
-  for (int j = 0; j < m; ++j) {
-    const float g = gp[(size_t)j * HW];
-    gsum += g;
-    const float* pv = protos + (size_t)members[m0 + j] * D;
+  for (int j0 = 0; j0 < m; j0 += 2) {   // two members per round: both gradients and all eight prototype quads in flight
+    const bool two = j0 + 1 < m;
+    const float g0 = gp[(size_t)j0 * HW];
+    const float g1 = two ? gp[(size_t)(j0 + 1) * HW] : 0.0f;
+    const float* pv0 = protos + (size_t)members[m0 + j0] * D;
+    const float* pv1 = protos + (size_t)members[m0 + (two ? j0 + 1 : j0)] * D;
+    float4 q0[DZ_SLICE / 4], q1[DZ_SLICE / 4];
 #pragma unroll
     for (int i4 = 0; i4 < DZ_SLICE / 4; ++i4) {
-      if (c0 + 4 * i4 < D) {
-        const float4 p = proto_quad(pv, c0 / 4 + i4, D, vec);
-        acc[4 * i4 + 0] = fmaf(-g, p.x, acc[4 * i4 + 0]);
-        acc[4 * i4 + 1] = fmaf(-g, p.y, acc[4 * i4 + 1]);
-        acc[4 * i4 + 2] = fmaf(-g, p.z, acc[4 * i4 + 2]);
-        acc[4 * i4 + 3] = fmaf(-g, p.w, acc[4 * i4 + 3]);
-      }
+      const bool in = c0 + 4 * i4 < D;
+      q0[i4] = in ? proto_quad(pv0, c0 / 4 + i4, D, vec) : make_float4(0.f, 0.f, 0.f, 0.f);
+      q1[i4] = in ? proto_quad(pv1, c0 / 4 + i4, D, vec) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    gsum += g0 + g1;
+#pragma unroll
+    for (int i4 = 0; i4 < DZ_SLICE / 4; ++i4) {
+      acc[4 * i4 + 0] = fmaf(-g1, q1[i4].x, fmaf(-g0, q0[i4].x, acc[4 * i4 + 0]));
+      acc[4 * i4 + 1] = fmaf(-g1, q1[i4].y, fmaf(-g0, q0[i4].y, acc[4 * i4 + 1]));
+      acc[4 * i4 + 2] = fmaf(-g1, q1[i4].z, fmaf(-g0, q0[i4].z, acc[4 * i4 + 2]));
+      acc[4 * i4 + 3] = fmaf(-g1, q1[i4].w, fmaf(-g0, q0[i4].w, acc[4 * i4 + 3]));
     }
   }
-  const float* zp = z + ((size_t)b * S * D + (size_t)s * D) * HW + x;
 #pragma unroll
   for (int i = 0; i < DZ_SLICE; ++i) {
     const int ch = c0 + i;
-    if (ch < D) dzp[(size_t)ch * HW] = m > 0 ? 2.0f * fmaf(gsum, zp[(size_t)ch * HW], acc[i]) : 0.0f;
+    if (ch < D) dzp[(size_t)ch * HW] = m > 0 ? 2.0f * fmaf(gsum, zr[i], acc[i]) : 0.0f;
   }
 }
 
@@ -375,6 +388,9 @@ constexpr int DP_THREADS = 256;
 constexpr int DP_JQ = DP_THREADS / FEAT_D;   // 4 member lanes
 constexpr int DP_MAXE = 8;                   // members per thread: covers groups of up to 32
 
+// E = members per thread = ceil(mmax / 4), a compile-time count: with a fixed 8 every pixel issued 8 predicated
+// LDS + FFMA + FADD triples, 5 of them idle at the reference's 10 prototypes per class and scale
+template <int E>
 __global__ void __launch_bounds__(DP_THREADS)
 kld_feat_dp_kernel(const float* __restrict__ z, const float* __restrict__ protos, int HW, int K, int S, int D, int P,
                    int mmax, const int* __restrict__ group_moff, const int* __restrict__ members,
@@ -391,9 +407,9 @@ kld_feat_dp_kernel(const float* __restrict__ z, const float* __restrict__ protos
   const int* ix = idx + (size_t)b * HW + off[b * K + c];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nw = DP_THREADS >> 5;
   const int ch = threadIdx.x % FEAT_D, jq = threadIdx.x / FEAT_D;
-  float sgz[DP_MAXE], sg[DP_MAXE];
+  float sgz[E], sg[E];
 #pragma unroll
-  for (int e = 0; e < DP_MAXE; ++e) sgz[e] = sg[e] = 0.0f;
+  for (int e = 0; e < E; ++e) sgz[e] = sg[e] = 0.0f;
   const float* zb = z + ((size_t)b * S * D + (size_t)s * D) * HW;
   const float* gb = gc + ((size_t)b * S * mmax + (size_t)s * mmax) * HW;
   for (int i0 = 0; i0 < n; i0 += 32) {
@@ -407,7 +423,7 @@ kld_feat_dp_kernel(const float* __restrict__ z, const float* __restrict__ protos
       for (int t = 0; t < 32; ++t) {
         const float zv = zt[ch * 33 + t];
 #pragma unroll
-        for (int e = 0; e < DP_MAXE; ++e) {
+        for (int e = 0; e < E; ++e) {
           const int j = jq + DP_JQ * e;
           if (j < m) {
             const float gv = gt[j * 33 + t];
@@ -421,7 +437,7 @@ kld_feat_dp_kernel(const float* __restrict__ z, const float* __restrict__ protos
   }
   if (ch < D) {
 #pragma unroll
-    for (int e = 0; e < DP_MAXE; ++e) {
+    for (int e = 0; e < E; ++e) {
       const int j = jq + DP_JQ * e;
       if (j < m) {
         const int p = members[m0 + j];
@@ -575,8 +591,21 @@ int launch_kld_feat_bwd(const HeadShape& s, const SpsKldDesc& k, const float* z,
     SPS_REQUIRE(k.mmax <= DP_JQ * DP_MAXE && s.D <= FEAT_D, SPS_ERR_UNSUPPORTED,
                 "kld feature mode: group size %d > %d or depth %d > %d", k.mmax, DP_JQ * DP_MAXE, s.D, FEAT_D);
     const size_t smem = sizeof(float) * 33 * (size_t)(s.D + k.mmax);
-    kld_feat_dp_kernel<<<dim3(k.G, s.B), DP_THREADS, smem, st>>>(z, protos, s.HW, s.K, s.S, s.D, s.P, k.mmax, k.group_moff,
-                                                              k.members, w.cnt, w.off, w.idx, w.gc, w.part);
+    const dim3 grid(k.G, s.B);
+#define SPS_DP_LAUNCH(E)                                                                                              \
+  kld_feat_dp_kernel<E><<<grid, DP_THREADS, smem, st>>>(z, protos, s.HW, s.K, s.S, s.D, s.P, k.mmax, k.group_moff, \
+                                                        k.members, w.cnt, w.off, w.idx, w.gc, w.part)
+    switch ((k.mmax + DP_JQ - 1) / DP_JQ) {
+      case 1: SPS_DP_LAUNCH(1); break;
+      case 2: SPS_DP_LAUNCH(2); break;
+      case 3: SPS_DP_LAUNCH(3); break;
+      case 4: SPS_DP_LAUNCH(4); break;
+      case 5: SPS_DP_LAUNCH(5); break;
+      case 6: SPS_DP_LAUNCH(6); break;
+      case 7: SPS_DP_LAUNCH(7); break;
+      default: SPS_DP_LAUNCH(8); break;
+    }
+#undef SPS_DP_LAUNCH
     const long long PD = (long long)s.P * s.D;
     kld_feat_dp_reduce_kernel<<<(unsigned)((PD + 255) / 256), 256, 0, st>>>(w.part, s.B, PD, k.proto_class, s.D, dprotos);
     count_launch(2);
