@@ -210,6 +210,16 @@ int sps_push_scan(const SpsHeadDesc* desc, const float* z, const float* protos, 
 int sps_push_reduce(const uint64_t* keys, int32_t n_maps, int32_t P, uint32_t map_base, uint64_t* best,
                     void* stream);
 
+/* k nearest maps per prototype: the generalisation of sps_push_reduce that find_k_nearest_patches_to_prototypes needs
+ * (find_nearest.py:89-175 keeps one heap of size k per prototype and feeds it every image's closest patch; the
+ * nearest_img / nearest_proto analyses use the same lists).  Scan with labels = 1 at every non-void pixel and
+ * proto_class = 0 to reproduce its void-only mask (find_nearest.py:138), or with the class labels for class-pure lists.
+ *   keys [n_maps, P] from sps_push_scan; k in [1,16];
+ *   top_key [P, k] uint64 ascending, MERGED: (float_bits(d) << 32) | global map index; pre-fill with 0xFF..FF
+ *   top_pix [P, k] int32 flat position h*W+w of each entry inside its map; pre-fill with 0. */
+int sps_push_topk(const uint64_t* keys, int32_t n_maps, int32_t P, uint32_t map_base, int32_t k, uint64_t* top_key,
+                  int32_t* top_pix, void* stream);
+
 /* Gather of the winning feature vectors (push_multiscale_optimization.py:182-188).
  *   z [n_maps,S*D,H,W]; best [P] (global map index in the low word); keys [n_maps,P]; only prototypes
  *   whose winning map lies in [map_base, map_base+n_maps) are written.

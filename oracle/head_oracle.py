@@ -18,6 +18,7 @@ Reference lines followed (relative to /root/reference):
   push_image_min            segmentation/push_multiscale_optimization.py:68-91
   push_dataset_argmin       segmentation/push_multiscale_optimization.py:135-137
   push_gather               segmentation/push_multiscale_optimization.py:161-188
+  topk_nearest              find_nearest.py:89-175 (restated; no reference-generated fixture: the function needs a dataset on disk)
   kld_loss                  segmentation/model/loss.py:53-146 (KLDLoss.forward)
 """
 from typing import Dict, List, Optional, Sequence, Tuple
@@ -216,6 +217,21 @@ def kld_loss(dist: torch.Tensor, target: torch.Tensor, identity: torch.Tensor,
     if not terms:
         return torch.zeros((), dtype=dist.dtype)
     return torch.exp(-torch.cat(terms)).mean()
+
+
+def topk_nearest(dist_maps: Sequence[torch.Tensor], labels: Sequence[torch.Tensor], k: int):
+    """find_k_nearest_patches_to_prototypes (find_nearest.py:89-175) on resident maps: per image the void pixels get
+    +10e6 (:138), the closest patch per prototype is the minimum over the map (:146), and a heap per prototype keeps the
+    k images with the smallest such distance (:160-175).  dist_maps[i] (1,P,h,w), labels[i] (h,w) with 0 = void.
+    Returns (dist (P,k) ascending, image (P,k), flat position (P,k))."""
+    mins, args = [], []
+    for d, lab in zip(dist_maps, labels):
+        masked = d[0] + 10e6 * (lab == 0).to(d.dtype).unsqueeze(0)
+        v, a = masked.flatten(1).min(dim=1)
+        mins.append(v), args.append(a)
+    mins, args = torch.stack(mins), torch.stack(args)                 # (n, P)
+    val, img = torch.topk(mins, k, dim=0, largest=False)              # (k, P)
+    return val.t().contiguous(), img.t().contiguous(), torch.gather(args, 0, img).t().contiguous()
 
 
 def uniform_ranges(P: int, S: int):

@@ -69,6 +69,7 @@ _SIGNATURES = {
                                       _P, _P, _P]),
     "sps_push_scan": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "sps_push_reduce": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint32, _P, _P]),
+    "sps_push_topk": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint32, C.c_int32, _P, _P, _P]),
     "sps_push_gather": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, C.c_int32, C.c_uint32, _P, _P, _P]),
 }
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -283,6 +283,14 @@ int sps_push_reduce(const uint64_t* keys, int32_t n_maps, int32_t P, uint32_t ma
                             reinterpret_cast<unsigned long long*>(best), reinterpret_cast<cudaStream_t>(stream));
 }
 
+int sps_push_topk(const uint64_t* keys, int32_t n_maps, int32_t P, uint32_t map_base, int32_t k, uint64_t* top_key,
+                  int32_t* top_pix, void* stream) {
+  SPS_REQUIRE(keys && top_key && top_pix && n_maps >= 0 && P >= 0, SPS_ERR_BAD_ARG, "push_topk: bad argument");
+  return launch_push_topk(reinterpret_cast<const unsigned long long*>(keys), n_maps, P, map_base, k,
+                          reinterpret_cast<unsigned long long*>(top_key), top_pix,
+                          reinterpret_cast<cudaStream_t>(stream));
+}
+
 int sps_push_gather(const SpsHeadDesc* desc, const float* z, const uint64_t* keys, const uint64_t* best,
                     int32_t n_maps, uint32_t map_base, const int32_t* proto_scale, float* out, void* stream) {
   int rc = validate_desc(desc);

@@ -132,6 +132,8 @@ int launch_kld_feat_bwd(const HeadShape& s, const SpsKldDesc& k, const float* z,
                         const int16_t* labels, void* ws, const float* dloss, float* dz, float* dprotos,
                         cudaStream_t st);
 
+int launch_push_topk(const unsigned long long* keys, int n_maps, int P, uint32_t map_base, int k,
+                     unsigned long long* top_key, int32_t* top_pix, cudaStream_t st);
 int launch_upsample_argext(const float* maps, int B, int C, int h, int w, int H, int W, int argmin, int32_t* out_idx,
                            float* out_val, cudaStream_t st);
 

@@ -142,6 +142,57 @@ int launch_push_reduce(const unsigned long long* keys, int n_maps, int P, uint32
   return SPS_OK;
 }
 
+// k nearest maps per prototype (find_nearest.py:89-175: one heap of size k per prototype, fed with every image's
+// closest patch).  One thread per prototype walks the maps of this shard in order and keeps a sorted list of the k
+// smallest (distance, global map index) pairs with their pixel; the list is MERGED into what top_key / top_pix hold
+// on entry (pre-filled with ~0 / 0, or a previous shard's result), so shards and ranks chain.
+constexpr int TOPK_MAX = 16;
+
+__global__ void push_topk_kernel(const unsigned long long* __restrict__ keys, int n_maps, int P, uint32_t map_base,
+                                 int k, unsigned long long* __restrict__ top_key, int32_t* __restrict__ top_pix) {
+  const int p = blockIdx.x * blockDim.x + threadIdx.x;
+  if (p >= P) return;
+  unsigned long long kk[TOPK_MAX];
+  int32_t pp[TOPK_MAX];
+#pragma unroll
+  for (int i = 0; i < TOPK_MAX; ++i) {
+    kk[i] = i < k ? top_key[(long long)p * k + i] : 0ULL;   // slots beyond k never accept a candidate
+    pp[i] = i < k ? top_pix[(long long)p * k + i] : 0;
+  }
+  for (int m = 0; m < n_maps; ++m) {
+    const unsigned long long key = keys[(long long)m * P + p];
+    unsigned long long cand = (key & 0xFFFFFFFF00000000ULL) | (unsigned long long)(map_base + m);
+    int32_t pix = (int32_t)(key & 0xFFFFFFFFULL);
+#pragma unroll
+    for (int i = 0; i < TOPK_MAX; ++i) {   // one pass: the candidate sinks in, the displaced entry rides along
+      if (i < k && cand < kk[i]) {
+        const unsigned long long tk = kk[i];
+        const int32_t tp = pp[i];
+        kk[i] = cand;
+        pp[i] = pix;
+        cand = tk;
+        pix = tp;
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < TOPK_MAX; ++i)
+    if (i < k) {
+      top_key[(long long)p * k + i] = kk[i];
+      top_pix[(long long)p * k + i] = pp[i];
+    }
+}
+
+int launch_push_topk(const unsigned long long* keys, int n_maps, int P, uint32_t map_base, int k,
+                     unsigned long long* top_key, int32_t* top_pix, cudaStream_t st) {
+  SPS_REQUIRE(k >= 1 && k <= TOPK_MAX, SPS_ERR_UNSUPPORTED, "push_topk: k=%d outside [1,%d]", k, TOPK_MAX);
+  if (n_maps == 0 || P == 0) return SPS_OK;
+  push_topk_kernel<<<(P + 63) / 64, 64, 0, st>>>(keys, n_maps, P, map_base, k, top_key, top_pix);
+  count_launch();
+  SPS_CUDA_TRY(cudaGetLastError());
+  return SPS_OK;
+}
+
 __global__ void push_gather_kernel(HeadShape s, const float* __restrict__ z, const unsigned long long* __restrict__ keys,
                                    const unsigned long long* __restrict__ best, int n_maps, uint32_t map_base,
                                    const int32_t* __restrict__ proto_scale, float* __restrict__ out) {

@@ -128,3 +128,59 @@ def push_project(z: torch.Tensor, labels: torch.Tensor, protos: torch.Tensor, id
         dist.all_reduce(out, op=dist.ReduceOp.SUM, group=group)
         dist.all_reduce(pix, op=dist.ReduceOp.SUM, group=group)
     return win_map, pix, win_dist, out, keys
+
+
+def nonvoid_labels(labels: torch.Tensor) -> torch.Tensor:
+    """Labels for a scan that masks only the void class, as find_nearest.py:138 does (distances + 10e6 at void pixels):
+    1 at every labelled pixel, 0 at void; use with proto_class = zeros."""
+    return (labels != 0).to(torch.int16)
+
+
+def topk_keys(keys: torch.Tensor, k: int, map_base: int = 0, top: Optional[Tuple[torch.Tensor, torch.Tensor]] = None):
+    """keys (n_maps,P) -> (top_key (P,k) int64 ascending, top_pix (P,k) int32), merged into `top` when given."""
+    lib = _lib.load()
+    n_maps, P = keys.shape
+    if top is None:
+        top = (torch.full((P, k), -1, device=keys.device, dtype=torch.int64),     # 0xFF..FF as uint64
+               torch.zeros((P, k), device=keys.device, dtype=torch.int32))
+    with torch.cuda.device(keys.device):
+        _lib.check(lib.sps_push_topk(_ptr(keys.contiguous()), n_maps, P, int(map_base), int(k), _ptr(top[0]), _ptr(top[1]),
+                                     _stream()), "sps_push_topk")
+    return top
+
+
+def topk_nearest(z: torch.Tensor, labels: torch.Tensor, protos: torch.Tensor, cfg: HeadConfig, k: int,
+                 proto_class: Optional[torch.Tensor] = None, map_base: int = 0, group=None, batch: int = 32):
+    """The k maps whose closest patch is nearest to each prototype (find_nearest.py:71-175 on resident maps).
+
+    labels (n,h,w) int16: 0 = void, c+1 = class c.  proto_class None = the reference's void-only mask; a (P,) class
+    vector = class-pure lists.  Returns (dist (P,k) fp32 ascending, map (P,k) int64 global index, pix (P,k) int64 flat
+    position); entries with dist >= 1e10 mean fewer than k maps had an admissible pixel.  With `group`, every rank
+    ends up with the merged lists (all-gather of the per-rank lists, merged by the same kernel)."""
+    n, P = z.shape[0], protos.shape[0]
+    if proto_class is None:
+        labels, proto_class = nonvoid_labels(labels), torch.zeros(P, dtype=torch.int32)
+    pc = proto_class.to(z.device)
+    keys = torch.empty((n, P), device=z.device, dtype=torch.int64)
+    for i in range(0, n, batch):
+        scan_maps(z[i:i + batch], labels[i:i + batch], protos, pc, cfg, keys_out=keys[i:i + batch])
+    top_key, top_pix = topk_keys(keys, k, map_base)
+    if group is not None:
+        import torch.distributed as dist
+        world = dist.get_world_size(group)
+        all_key = [torch.empty_like(top_key) for _ in range(world)]
+        all_pix = [torch.empty_like(top_pix) for _ in range(world)]
+        dist.all_gather(all_key, top_key, group=group)
+        dist.all_gather(all_pix, top_pix, group=group)
+        top_key, top_pix = merge_topk(all_key, all_pix)
+    dist_bits = (top_key >> 32).to(torch.int32).view(torch.float32)
+    return dist_bits, top_key & 0xFFFFFFFF, top_pix.to(torch.int64)
+
+
+def merge_topk(all_key, all_pix):
+    """Merge per-rank (P,k) lists: ascending packed keys are totally ordered, so a sort of the concatenation and the
+    first k columns is the merged list (a few KB; plumbing, not a kernel)."""
+    k = all_key[0].shape[1]
+    cat_key, cat_pix = torch.cat(all_key, dim=1), torch.cat(all_pix, dim=1)
+    order = torch.argsort(cat_key.view(torch.int64) ^ (-0x8000000000000000), dim=1, stable=True)[:, :k]   # unsigned order
+    return torch.gather(cat_key, 1, order), torch.gather(cat_pix, 1, order)

@@ -445,3 +445,56 @@ def test_single_scale_head_and_push(built_lib, shape, math):
     keys = spush.scan_maps(z.to(DEV), torch.stack(labels).to(torch.int16).to(DEV), protos.view(P, 64).to(DEV), pcl, cfg)
     best = spush.reduce_keys(keys, 0)
     check_push(keys, (best & 0xFFFFFFFF).cpu(), z_maps, labels, protos, ranges, ident, K, max(_tol(math), 1e-4))
+
+
+@pytest.mark.parametrize("math", [sps.MATH_FP32, sps.MATH_F16X3])
+def test_topk_nearest_vs_oracle(built_lib, math):
+    """k nearest maps per prototype (find_nearest.py:89-175): distances within tolerance, map and pixel indices exact
+    where the neighbouring distances differ by more than the tolerance; two shards chained through the merge give
+    exactly the single-pass lists."""
+    n, h, w, P, K, k = 9, 12, 10, 40, 5, 4
+    ident, ranges = ho.make_identity(P, K, 4), ho.uniform_ranges(P, 4)
+    z = torch.cat([ho.make_feature_map(i, 256, h, w) for i in range(n)])
+    labels = torch.stack([ho.make_labels(i, h, w, K, block=3) for i in range(n)])
+    labels[4] = 0                                                  # a void-only image never enters a list
+    gen = torch.Generator().manual_seed(5)
+    protos = torch.rand(P, 64, 1, 1, generator=gen)
+    cfg = sps.HeadConfig.from_ranges(ranges, K, math=math)
+    tol = max(_tol(math), 1e-4)
+    dref, iref, pref = ho.topk_nearest([ho.scale_l2_convolution(z[i:i + 1], protos, ranges) for i in range(n)],
+                                       list(labels), k)
+    lab16 = labels.to(torch.int16).to(DEV)
+    dist, img, pix = spush.topk_nearest(z.to(DEV), lab16, protos.to(DEV), cfg, k)
+    dist, img, pix = dist.cpu(), img.cpu(), pix.cpu()
+    assert ((dist - dref).abs() <= tol * dref.clamp_min(1.0)).all()
+    assert (dist[:, 1:] >= dist[:, :-1]).all() and (img != 4).all()
+    full = torch.stack([(ho.scale_l2_convolution(z[i:i + 1], protos, ranges)[0] + 10e6 * (labels[i] == 0)).flatten(1).min(1).values
+                        for i in range(n)]).t()                  # (P, n) per-image minima
+    srt = full.sort(dim=1).values
+    gap_ok = torch.ones(P, k, dtype=torch.bool)
+    for r in range(k):                                             # rank r is unambiguous when both neighbours are far
+        lo = srt[:, r] - (srt[:, r - 1] if r > 0 else -1e30)
+        hi = srt[:, r + 1] - srt[:, r]
+        gap_ok[:, r] = (lo > 2 * tol * srt[:, r].clamp_min(1.0)) & (hi > 2 * tol * srt[:, r].clamp_min(1.0))
+    assert torch.equal(img[gap_ok], iref[gap_ok]) and gap_ok.float().mean() > 0.9
+    same_img = img == iref
+    d_at = torch.stack([ho.scale_l2_convolution(z[i:i + 1], protos, ranges)[0].flatten(1) for i in range(n)])   # (n,P,hw)
+    got_d = d_at[img, torch.arange(P).unsqueeze(1), pix]
+    assert ((got_d[same_img] - dref[same_img]).abs() <= 2 * tol * dref[same_img].clamp_min(1.0)).all()
+    # class-pure lists: the mask of the push scan instead of the void-only mask
+    pc = spush.proto_class_of(ident)
+    dcls, icls, _ = spush.topk_nearest(z.to(DEV), lab16, protos.to(DEV), cfg, 1, proto_class=pc)
+    keys = spush.scan_maps(z.to(DEV), lab16, protos.view(P, 64).to(DEV), pc.to(DEV), cfg)
+    best = spush.reduce_keys(keys, 0)
+    assert torch.equal(icls[:, 0].cpu(), (best & 0xFFFFFFFF).cpu())
+    # shards: maps 0..4 then 5..8 with map_base, chained through the merge
+    pc0 = torch.zeros(P, dtype=torch.int32, device=DEV)
+    nv = spush.nonvoid_labels(lab16)
+    k0 = spush.scan_maps(z[:5].to(DEV), nv[:5], protos.view(P, 64).to(DEV), pc0, cfg)
+    k1 = spush.scan_maps(z[5:].to(DEV), nv[5:], protos.view(P, 64).to(DEV), pc0, cfg)
+    top = spush.topk_keys(k0, k, 0)
+    top = spush.topk_keys(k1, k, 5, top)
+    assert torch.equal((top[0] & 0xFFFFFFFF).cpu(), img) and torch.equal(top[1].cpu().long(), pix)
+    a, b = spush.topk_keys(k0, k, 0), spush.topk_keys(k1, k, 5)
+    mk, mp = spush.merge_topk([a[0], b[0]], [a[1], b[1]])
+    assert torch.equal(mk.cpu(), top[0].cpu()) and torch.equal(mp.cpu(), top[1].cpu())

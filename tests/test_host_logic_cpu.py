@@ -127,3 +127,16 @@ def test_kld_tables_follow_the_reference_pair_order():
             assert int(t.proto_group[p]) == g and int(t.proto_local[p]) == r
     lab = labels_int16(torch.tensor([[0, 1, 2, 3, 255, 65537, -1]]), 2)
     assert lab.tolist() == [[0, 1, 2, 0, 0, 0, 0]]
+
+
+def test_merge_topk_orders_packed_keys_as_unsigned():
+    """Per-rank (P,k) lists of packed (distance bits << 32 | map) keys merge to the k smallest; the fill value
+    0xFFFF... (negative as int64) sorts last."""
+    def key(d, m):
+        return (int(np.float32(d).view(np.int32)) << 32) | m
+    a = torch.tensor([[key(0.5, 3), key(2.0, 1), -1], [key(1.0, 0), -1, -1]], dtype=torch.int64)
+    b = torch.tensor([[key(0.25, 9), key(2.0, 0), key(7.0, 4)], [-1, -1, -1]], dtype=torch.int64)
+    pa, pb = torch.arange(6, dtype=torch.int32).view(2, 3), torch.arange(6, 12, dtype=torch.int32).view(2, 3)
+    mk, mp = spush.merge_topk([a, b], [pa, pb])
+    assert mk[0].tolist() == [key(0.25, 9), key(0.5, 3), key(2.0, 0)] and mp[0].tolist() == [6, 0, 7]
+    assert mk[1].tolist() == [key(1.0, 0), -1, -1] and mp[1, 0].item() == 3
