@@ -433,6 +433,40 @@ def measure_kld(ctx, args):
     return out
 
 
+def measure_eval_topk(ctx, args):
+    """Secondaries for two more SURVEY 8f rows.  (i) Eval epilogue of one Cityscapes validation image
+    (eval_valid_multiscale.py:229-234): distances (760,129,257) and logits (19,129,257) upsampled to 1024x2048 and
+    reduced to nearest-prototype / predicted-class maps; next to it the reference's own two lines (F.interpolate +
+    argmin / argmax) in stock PyTorch on the same GPU.  (ii) k = 5 nearest maps per prototype over 3 000 maps' keys."""
+    import torch.nn.functional as F
+    sps, spush, dev = ctx["sps"], ctx["spush"], ctx["dev"]
+    g = torch.Generator(device=dev).manual_seed(SEED + 21)
+    P, K, h, w, H, W = C2["P"], C2["K"], 129, 257, 1024, 2048
+    dist = torch.rand(1, P, h, w, device=dev, generator=g) * 8.0
+    logits = torch.randn(1, K, h, w, device=dev, generator=g)
+
+    def ours(i):
+        sps.upsample_argmin(dist, (H, W))
+        sps.upsample_argmax(logits, (H, W))
+
+    def stock(i):
+        torch.argmin(F.interpolate(dist, size=(H, W), mode="bilinear", align_corners=False)[0], dim=0)
+        torch.argmax(F.interpolate(logits, size=(H, W), mode="bilinear", align_corners=False)[0], dim=0)
+
+    for i in range(2):
+        ours(i), stock(i)
+    ms_ours, ms_stock = event_ms(ours, 10), event_ms(stock, 5)
+    n_maps, k = PUSH["n_maps"], 5
+    keys = torch.randint(0, 2 ** 62, (n_maps, P), device=dev, dtype=torch.int64, generator=g)
+    spush.topk_keys(keys, k)
+    ms_topk = event_ms(lambda i: spush.topk_keys(keys, k), 10)
+    return {"eval_epilogue": {"workload": "one image: distances (760,129,257) + logits (19,129,257) -> argmin / argmax at 1024x2048",
+                              "ms": ms_ours, "torch_gpu_ms": ms_stock,
+                              "note": "stock PyTorch materialises the 6.4 GB upsampled distance map; ours writes two index maps (2 x 8 MB)",
+                              "out_pixels_x_channels_per_s": (H * W * (P + K)) / (ms_ours * 1e-3)},
+            "topk": {"workload": "k=5 nearest maps per prototype from %d x %d packed keys (sps_push_topk)" % (n_maps, P), "ms": ms_topk}}
+
+
 def measure_c5(ctx, args):
     """Secondary: the COCO-Stuff head shape of BASELINE.json configs[4] (K=171, P=6840, B=32, 65x65), fused forward
     (the headline of this object, tensor-bound) and the backward (class slabs)."""
@@ -574,6 +608,7 @@ def main():
     stage2 = None if (args.no_c5 or ctx["world"] > 1) else measure_stage2(ctx, args)
     torch_gpu = None if (args.no_c5 or ctx["world"] > 1) else measure_torch_gpu(ctx, args)
     kld = None if (args.no_c5 or ctx["world"] > 1) else measure_kld(ctx, args)
+    extra = None if (args.no_c5 or ctx["world"] > 1) else measure_eval_topk(ctx, args)
     if ctx["world"] > 1:
         ctx["barrier"]()
     if rank != 0:
@@ -619,6 +654,8 @@ def main():
         out["stage2"] = stage2
     if kld is not None:
         out["kld"] = kld
+    if extra is not None:
+        out.update(extra)
     if torch_gpu is not None:
         out["torch_gpu_baseline"] = torch_gpu
     if not args.no_cpu and ctx["world"] == 1:
