@@ -256,7 +256,7 @@ int sps_upsample_argext(const float* maps, int32_t B, int32_t C, int32_t h, int3
                         int32_t argmin, int32_t* out_idx, float* out_val, void* stream) {
   SPS_REQUIRE(B >= 0 && C >= 1 && h >= 1 && w >= 1 && H >= 0 && W >= 0, SPS_ERR_BAD_ARG,
               "upsample_argext: bad shape B=%d C=%d h=%d w=%d H=%d W=%d", B, C, h, w, H, W);
-  SPS_REQUIRE(B <= 65535 && (H + 7) / 8 <= 65535, SPS_ERR_UNSUPPORTED, "upsample_argext: B=%d or H=%d too large", B, H);
+  SPS_REQUIRE(B <= 65535 && (H + 3) / 4 <= 65535, SPS_ERR_UNSUPPORTED, "upsample_argext: B=%d or H=%d too large", B, H);
   SPS_REQUIRE(maps != nullptr && out_idx != nullptr, SPS_ERR_BAD_ARG, "upsample_argext: NULL argument");
   return launch_upsample_argext(maps, B, C, h, w, H, W, argmin, out_idx, out_val, reinterpret_cast<cudaStream_t>(stream));
 }

@@ -54,11 +54,96 @@ __global__ void upsample_argext_kernel(const float* __restrict__ maps, int C, in
   if (out_val != nullptr) out_val[o] = best;
 }
 
+
+// Strip variant for upsampling factors of 3.5 and more along x (the evaluation's 8x): one thread owns 8 consecutive
+// output pixels of a row.  Their bilinear footprints fall inside 4 consecutive source columns, so a channel costs
+// 8 loads (2 rows x 4 columns, blended vertically once) instead of 32, and the per-pixel column picks are register
+// selects fixed before the channel loop.  The per-pixel kernel above is LSU-bound on exactly those loads.
+constexpr int STRIP = 8;
+constexpr int STRIP_COLS = 4;
+
+__device__ __forceinline__ float pick4(const float (&v)[STRIP_COLS], int r) {
+  const float lo = r == 0 ? v[0] : v[1], hi = r == 2 ? v[2] : v[3];
+  return r < 2 ? lo : hi;
+}
+
+template <bool ARGMIN>
+__global__ void upsample_argext_strip_kernel(const float* __restrict__ maps, int C, int h, int w, int H, int W,
+                                             int32_t* __restrict__ out_idx, float* __restrict__ out_val) {
+  const int xs = (blockIdx.x * blockDim.x + threadIdx.x) * STRIP;
+  const int y = blockIdx.y * blockDim.y + threadIdx.y;
+  const int b = blockIdx.z;
+  if (xs >= W || y >= H) return;
+  int y0, y1;
+  float ly;
+  source_of(y, (float)h / (float)H, h, &y0, &y1, &ly);
+  const float hy = 1.0f - ly;
+  int r0[STRIP], r1[STRIP];
+  float lx[STRIP], hx[STRIP];
+  int xb = 0;
+#pragma unroll
+  for (int i = 0; i < STRIP; ++i) {
+    const int x = xs + i < W ? xs + i : W - 1;
+    int x0, x1;
+    source_of(x, (float)w / (float)W, w, &x0, &x1, &lx[i]);
+    if (i == 0) xb = x0;
+    r0[i] = x0 - xb;
+    r1[i] = x1 - xb;
+    hx[i] = 1.0f - lx[i];
+  }
+  int col[STRIP_COLS];
+#pragma unroll
+  for (int c = 0; c < STRIP_COLS; ++c) col[c] = xb + c < w ? xb + c : w - 1;
+  float best[STRIP];
+  int arg[STRIP];
+#pragma unroll
+  for (int i = 0; i < STRIP; ++i) {
+    best[i] = ARGMIN ? INFINITY : -INFINITY;
+    arg[i] = 0;
+  }
+  const float* m0 = maps + (size_t)b * C * h * w + (size_t)y0 * w;
+  const float* m1 = maps + (size_t)b * C * h * w + (size_t)y1 * w;
+  const size_t hw = (size_t)h * w;
+#pragma unroll 2
+  for (int c = 0; c < C; ++c) {
+    float v[STRIP_COLS];
+#pragma unroll
+    for (int k = 0; k < STRIP_COLS; ++k) v[k] = hy * m0[(size_t)c * hw + col[k]] + ly * m1[(size_t)c * hw + col[k]];
+#pragma unroll
+    for (int i = 0; i < STRIP; ++i) {
+      const float val = hx[i] * pick4(v, r0[i]) + lx[i] * pick4(v, r1[i]);
+      const bool better = ARGMIN ? (val < best[i]) : (val > best[i]);
+      if (better) {
+        best[i] = val;
+        arg[i] = c;
+      }
+    }
+  }
+  const size_t o = ((size_t)b * H + y) * W + xs;
+#pragma unroll
+  for (int i = 0; i < STRIP; ++i)
+    if (xs + i < W) {
+      out_idx[o + i] = arg[i];
+      if (out_val != nullptr) out_val[o + i] = best[i];
+    }
+}
+
 }  // namespace
 
 int launch_upsample_argext(const float* maps, int B, int C, int h, int w, int H, int W, int argmin, int32_t* out_idx,
                            float* out_val, cudaStream_t st) {
   if (B == 0 || H == 0 || W == 0) return SPS_OK;
+  // 8 outputs per thread need 7 * w/W + 2 <= 4 source columns
+  if (7.0f * (float)w / (float)W + 2.0f <= (float)STRIP_COLS - 1e-3f) {
+    dim3 block(32, 4), grid((W + 32 * STRIP - 1) / (32 * STRIP), (H + 3) / 4, B);
+    if (argmin)
+      upsample_argext_strip_kernel<true><<<grid, block, 0, st>>>(maps, C, h, w, H, W, out_idx, out_val);
+    else
+      upsample_argext_strip_kernel<false><<<grid, block, 0, st>>>(maps, C, h, w, H, W, out_idx, out_val);
+    count_launch(1);
+    SPS_CUDA_TRY(cudaGetLastError());
+    return SPS_OK;
+  }
   dim3 block(32, 8), grid((W + 31) / 32, (H + 7) / 8, B);
   if (argmin)
     upsample_argext_kernel<true><<<grid, block, 0, st>>>(maps, C, h, w, H, W, out_idx, out_val);
