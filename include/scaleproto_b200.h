@@ -13,7 +13,10 @@
  *  - the caller owns all memory; the library never allocates or frees device memory;
  *  - all work is enqueued on `stream` (a cudaStream_t passed as void*); no implicit syncs;
  *  - return value 0 = OK, otherwise an SpsStatus; text via sps_last_error() (thread local);
- *  - feature maps are fp32 NCHW exactly as the reference holds them: z[b][s*D + c][h][w];
+ *  - feature maps are fp32 NCHW exactly as the reference holds them, z[b][s*D + c][h][w] (z_dtype = SPS_Z_F32,
+ *    z_layout = SPS_Z_NCHW, the default), or 16-bit channels-last, z[b][h][w][s*D + c] (SPS_Z_F16 / SPS_Z_BF16 with
+ *    SPS_Z_NHWC: what the stock backbone emits under channels_last + autocast); the 16-bit layout is a legal 2-D tensor
+ *    map ([N][C], 512-byte rows) and is fed to the tensor cores by TMA with no conversion work;
  *  - N = B*H*W positions, row n = (b*H + h)*W + w (the order of permute(0,2,3,1).reshape(-1,P),
  *    segmentation/model/model_multiscale.py:369-370).
  */
@@ -27,7 +30,7 @@
 extern "C" {
 #endif
 
-#define SPS_ABI_VERSION 1
+#define SPS_ABI_VERSION 2
 #define SPS_MAX_SCALES 8
 
 typedef enum {
@@ -51,6 +54,18 @@ typedef enum {
 
 /* flags */
 #define SPS_FLAG_DETERMINISTIC 1 /* backward reductions over N in a fixed order (no fp32 atomics) */
+#define SPS_FLAG_ZPACK 2         /* fp32 NCHW input: re-lay the map as 16-bit channels-last tiles in a pre-pass (inside the
+                                    workspace) and run the TMA-fed kernels; tensor-core math modes only */
+#define SPS_FLAG_ZRELAYED 4      /* the z pointer of sps_head_fwd / sps_head_bwd is not the fp32 NCHW map itself but its
+                                    re-lay, written earlier by sps_z_relay (one re-lay shared by the forward and the
+                                    backward of a step); the descriptor still describes the fp32 map, dz stays fp32 NCHW */
+
+/* element type and layout of the feature maps z (and of dz, which always mirrors z) */
+#define SPS_Z_F32 0
+#define SPS_Z_F16 1   /* requires SPS_MATH_F16 or SPS_MATH_F16X3 */
+#define SPS_Z_BF16 2  /* requires SPS_MATH_BF16 or SPS_MATH_BF16X3 */
+#define SPS_Z_NCHW 0  /* z[b][c][h][w]  (SPS_Z_F32 only) */
+#define SPS_Z_NHWC 1  /* z[b][h][w][c]  (SPS_Z_F16 / SPS_Z_BF16 only; D = 64, 16-byte aligned base) */
 
 /* Shape of one head invocation.  Mirrors the state the reference keeps on the module
  * (segmentation/model/model_multiscale.py:104-149): prototype_vectors (P,D,1,1), num_scales,
@@ -64,6 +79,8 @@ typedef struct SpsHeadDesc {
   float eps;                            /* 1e-4 in the reference */
   int32_t math;                         /* SPS_MATH_* */
   int32_t flags;                        /* SPS_FLAG_* */
+  int32_t z_dtype;                      /* SPS_Z_F32 (default 0) | SPS_Z_F16 | SPS_Z_BF16 */
+  int32_t z_layout;                     /* SPS_Z_NCHW (default 0) | SPS_Z_NHWC */
 } SpsHeadDesc;
 
 /* Stage-2 grouping head (segmentation/model/model_multiscale_group.py:249-308).
@@ -104,6 +121,15 @@ const char* sps_last_error(void);
 /* Number of kernels this library has launched in this process (bench.py reports it as gpu_launches). */
 uint64_t sps_launch_count(void);
 
+/* Calls that asked for a tensor-core math mode and were served by the exact fp32 CUDA-core kernels instead, because the
+ * shape does not fit the tcgen05 kernels (bench.py prints it; 0 on every BASELINE shape). */
+uint64_t sps_fp32_reroute_count(void);
+
+/* 16-bit channels-last re-lay of an fp32 NCHW map for the TMA-fed kernels: [N][C] hi part, then (3-term math modes) the
+ * [N][C] lo part.  out: >= sps_z_relay_bytes(desc) bytes.  Pass `out` as z with SPS_FLAG_ZRELAYED. */
+size_t sps_z_relay_bytes(const SpsHeadDesc* desc);
+int sps_z_relay(const SpsHeadDesc* desc, const float* z, void* out, size_t out_bytes, void* stream);
+
 /* Bytes of scratch sps_head_bwd needs for this shape (0 is possible). */
 size_t sps_workspace_bytes(const SpsHeadDesc* desc);
 /* Bytes of scratch sps_head_fwd / sps_push_scan need (packed 16-bit prototype images of the tensor-core
@@ -114,27 +140,27 @@ size_t sps_head_fwd_workspace_bytes(const SpsHeadDesc* desc);
  * Replaces PPNetMultiScale._scale_l2_convolution + _l2_convolution + distance_2_similarity +
  * run_last_layer as chained by forward_from_conv_features
  * (segmentation/model/model_multiscale.py:256-317, 324-330, 243-244, 340-388).
- *   z        [B, S*D, H, W] fp32
+ *   z        [B, S*D, H, W] fp32, or [B, H, W, S*D] fp16 / bf16 (desc->z_dtype, z_layout)
  *   protos   [P, D] fp32
  *   last_w   [K, P] fp32 or NULL (NULL: no logits, e.g. prototype_distances / push_forward / stage 2)
  *   logits   [N, K] fp32 or NULL (required iff last_w != NULL)
  *   dist     [B, P, H, W] fp32 or NULL   (NULL = fused mode, the map is never written to HBM)
  *   act      [N, P] fp32 or NULL
  *   workspace >= sps_head_fwd_workspace_bytes(desc) bytes (may be NULL when that is 0) */
-int sps_head_fwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w,
+int sps_head_fwd(const SpsHeadDesc* desc, const void* z, const float* protos, const float* last_w,
                  float* logits, float* dist, float* act, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Prototype head backward (what autograd derives from the lines above; driven by manual_backward,
  * segmentation/model/module_multiscale.py:292).  d and a are recomputed from z and protos.
  *   dlogits [N,K] or NULL, ddist [B,P,H,W] or NULL (KLD loss back-props straight into distances,
  *   module_multiscale.py:242), dact [N,P] or NULL.
- *   dz [B,S*D,H,W] or NULL, dprotos [P,D] or NULL, dlast_w [K,P] or NULL: OVERWRITTEN.
+ *   dz (same element type and layout as z) or NULL, dprotos [P,D] or NULL, dlast_w [K,P] or NULL: OVERWRITTEN.
  *   workspace: >= sps_workspace_bytes(desc) bytes, contents undefined on entry and exit.
  * Routing: a tensor-core math mode with last_w, dlogits (and optionally ddist) runs the tcgen05 backward (K <= 256; more
  * than 32 classes run as slabs of 32, the gradients being linear in dlogits); a gradient through act, a call without
  * last_w/dlogits, K > 256, or SPS_MATH_FP32 runs the exact-operand CUDA-core kernels. */
-int sps_head_bwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w,
-                 const float* dlogits, const float* ddist, const float* dact, float* dz, float* dprotos,
+int sps_head_bwd(const SpsHeadDesc* desc, const void* z, const float* protos, const float* last_w,
+                 const float* dlogits, const float* ddist, const float* dact, void* dz, float* dprotos,
                  float* dlast_w, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Stage-2 group projection + last_layer_group.
@@ -200,7 +226,7 @@ int sps_upsample_argext(const float* maps, int32_t B, int32_t C, int32_t h, int3
  *   keys        [B, P] uint64, OVERWRITTEN: (float_bits(min masked distance) << 32) | flat index h*W+w
  *               of its first occurrence; (bits(1e10f) << 32) | 0 when the class is absent.
  *   workspace   >= sps_head_fwd_workspace_bytes(desc) bytes (NULL / 0 for SPS_MATH_FP32) */
-int sps_push_scan(const SpsHeadDesc* desc, const float* z, const float* protos, const int16_t* labels,
+int sps_push_scan(const SpsHeadDesc* desc, const void* z, const float* protos, const int16_t* labels,
                   const int32_t* proto_class, uint64_t* keys, void* workspace, size_t workspace_bytes, void* stream);
 
 /* Dataset arg-min over maps (push_multiscale_optimization.py:135-137, argmin(dim=0): first map wins).
@@ -225,7 +251,7 @@ int sps_push_topk(const uint64_t* keys, int32_t n_maps, int32_t P, uint32_t map_
  *   whose winning map lies in [map_base, map_base+n_maps) are written.
  *   proto_scale [P] int32 scale whose channel block is read (the reference uses p // (P/S), :161,:167).
  *   out [P, D] fp32. */
-int sps_push_gather(const SpsHeadDesc* desc, const float* z, const uint64_t* keys, const uint64_t* best,
+int sps_push_gather(const SpsHeadDesc* desc, const void* z, const uint64_t* keys, const uint64_t* best,
                     int32_t n_maps, uint32_t map_base, const int32_t* proto_scale, float* out, void* stream);
 
 #ifdef __cplusplus

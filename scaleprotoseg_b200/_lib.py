@@ -10,6 +10,10 @@ SPS_MAX_SCALES = 8
 ACT_LOG, ACT_LINEAR = 0, 1
 MATH_FP32, MATH_BF16X3, MATH_BF16, MATH_F16, MATH_F16X3 = 0, 1, 2, 3, 4
 FLAG_DETERMINISTIC = 1
+FLAG_ZPACK = 2       # fp32 NCHW input: 16-bit channels-last re-lay in a pre-pass, then the TMA-fed kernels
+FLAG_ZRELAYED = 4    # the z pointer is a re-lay written earlier by sps_z_relay
+Z_F32, Z_F16, Z_BF16 = 0, 1, 2
+Z_NCHW, Z_NHWC = 0, 1
 
 LIB_NAME = "libscaleproto_sm100.so"
 LIB_PATH = os.environ.get("SCALEPROTO_B200_LIB") or os.path.join(os.path.dirname(os.path.abspath(__file__)), LIB_NAME)
@@ -25,6 +29,8 @@ class SpsHeadDesc(C.Structure):
         ("eps", C.c_float),
         ("math", C.c_int32),
         ("flags", C.c_int32),
+        ("z_dtype", C.c_int32),
+        ("z_layout", C.c_int32),
     ]
 
 
@@ -50,6 +56,9 @@ _SIGNATURES = {
     "sps_version": (C.c_int, []),
     "sps_last_error": (C.c_char_p, []),
     "sps_launch_count": (C.c_uint64, []),
+    "sps_fp32_reroute_count": (C.c_uint64, []),
+    "sps_z_relay_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc)]),
+    "sps_z_relay": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, C.c_size_t, _P]),
     "sps_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc)]),
     "sps_head_fwd_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc)]),
     "sps_head_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),

@@ -24,6 +24,10 @@ int cuda_fail(cudaError_t e, const char* what) {
 
 static std::atomic<unsigned long long> g_launches{0};
 void count_launch(int n) { g_launches.fetch_add((unsigned long long)n, std::memory_order_relaxed); }
+// calls that asked for a tensor-core math mode but were served by the exact fp32 CUDA-core kernels because the shape
+// does not fit the tcgen05 kernels: reported (sps_fp32_reroute_count), never hidden
+static std::atomic<unsigned long long> g_reroutes{0};
+void note_fp32_reroute() { g_reroutes.fetch_add(1ull, std::memory_order_relaxed); }
 
 int sm_count() {
   static int cached = 0;
@@ -51,6 +55,17 @@ int validate_desc(const SpsHeadDesc* d) {
   SPS_REQUIRE(d->act_kind == SPS_ACT_LOG || d->act_kind == SPS_ACT_LINEAR, SPS_ERR_BAD_ARG, "act_kind=%d", d->act_kind);
   SPS_REQUIRE(d->math >= SPS_MATH_FP32 && d->math <= SPS_MATH_F16X3, SPS_ERR_BAD_ARG, "math=%d", d->math);
   SPS_REQUIRE((long long)d->H * d->W < (1LL << 31), SPS_ERR_UNSUPPORTED, "H*W too large");
+  if (d->z_dtype == SPS_Z_F32) {
+    SPS_REQUIRE(d->z_layout == SPS_Z_NCHW, SPS_ERR_UNSUPPORTED, "fp32 feature maps must be NCHW (z_layout=%d)", d->z_layout);
+  } else {
+    SPS_REQUIRE(d->z_dtype == SPS_Z_F16 || d->z_dtype == SPS_Z_BF16, SPS_ERR_BAD_ARG, "z_dtype=%d", d->z_dtype);
+    SPS_REQUIRE(d->z_layout == SPS_Z_NHWC, SPS_ERR_UNSUPPORTED, "16-bit feature maps must be channels-last (z_layout=%d)", d->z_layout);
+    const bool f16 = d->z_dtype == SPS_Z_F16;
+    SPS_REQUIRE(f16 ? (d->math == SPS_MATH_F16 || d->math == SPS_MATH_F16X3) : (d->math == SPS_MATH_BF16 || d->math == SPS_MATH_BF16X3),
+                SPS_ERR_UNSUPPORTED, "math=%d does not match the %s feature maps (fp16 maps: F16 / F16X3, bf16 maps: BF16 / BF16X3)", d->math,
+                f16 ? "fp16" : "bf16");
+    SPS_REQUIRE(d->D == 64, SPS_ERR_UNSUPPORTED, "16-bit channels-last feature maps: D=%d, only 64 channels per scale are supported", d->D);
+  }
   return SPS_OK;
 }
 
@@ -66,50 +81,142 @@ const char* sps_last_error(void) { return g_err; }
 
 uint64_t sps_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
+uint64_t sps_fp32_reroute_count(void) { return g_reroutes.load(std::memory_order_relaxed); }
+
+static bool use_zpack(const SpsHeadDesc* d) {
+  return d->z_dtype == SPS_Z_F32 && d->math != SPS_MATH_FP32 && (d->flags & (SPS_FLAG_ZPACK | SPS_FLAG_ZRELAYED)) != 0 && d->D == 64;
+}
+static bool is_split(int math) { return math == SPS_MATH_F16X3 || math == SPS_MATH_BF16X3; }
+static size_t align1k(size_t v) { return (v + 1023) / 1024 * 1024; }
+
 size_t sps_head_fwd_workspace_bytes(const SpsHeadDesc* desc) {
   if (validate_desc(desc) != SPS_OK || desc->math == SPS_MATH_FP32) return 0;
-  return head_fwd_tc_workspace(make_shape(desc));
+  const HeadShape s = make_shape(desc);
+  size_t n = align1k(head_fwd_tc_workspace(s));
+  if (use_zpack(desc) && !(desc->flags & SPS_FLAG_ZRELAYED)) n += z_pack_bytes(s, desc->math);
+  return n;
 }
 
 size_t sps_workspace_bytes(const SpsHeadDesc* desc) {
   if (validate_desc(desc) != SPS_OK) return 0;
   HeadShape s = make_shape(desc);
-  size_t a = head_bwd_simt_workspace(s, desc->flags);
+  size_t a = desc->z_dtype == SPS_Z_F32 ? head_bwd_simt_workspace(s, desc->flags) : 0;
   size_t b = desc->math != SPS_MATH_FP32 ? head_bwd_tc_workspace(s) : 0;
-  return a > b ? a : b;
+  size_t n = align1k(a > b ? a : b);
+  if (use_zpack(desc) && !(desc->flags & SPS_FLAG_ZRELAYED)) n += z_pack_bytes(s, desc->math);
+  return n;
 }
 
-int sps_head_fwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w, float* logits,
+size_t sps_z_relay_bytes(const SpsHeadDesc* desc) {
+  if (validate_desc(desc) != SPS_OK || desc->math == SPS_MATH_FP32 || desc->z_dtype != SPS_Z_F32) return 0;
+  return z_pack_bytes(make_shape(desc), desc->math);
+}
+
+int sps_z_relay(const SpsHeadDesc* desc, const float* z, void* out, size_t out_bytes, void* stream) {
+  int rc = validate_desc(desc);
+  if (rc != SPS_OK) return rc;
+  SPS_REQUIRE(desc->z_dtype == SPS_Z_F32 && desc->math != SPS_MATH_FP32, SPS_ERR_BAD_ARG,
+              "z_relay: needs an fp32 NCHW map and a tensor-core math mode");
+  HeadShape s = make_shape(desc);
+  if (s.N == 0) return SPS_OK;
+  SPS_REQUIRE(z != nullptr && out != nullptr && out_bytes >= z_pack_bytes(s, desc->math), SPS_ERR_WORKSPACE,
+              "z_relay: need %zu bytes, got %zu", z_pack_bytes(s, desc->math), out_bytes);
+  return launch_z_pack(s, desc->math, z, out, reinterpret_cast<cudaStream_t>(stream));
+}
+
+int sps_head_fwd(const SpsHeadDesc* desc, const void* z, const float* protos, const float* last_w, float* logits,
                  float* dist, float* act, void* workspace, size_t workspace_bytes, void* stream) {
   int rc = validate_desc(desc);
   if (rc != SPS_OK) return rc;
   HeadShape s = make_shape(desc);
-  if (s.N == 0 || s.P == 0) return SPS_OK;
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  if (s.N == 0 || s.P == 0) {
+    // nothing to contract over: the logits of an empty prototype set are zeros (torch: (N,0) @ (0,K))
+    if (logits != nullptr && s.N > 0) SPS_CUDA_TRY(cudaMemsetAsync(logits, 0, sizeof(float) * (size_t)s.N * s.K, st));
+    return SPS_OK;
+  }
   SPS_REQUIRE(z != nullptr && protos != nullptr, SPS_ERR_BAD_ARG, "z/protos NULL");
   SPS_REQUIRE((last_w == nullptr) == (logits == nullptr), SPS_ERR_BAD_ARG, "last_w and logits go together");
   SPS_REQUIRE(last_w != nullptr || dist != nullptr || act != nullptr, SPS_ERR_BAD_ARG, "no output requested");
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
-  if (desc->math == SPS_MATH_FP32 || !head_fwd_tc_supported(s, desc->math, last_w != nullptr, act != nullptr))
-    return launch_head_fwd_simt(s, z, protos, last_w, logits, dist, act, st);
-  return launch_head_fwd_tc(s, desc->math, z, protos, last_w, logits, dist, act, workspace, workspace_bytes, st);
+  if (desc->z_dtype != SPS_Z_F32) {   // 16-bit channels-last map: TMA-fed kernel or nothing (no silent re-route)
+    SPS_REQUIRE(head_fwd_tma_supported(s, desc->math, last_w != nullptr, act != nullptr, false), SPS_ERR_UNSUPPORTED,
+                "16-bit channels-last forward: this shape does not fit the tensor-core kernel (K=%d, P=%d)", s.K, s.P);
+    return launch_head_fwd_tma(s, desc->math, z, nullptr, protos, last_w, logits, dist, act, workspace, workspace_bytes, st);
+  }
+  const float* zf = reinterpret_cast<const float*>(z);
+  if (use_zpack(desc) && head_fwd_tma_supported(s, desc->math, last_w != nullptr, act != nullptr, is_split(desc->math))) {
+    const size_t img_bytes = align1k(head_fwd_tc_workspace(s));
+    const void *hi, *lo;
+    if (desc->flags & SPS_FLAG_ZRELAYED) {
+      z_pack_parts(s, desc->math, z, &hi, &lo);
+    } else {
+      SPS_REQUIRE(workspace != nullptr && workspace_bytes >= img_bytes + z_pack_bytes(s, desc->math), SPS_ERR_WORKSPACE,
+                  "head_fwd workspace: need %zu bytes, got %zu", img_bytes + z_pack_bytes(s, desc->math), workspace_bytes);
+      void* area = reinterpret_cast<unsigned char*>(workspace) + img_bytes;
+      rc = launch_z_pack(s, desc->math, zf, area, st);
+      if (rc != SPS_OK) return rc;
+      z_pack_parts(s, desc->math, area, &hi, &lo);
+    }
+    return launch_head_fwd_tma(s, desc->math, hi, lo, protos, last_w, logits, dist, act, workspace, img_bytes, st);
+  }
+  SPS_REQUIRE(!(desc->flags & SPS_FLAG_ZRELAYED), SPS_ERR_UNSUPPORTED, "SPS_FLAG_ZRELAYED: this shape has no TMA-fed forward");
+  if (desc->math == SPS_MATH_FP32 || !head_fwd_tc_supported(s, desc->math, last_w != nullptr, act != nullptr)) {
+    if (desc->math != SPS_MATH_FP32) note_fp32_reroute();
+    return launch_head_fwd_simt(s, zf, protos, last_w, logits, dist, act, st);
+  }
+  return launch_head_fwd_tc(s, desc->math, zf, protos, last_w, logits, dist, act, workspace, workspace_bytes, st);
 }
 
-int sps_head_bwd(const SpsHeadDesc* desc, const float* z, const float* protos, const float* last_w,
-                 const float* dlogits, const float* ddist, const float* dact, float* dz, float* dprotos,
+int sps_head_bwd(const SpsHeadDesc* desc, const void* z, const float* protos, const float* last_w,
+                 const float* dlogits, const float* ddist, const float* dact, void* dz, float* dprotos,
                  float* dlast_w, void* workspace, size_t workspace_bytes, void* stream) {
   int rc = validate_desc(desc);
   if (rc != SPS_OK) return rc;
   HeadShape s = make_shape(desc);
+  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const bool z16 = desc->z_dtype != SPS_Z_F32;
+  if (s.N == 0 || s.P == 0 || (dlogits == nullptr && ddist == nullptr && dact == nullptr)) {
+    // empty batch / no prototypes / no upstream gradient: every requested gradient is zero (never uninitialised memory)
+    if (dz != nullptr && s.N > 0) SPS_CUDA_TRY(cudaMemsetAsync(dz, 0, (z16 ? 2 : 4) * (size_t)s.N * s.C, st));
+    if (dprotos != nullptr && s.P > 0) SPS_CUDA_TRY(cudaMemsetAsync(dprotos, 0, sizeof(float) * (size_t)s.P * s.D, st));
+    if (dlast_w != nullptr && s.P > 0) SPS_CUDA_TRY(cudaMemsetAsync(dlast_w, 0, sizeof(float) * (size_t)s.K * s.P, st));
+    return SPS_OK;
+  }
   SPS_REQUIRE(z != nullptr && protos != nullptr, SPS_ERR_BAD_ARG, "z/protos NULL");
   SPS_REQUIRE(dlogits == nullptr || last_w != nullptr, SPS_ERR_BAD_ARG, "dlogits given without last_w");
-  cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
   // tensor-core math mode with a last layer (upstream gradient = dlogits, optionally + ddist from the KLD loss):
   // tcgen05 backward; a gradient through the activation map (dact), no dlogits, or SPS_MATH_FP32: exact-operand
   // CUDA-core kernels
-  if (head_bwd_tc_supported(s, desc->math, last_w, dlogits, ddist, dact))
-    return launch_head_bwd_tc(s, desc->math, z, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, workspace, workspace_bytes, st);
-  return launch_head_bwd_simt(s, desc->flags, z, protos, last_w, dlogits, ddist, dact, dz, dprotos, dlast_w, workspace,
+  const bool tc_ok = head_bwd_tc_supported(s, desc->math, last_w, dlogits, ddist, dact);
+  if (z16) {
+    SPS_REQUIRE(tc_ok, SPS_ERR_UNSUPPORTED,
+                "16-bit channels-last backward needs last_w + dlogits (no gradient through the activation map) and K <= 256");
+    return launch_head_bwd_tc(s, desc->math, 1, z, nullptr, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, workspace,
                               workspace_bytes, st);
+  }
+  const float* zf = reinterpret_cast<const float*>(z);
+  if (tc_ok && use_zpack(desc)) {
+    const size_t base_bytes = align1k(head_bwd_tc_workspace(s));
+    const void *hi, *lo;
+    if (desc->flags & SPS_FLAG_ZRELAYED) {
+      z_pack_parts(s, desc->math, z, &hi, &lo);
+    } else {
+      SPS_REQUIRE(workspace != nullptr && workspace_bytes >= base_bytes + z_pack_bytes(s, desc->math), SPS_ERR_WORKSPACE,
+                  "head_bwd workspace: need %zu bytes, got %zu", base_bytes + z_pack_bytes(s, desc->math), workspace_bytes);
+      void* area = reinterpret_cast<unsigned char*>(workspace) + base_bytes;
+      rc = launch_z_pack(s, desc->math, zf, area, st);
+      if (rc != SPS_OK) return rc;
+      z_pack_parts(s, desc->math, area, &hi, &lo);
+    }
+    return launch_head_bwd_tc(s, desc->math, 2, hi, lo, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, workspace, base_bytes, st);
+  }
+  SPS_REQUIRE(!(desc->flags & SPS_FLAG_ZRELAYED), SPS_ERR_UNSUPPORTED, "SPS_FLAG_ZRELAYED: this call has no TMA-fed backward");
+  if (tc_ok)
+    return launch_head_bwd_tc(s, desc->math, 0, zf, nullptr, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, workspace,
+                              workspace_bytes, st);
+  if (desc->math != SPS_MATH_FP32 && dact == nullptr && dlogits != nullptr) note_fp32_reroute();
+  return launch_head_bwd_simt(s, desc->flags, zf, protos, last_w, dlogits, ddist, dact, reinterpret_cast<float*>(dz), dprotos, dlast_w,
+                              workspace, workspace_bytes, st);
 }
 
 static int check_group(const SpsGroupDesc* g) {
@@ -261,18 +368,20 @@ int sps_upsample_argext(const float* maps, int32_t B, int32_t C, int32_t h, int3
   return launch_upsample_argext(maps, B, C, h, w, H, W, argmin, out_idx, out_val, reinterpret_cast<cudaStream_t>(stream));
 }
 
-int sps_push_scan(const SpsHeadDesc* desc, const float* z, const float* protos, const int16_t* labels,
+int sps_push_scan(const SpsHeadDesc* desc, const void* z, const float* protos, const int16_t* labels,
                   const int32_t* proto_class, uint64_t* keys, void* workspace, size_t workspace_bytes, void* stream) {
   int rc = validate_desc(desc);
   if (rc != SPS_OK) return rc;
   SPS_REQUIRE(z && protos && labels && proto_class && keys, SPS_ERR_BAD_ARG, "push_scan: NULL argument");
   HeadShape s = make_shape(desc);
   cudaStream_t st = reinterpret_cast<cudaStream_t>(stream);
+  const bool z16 = desc->z_dtype != SPS_Z_F32;
   if (desc->math == SPS_MATH_FP32)
-    return launch_push_scan_simt(s, z, protos, labels, proto_class, reinterpret_cast<unsigned long long*>(keys), st);
+    return launch_push_scan_simt(s, reinterpret_cast<const float*>(z), protos, labels, proto_class,
+                                 reinterpret_cast<unsigned long long*>(keys), st);
   rc = launch_push_fill(reinterpret_cast<unsigned long long*>(keys), (long long)s.B * s.P, st);
   if (rc != SPS_OK || s.B == 0 || s.P == 0 || s.HW == 0) return rc;
-  return launch_push_scan_tc(s, desc->math, z, protos, labels, proto_class, reinterpret_cast<unsigned long long*>(keys),
+  return launch_push_scan_tc(s, desc->math, z, z16, protos, labels, proto_class, reinterpret_cast<unsigned long long*>(keys),
                              workspace, workspace_bytes, st);
 }
 
@@ -291,7 +400,7 @@ int sps_push_topk(const uint64_t* keys, int32_t n_maps, int32_t P, uint32_t map_
                           reinterpret_cast<cudaStream_t>(stream));
 }
 
-int sps_push_gather(const SpsHeadDesc* desc, const float* z, const uint64_t* keys, const uint64_t* best,
+int sps_push_gather(const SpsHeadDesc* desc, const void* z, const uint64_t* keys, const uint64_t* best,
                     int32_t n_maps, uint32_t map_base, const int32_t* proto_scale, float* out, void* stream) {
   int rc = validate_desc(desc);
   if (rc != SPS_OK) return rc;

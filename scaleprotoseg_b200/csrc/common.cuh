@@ -33,6 +33,9 @@ struct HeadShape {
   int scale_lo[SPS_MAX_SCALES + 1];
   int act_kind;
   float eps;
+  int z_dtype;   // SPS_Z_*
+  int z_layout;  // SPS_Z_NCHW / SPS_Z_NHWC
+  int flags;     // SPS_FLAG_*
 };
 
 inline HeadShape make_shape(const SpsHeadDesc* d) {
@@ -48,12 +51,16 @@ inline HeadShape make_shape(const SpsHeadDesc* d) {
   for (int i = 0; i <= SPS_MAX_SCALES; ++i) s.scale_lo[i] = (i <= d->S) ? d->scale_lo[i] : d->P;
   s.act_kind = d->act_kind;
   s.eps = d->eps;
+  s.z_dtype = d->z_dtype;
+  s.z_layout = d->z_layout;
+  s.flags = d->flags;
   return s;
 }
 
 int validate_desc(const SpsHeadDesc* d);
 int sm_count();
 void count_launch(int n = 1);
+void note_fp32_reroute();
 
 // Programmatic dependent launch: the kernel may start while the previous kernel of the stream is still running (that
 // kernel calls pdl_launch_dependents() early); every thread that reads what the previous kernel wrote calls
@@ -94,12 +101,23 @@ size_t head_fwd_tc_workspace(const HeadShape& s);
 bool head_fwd_tc_supported(const HeadShape& s, int math, bool with_last_layer, bool dense_act);
 int launch_head_fwd_tc(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w,
                        float* logits, float* dist, float* act, void* ws, size_t ws_bytes, cudaStream_t st);
+// TMA-fed kernels (16-bit channels-last maps, or the hi / lo re-lay of an fp32 map)
+bool head_fwd_tma_supported(const HeadShape& s, int math, bool with_last_layer, bool dense_act, bool zlo);
+int launch_head_fwd_tma(const HeadShape& s, int math, const void* z_hi, const void* z_lo, const float* protos,
+                        const float* last_w, float* logits, float* dist, float* act, void* ws, size_t ws_bytes,
+                        cudaStream_t st);
+size_t z_pack_bytes(const HeadShape& s, int math);
+int launch_z_pack(const HeadShape& s, int math, const float* z, void* out, cudaStream_t st);
+// hi / lo parts inside a re-lay buffer of z_pack_bytes (lo = nullptr in the single-term modes)
+void z_pack_parts(const HeadShape& s, int math, const void* area, const void** hi, const void** lo);
 bool head_bwd_tc_supported(const HeadShape& s, int math, const float* last_w, const float* dlogits, const float* ddist,
                            const float* dact);
 size_t head_bwd_tc_workspace(const HeadShape& s);
-int launch_head_bwd_tc(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w,
-                       const float* dlogits, const float* ddist, float* dz, float* dprotos, float* dlast_w, void* ws,
-                       size_t ws_bytes, cudaStream_t st);
+// zmode: 0 = z is the fp32 NCHW map; 1 = z is a 16-bit channels-last map (dz likewise); 2 = z / z_lo are the hi / lo
+// re-lay of an fp32 map (dz fp32 NCHW)
+int launch_head_bwd_tc(const HeadShape& s, int math, int zmode, const void* z, const void* z_lo, const float* protos,
+                       const float* last_w, const float* dlogits, const float* ddist, void* dz, float* dprotos,
+                       float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st);
 int launch_head_bwd_simt(const HeadShape& s, int flags, const float* z, const float* protos, const float* last_w,
                          const float* dlogits, const float* ddist, const float* dact, float* dz, float* dprotos,
                          float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st);
@@ -111,11 +129,11 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
 int launch_push_scan_simt(const HeadShape& s, const float* z, const float* protos, const int16_t* labels,
                           const int32_t* proto_class, unsigned long long* keys, cudaStream_t st);
 int launch_push_fill(unsigned long long* keys, long long count, cudaStream_t st);
-int launch_push_scan_tc(const HeadShape& s, int math, const float* z, const float* protos, const int16_t* labels,
+int launch_push_scan_tc(const HeadShape& s, int math, const void* z, bool z16, const float* protos, const int16_t* labels,
                         const int32_t* proto_class, unsigned long long* keys, void* ws, size_t ws_bytes, cudaStream_t st);
 int launch_push_reduce(const unsigned long long* keys, int n_maps, int P, uint32_t map_base,
                        unsigned long long* best, cudaStream_t st);
-int launch_push_gather(const HeadShape& s, const float* z, const unsigned long long* keys,
+int launch_push_gather(const HeadShape& s, const void* z, const unsigned long long* keys,
                        const unsigned long long* best, int n_maps, uint32_t map_base, const int32_t* proto_scale,
                        float* out, cudaStream_t st);
 

@@ -21,7 +21,7 @@
 // TMEM (512 columns): S x2 [0,128), dA x2 [128,256), dz [256,320), chunk j accumulators [320+64j, 384+64j):
 //   lanes 0-15 (+32q): dp^T 64 columns; lanes 16-31 (+32q): dW^T columns [0,32), csum columns [32,40).
 #include <type_traits>
-#include "tc_common.cuh"
+#include "tma.cuh"
 
 namespace sps {
 namespace tcb {
@@ -61,6 +61,8 @@ struct GroupTable {
 };
 
 struct BwdParams {
+  CUtensorMap tm_hi;            // ZM_TMA16 / ZM_TMAHL: [N][C] 16-bit map (or its hi part)
+  CUtensorMap tm_lo;            // ZM_TMAHL in a split mode: lo part
   HeadShape s;
   ChunkTable ct;
   GroupTable gt;
@@ -171,12 +173,14 @@ template <int NSPLIT> struct Lay {
 };
 constexpr int T_S = 0, T_DA = 128, T_DZ = 256, T_ACC = 320;
 enum { B_AFULL = 0, B_AEMPTY = 2, B_SFULL = 4, B_SEMPTY = 6, B_GFULL = 8, B_GEMPTY = 10, B_DZFULL = 12, B_DZEMPTY = 13,
-       B_RES = 14, B_ACC = 15, B_COUNT = 16 };
+       B_RES = 14, B_ACC = 15, B_TFULL = 16, B_COUNT = 18 };
 
 // HAS_DD: a gradient also arrives through the dense distance map (prm.ddist; the KLD loss of stage-1 training).
-template <typename X, int NSPLIT, bool HAS_DD>
+template <typename X, int NSPLIT, bool HAS_DD, int ZMODE>
 __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_constant__ BwdParams prm) {
   using L = Lay<NSPLIT>;
+  // the feature tile has a lo part: fp32 source in a split mode (a 16-bit map is exact in one term)
+  constexpr bool ZLO = NSPLIT == 3 && ZMODE != ZM_TMA16;
   constexpr int A_BUF = L::A_BUF, RES = L::RES, SM_RES = L::SM_RES, SM_A = L::SM_A, SM_G = L::SM_G, SM_SG = L::SM_SG,
                 SM_BAR = L::SM_BAR;
   extern __shared__ unsigned char smem_raw[];
@@ -208,6 +212,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       mbar_init(bar(B_GFULL + i), 8);
       mbar_init(bar(B_GEMPTY + i), 1);
     }
+    mbar_init(bar(B_TFULL), 1);      // TMA modes: arrive.expect_tx + the tile bytes
+    mbar_init(bar(B_TFULL + 1), 1);
     mbar_init(bar(B_DZFULL), 1);
     mbar_init(bar(B_DZEMPTY), 8);
     mbar_init(bar(B_RES), 1);
@@ -249,8 +255,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
         if (NSPLIT == 3) {
 #pragma unroll
           for (int k = 0; k < 4; ++k) mma_f16(dS, desc_sw128(ab0 + AOFF_Z + 32 * k), desc_sw128(img + BOFF_BL + 32 * k), ID, 1);
+          if (ZLO) {
 #pragma unroll
-          for (int k = 0; k < 4; ++k) mma_f16(dS, desc_sw128(ab0 + AOFF_ZL + 32 * k), desc_sw128(img + BOFF_BH + 32 * k), ID, 1);
+            for (int k = 0; k < 4; ++k) mma_f16(dS, desc_sw128(ab0 + AOFF_ZL + 32 * k), desc_sw128(img + BOFF_BH + 32 * k), ID, 1);
+          }
         }
 #pragma unroll
         for (int k = 0; k < 2; ++k) mma_f16(dA, desc_k_sw64(ab0 + AOFF_DL + 32 * k), desc_k_sw64(img + BOFF_W3 + 32 * k), ID, k);
@@ -326,9 +334,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
     float dl[KP_BWD];
     if (my_tiles > 0) {
       const long long n0 = row_of(0);
-      const float* p0 = row_ptr(n0);
-      zst.issue_half(0, p0, hw, s.D);
-      zst.issue_half(1, p0, hw, s.D);
+      if (ZMODE == ZM_LDG) {
+        const float* p0 = row_ptr(n0);
+        zst.issue_half(0, p0, hw, s.D);
+        zst.issue_half(1, p0, hw, s.D);
+      }
       load_dl(n0, dl);
     }
     pdl_wait();  // max |dlogits| comes from the pre-pass launched just before this kernel (the loads above are in flight)
@@ -339,6 +349,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       mbar_wait(bar(B_AEMPTY + ab), ((ti >> 1) & 1) ^ 1);
       if (m == 0) TLB(2, 4 * ti + 1);
       unsigned char* a0 = gbase + SM_A + ab * A_BUF;
+      if (ZMODE != ZM_LDG && m == 0) {   // the buffer is free: one thread sends the tile's TMA (hi [+ lo] part)
+        const int row0 = (int)(((long long)cta_local + (long long)ti * ncta) * TILE_M);
+        mbar_arrive_expect_tx(bar(B_TFULL + ab), (ZLO ? 2u : 1u) * TILE_M * 128u);
+        tma_load_2d(base + SM_A + ab * A_BUF + AOFF_Z, &prm.tm_hi, sc * s.D, row0, bar(B_TFULL + ab));
+        if (ZLO) tma_load_2d(base + SM_A + ab * A_BUF + AOFF_ZL, &prm.tm_lo, sc * s.D, row0, bar(B_TFULL + ab));
+      }
       // dlogits first: its 32 registers are dead while the feature row is converted
 #pragma unroll
       for (int gq = 0; gq < 4; ++gq) {
@@ -349,10 +365,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
             make_uint4(w[0], w[1], w[2], w[3]);
       }
       float zn = 0.f;
-      zst.template convert_half<4>(0, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
-      if (m == 0) TLB(6, 512 + 2 * ti);
-      zst.template convert_half<4>(1, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
-      if (m == 0) TLB(6, 513 + 2 * ti);
+      if (ZMODE == ZM_LDG) {
+        zst.template convert_half<4>(0, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
+        if (m == 0) TLB(6, 512 + 2 * ti);
+        zst.template convert_half<4>(1, m, a0 + AOFF_Z, a0 + AOFF_ZL, zn);
+        if (m == 0) TLB(6, 513 + 2 * ti);
+      } else {
+        // the tile has landed in its final layout; what is left is the squared norm of this thread's row
+        mbar_wait(bar(B_TFULL + ab), (ti >> 1) & 1);
+        zn = tile_row_norm<X, ZLO>(a0 + AOFF_Z, a0 + AOFF_ZL, m);
+      }
       ZStage<X, NSPLIT>::store_norm(m, a0 + AOFF_N, zn);
       if (m == 0) TLB(2, 4 * ti + 3);
       fence_proxy_async();
@@ -362,9 +384,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       // the next tile's loads go out AFTER the arrive: mbarrier.arrive has release semantics and would wait for them
       if (ti + 1 < my_tiles) {
         const long long nn = row_of(ti + 1);
-        const float* pn = row_ptr(nn);
-        zst.issue_half(0, pn, hw, s.D);
-        zst.issue_half(1, pn, hw, s.D);
+        if (ZMODE == ZM_LDG) {
+          const float* pn = row_ptr(nn);
+          zst.issue_half(0, pn, hw, s.D);
+          zst.issue_half(1, pn, hw, s.D);
+        }
         load_dl(nn, dl);
       }
     }
@@ -410,14 +434,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
         const uint4 zz = *reinterpret_cast<const uint4*>(zrow + zo);
         const uint32_t zw[4] = {zz.x, zz.y, zz.z, zz.w};
         uint32_t zlw[4] = {0u, 0u, 0u, 0u};
-        if (NSPLIT == 3) {
+        if (ZLO) {
           const uint4 zl = *reinterpret_cast<const uint4*>(zrow + (AOFF_ZL - AOFF_Z) + zo);
           zlw[0] = zl.x, zlw[1] = zl.y, zlw[2] = zl.z, zlw[3] = zl.w;
         }
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
           float2 zf = Pack2<X>::unpack(zw[e]);
-          if (NSPLIT == 3) {
+          if (ZLO) {
             const float2 zl2 = Pack2<X>::unpack(zlw[e]);
             zf.x += zl2.x;
             zf.y += zl2.y;
@@ -428,7 +452,19 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       }
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(B_AEMPTY + ab));   // the shared-memory z tile has been read
-      if (prm.dz != nullptr && valid) {
+      if (ZMODE == ZM_TMA16) {
+        // dz mirrors z: 16-bit channels-last.  This thread owns 32 consecutive channels of row n: 64 contiguous bytes.
+        if (prm.dz != nullptr && valid) {
+          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<unsigned char*>(prm.dz) +
+                                                ((size_t)n * s.C + (size_t)sc * s.D + half * 32) * 2);
+          if (!multi) {
+#pragma unroll
+            for (int gq = 0; gq < 4; ++gq)
+              dst[gq] = make_uint4(Pack2<X>::pack(dv[gq * 8], dv[gq * 8 + 1]), Pack2<X>::pack(dv[gq * 8 + 2], dv[gq * 8 + 3]),
+                                   Pack2<X>::pack(dv[gq * 8 + 4], dv[gq * 8 + 5]), Pack2<X>::pack(dv[gq * 8 + 6], dv[gq * 8 + 7]));
+          }
+        }
+      } else if (prm.dz != nullptr && valid) {
         const int ch0 = half * 32;
         const int nlive = s.D - ch0 < 32 ? s.D - ch0 : 32;   // channels of this half that exist (D may be < 64)
         float* dzp = prm.dz + (b * (long long)s.C + (long long)sc * s.D + ch0) * s.HW + pix;
@@ -691,8 +727,21 @@ static int bwd_nsplit(const tcb::GroupTable& gt) {
 
 bool head_bwd_tc_supported(const HeadShape& s, int math, const float* last_w, const float* dlogits, const float* ddist,
                            const float* dact) {
-  return math != SPS_MATH_FP32 && last_w != nullptr && dlogits != nullptr && dact == nullptr &&
-         s.K <= 8 * tcb::KP_BWD && s.D <= 64 && s.D % 8 == 0 && s.N > 0 && s.N < (1ll << 31) && s.P > 0;
+  if (!(math != SPS_MATH_FP32 && last_w != nullptr && dlogits != nullptr && dact == nullptr && s.K <= 8 * tcb::KP_BWD &&
+        s.D <= 64 && s.D % 8 == 0 && s.N > 0 && s.N < (1ll << 31) && s.P > 0))
+    return false;
+  // the chunk / group tables must fit as well (the forward checks the same limits): otherwise the fp32 kernels run
+  tc::ChunkTable ct;
+  int nc = 0;
+  for (int sc = 0; sc < s.S; ++sc) nc += (s.scale_lo[sc + 1] - s.scale_lo[sc] + tc::CN - 1) / tc::CN;
+  if (nc > tc::MAX_CHUNKS) return false;
+  int ng = 0;
+  for (int sc = 0; sc < s.S; ++sc) {
+    const int c = (s.scale_lo[sc + 1] - s.scale_lo[sc] + tc::CN - 1) / tc::CN;
+    ng += (c + tcb::GROUP_CHUNKS - 1) / tcb::GROUP_CHUNKS;
+  }
+  (void)ct;
+  return ng <= tcb::MAX_GROUPS && ng <= sm_count();
 }
 
 size_t head_bwd_tc_workspace(const HeadShape& s) {
@@ -713,9 +762,9 @@ size_t head_bwd_tc_workspace(const HeadShape& s) {
 //   dlogits  : column k0 of the (N x K_total) upstream gradient, rows dl_stride = K_total floats apart
 //   dl_all / dl_all_count : the whole dlogits buffer (scanned for max |.|)
 template <typename X, int NSPLIT>
-static int launch_bwd_slab(const HeadShape& s, const float* z, const float* protos, const float* last_w, const float* dlogits,
-                           int dl_stride, const float* dl_all, long long dl_all_count, const float* ddist, float* dz,
-                           float* dprotos, float* dlast_w, bool first_slab, bool several_slabs, void* ws, size_t ws_bytes,
+static int launch_bwd_slab(const HeadShape& s, int zmode, const void* z, const void* z_lo, const float* protos, const float* last_w,
+                           const float* dlogits, int dl_stride, const float* dl_all, long long dl_all_count, const float* ddist,
+                           void* dz, float* dprotos, float* dlast_w, bool first_slab, bool several_slabs, void* ws, size_t ws_bytes,
                            cudaStream_t st) {
   tcb::BwdParams prm;
   int rc = build_chunk_table(s, true, &prm.ct);
@@ -739,8 +788,19 @@ static int launch_bwd_slab(const HeadShape& s, const float* z, const float* prot
   SPS_CUDA_TRY(cudaMemsetAsync(amax, 0, all_written ? 256 : 256 + part_bytes, st));
   bool any_multi = false;
   for (int g = 0; g < prm.gt.n_groups; ++g) any_multi |= prm.gt.multi[g] != 0;
-  if (dz != nullptr && first_slab && (any_multi || several_slabs))
+  const bool dz_atomic = any_multi || several_slabs;
+  SPS_REQUIRE(!(zmode == tcb::ZM_TMA16 && dz_atomic && dz != nullptr), SPS_ERR_UNSUPPORTED,
+              "16-bit channels-last backward: a scale with more than %d prototypes or more than %d classes needs dz accumulation, "
+              "which the 16-bit dz layout does not support (P=%d, K=%d)", tcb::GROUP_CHUNKS * tc::CN, tcb::KP_BWD, s.P, s.K);
+  if (dz != nullptr && first_slab && dz_atomic)
     SPS_CUDA_TRY(cudaMemsetAsync(dz, 0, sizeof(float) * (size_t)s.B * s.C * s.HW, st));
+  if (zmode != tcb::ZM_LDG) {
+    const bool bf = std::is_same<X, __nv_bfloat16>::value;
+    rc = make_tmap_2d_16bit(&prm.tm_hi, z, bf, s.N, s.C, tc::TILE_M, 64, 128);
+    if (rc != SPS_OK) return rc;
+    rc = make_tmap_2d_16bit(&prm.tm_lo, z_lo != nullptr ? z_lo : z, bf, s.N, s.C, tc::TILE_M, 64, 128);
+    if (rc != SPS_OK) return rc;
+  }
   // one launch: chunk images (n_chunks blocks) + max |dlogits| (the remaining blocks)
   // (the amax blocks also scan the dense ddist map when there is one: enough of them to stream it at HBM rate)
   const int amax_blocks = sm_count() * (ddist != nullptr ? 16 : 1);
@@ -750,7 +810,7 @@ static int launch_bwd_slab(const HeadShape& s, const float* z, const float* prot
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   prm.s = s;
-  prm.z = z;
+  prm.z = reinterpret_cast<const float*>(z);
   prm.protos = protos;
   prm.dlogits = dlogits;
   prm.dl_stride = dl_stride;
@@ -758,19 +818,27 @@ static int launch_bwd_slab(const HeadShape& s, const float* z, const float* prot
   prm.ddist = ddist;
   prm.img = img;
   prm.amax_bits = amax;
-  prm.dz = dz;
+  prm.dz = reinterpret_cast<float*>(dz);
   prm.part_dp = part_dp;
   prm.part_dw = part_dw;
   prm.part_cs = part_cs;
   constexpr int SMEM = tcb::Lay<NSPLIT>::SM_TOTAL;
   static_assert(SMEM <= 227 * 1024, "backward kernel shared memory");
+#define SPS_BWD_LAUNCH(DD, ZM)                                                                                                     \
+  do {                                                                                                                             \
+    SPS_CUDA_TRY(cudaFuncSetAttribute(tcb::head_bwd_tc_kernel<X, NSPLIT, DD, ZM>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM)); \
+    SPS_CUDA_TRY(launch_pdl(tcb::head_bwd_tc_kernel<X, NSPLIT, DD, ZM>, dim3(grid), dim3(tcb::NTHREADS), (size_t)SMEM, st, prm));      \
+  } while (0)
   if (ddist != nullptr) {
-    SPS_CUDA_TRY(cudaFuncSetAttribute(tcb::head_bwd_tc_kernel<X, NSPLIT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    SPS_CUDA_TRY(launch_pdl(tcb::head_bwd_tc_kernel<X, NSPLIT, true>, dim3(grid), dim3(tcb::NTHREADS), (size_t)SMEM, st, prm));
+    if (zmode == tcb::ZM_LDG) SPS_BWD_LAUNCH(true, tcb::ZM_LDG);
+    else if (zmode == tcb::ZM_TMA16) SPS_BWD_LAUNCH(true, tcb::ZM_TMA16);
+    else SPS_BWD_LAUNCH(true, tcb::ZM_TMAHL);
   } else {
-    SPS_CUDA_TRY(cudaFuncSetAttribute(tcb::head_bwd_tc_kernel<X, NSPLIT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-    SPS_CUDA_TRY(launch_pdl(tcb::head_bwd_tc_kernel<X, NSPLIT, false>, dim3(grid), dim3(tcb::NTHREADS), (size_t)SMEM, st, prm));
+    if (zmode == tcb::ZM_LDG) SPS_BWD_LAUNCH(false, tcb::ZM_LDG);
+    else if (zmode == tcb::ZM_TMA16) SPS_BWD_LAUNCH(false, tcb::ZM_TMA16);
+    else SPS_BWD_LAUNCH(false, tcb::ZM_TMAHL);
   }
+#undef SPS_BWD_LAUNCH
   count_launch();
   {
     const long long c1 = dprotos != nullptr ? (long long)s.P * s.D : 0, c2 = dlast_w != nullptr ? (long long)s.K * s.P : 0;
@@ -786,31 +854,36 @@ static int launch_bwd_slab(const HeadShape& s, const float* z, const float* prot
 }
 
 template <typename X, int NSPLIT>
-static int launch_bwd_tc_t(const HeadShape& s, const float* z, const float* protos, const float* last_w, const float* dlogits,
-                           const float* ddist, float* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st) {
+static int launch_bwd_tc_t(const HeadShape& s, int zmode, const void* z, const void* z_lo, const float* protos, const float* last_w,
+                           const float* dlogits, const float* ddist, void* dz, float* dprotos, float* dlast_w, void* ws,
+                           size_t ws_bytes, cudaStream_t st) {
   const int n_slabs = (s.K + tcb::KP_BWD - 1) / tcb::KP_BWD;
   for (int sl = 0; sl < n_slabs; ++sl) {
     const int k0 = sl * tcb::KP_BWD;
     HeadShape ss = s;
     ss.K = s.K - k0 < tcb::KP_BWD ? s.K - k0 : tcb::KP_BWD;
-    const int rc = launch_bwd_slab<X, NSPLIT>(ss, z, protos, last_w + (size_t)k0 * s.P, dlogits + k0, s.K, dlogits, (long long)s.N * s.K,
-                                              sl == 0 ? ddist : nullptr, dz, dprotos, dlast_w != nullptr ? dlast_w + (size_t)k0 * s.P : nullptr,
-                                              sl == 0, n_slabs > 1, ws, ws_bytes, st);
+    const int rc = launch_bwd_slab<X, NSPLIT>(ss, zmode, z, z_lo, protos, last_w + (size_t)k0 * s.P, dlogits + k0, s.K, dlogits,
+                                              (long long)s.N * s.K, sl == 0 ? ddist : nullptr, dz, dprotos,
+                                              dlast_w != nullptr ? dlast_w + (size_t)k0 * s.P : nullptr, sl == 0, n_slabs > 1, ws,
+                                              ws_bytes, st);
     if (rc != SPS_OK) return rc;
   }
   return SPS_OK;
 }
 
-int launch_head_bwd_tc(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w,
-                       const float* dlogits, const float* ddist, float* dz, float* dprotos, float* dlast_w, void* ws,
-                       size_t ws_bytes, cudaStream_t st) {
+// zmode: tcb::ZM_LDG (z = fp32 NCHW map), ZM_TMA16 (z = 16-bit channels-last map, dz likewise), ZM_TMAHL (z / z_lo = hi / lo
+// re-lay of an fp32 map, dz fp32 NCHW)
+int launch_head_bwd_tc(const HeadShape& s, int math, int zmode, const void* z, const void* z_lo, const float* protos,
+                       const float* last_w, const float* dlogits, const float* ddist, void* dz, float* dprotos, float* dlast_w,
+                       void* ws, size_t ws_bytes, cudaStream_t st) {
+  SPS_REQUIRE(zmode == tcb::ZM_LDG || s.D == 64, SPS_ERR_UNSUPPORTED, "TMA-fed backward: D=%d, only 64 channels per scale", s.D);
   // the split modes recompute the distances with the 3-term product (a' = da/dd is as sensitive to d as a is);
   // the gradient GEMMs themselves run single-term 16-bit operands with fp32 accumulation
   switch (math) {
-    case SPS_MATH_BF16: return launch_bwd_tc_t<__nv_bfloat16, 1>(s, z, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
-    case SPS_MATH_BF16X3: return launch_bwd_tc_t<__nv_bfloat16, 3>(s, z, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
-    case SPS_MATH_F16X3: return launch_bwd_tc_t<__half, 3>(s, z, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
-    default: return launch_bwd_tc_t<__half, 1>(s, z, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
+    case SPS_MATH_BF16: return launch_bwd_tc_t<__nv_bfloat16, 1>(s, zmode, z, z_lo, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
+    case SPS_MATH_BF16X3: return launch_bwd_tc_t<__nv_bfloat16, 3>(s, zmode, z, z_lo, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
+    case SPS_MATH_F16X3: return launch_bwd_tc_t<__half, 3>(s, zmode, z, z_lo, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
+    default: return launch_bwd_tc_t<__half, 1>(s, zmode, z, z_lo, protos, last_w, dlogits, ddist, dz, dprotos, dlast_w, ws, ws_bytes, st);
   }
 }
 

@@ -1,0 +1,660 @@
+// Tensor-core prototype head (sm_100a): fused forward FED BY TMA from 16-bit channels-last feature maps.
+//
+// Same arithmetic as head_tc.cu (distance GEMM with the squared norms riding in one extra K step, log-similarity
+// epilogue, logits GEMM accumulated in TMEM over every chunk of a tile; segmentation/model/model_multiscale.py:256-317,
+// 324-330, 243-244 of the reference), but the feature tile is not built by loader warps: the map is a 16-bit
+// [N positions][C channels] array (the user's fp16 / bf16 channels-last tensor, or the hi / lo re-lay of an fp32 NCHW map
+// written by z_pack_kernel), and a {64 channels x 128 positions} box with the 128-byte swizzle is exactly the K-major
+// SWIZZLE_128B operand tile of the distance GEMM: one cp.async.bulk.tensor per tile, no conversion work on the SM.
+// What is left of the loader's job is the row norm |z_s(n)|^2 (one warp, four rows per lane, read back from the landed
+// tile), written into the 16-wide norm K step as before.  The four loader warps of head_tc.cu are gone, so a third set
+// of epilogue warps fits in the register file: three warps per SM sub-partition take units round-robin (the epilogue -
+// two MUFU per element - is what bounds this kernel).
+//
+// Warp roles (NSETS = 3 fused, 2 dense): warps [0, 4*NSETS) epilogue (warp % 4 = TMEM lane quarter, warp / 4 = set; set s
+// takes units u = s mod NSETS), then one feature-tile producer + row-norm warp, one prototype-chunk producer, the
+// distance-GEMM issuer and the logits-GEMM issuer.  Every set owns ITS distance accumulator (TMEM) and activation tile
+// (shared memory): a barrier is then only ever waited on by one set, one phase after the other (a parity wait cannot
+// tell phase k from phase k + 2, so a set must never skip a phase of a barrier it shares).
+#include "tma.cuh"
+
+namespace sps {
+namespace tf {
+using namespace sps::tc;
+
+struct FwdTmaParams {
+  CUtensorMap tm_hi;   // [N][C] 16-bit: the map itself, or the hi part of an fp32 map
+  CUtensorMap tm_lo;   // lo part (ZLO only)
+  HeadShape s;
+  ChunkTable ct;
+  const unsigned char* img;
+  float* logits;
+  float* dist;
+  float* act;
+  int n_tiles;
+};
+
+constexpr int MAX_NST = 8;
+constexpr int A_TILE = TILE_M * 128;          // 16 KB: 128 positions x 64 channels, 16 bit
+constexpr int A_NORM = TILE_M * 32;           // 4 KB norm K step
+constexpr int P_BYTES = TILE_M * 128;
+constexpr int TMEM_S0 = 0;
+constexpr int NSTW = 2;
+constexpr int ACT_SCRATCH = 32 * 33 * 4;
+
+template <bool ZLO> __host__ __device__ constexpr int a_stage_bytes() { return (ZLO ? 2 : 1) * A_TILE + A_NORM; }
+template <bool ZLO> __host__ __device__ constexpr int a_stages() { return ZLO ? 2 : 3; }
+
+struct Plan {
+  int a_stride, na, p0, p_stride, b0, b_stride, nst, w0, w_stride, scr0, bar_off, total;
+  __host__ __device__ int a_off(int i) const { return i * a_stride; }
+  __host__ __device__ int p_off(int i) const { return p0 + i * p_stride; }
+  __host__ __device__ int b_off(int i) const { return b0 + i * b_stride; }
+  __host__ __device__ int w_off(int i) const { return w0 + i * w_stride; }
+};
+template <int NSPLIT, bool ZLO, int NSETS> __host__ __device__ inline Plan make_plan(int kp, int scratch_warps) {
+  Plan pl;
+  pl.a_stride = a_stage_bytes<ZLO>();
+  pl.na = a_stages<ZLO>();
+  pl.p0 = pl.na * pl.a_stride;
+  pl.p_stride = (NSPLIT == 3 ? 2 : 1) * P_BYTES;
+  pl.b0 = pl.p0 + NSETS * pl.p_stride;
+  pl.b_stride = ((NSPLIT == 3 ? 2 : 1) * CN * 128 + CN * 32 + 1023) / 1024 * 1024;
+  pl.w_stride = ((NSPLIT == 3 ? 2 : 1) * kp * 128 + 1023) / 1024 * 1024;
+  const int w_total = kp > 0 ? NSTW * pl.w_stride : 0;
+  const int scr_total = scratch_warps * ACT_SCRATCH;
+  int nst = (227 * 1024 - 512 - 1024 - pl.b0 - w_total - scr_total) / pl.b_stride;
+  pl.nst = nst > MAX_NST ? MAX_NST : nst;
+  pl.w0 = pl.b0 + (pl.nst > 0 ? pl.nst : 0) * pl.b_stride;
+  pl.scr0 = pl.w0 + w_total;
+  pl.bar_off = pl.scr0 + scr_total;
+  pl.total = pl.bar_off + 512 + 1024;
+  return pl;
+}
+
+enum { BAR_TFULL = 0, BAR_AFULL = 4, BAR_AEMPTY = 8, BAR_BFULL = 12, BAR_BEMPTY = 12 + MAX_NST, BAR_SFULL = 12 + 2 * MAX_NST,
+       BAR_SEMPTY = 16 + 2 * MAX_NST, BAR_PFULL = 20 + 2 * MAX_NST, BAR_PEMPTY = 24 + 2 * MAX_NST, BAR_LFULL = 28 + 2 * MAX_NST,
+       BAR_LEMPTY = 30 + 2 * MAX_NST, BAR_WFULL = 32 + 2 * MAX_NST, BAR_WEMPTY = 34 + 2 * MAX_NST, BAR_COUNT = 36 + 2 * MAX_NST };
+
+__host__ __device__ constexpr int n_threads(int nsets) { return (4 * nsets + 4) * 32; }
+
+template <typename X, int NSPLIT, bool ZLO, bool DENSE, int NSETS>
+__global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const __grid_constant__ FwdTmaParams prm) {
+  constexpr int NEPI = 4 * NSETS;
+  constexpr int TMEM_L0 = NSETS * CN;
+  constexpr int WARP_Z = NEPI, WARP_PROD = NEPI + 1, WARP_MMA = NEPI + 2, WARP_MMA2 = NEPI + 3;
+  constexpr int NA = a_stages<ZLO>();
+  extern __shared__ unsigned char smem_raw[];
+  const HeadShape& s = prm.s;
+  const ChunkTable& ct = prm.ct;
+  const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
+  unsigned char* gbase = smem_raw + (base - smem_u32(smem_raw));
+  const Plan pl = make_plan<NSPLIT, ZLO, NSETS>(ct.kp, prm.act != nullptr ? NEPI : 0);
+  const uint32_t bar0 = base + pl.bar_off;
+  auto bar = [&](int i) { return bar0 + 8u * (uint32_t)i; };
+  volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + pl.bar_off + 8 * BAR_COUNT);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int NC = ct.n_chunks, KP = ct.kp, NST = pl.nst;
+  const bool has_w = KP > 0;
+  uint32_t tmem_cols = 32;
+  while ((int)tmem_cols < TMEM_L0 + 2 * KP) tmem_cols <<= 1;
+
+  if (threadIdx.x == 0) {
+    for (int i = 0; i < NA; ++i) {
+      mbar_init(bar(BAR_TFULL + i), 1);    // arrive.expect_tx by the producer lane + the TMA bytes
+      mbar_init(bar(BAR_AFULL + i), 1);    // norm K step written
+      mbar_init(bar(BAR_AEMPTY + i), 1);   // tcgen05.commit
+    }
+    for (int i = 0; i < NSETS; ++i) {
+      mbar_init(bar(BAR_SFULL + i), 1);
+      mbar_init(bar(BAR_SEMPTY + i), 4);   // the four warps of the set that owns the buffer
+      mbar_init(bar(BAR_PFULL + i), 4);
+      mbar_init(bar(BAR_PEMPTY + i), 1);
+    }
+    for (int i = 0; i < 2; ++i) {
+      mbar_init(bar(BAR_LFULL + i), 1);
+      mbar_init(bar(BAR_LEMPTY + i), 4);
+      mbar_init(bar(BAR_WFULL + i), 1);
+      mbar_init(bar(BAR_WEMPTY + i), 1);
+    }
+    for (int i = 0; i < MAX_NST; ++i) {
+      mbar_init(bar(BAR_BFULL + i), 1);
+      mbar_init(bar(BAR_BEMPTY + i), 1);
+    }
+    mbar_fence_init();
+  }
+  if (warp == WARP_MMA) tmem_alloc(smem_u32((const void*)tmem_slot), tmem_cols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  const int my_tiles = prm.n_tiles > (int)blockIdx.x ? (prm.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+
+  if (warp == WARP_MMA) {
+    // ================================ distance-GEMM issuer ================================
+    constexpr uint32_t ID1 = idesc_f16(Fmt<X>::id, TILE_M, CN);
+    const int U = my_tiles * NC;
+    uint32_t acount = 0;
+    int c = 0;
+    for (int i = 0; i < U; ++i) {
+      const bool first_of_scale = c == 0 || ct.scale[c] != ct.scale[c - 1];
+      const bool last_of_scale = c == NC - 1 || ct.scale[c + 1] != ct.scale[c];
+      const uint32_t ab = acount % NA, aph = (acount / NA) & 1, st = i % NST, sb = i % NSETS;
+      if (first_of_scale) {
+        mbar_wait(bar(BAR_TFULL + ab), aph);
+        mbar_wait(bar(BAR_AFULL + ab), aph);
+      }
+      mbar_wait(bar(BAR_BFULL + st), (i / NST) & 1);
+      mbar_wait(bar(BAR_SEMPTY + sb), ((i / NSETS) & 1) ^ 1);
+      tc_fence_after();
+      {
+        const uint32_t a_hi = base + pl.a_off(ab), a_lo = a_hi + A_TILE;
+        const uint32_t a_n = a_hi + (ZLO ? 2 : 1) * A_TILE;
+        const uint32_t b_hi = base + pl.b_off(st) + OFF_BHI, b_lo = base + pl.b_off(st) + OFF_BLO;
+        const uint32_t b_n = base + pl.b_off(st) + (NSPLIT == 3 ? 2 : 1) * CN * 128;
+        const uint32_t d = tmem + TMEM_S0 + sb * CN;
+        mma_f16(d, desc_noswz(a_n, NORM_LBO, NORM_SBO), desc_noswz(b_n, NORM_LBO, NORM_SBO), ID1, 0);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_hi + 32 * k), desc_sw128(b_hi + 32 * k), ID1, 1);
+        if (NSPLIT == 3) {
+#pragma unroll
+          for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_hi + 32 * k), desc_sw128(b_lo + 32 * k), ID1, 1);
+          if (ZLO) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_lo + 32 * k), desc_sw128(b_hi + 32 * k), ID1, 1);
+          }
+        }
+        mma_commit(bar(BAR_SFULL + sb));
+        if (last_of_scale) mma_commit(bar(BAR_AEMPTY + ab));
+        mma_commit(bar(BAR_BEMPTY + st));
+      }
+      __syncwarp();
+      if (last_of_scale) ++acount;
+      if (++c == NC) c = 0;
+    }
+  } else if (warp == WARP_MMA2) {
+    // ================================ logits-GEMM issuer ================================
+    if (has_w) {
+      const uint32_t ID2 = idesc_f16(Fmt<X>::id, TILE_M, KP);
+      const int U = my_tiles * NC;
+      int c = 0, tl = 0;
+      for (int u = 0; u < U; ++u) {
+        const uint32_t pb = u % NSETS, sw = u % NSTW, lb = tl & 1;
+        if (c == 0) mbar_wait(bar(BAR_LEMPTY + lb), ((tl >> 1) & 1) ^ 1);
+        mbar_wait(bar(BAR_WFULL + sw), (u / NSTW) & 1);
+        mbar_wait(bar(BAR_PFULL + pb), (u / NSETS) & 1);
+        tc_fence_after();
+        {
+          const uint32_t pa = base + pl.p_off(pb), w2 = base + pl.w_off(sw);
+          const uint32_t d = tmem + TMEM_L0 + lb * KP;
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            mma_f16(d, desc_sw128(pa + 32 * k), desc_sw128(w2 + 32 * k), ID2, (c > 0 || k > 0) ? 1 : 0);
+          if (NSPLIT == 3) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pa + 32 * k), desc_sw128(w2 + KP * 128 + 32 * k), ID2, 1);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pa + P_BYTES + 32 * k), desc_sw128(w2 + 32 * k), ID2, 1);
+          }
+          mma_commit(bar(BAR_PEMPTY + pb));
+          mma_commit(bar(BAR_WEMPTY + sw));
+          if (c == NC - 1) mma_commit(bar(BAR_LFULL + lb));
+        }
+        __syncwarp();
+        if (++c == NC) { c = 0; ++tl; }
+      }
+    }
+  } else if (warp == WARP_PROD) {
+    // ================================ prototype-chunk producer ================================
+    pdl_wait();  // the packed prototype images come from the pre-pass launched just before this kernel
+    const int U = my_tiles * NC;
+    const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128, bytes_n = CN * 32, bytes_w = (NSPLIT == 3 ? 2 : 1) * KP * 128;
+    auto fetch_b = [&](int i) {
+      const int c = i % NC, st = i % NST;
+      mbar_wait(bar(BAR_BEMPTY + st), ((i / NST) & 1) ^ 1);
+      if (lane == 0) {
+        mbar_arrive_expect_tx(bar(BAR_BFULL + st), bytes_b + bytes_n);
+        const unsigned char* src = prm.img + (size_t)c * ct.img_bytes;
+        const uint32_t dst = base + pl.b_off(st);
+        bulk_g2s(dst + OFF_BHI, src + OFF_BHI, bytes_b, bar(BAR_BFULL + st));
+        bulk_g2s(dst + (NSPLIT == 3 ? 2 : 1) * CN * 128, src + OFF_BN, bytes_n, bar(BAR_BFULL + st));
+      }
+      __syncwarp();
+    };
+    auto fetch_w = [&](int i) {
+      const int c = i % NC, sw = i % NSTW;
+      mbar_wait(bar(BAR_WEMPTY + sw), ((i / NSTW) & 1) ^ 1);
+      if (lane == 0) {
+        mbar_arrive_expect_tx(bar(BAR_WFULL + sw), bytes_w);
+        bulk_g2s(base + pl.w_off(sw), prm.img + (size_t)c * ct.img_bytes + OFF_W2, bytes_w, bar(BAR_WFULL + sw));
+      }
+      __syncwarp();
+    };
+    if (U > 0) fetch_b(0);
+    for (int i = 0; i < U; ++i) {
+      if (i + 1 < U) fetch_b(i + 1);
+      if (has_w) fetch_w(i);
+    }
+  } else if (warp == WARP_Z) {
+    // ================================ feature-tile producer + row norms ================================
+    // Work list: (tile, scale) pairs in the order the distance-GEMM issuer consumes them.  The TMA of pair i + 1 goes
+    // out as soon as its stage is free (tried before the norms of pair i, waited for after them).
+    // (a 16-bit re-lay of an fp32 map was written by a kernel that completed before the prototype pre-pass started)
+    auto advance = [&](int& ti, int& c) {
+      const int sc = ct.scale[c];
+      do { ++c; } while (c < NC && ct.scale[c] == sc);
+      if (c == NC) { c = 0; ++ti; }
+    };
+    constexpr uint32_t TX = (ZLO ? 2 : 1) * A_TILE;
+    int iti = 0, ic = 0;        // next pair to issue
+    uint32_t issued = 0;
+    auto issue = [&](bool blocking) -> bool {
+      if (iti >= my_tiles) return true;
+      const uint32_t ab = issued % NA, aph = (issued / NA) & 1;
+      if (blocking) {
+        mbar_wait(bar(BAR_AEMPTY + ab), aph ^ 1);
+      } else {   // warp-uniform outcome: the lanes of a warp may see the phase flip at different polls
+        const bool ok = mbar_try_wait(bar(BAR_AEMPTY + ab), aph ^ 1);
+        if (!__all_sync(0xffffffffu, ok)) return false;
+      }
+      if (lane == 0) {
+        const int row0 = (int)(((long long)blockIdx.x + (long long)iti * gridDim.x) * TILE_M);
+        const int c0 = ct.scale[ic] * s.D;
+        mbar_arrive_expect_tx(bar(BAR_TFULL + ab), TX);
+        tma_load_2d(base + pl.a_off(ab), &prm.tm_hi, c0, row0, bar(BAR_TFULL + ab));
+        if (ZLO) tma_load_2d(base + pl.a_off(ab) + A_TILE, &prm.tm_lo, c0, row0, bar(BAR_TFULL + ab));
+      }
+      __syncwarp();
+      ++issued;
+      advance(iti, ic);
+      return true;
+    };
+    int ti = 0, c = 0;
+    uint32_t acount = 0;
+    issue(true);
+    while (ti < my_tiles) {
+      const uint32_t ab = acount % NA, aph = (acount / NA) & 1;
+      while (issued < acount + NA && iti < my_tiles && issue(false)) {   // keep up to NA pairs in flight
+      }
+      mbar_wait(bar(BAR_TFULL + ab), aph);
+      unsigned char* a_hi = gbase + pl.a_off(ab);
+      unsigned char* a_lo = a_hi + A_TILE;
+      unsigned char* a_n = a_hi + (ZLO ? 2 : 1) * A_TILE;
+#pragma unroll
+      for (int rr = 0; rr < 4; ++rr) {
+        const int r = lane + 32 * rr;
+        ZStage<X, NSPLIT>::store_norm(r, a_n, tile_row_norm<X, ZLO>(a_hi, a_lo, r));
+      }
+      fence_proxy_async();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(BAR_AFULL + ab));
+      ++acount;
+      advance(ti, c);
+      if (issued <= acount && iti < my_tiles) issue(true);   // the pair waited for next must be on its way
+    }
+  } else {
+    // ================================ epilogue ================================
+    const int q = warp & 3, set = warp >> 2;
+    const int m = q * 32 + lane;
+    const uint32_t lane_base = ((uint32_t)(q * 32)) << 16;
+    const float eps = s.eps, ome = 1.0f - s.eps;
+    const bool is_log = s.act_kind == SPS_ACT_LOG;
+    auto store_logits = [&](int tj) {
+      const long long nn = ((long long)blockIdx.x + (long long)tj * gridDim.x) * TILE_M + m;
+      const uint32_t lb = tj & 1;
+      mbar_wait(bar(BAR_LFULL + lb), (tj >> 1) & 1);
+      tc_fence_after();
+      for (int k0 = 0; k0 < KP; k0 += 16) {
+        uint32_t lr[16];
+        tmem_ld16(tmem + lane_base + TMEM_L0 + lb * KP + k0, lr);
+        tmem_ld_wait();
+        if (nn < s.N) {
+#pragma unroll
+          for (int k = 0; k < 16; ++k)
+            if (k0 + k < s.K) prm.logits[nn * s.K + k0 + k] = __uint_as_float(lr[k]);
+        }
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(BAR_LEMPTY + lb));
+    };
+    const int defer_c = NC > 1 ? 1 : 0;
+    int next_store = 0;   // set 0: next tile whose logits go to HBM
+    const int U = my_tiles * NC;
+    int ti = 0, c = set;
+    long long n = (long long)blockIdx.x * TILE_M + m;
+    while (c >= NC && NC > 0) { c -= NC; ++ti; n += (long long)gridDim.x * TILE_M; }
+    for (int u = set; u < U; u += NSETS) {
+      const bool valid = n < s.N;
+      const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
+      float* drow = DENSE && prm.dist != nullptr ? prm.dist + b * (long long)s.P * s.HW + pix : nullptr;
+      const uint32_t sb = set, pb = set, ph = (u / NSETS) & 1;
+      mbar_wait(bar(BAR_SFULL + sb), ph);
+      tc_fence_after();
+      unsigned char* prow = gbase + pl.p_off(pb) + (uint32_t)m * 128u;
+#pragma unroll 1
+      for (int hf = 0; hf < 2; ++hf) {
+        uint32_t r[32];
+        tmem_ld32(tmem + lane_base + TMEM_S0 + sb * CN + hf * 32, r);
+        tmem_ld_wait();
+        if (hf == 1) {
+          tc_fence_before();
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar(BAR_SEMPTY + sb));
+        }
+        const int col0 = hf * 32, ncols = ct.n[c] - col0;
+        const int p0 = ct.p0[c] + col0;
+        float av[32];
+        if (is_log) {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float d = fmaxf(__uint_as_float(r[j]), 0.0f);
+            av[j] = lg2_approx(fmaf(ome, rcp_approx(d + eps), 1.0f));
+            if (DENSE) r[j] = __float_as_uint(d);
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j) {
+            const float d = fmaxf(__uint_as_float(r[j]), 0.0f);
+            av[j] = -d;
+            if (DENSE) r[j] = __float_as_uint(d);
+          }
+        }
+        if (DENSE) {
+          if (drow != nullptr && valid) {
+            float* dp = drow + (long long)p0 * s.HW;
+            const size_t pitch = (size_t)s.HW;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (j < ncols) *dp = __uint_as_float(r[j]);
+              dp += pitch;
+            }
+          }
+          if (prm.act != nullptr) {
+            const float sc = is_log ? 0.69314718055994531f : 1.0f;
+            float* scr = reinterpret_cast<float*>(gbase + pl.scr0 + warp * ACT_SCRATCH);
+            __syncwarp();
+#pragma unroll
+            for (int j = 0; j < 32; ++j) scr[lane * 33 + j] = av[j] * sc;
+            __syncwarp();
+            const long long n_first = n - lane;
+            float* abase = prm.act + n_first * (long long)s.P + p0 + lane;
+            const int rows = s.N - n_first < 32 ? (int)(s.N - n_first) : 32;
+            if (lane < ncols) {
+#pragma unroll 8
+              for (int rr = 0; rr < 32; ++rr)
+                if (rr < rows) abase[(long long)rr * s.P] = scr[rr * 33 + lane];
+            }
+          }
+        }
+        if (has_w) {
+          if (hf == 0) mbar_wait(bar(BAR_PEMPTY + pb), ph ^ 1);
+#pragma unroll
+          for (int g = 0; g < 4; ++g) {
+            uint32_t w[4], wl[4];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              const float x0 = av[g * 8 + 2 * e], x1 = av[g * 8 + 2 * e + 1];
+              w[e] = Pack2<X>::pack(x0, x1);
+              if (NSPLIT == 3) {
+                const float2 h = Pack2<X>::unpack(w[e]);
+                wl[e] = Pack2<X>::pack(x0 - h.x, x1 - h.y);
+              }
+            }
+            const uint32_t poff = (((uint32_t)(hf * 4 + g)) ^ ((uint32_t)m & 7u)) << 4;
+            *reinterpret_cast<uint4*>(prow + poff) = make_uint4(w[0], w[1], w[2], w[3]);
+            if (NSPLIT == 3) *reinterpret_cast<uint4*>(prow + P_BYTES + poff) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
+          }
+        }
+      }
+      if (has_w) {
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(BAR_PFULL + pb));
+      }
+      if (has_w && set == 0) {
+        while (next_store < ti - 1) store_logits(next_store++);
+        if (next_store == ti - 1 && c >= defer_c) store_logits(next_store++);
+      }
+      c += NSETS;
+      while (c >= NC) { c -= NC; ++ti; n += (long long)gridDim.x * TILE_M; }
+    }
+    if (has_w && set == 0)
+      while (next_store < my_tiles) store_logits(next_store++);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == WARP_MMA) {
+    tc_fence_after();
+    tmem_dealloc(tmem, tmem_cols);
+  }
+}
+
+// ---------------------------------------------------------------------------------------------
+// fp32 NCHW -> 16-bit channels-last re-lay (hi [+ lo]) for the TMA-fed kernels (SPS_FLAG_ZPACK).
+// One block = 32 consecutive positions x all C channels: reads are 128-byte warp loads along the position axis, the
+// packed (channel pair) words go through a shared-memory tile with an odd pitch, writes are 128-byte warp stores
+// along the channel axis.
+// ---------------------------------------------------------------------------------------------
+template <typename X, bool ZLO>
+__global__ void __launch_bounds__(256) z_pack_kernel(const float* __restrict__ z, int C, int HW, long long N,
+                                                     uint32_t* __restrict__ out_hi, uint32_t* __restrict__ out_lo) {
+  extern __shared__ uint32_t pk_smem[];
+  const int C2 = C >> 1, pitch = C2 + 1;
+  uint32_t* t_hi = pk_smem;
+  uint32_t* t_lo = pk_smem + 32 * pitch;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long n0 = (long long)blockIdx.x * 32, n = n0 + lane;
+  const bool live = n < N;
+  const long long nn = live ? n : N - 1;
+  const long long b = nn / HW, pix = nn % HW;
+  const float* src = z + (b * C) * (long long)HW + pix;
+  for (int c2 = warp; c2 < C2; c2 += 8 * 4) {
+    float v0[4], v1[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int cc = c2 + 8 * u;
+      v0[u] = cc < C2 ? __ldg(src + (long long)(2 * cc) * HW) : 0.f;
+      v1[u] = cc < C2 ? __ldg(src + (long long)(2 * cc + 1) * HW) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int cc = c2 + 8 * u;
+      if (cc < C2) {
+        const uint32_t h = Pack2<X>::pack(v0[u], v1[u]);
+        t_hi[lane * pitch + cc] = h;
+        if (ZLO) {
+          const float2 e = Pack2<X>::unpack(h);
+          t_lo[lane * pitch + cc] = Pack2<X>::pack(v0[u] - e.x, v1[u] - e.y);
+        }
+      }
+    }
+  }
+  __syncthreads();
+  const int rows = N - n0 < 32 ? (int)(N - n0) : 32;
+  for (int r = warp; r < rows; r += 8) {
+    for (int w = lane; w < C2; w += 32) {
+      out_hi[(n0 + r) * C2 + w] = t_hi[r * pitch + w];
+      if (ZLO) out_lo[(n0 + r) * C2 + w] = t_lo[r * pitch + w];
+    }
+  }
+}
+
+}  // namespace tf
+
+// ---------------------------------------------------------------------------------------------
+// Host side
+// ---------------------------------------------------------------------------------------------
+int build_chunk_table(const HeadShape& s, bool with_last_layer, tc::ChunkTable* ct);
+int launch_proto_prep(const HeadShape& s, int math, const tc::ChunkTable& ct, const float* protos, const float* last_w,
+                      unsigned char* img, cudaStream_t st);
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int make_tmap_2d_16bit(CUtensorMap* out, const void* base, bool bf16, long long rows, long long cols, int box_rows, int box_cols,
+                       int swizzle_bytes) {
+  static EncodeTiledFn fn = nullptr;
+  if (fn == nullptr) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    SPS_CUDA_TRY(cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres));
+    SPS_REQUIRE(p != nullptr && qres == cudaDriverEntryPointSuccess, SPS_ERR_CUDA, "cuTensorMapEncodeTiled not available in this driver");
+    fn = reinterpret_cast<EncodeTiledFn>(p);
+  }
+  SPS_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, SPS_ERR_BAD_ARG, "16-bit channels-last map: base address must be 16-byte aligned");
+  SPS_REQUIRE((cols * 2) % 16 == 0, SPS_ERR_UNSUPPORTED, "16-bit channels-last map: %lld channels give a row pitch that is not a multiple of 16 bytes", cols);
+  const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)(rows > 0 ? rows : 1)};
+  const cuuint64_t gstride[1] = {(cuuint64_t)cols * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUtensorMapSwizzle sw = swizzle_bytes == 128 ? CU_TENSOR_MAP_SWIZZLE_128B
+                                : swizzle_bytes == 64 ? CU_TENSOR_MAP_SWIZZLE_64B
+                                                      : CU_TENSOR_MAP_SWIZZLE_NONE;
+  const CUresult r = fn(out, bf16 ? CU_TENSOR_MAP_DATA_TYPE_BFLOAT16 : CU_TENSOR_MAP_DATA_TYPE_FLOAT16, 2, const_cast<void*>(base), gdim,
+                        gstride, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, sw, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  SPS_REQUIRE(r == CUDA_SUCCESS, SPS_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for a [%lld x %lld] 16-bit map", (int)r, rows, cols);
+  return SPS_OK;
+}
+
+static bool math_is_split(int math) { return math == SPS_MATH_F16X3 || math == SPS_MATH_BF16X3; }
+
+// bytes of the 16-bit re-lay of an fp32 map (hi [+ lo]), each part 1 KB aligned
+size_t z_pack_bytes(const HeadShape& s, int math) {
+  const size_t part = ((size_t)s.N * s.C * 2 + 1023) / 1024 * 1024;
+  return (math_is_split(math) ? 2 : 1) * part + 1024;
+}
+
+void z_pack_parts(const HeadShape& s, int math, const void* area, const void** hi, const void** lo) {
+  const unsigned char* base = reinterpret_cast<const unsigned char*>(((uintptr_t)area + 1023) & ~(uintptr_t)1023);
+  const size_t part = ((size_t)s.N * s.C * 2 + 1023) / 1024 * 1024;
+  *hi = base;
+  *lo = math_is_split(math) ? base + part : nullptr;
+}
+
+int launch_z_pack(const HeadShape& s, int math, const float* z, void* out, cudaStream_t st) {
+  SPS_REQUIRE(s.C % 2 == 0 && s.C <= 1024, SPS_ERR_UNSUPPORTED, "z re-lay: C=%d must be even and <= 1024", s.C);
+  if (s.N == 0) return SPS_OK;
+  unsigned char* base = reinterpret_cast<unsigned char*>(((uintptr_t)out + 1023) & ~(uintptr_t)1023);
+  const size_t part = ((size_t)s.N * s.C * 2 + 1023) / 1024 * 1024;
+  uint32_t* hi = reinterpret_cast<uint32_t*>(base);
+  uint32_t* lo = reinterpret_cast<uint32_t*>(base + part);
+  const unsigned grid = (unsigned)((s.N + 31) / 32);
+  const size_t smem = (size_t)32 * (s.C / 2 + 1) * 4 * (math_is_split(math) ? 2 : 1);
+  switch (math) {
+    case SPS_MATH_F16:
+      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::z_pack_kernel<__half, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      tf::z_pack_kernel<__half, false><<<grid, 256, smem, st>>>(z, s.C, s.HW, s.N, hi, lo);
+      break;
+    case SPS_MATH_F16X3:
+      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::z_pack_kernel<__half, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      tf::z_pack_kernel<__half, true><<<grid, 256, smem, st>>>(z, s.C, s.HW, s.N, hi, lo);
+      break;
+    case SPS_MATH_BF16:
+      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::z_pack_kernel<__nv_bfloat16, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      tf::z_pack_kernel<__nv_bfloat16, false><<<grid, 256, smem, st>>>(z, s.C, s.HW, s.N, hi, lo);
+      break;
+    case SPS_MATH_BF16X3:
+      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::z_pack_kernel<__nv_bfloat16, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+      tf::z_pack_kernel<__nv_bfloat16, true><<<grid, 256, smem, st>>>(z, s.C, s.HW, s.N, hi, lo);
+      break;
+    default: SPS_REQUIRE(false, SPS_ERR_BAD_ARG, "z re-lay: math=%d is not a tensor-core mode", math);
+  }
+  count_launch();
+  SPS_CUDA_TRY(cudaGetLastError());
+  return SPS_OK;
+}
+
+// three epilogue sets when the outputs are only the logits and the third distance accumulator / activation tile fit
+template <int NSPLIT, bool ZLO> static bool three_sets_fit(int kp, bool dense) {
+  if (dense || 3 * tc::CN + 2 * kp > 512) return false;
+  const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 3>(kp, 0);
+  return pl.nst >= 2 && pl.total <= 227 * 1024;
+}
+
+template <typename X, int NSPLIT, bool ZLO>
+static int launch_fwd_tma_t(const HeadShape& s, const tc::ChunkTable& ct, const void* z_hi, const void* z_lo, const float* protos,
+                            const float* last_w, float* logits, float* dist, float* act, unsigned char* img, int math,
+                            cudaStream_t st) {
+  int rc = launch_proto_prep(s, math, ct, protos, last_w, img, st);
+  if (rc != SPS_OK) return rc;
+  tf::FwdTmaParams prm;
+  const bool bf = std::is_same<X, __nv_bfloat16>::value;
+  rc = make_tmap_2d_16bit(&prm.tm_hi, z_hi, bf, s.N, s.C, tc::TILE_M, 64, 128);
+  if (rc != SPS_OK) return rc;
+  rc = make_tmap_2d_16bit(&prm.tm_lo, ZLO ? z_lo : z_hi, bf, s.N, s.C, tc::TILE_M, 64, 128);
+  if (rc != SPS_OK) return rc;
+  prm.s = s;
+  prm.ct = ct;
+  prm.img = img;
+  prm.logits = logits;
+  prm.dist = dist;
+  prm.act = act;
+  prm.n_tiles = (int)((s.N + tc::TILE_M - 1) / tc::TILE_M);
+  const bool dense = dist != nullptr || act != nullptr;
+  const int grid = prm.n_tiles < sm_count() ? prm.n_tiles : sm_count();
+  if (three_sets_fit<NSPLIT, ZLO>(ct.kp, dense)) {
+    const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 3>(ct.kp, 0);
+    SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+    SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 3>, dim3(grid), dim3(tf::n_threads(3)), (size_t)pl.total, st, prm));
+  } else {
+    const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 2>(ct.kp, act != nullptr ? 8 : 0);
+    SPS_REQUIRE(pl.nst >= 2 && pl.total <= 227 * 1024, SPS_ERR_UNSUPPORTED,
+                "TMA-fed head: %d bytes of shared memory needed (K=%d)", pl.total, s.K);
+    if (dense) {
+      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+      SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, true, 2>, dim3(grid), dim3(tf::n_threads(2)), (size_t)pl.total, st, prm));
+    } else {
+      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+      SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 2>, dim3(grid), dim3(tf::n_threads(2)), (size_t)pl.total, st, prm));
+    }
+  }
+  count_launch();
+  return SPS_OK;
+}
+
+// Shapes the TMA-fed forward covers.  zlo: the map has a lo part (fp32 source re-laid by z_pack_kernel in a split mode).
+bool head_fwd_tma_supported(const HeadShape& s, int math, bool with_last_layer, bool dense_act, bool zlo) {
+  if (math == SPS_MATH_FP32 || s.D != 64 || s.K > 192 || s.N >= (1ll << 31)) return false;
+  int nc = 0;
+  for (int sc = 0; sc < s.S; ++sc) nc += (s.scale_lo[sc + 1] - s.scale_lo[sc] + tc::CN - 1) / tc::CN;
+  if (nc > tc::MAX_CHUNKS) return false;
+  const int kp = with_last_layer ? (s.K + 15) / 16 * 16 : 0;
+  const int scr = dense_act ? 8 : 0;
+  const bool split = math_is_split(math);
+  const tf::Plan pl = split ? (zlo ? tf::make_plan<3, true, 2>(kp, scr) : tf::make_plan<3, false, 2>(kp, scr)) : tf::make_plan<1, false, 2>(kp, scr);
+  return pl.nst >= 2 && pl.total <= 227 * 1024;
+}
+
+// z_hi / z_lo: 16-bit [N][C] arrays (z_lo may be null: the map is exactly 16 bit).  img: 1 KB aligned workspace for the
+// packed prototype images (head_fwd_tc_workspace bytes).
+int launch_head_fwd_tma(const HeadShape& s, int math, const void* z_hi, const void* z_lo, const float* protos, const float* last_w,
+                        float* logits, float* dist, float* act, void* ws, size_t ws_bytes, cudaStream_t st) {
+  SPS_REQUIRE(s.D == 64, SPS_ERR_UNSUPPORTED, "TMA-fed head: D=%d, only 64 channels per scale are supported", s.D);
+  if (s.N == 0 || s.P == 0) return SPS_OK;
+  tc::ChunkTable ct;
+  int rc = build_chunk_table(s, last_w != nullptr, &ct);
+  if (rc != SPS_OK) return rc;
+  const size_t need = (size_t)ct.n_chunks * ct.img_bytes + 1024;
+  SPS_REQUIRE(ws != nullptr && ws_bytes >= need, SPS_ERR_WORKSPACE, "head_fwd workspace: need %zu bytes, got %zu", need, ws_bytes);
+  unsigned char* img = reinterpret_cast<unsigned char*>(((uintptr_t)ws + 1023) & ~(uintptr_t)1023);
+  const bool zlo = z_lo != nullptr;
+  switch (math) {
+    case SPS_MATH_F16: return launch_fwd_tma_t<__half, 1, false>(s, ct, z_hi, z_lo, protos, last_w, logits, dist, act, img, math, st);
+    case SPS_MATH_BF16: return launch_fwd_tma_t<__nv_bfloat16, 1, false>(s, ct, z_hi, z_lo, protos, last_w, logits, dist, act, img, math, st);
+    case SPS_MATH_F16X3:
+      return zlo ? launch_fwd_tma_t<__half, 3, true>(s, ct, z_hi, z_lo, protos, last_w, logits, dist, act, img, math, st)
+                 : launch_fwd_tma_t<__half, 3, false>(s, ct, z_hi, z_lo, protos, last_w, logits, dist, act, img, math, st);
+    case SPS_MATH_BF16X3:
+      return zlo ? launch_fwd_tma_t<__nv_bfloat16, 3, true>(s, ct, z_hi, z_lo, protos, last_w, logits, dist, act, img, math, st)
+                 : launch_fwd_tma_t<__nv_bfloat16, 3, false>(s, ct, z_hi, z_lo, protos, last_w, logits, dist, act, img, math, st);
+  }
+  SPS_REQUIRE(false, SPS_ERR_BAD_ARG, "math=%d is not a tensor-core mode", math);
+}
+
+}  // namespace sps

@@ -9,6 +9,8 @@
 // rounds to 1e10f for every d < 512 (D <= 64 and z, p in [0,1] give d <= 64), so unmatched positions
 // never beat the initial key (bits(1e10f) << 32) | 0 — also the reference's answer (value 1e10,
 // index 0) for a class that is absent from the map.
+#include <cuda_fp16.h>
+
 #include "simt_tile.cuh"
 
 namespace sps {
@@ -193,7 +195,9 @@ int launch_push_topk(const unsigned long long* keys, int n_maps, int P, uint32_t
   return SPS_OK;
 }
 
-__global__ void push_gather_kernel(HeadShape s, const float* __restrict__ z, const unsigned long long* __restrict__ keys,
+// ZT: 0 = fp32 NCHW maps, 1 = fp16 channels-last, 2 = bf16 channels-last (out is always fp32)
+template <int ZT>
+__global__ void push_gather_kernel(HeadShape s, const void* __restrict__ zv, const unsigned long long* __restrict__ keys,
                                    const unsigned long long* __restrict__ best, int n_maps, uint32_t map_base,
                                    const int32_t* __restrict__ proto_scale, float* __restrict__ out) {
   const int p = blockIdx.x;
@@ -203,15 +207,25 @@ __global__ void push_gather_kernel(HeadShape s, const float* __restrict__ z, con
   const long long m = (long long)(gmap - map_base);
   const long long pix = (long long)(keys[m * s.P + p] & 0xFFFFFFFFULL);
   const int sc = proto_scale[p];
-  for (int c = threadIdx.x; c < s.D; c += blockDim.x)
-    out[(long long)p * s.D + c] = z[(m * s.C + sc * s.D + c) * s.HW + pix];
+  for (int c = threadIdx.x; c < s.D; c += blockDim.x) {
+    float v;
+    if (ZT == 0) {
+      v = reinterpret_cast<const float*>(zv)[(m * s.C + sc * s.D + c) * s.HW + pix];
+    } else {
+      const unsigned short h = reinterpret_cast<const unsigned short*>(zv)[(m * s.HW + pix) * s.C + sc * s.D + c];
+      v = ZT == 1 ? __half2float(__ushort_as_half(h)) : __uint_as_float((unsigned)h << 16);
+    }
+    out[(long long)p * s.D + c] = v;
+  }
 }
 
-int launch_push_gather(const HeadShape& s, const float* z, const unsigned long long* keys,
+int launch_push_gather(const HeadShape& s, const void* z, const unsigned long long* keys,
                        const unsigned long long* best, int n_maps, uint32_t map_base, const int32_t* proto_scale,
                        float* out, cudaStream_t st) {
   if (s.P == 0 || n_maps == 0) return SPS_OK;
-  push_gather_kernel<<<s.P, 64, 0, st>>>(s, z, keys, best, n_maps, map_base, proto_scale, out);
+  if (s.z_dtype == SPS_Z_F16) push_gather_kernel<1><<<s.P, 64, 0, st>>>(s, z, keys, best, n_maps, map_base, proto_scale, out);
+  else if (s.z_dtype == SPS_Z_BF16) push_gather_kernel<2><<<s.P, 64, 0, st>>>(s, z, keys, best, n_maps, map_base, proto_scale, out);
+  else push_gather_kernel<0><<<s.P, 64, 0, st>>>(s, z, keys, best, n_maps, map_base, proto_scale, out);
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;

@@ -12,7 +12,7 @@
 // prototypes of its scale (once in total for the shipped configs).  The scan is HBM-bound: the feature loaders
 // (8 warps, two tiles in flight) are the critical resource; MMA and the compare/select epilogue hide under them.
 // Results are merged into keys[map][p] with one 64-bit atomicMin per (CTA, map, prototype).
-#include "tc_common.cuh"
+#include "tma.cuh"
 
 namespace sps {
 namespace tcp {
@@ -33,6 +33,7 @@ struct PGroupTable {
 };
 
 struct PushParams {
+  CUtensorMap tm_z;                // ZM_TMA16: the 16-bit channels-last maps as one [B*HW][C] array
   HeadShape s;
   ChunkTable ct;
   PGroupTable gt;
@@ -45,11 +46,12 @@ struct PushParams {
   long long n_tiles;               // B * tiles_per_map
 };
 
-template <int NSPLIT> struct PLay {
+// ZLO: the streamed feature tile has a lo part (fp32 source in a split mode; a 16-bit map is exact in one term)
+template <int NSPLIT, bool ZLO> struct PLay {
   static constexpr int RES_T = (NSPLIT == 3 ? 2 : 1) * TILE_M * 128 + TILE_M * 32;        // one 128-row prototype tile
   static constexpr int ROFF_LO = TILE_M * 128, ROFF_N = (NSPLIT == 3 ? 2 : 1) * TILE_M * 128;
-  static constexpr int STAGE = (NSPLIT == 3 ? 2 : 1) * TILE_M * 128 + TILE_M * 32;        // z hi [lo] | norm
-  static constexpr int SOFF_LO = TILE_M * 128, SOFF_N = (NSPLIT == 3 ? 2 : 1) * TILE_M * 128;
+  static constexpr int STAGE = (ZLO ? 2 : 1) * TILE_M * 128 + TILE_M * 32;                // z hi [lo] | norm
+  static constexpr int SOFF_LO = TILE_M * 128, SOFF_N = (ZLO ? 2 : 1) * TILE_M * 128;
   static constexpr int SM_RES = 0;
   static constexpr int SM_Z = 2 * RES_T;
   static constexpr int NSTAGE = (227 * 1024 - 2048 - 4096 - SM_Z) / STAGE >= 6 ? 6 : (227 * 1024 - 2048 - 4096 - SM_Z) / STAGE;
@@ -60,15 +62,16 @@ template <int NSPLIT> struct PLay {
   static constexpr int SM_BAR = SM_LAB + LAB_RING * TILE_M * 4;
   static constexpr int SM_TOTAL = SM_BAR + 256 + 1024;
 };
-enum { PB_ZFULL = 0, PB_ZEMPTY = 8, PB_DFULL = 16, PB_DEMPTY = 18, PB_RES = 20, PB_RES2 = 21, PB_COUNT = 22 };
+enum { PB_ZFULL = 0, PB_ZEMPTY = 8, PB_DFULL = 16, PB_DEMPTY = 18, PB_RES = 20, PB_RES2 = 21, PB_TFULL = 22, PB_COUNT = 30 };
 
 __device__ __forceinline__ unsigned long long absent_key64() { return ((unsigned long long)0x501502F9u) << 32; }  // 1e10f
 
 // MASKED: the class mask rides in the norm K step of the GEMM (labels <= MASK_MAX_LABEL, see ZStage::store_norm_mask)
 // and the epilogue is a plain running minimum; otherwise the epilogue compares labels element by element.
-template <typename X, int NSPLIT, bool MASKED>
+template <typename X, int NSPLIT, bool MASKED, int ZMODE>
 __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_constant__ PushParams prm) {
-  using L = PLay<NSPLIT>;
+  constexpr bool ZLO = NSPLIT == 3 && ZMODE == ZM_LDG;
+  using L = PLay<NSPLIT, ZLO>;
   extern __shared__ unsigned char smem_raw[];
   const HeadShape& s = prm.s;
   const ChunkTable& ct = prm.ct;
@@ -93,6 +96,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
     for (int i = 0; i < L::NSTAGE; ++i) {
       mbar_init(bar(PB_ZFULL + i), 4);     // the 4 warps of one loader group
       mbar_init(bar(PB_ZEMPTY + i), 1);    // tcgen05.commit
+      mbar_init(bar(PB_TFULL + i), 1);     // TMA mode: arrive.expect_tx + the tile bytes
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(PB_DFULL + i), 1);
@@ -153,8 +157,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
 #pragma unroll
           for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pt + 32 * k), desc_sw128(zt + 32 * k), ID, 1);
           if (NSPLIT == 3) {
+            if (ZLO) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pt + 32 * k), desc_sw128(zt + L::SOFF_LO + 32 * k), ID, 1);
+              for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pt + 32 * k), desc_sw128(zt + L::SOFF_LO + 32 * k), ID, 1);
+            }
 #pragma unroll
             for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pt + L::ROFF_LO + 32 * k), desc_sw128(zt + 32 * k), ID, 1);
           }
@@ -177,6 +183,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       const int px = pix < s.HW ? pix : s.HW - 1;  // rows past the end of the map read a valid row; their label is void
       return prm.z + (b * s.C + (long long)sc * s.D) * s.HW + px;
     };
+    if (ZMODE == ZM_LDG) {
     ZStage<X, NSPLIT> zst;
     long long b = 0, nb = 0;
     int pix = 0, npix = 0;
@@ -213,6 +220,45 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       cur = nxt;
       b = nb;
       pix = npix;
+    }
+    } else {
+      // 16-bit channels-last maps: each tile is ONE TMA box {64 channels of this scale, 128 positions} landing in the
+      // MMA's own layout; every loader group keeps three tiles in flight.  The thread's job per row: label, squared norm
+      // (read back from the landed tile) and the norm / class-mask K step.
+      int next_issue = grp;
+      auto issue_upto = [&](int upto) {
+        if (m != 0) return;
+        while (next_issue <= upto && next_issue < my_tiles) {
+          const int st = next_issue % L::NSTAGE;
+          mbar_wait(bar(PB_ZEMPTY + st), ((next_issue / L::NSTAGE) & 1) ^ 1);
+          const long long t = t_lo + next_issue;
+          const long long row0 = (t / prm.tiles_per_map) * s.HW + (t % prm.tiles_per_map) * TILE_M;
+          mbar_arrive_expect_tx(bar(PB_TFULL + st), TILE_M * 128u);
+          tma_load_2d(base + L::SM_Z + st * L::STAGE, &prm.tm_z, sc * s.D, (int)row0, bar(PB_TFULL + st));
+          next_issue += 2;
+        }
+      };
+      issue_upto(grp + 2);
+      for (int i = grp; i < my_tiles; i += 2) {
+        issue_upto(i + 4);
+        const long long t = t_lo + i;
+        const long long b = t / prm.tiles_per_map;
+        const int pix = (int)(t % prm.tiles_per_map) * TILE_M + m;
+        const int lab = pix < s.HW ? (int)__ldg(prm.labels + b * s.HW + pix) : 0;
+        const int st = i % L::NSTAGE;
+        mbar_wait(bar(PB_TFULL + st), (i / L::NSTAGE) & 1);
+        unsigned char* a0 = gbase + L::SM_Z + st * L::STAGE;
+        const float zn = tile_row_norm<X, false>(a0, a0, m);
+        if (MASKED) {
+          ZStage<X, NSPLIT>::store_norm_mask(m, a0 + L::SOFF_N, zn, lab);
+        } else {
+          ZStage<X, NSPLIT>::store_norm(m, a0 + L::SOFF_N, zn);
+          reinterpret_cast<int*>(gbase + L::SM_LAB)[(i % L::LAB_RING) * TILE_M + m] = lab;
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(PB_ZFULL + st));
+      }
     }
   }
   else if (warp < WARP_LOAD0) {
@@ -338,8 +384,8 @@ static int build_pgroups(const tc::ChunkTable& ct, long long n_tiles, int n_sm, 
   return next;
 }
 
-template <typename X, int NSPLIT, bool MASKED>
-static int launch_push_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const float* z, const int16_t* labels,
+template <typename X, int NSPLIT, bool MASKED, int ZMODE>
+static int launch_push_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const void* z, const int16_t* labels,
                             const int32_t* proto_class, unsigned long long* keys, const unsigned char* img, cudaStream_t st) {
   tcp::PushParams prm;
   prm.s = s;
@@ -348,25 +394,30 @@ static int launch_push_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const 
   prm.n_tiles = (long long)s.B * prm.tiles_per_map;
   const int grid = build_pgroups(ct, prm.n_tiles, sm_count(), &prm.gt);
   if (grid <= 0) return SPS_ERR_UNSUPPORTED;
-  prm.z = z;
+  prm.z = reinterpret_cast<const float*>(z);
+  if (ZMODE != tc::ZM_LDG) {
+    const int rc = make_tmap_2d_16bit(&prm.tm_z, z, std::is_same<X, __nv_bfloat16>::value, s.N, s.C, tc::TILE_M, 64, 128);
+    if (rc != SPS_OK) return rc;
+  }
   prm.img = img;
   prm.labels = labels;
   prm.proto_class = proto_class;
   prm.keys = keys;
-  constexpr int SMEM = tcp::PLay<NSPLIT>::SM_TOTAL;
-  static_assert(SMEM <= 227 * 1024 && tcp::PLay<NSPLIT>::NSTAGE >= 2 && tcp::PLay<NSPLIT>::NSTAGE + 2 <= tcp::PLay<NSPLIT>::LAB_RING,
-                "push kernel shared memory plan");
-  SPS_CUDA_TRY(cudaFuncSetAttribute(tcp::push_scan_tc_kernel<X, NSPLIT, MASKED>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
-  tcp::push_scan_tc_kernel<X, NSPLIT, MASKED><<<grid, tcp::NTHREADS, SMEM, st>>>(prm);
+  using L = tcp::PLay<NSPLIT, NSPLIT == 3 && ZMODE == tc::ZM_LDG>;
+  constexpr int SMEM = L::SM_TOTAL;
+  static_assert(SMEM <= 227 * 1024 && L::NSTAGE >= 2 && L::NSTAGE + 2 <= L::LAB_RING, "push kernel shared memory plan");
+  SPS_CUDA_TRY(cudaFuncSetAttribute(tcp::push_scan_tc_kernel<X, NSPLIT, MASKED, ZMODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
+  tcp::push_scan_tc_kernel<X, NSPLIT, MASKED, ZMODE><<<grid, tcp::NTHREADS, SMEM, st>>>(prm);
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
   return SPS_OK;
 }
 
-// keys must already hold the "absent" key (launch_push_fill)
-int launch_push_scan_tc(const HeadShape& s, int math, const float* z, const float* protos, const int16_t* labels,
+// keys must already hold the "absent" key (launch_push_fill).  z16: the maps are 16-bit channels-last (TMA-fed).
+int launch_push_scan_tc(const HeadShape& s, int math, const void* z, bool z16, const float* protos, const int16_t* labels,
                         const int32_t* proto_class, unsigned long long* keys, void* ws, size_t ws_bytes, cudaStream_t st) {
   SPS_REQUIRE(s.D <= 64 && s.D % 8 == 0, SPS_ERR_UNSUPPORTED, "tensor-core push: D=%d must be a multiple of 8, <= 64", s.D);
+  SPS_REQUIRE(!z16 || (s.D == 64 && s.N < (1ll << 31)), SPS_ERR_UNSUPPORTED, "TMA-fed push: D=%d (64 only), N=%lld (< 2^31)", s.D, s.N);
   tc::ChunkTable ct;
   int rc = build_chunk_table(s, false, &ct);
   if (rc != SPS_OK) return rc;
@@ -377,9 +428,12 @@ int launch_push_scan_tc(const HeadShape& s, int math, const float* z, const floa
   if (rc != SPS_OK) return rc;
   // label values are class + 1 <= K; the in-GEMM class mask covers label values up to MASK_MAX_LABEL
   const bool masked = s.K <= tc::MASK_MAX_LABEL;
-#define SPS_PUSH_CASE(X, NS)                                                                                  \
-  return masked ? launch_push_tc_t<X, NS, true>(s, ct, z, labels, proto_class, keys, img, st)                 \
-                : launch_push_tc_t<X, NS, false>(s, ct, z, labels, proto_class, keys, img, st)
+#define SPS_PUSH_CASE(X, NS)                                                                                              \
+  if (z16)                                                                                                                \
+    return masked ? launch_push_tc_t<X, NS, true, tc::ZM_TMA16>(s, ct, z, labels, proto_class, keys, img, st)             \
+                  : launch_push_tc_t<X, NS, false, tc::ZM_TMA16>(s, ct, z, labels, proto_class, keys, img, st);           \
+  return masked ? launch_push_tc_t<X, NS, true, tc::ZM_LDG>(s, ct, z, labels, proto_class, keys, img, st)                 \
+                : launch_push_tc_t<X, NS, false, tc::ZM_LDG>(s, ct, z, labels, proto_class, keys, img, st)
   switch (math) {
     case SPS_MATH_F16: SPS_PUSH_CASE(__half, 1);
     case SPS_MATH_F16X3: SPS_PUSH_CASE(__half, 3);

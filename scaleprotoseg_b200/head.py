@@ -13,7 +13,8 @@ from typing import List, Optional, Sequence, Tuple
 import torch
 
 from . import _lib
-from ._lib import ACT_LINEAR, ACT_LOG, MATH_BF16, MATH_BF16X3, MATH_F16, MATH_F16X3, MATH_FP32, SpsGroupDesc, SpsHeadDesc
+from ._lib import (ACT_LINEAR, ACT_LOG, FLAG_ZPACK, FLAG_ZRELAYED, MATH_BF16, MATH_BF16X3, MATH_F16, MATH_F16X3, MATH_FP32,
+                   SpsGroupDesc, SpsHeadDesc, Z_BF16, Z_F16, Z_F32, Z_NCHW, Z_NHWC)
 
 # what install() uses: tcgen05 kernels with 3-term fp16 products (fp32-class distances, |z|,|p| < 6e4 — the
 # reference's add-on layers end in a Sigmoid, segmentation/model/model_multiscale.py:206-208)
@@ -65,13 +66,41 @@ def _check_cuda_f32(name: str, t: torch.Tensor):
         raise RuntimeError(f"{name} must be float32, got {t.dtype}")
 
 
-def make_desc(cfg: HeadConfig, B: int, H: int, W: int, D: int, P: int) -> SpsHeadDesc:
+_SPLIT = (MATH_F16X3, MATH_BF16X3)
+
+
+def prepare_z(z: torch.Tensor, cfg: HeadConfig):
+    """Feature maps as the kernels take them: fp32 NCHW (the reference's own layout), or fp16 / bf16 channels-last
+    (what the stock backbone emits under channels_last + autocast; fed to the tensor cores by TMA).
+    -> (z in a layout the library accepts, HeadConfig whose math mode matches the element type)."""
+    if not z.is_cuda:
+        raise RuntimeError("z must be a CUDA tensor: the prototype head has no CPU path")
+    if z.dim() != 4:
+        raise RuntimeError(f"z must be (B,C,H,W), got {tuple(z.shape)}")
+    if z.dtype == torch.float32:
+        return z.contiguous(), cfg
+    if z.dtype not in (torch.float16, torch.bfloat16):
+        raise RuntimeError(f"z must be float32, float16 or bfloat16, got {z.dtype}")
+    if cfg.math == MATH_FP32:   # exact-operand mode asked for: widen (a 16-bit value is exact in fp32)
+        return z.float().contiguous(), cfg
+    split = cfg.math in _SPLIT
+    math = (MATH_F16X3 if split else MATH_F16) if z.dtype == torch.float16 else (MATH_BF16X3 if split else MATH_BF16)
+    if math != cfg.math:
+        cfg = HeadConfig(cfg.scale_lo, cfg.num_classes, cfg.act_kind, cfg.eps, math, cfg.flags)
+    return z.contiguous(memory_format=torch.channels_last), cfg
+
+
+def make_desc(cfg: HeadConfig, B: int, H: int, W: int, D: int, P: int, z: Optional[torch.Tensor] = None,
+              extra_flags: int = 0) -> SpsHeadDesc:
     S = len(cfg.scale_lo) - 1
     d = SpsHeadDesc()
     d.B, d.H, d.W, d.S, d.D, d.P, d.K = B, H, W, S, D, P, cfg.num_classes
     for i in range(_lib.SPS_MAX_SCALES + 1):
         d.scale_lo[i] = cfg.scale_lo[i] if i <= S else P
-    d.act_kind, d.eps, d.math, d.flags = cfg.act_kind, cfg.eps, cfg.math, cfg.flags
+    d.act_kind, d.eps, d.math, d.flags = cfg.act_kind, cfg.eps, cfg.math, cfg.flags | extra_flags
+    d.z_dtype, d.z_layout = Z_F32, Z_NCHW
+    if z is not None and z.dtype != torch.float32:
+        d.z_dtype, d.z_layout = (Z_F16 if z.dtype == torch.float16 else Z_BF16), Z_NHWC
     return d
 
 
@@ -90,11 +119,32 @@ def _shape_of(z: torch.Tensor, protos: torch.Tensor, cfg: HeadConfig):
     return B, H, W, S, D, P
 
 
-def head_forward_raw(z, protos, last_w, cfg: HeadConfig, want_dist: bool, want_act: bool):
-    """No autograd.  -> (logits (N,K) | None, dist (B,P,H,W) | None, act (N,P) | None)."""
+def wants_relay(z: torch.Tensor, cfg: HeadConfig) -> bool:
+    """fp32 NCHW map + FLAG_ZPACK + tensor-core math + D = 64: the map is re-laid ONCE per step (sps_z_relay) as 16-bit
+    channels-last hi / lo arrays and both the forward and the backward run their TMA-fed kernels on it."""
+    S = len(cfg.scale_lo) - 1
+    return (z.dtype == torch.float32 and bool(cfg.flags & FLAG_ZPACK) and cfg.math != MATH_FP32 and z.shape[1] == 64 * S
+            and z.numel() > 0)
+
+
+def z_relay(z: torch.Tensor, protos: torch.Tensor, cfg: HeadConfig) -> torch.Tensor:
     lib = _lib.load()
-    _check_cuda_f32("z", z), _check_cuda_f32("prototype_vectors", protos)
     z = z.contiguous()
+    B, H, W, S, D, P = _shape_of(z, protos, cfg)
+    desc = make_desc(cfg, B, H, W, D, P)
+    nbytes = int(lib.sps_z_relay_bytes(C.byref(desc)))
+    out = torch.empty(max(nbytes, 16), device=z.device, dtype=torch.uint8)
+    with torch.cuda.device(z.device):
+        _lib.check(lib.sps_z_relay(C.byref(desc), _ptr(z), _ptr(out), nbytes, _stream()), "sps_z_relay")
+    return out
+
+
+def head_forward_raw(z, protos, last_w, cfg: HeadConfig, want_dist: bool, want_act: bool, relay=None):
+    """No autograd.  -> (logits (N,K) | None, dist (B,P,H,W) | None, act (N,P) | None).
+    relay: a buffer written by z_relay for this z (then z itself is only used for its shape)."""
+    lib = _lib.load()
+    _check_cuda_f32("prototype_vectors", protos)
+    z, cfg = prepare_z(z, cfg)
     protos = protos.contiguous()
     B, H, W, S, D, P = _shape_of(z, protos, cfg)
     N = B * H * W
@@ -109,29 +159,32 @@ def head_forward_raw(z, protos, last_w, cfg: HeadConfig, want_dist: bool, want_a
         dist = torch.empty((B, P, H, W), device=z.device, dtype=torch.float32)
     if want_act:
         act = torch.empty((N, P), device=z.device, dtype=torch.float32)
-    desc = make_desc(cfg, B, H, W, D, P)
+    desc = make_desc(cfg, B, H, W, D, P, z, FLAG_ZRELAYED if relay is not None else 0)
     nbytes = int(lib.sps_head_fwd_workspace_bytes(C.byref(desc)))
     ws = torch.empty(nbytes, device=z.device, dtype=torch.uint8) if nbytes else None
     with torch.cuda.device(z.device):
-        _lib.check(lib.sps_head_fwd(C.byref(desc), _ptr(z), _ptr(protos), _ptr(last_w), _ptr(logits), _ptr(dist),
-                                    _ptr(act), _ptr(ws), nbytes, _stream()), "sps_head_fwd")
+        _lib.check(lib.sps_head_fwd(C.byref(desc), _ptr(relay if relay is not None else z), _ptr(protos), _ptr(last_w),
+                                    _ptr(logits), _ptr(dist), _ptr(act), _ptr(ws), nbytes, _stream()), "sps_head_fwd")
     return logits, dist, act
 
 
-def head_backward_raw(z, protos, last_w, cfg: HeadConfig, dlogits, ddist, dact, need_dz, need_dp, need_dw):
+def head_backward_raw(z, protos, last_w, cfg: HeadConfig, dlogits, ddist, dact, need_dz, need_dp, need_dw, relay=None):
     lib = _lib.load()
-    z = z.contiguous()
+    z_in = z
+    z, cfg = prepare_z(z, cfg)
     protos = protos.contiguous()
     B, H, W, S, D, P = _shape_of(z, protos, cfg)
-    desc = make_desc(cfg, B, H, W, D, P)
+    desc = make_desc(cfg, B, H, W, D, P, z, FLAG_ZRELAYED if relay is not None else 0)
     if last_w is not None:
         last_w = last_w.contiguous()
-    # memory_format=contiguous: empty_like would inherit the strides of a transposed view
-    dz = torch.empty_like(z, memory_format=torch.contiguous_format) if need_dz else None
+    # dz mirrors z (element type and layout); preserve_format keeps channels-last for the 16-bit maps
+    dz = torch.empty_like(z, memory_format=torch.preserve_format) if need_dz else None
     dp = torch.empty_like(protos, memory_format=torch.contiguous_format) if need_dp else None
     dw = torch.empty_like(last_w, memory_format=torch.contiguous_format) if (need_dw and last_w is not None) else None
     if dlogits is not None:
         dlogits = dlogits.contiguous().view(-1, cfg.num_classes)
+        if dlogits.dtype != torch.float32:
+            dlogits = dlogits.float()
     if ddist is not None:
         ddist = ddist.contiguous()
     if dact is not None:
@@ -139,9 +192,11 @@ def head_backward_raw(z, protos, last_w, cfg: HeadConfig, dlogits, ddist, dact, 
     nbytes = int(lib.sps_workspace_bytes(C.byref(desc)))
     ws = torch.empty(max(nbytes, 16), device=z.device, dtype=torch.uint8)
     with torch.cuda.device(z.device):
-        _lib.check(lib.sps_head_bwd(C.byref(desc), _ptr(z), _ptr(protos), _ptr(last_w), _ptr(dlogits), _ptr(ddist),
-                                    _ptr(dact), _ptr(dz), _ptr(dp), _ptr(dw), _ptr(ws), nbytes, _stream()),
-                   "sps_head_bwd")
+        _lib.check(lib.sps_head_bwd(C.byref(desc), _ptr(relay if relay is not None else z), _ptr(protos), _ptr(last_w),
+                                    _ptr(dlogits), _ptr(ddist), _ptr(dact), _ptr(dz), _ptr(dp), _ptr(dw), _ptr(ws), nbytes,
+                                    _stream()), "sps_head_bwd")
+    if dz is not None and dz.dtype != z_in.dtype:     # a 16-bit map widened for the exact fp32 mode
+        dz = dz.to(z_in.dtype)
     return dz, dp, dw
 
 
@@ -151,10 +206,12 @@ class PrototypeHeadFn(torch.autograd.Function):
     @staticmethod
     def forward(ctx, z, protos, last_w, cfg: HeadConfig, want_dist: bool, want_act: bool):
         p2 = protos.reshape(protos.shape[0], -1)
-        logits, dist, act = head_forward_raw(z, p2, last_w, cfg, want_dist, want_act)
+        relay = z_relay(z, p2, cfg) if wants_relay(z, cfg) else None
+        logits, dist, act = head_forward_raw(z, p2, last_w, cfg, want_dist, want_act, relay=relay)
         ctx.cfg = cfg
         ctx.proto_shape = protos.shape
         ctx.has_w = last_w is not None
+        ctx.relay = relay          # one re-lay per step: the backward's TMA-fed kernel reads the same buffer
         ctx.save_for_backward(z, p2, last_w if last_w is not None else torch.empty(0, device=z.device))
         ctx.set_materialize_grads(False)
         return logits, dist, act
@@ -167,8 +224,10 @@ class PrototypeHeadFn(torch.autograd.Function):
         need_dz, need_dp, need_dw = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.needs_input_grad[2]
         if dlogits is None and ddist is None and dact is None:
             return None, None, None, None, None, None
+        relay = ctx.relay if (dact is None and dlogits is not None and ctx.has_w) else None
         dz, dp, dw = head_backward_raw(z, p2, last_w, ctx.cfg, dlogits, ddist, dact, need_dz, need_dp,
-                                       need_dw and ctx.has_w)
+                                       need_dw and ctx.has_w, relay=relay)
+        ctx.relay = None
         if dp is not None:
             dp = dp.view(ctx.proto_shape)
         return dz, dp, dw, None, None, None

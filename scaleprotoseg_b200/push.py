@@ -17,7 +17,7 @@ import numpy as np
 import torch
 
 from . import _lib
-from .head import HeadConfig, _check_cuda_f32, _ptr, _stream, make_desc
+from .head import HeadConfig, _ptr, _stream, make_desc, prepare_z
 
 KEY_INIT = 0x7FFFFFFFFFFFFFFF  # > any packed key; positive as int64 so an NCCL int64 min works
 ABSENT_BITS = 0x501502F9       # float bits of 1e10f (push_multiscale_optimization.py:41)
@@ -37,11 +37,10 @@ def proto_scale_reference(P: int, S: int) -> torch.Tensor:
 
 def scan_maps(z: torch.Tensor, labels: torch.Tensor, protos: torch.Tensor, proto_class: torch.Tensor,
               cfg: HeadConfig, keys_out: Optional[torch.Tensor] = None) -> torch.Tensor:
-    """z (B,C,h,w) fp32 post-sigmoid maps, labels (B,h,w) int16 (0 = void, c+1 = class c).
-    -> keys (B,P) int64: (float_bits(min distance) << 32) | flat index."""
+    """z (B,C,h,w) post-sigmoid maps (fp32 NCHW, or fp16 / bf16 channels-last: TMA-fed), labels (B,h,w) int16
+    (0 = void, c+1 = class c).  -> keys (B,P) int64: (float_bits(min distance) << 32) | flat index."""
     lib = _lib.load()
-    _check_cuda_f32("z", z)
-    z = z.contiguous()
+    z, cfg = prepare_z(z, cfg)
     p2 = protos.reshape(protos.shape[0], -1).contiguous()
     B, Cc, H, W = z.shape
     P, D = p2.shape
@@ -50,7 +49,7 @@ def scan_maps(z: torch.Tensor, labels: torch.Tensor, protos: torch.Tensor, proto
     labels = labels.contiguous()
     proto_class = proto_class.to(device=z.device, dtype=torch.int32).contiguous()
     keys = keys_out if keys_out is not None else torch.empty((B, P), device=z.device, dtype=torch.int64)
-    desc = make_desc(cfg, B, H, W, D, P)
+    desc = make_desc(cfg, B, H, W, D, P, z)
     nbytes = int(lib.sps_head_fwd_workspace_bytes(C.byref(desc)))
     ws = torch.empty(nbytes, device=z.device, dtype=torch.uint8) if nbytes else None
     with torch.cuda.device(z.device):
@@ -75,7 +74,7 @@ def gather_winners(z: torch.Tensor, keys: torch.Tensor, best: torch.Tensor, map_
                    cfg: HeadConfig, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """Writes out[p] = z[win_map(p), scale(p)*D:(scale(p)+1)*D, i, j] for the winners held in z."""
     lib = _lib.load()
-    z = z.contiguous()
+    z, cfg = prepare_z(z, cfg)
     B, Cc, H, W = z.shape
     P = keys.shape[1]
     S = len(cfg.scale_lo) - 1
@@ -83,7 +82,7 @@ def gather_winners(z: torch.Tensor, keys: torch.Tensor, best: torch.Tensor, map_
     if out is None:
         out = torch.zeros((P, D), device=z.device, dtype=torch.float32)
     proto_scale = proto_scale.to(device=z.device, dtype=torch.int32).contiguous()
-    desc = make_desc(cfg, B, H, W, D, P)
+    desc = make_desc(cfg, B, H, W, D, P, z)
     with torch.cuda.device(z.device):
         _lib.check(lib.sps_push_gather(C.byref(desc), _ptr(z), _ptr(keys), _ptr(best), B, int(map_base),
                                        _ptr(proto_scale), _ptr(out), _stream()), "sps_push_gather")

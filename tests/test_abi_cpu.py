@@ -30,7 +30,7 @@ def test_binding_covers_header(built_lib):
 
 def test_version_and_validation(built_lib):
     from scaleprotoseg_b200._lib import SpsHeadDesc
-    assert built_lib.sps_version() == 1
+    assert built_lib.sps_version() == 2
     d = SpsHeadDesc()
     d.B, d.H, d.W, d.S, d.D, d.P, d.K = 1, 4, 4, 4, 64, 24, 2
     for i in range(9):
@@ -44,11 +44,21 @@ def test_version_and_validation(built_lib):
     rc = built_lib.sps_head_fwd(C.byref(d), None, None, None, None, None, None, None, 0, None)
     assert rc == 1 and b"NULL" in built_lib.sps_last_error()
     assert built_lib.sps_workspace_bytes(C.byref(d)) > 0
+    # feature-map element type / layout (z_dtype, z_layout): 16-bit maps are channels-last and need the matching math
+    d.z_dtype, d.z_layout, d.math = 1, 0, 3                     # fp16 but NCHW
+    rc = built_lib.sps_head_fwd(C.byref(d), None, None, None, None, None, None, None, 0, None)
+    assert rc == 2 and b"channels-last" in built_lib.sps_last_error()
+    d.z_layout, d.math = 1, 2                                   # fp16 channels-last with bf16 math
+    rc = built_lib.sps_head_fwd(C.byref(d), None, None, None, None, None, None, None, 0, None)
+    assert rc == 2 and b"does not match" in built_lib.sps_last_error()
+    d.math = 4                                                  # fp16 channels-last, 3-term fp16 math: valid (NULL pointers)
+    rc = built_lib.sps_head_fwd(C.byref(d), None, None, None, None, None, None, None, 0, None)
+    assert rc == 1 and b"NULL" in built_lib.sps_last_error()
 
 
 def test_struct_layout_matches_header():
     from scaleprotoseg_b200._lib import SpsGroupDesc, SpsHeadDesc
-    assert C.sizeof(SpsHeadDesc) == 4 * (7 + 9 + 4)
+    assert C.sizeof(SpsHeadDesc) == 4 * (7 + 9 + 4 + 2)
     assert C.sizeof(SpsGroupDesc) == 8 + 6 * 8
 
 
