@@ -213,6 +213,98 @@ def kld_case(name, B, H, W, P, K, S=4, prune=(), absent_class=None, void_only=Fa
     print(name, "loss", lv)
 
 
+def kld_group_case(name, B, H, W, K, J=3, per_class=3, drop_class=None, absent_class=None, void_only=False, seed=0):
+    """Reference KLDLossGroup (segmentation/model/loss.py:467-545) on random group activations; value and gradient."""
+    from segmentation.model.loss import KLDLossGroup
+    g = torch.Generator().manual_seed(ho.SEED + 57 * (seed + 1))
+    classes = [c for c in range(K) if c != drop_class]           # a class without prototypes has no projection (:486-487)
+    pident = torch.zeros(per_class * len(classes), K)
+    gident = torch.zeros(J * len(classes), K)
+    for k, c in enumerate(classes):
+        pident[k * per_class:(k + 1) * per_class, c] = 1
+        gident[k * J:(k + 1) * J, c] = 1                          # model_multiscale_group.py:262-267
+    N = B * H * W
+    acts = torch.exp(torch.randn(N, J * len(classes), generator=g)).requires_grad_(True)   # compute_group ends in exp
+    labels = torch.stack([ho.make_labels(seed * 100 + i, H, W, K, absent_class=absent_class, block=3) for i in range(B)])
+    if void_only:
+        labels[0] = 0
+    ref = KLDLossGroup(pident, gident, J)
+    loss = ref(list(torch.split(acts, J, dim=-1)), labels)
+    if loss.requires_grad:
+        (dacts,) = torch.autograd.grad(loss * 2.0, acts)
+    else:
+        dacts = torch.zeros_like(acts)
+    mine = ho.kld_group_loss(acts.detach(), labels, gident)
+    lv = float(loss.detach())
+    assert abs(float(mine) - lv) <= 1e-5 * max(1.0, abs(lv)), (name, float(mine), lv)
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", name + ".npz"), acts=acts.detach().numpy(), labels=labels.numpy(),
+                        proto_identity=pident.numpy(), group_identity=gident.numpy(), J=np.array(J),
+                        loss=np.float32(lv), dacts=dacts.numpy(), upstream=np.float32(2.0))
+    print(name, "loss", lv)
+
+
+def topk_case(mm, name, n_img, h, w, P, K, k, seed=0):
+    """Runs the reference's own find_k_nearest_patches_to_prototypes (find_nearest.py:71-352) on a small dataset ON DISK
+    (PNG images + .npy annotations in a temp directory).  to_normalized_tensor is rebound so that the PNG, whose first
+    pixel carries the image number, stands for a pre-sigmoid feature map; Tensor.cuda is a no-op here (no GPU).  The
+    function returns, per prototype, the annotation maps of the k nearest images in ascending distance: matching them
+    against the (distinct) annotations gives the ranked image list, which is what pins the oracle."""
+    import tempfile
+    import types
+    from PIL import Image
+    import find_nearest as fn
+    m = build_stage1(mm, P, K)
+    m.eval()
+    xs, labels = [], []
+    tmp = tempfile.mkdtemp(prefix="sps_topk_")
+    ids = [f"im{i}" for i in range(n_img)]
+    for i in range(n_img):
+        g = torch.Generator().manual_seed(ho.SEED + 7001 * (i + 1) + seed)
+        xs.append(torch.randn(256, h, w, generator=g))
+        lab = ho.make_labels(i + seed, h, w, K, block=3)
+        lab[0, 0] = 0                                            # every image holds a void pixel (the +10e6 mask, :138)
+        labels.append(lab)
+        px = np.zeros((h, w, 3), dtype=np.uint8)
+        px[0, 0, 0] = i
+        Image.fromarray(px).save(os.path.join(tmp, ids[i] + ".png"))
+        np.save(os.path.join(tmp, ids[i] + ".npy"), lab.numpy())
+    ds = types.SimpleNamespace(img_ids=ids, get_img_path=lambda iid: os.path.join(tmp, iid + ".png"), image_margin_size=0,
+                               annotations_dir=tmp, convert_targets=None, __len__=lambda: n_img)
+
+    class _DS:
+        img_ids, image_margin_size, annotations_dir, convert_targets = ids, 0, tmp, None
+
+        def get_img_path(self, iid):
+            return os.path.join(tmp, iid + ".png")
+
+        def __len__(self):
+            return n_img
+
+    old_norm, old_cuda = fn.to_normalized_tensor, torch.Tensor.cuda
+    fn.to_normalized_tensor = lambda img: xs[img.getpixel((0, 0))[0]]
+    torch.Tensor.cuda = lambda self, *a, **kw: self
+    try:
+        out = fn.find_k_nearest_patches_to_prototypes(_DS(), types.SimpleNamespace(module=m, eval=lambda: None), k=k,
+                                                      full_save=False, log=lambda *a: None)
+    finally:
+        fn.to_normalized_tensor, torch.Tensor.cuda = old_norm, old_cuda
+    shifted = [lab.numpy() - 1 for lab in labels]                  # the function keeps search_y - 1 (:127)
+    rank = np.full((P, k), -1, dtype=np.int64)
+    for p in range(P):
+        for r in range(k):
+            hits = [i for i in range(n_img) if np.array_equal(out[p][r], shifted[i])]
+            assert len(hits) == 1, (p, r, hits)
+            rank[p, r] = hits[0]
+    ranges = ranges_of(m)
+    mine = ho.topk_nearest([ho.scale_l2_convolution(torch.sigmoid(x).unsqueeze(0), m.prototype_vectors.detach(), [tuple(r) for r in ranges])
+                            for x in xs], labels, k)
+    assert np.array_equal(mine[1].numpy(), rank), name
+    np.savez_compressed(os.path.join(ROOT, "tests", "golden", name + ".npz"), x=torch.stack(xs).numpy(),
+                        labels=torch.stack(labels).numpy().astype(np.int16), protos=m.prototype_vectors.detach().numpy(),
+                        ranges=ranges, identity=m.prototype_class_identity.numpy(), rank_img=rank, K=np.array(K), k=np.array(k))
+    print(name, "ranked images of prototype 0:", rank[0].tolist())
+
+
 def main():
     mm, mg, pm = import_reference()
     torch.manual_seed(ho.SEED)
@@ -230,6 +322,9 @@ def main():
     kld_case("kld_em", B=2, H=9, W=7, P=24, K=2)
     kld_case("kld_small_ragged", B=2, H=7, W=8, P=40, K=5, prune=(0, 1, 11, 39), absent_class=3, void_only=True, seed=1)
     kld_case("kld_city228", B=1, H=12, W=10, P=228, K=19, seed=2)
+    kld_group_case("kld_group_em", B=2, H=9, W=7, K=2)
+    kld_group_case("kld_group_city_ragged", B=2, H=8, W=9, K=19, drop_class=4, absent_class=3, void_only=True, seed=1)
+    topk_case(mm, "topk_small", n_img=7, h=9, w=11, P=40, K=5, k=3)
 
 
 if __name__ == "__main__":

@@ -18,8 +18,10 @@ Reference lines followed (relative to /root/reference):
   push_image_min            segmentation/push_multiscale_optimization.py:68-91
   push_dataset_argmin       segmentation/push_multiscale_optimization.py:135-137
   push_gather               segmentation/push_multiscale_optimization.py:161-188
-  topk_nearest              find_nearest.py:89-175 (restated; no reference-generated fixture: the function needs a dataset on disk)
+  topk_nearest              find_nearest.py:89-175 (pinned by topk_small.npz: the reference's own function run on a small
+                            on-disk dataset, oracle/gen_golden.py::topk_case)
   kld_loss                  segmentation/model/loss.py:53-146 (KLDLoss.forward)
+  kld_group_loss            segmentation/model/loss.py:467-545 (KLDLossGroup.forward; pinned by kld_group_*.npz)
 """
 from typing import Dict, List, Optional, Sequence, Tuple
 
@@ -217,6 +219,16 @@ def kld_loss(dist: torch.Tensor, target: torch.Tensor, identity: torch.Tensor,
     if not terms:
         return torch.zeros((), dtype=dist.dtype)
     return torch.exp(-torch.cat(terms)).mean()
+
+
+def kld_group_loss(acts: torch.Tensor, target: torch.Tensor, group_identity: torch.Tensor) -> torch.Tensor:
+    """KLDLossGroup.forward (segmentation/model/loss.py:478-545): acts (N, J*Kc) = the concatenated group activations
+    (compute_group's list, class-slot order), target (B,H,W) with 0 = void, group_identity (J*Kc, K).  It is KLDLoss with
+    the group activations in the role of the distances and one 'scale' owning every column."""
+    B = target.shape[0]
+    G = acts.shape[1]
+    as_map = acts.reshape(B, -1, G).permute(0, 2, 1).reshape(B, G, -1, 1)
+    return kld_loss(as_map, target.reshape(B, -1, 1), group_identity, [(0, G)])
 
 
 def topk_nearest(dist_maps: Sequence[torch.Tensor], labels: Sequence[torch.Tensor], k: int):

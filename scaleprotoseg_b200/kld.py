@@ -189,7 +189,11 @@ def kld_loss_from_features(z: torch.Tensor, protos: torch.Tensor, target_labels:
     return KldFeatureLossFn.apply(z, protos, labels_int16(target_labels, tables.K).to(z.device), tables, cfg)
 
 
-_TABLE_CACHE: Dict[int, Tuple[tuple, KldTables]] = {}
+import weakref
+
+# loss module -> (signature of what the tables were built from, tables).  Weak keys: an entry dies with its module, so a
+# recycled id() / data_ptr() can never serve stale tables.
+_TABLE_CACHE: "weakref.WeakKeyDictionary" = weakref.WeakKeyDictionary()
 
 
 def kld_forward(self, prototype_distances: torch.Tensor, target_labels: torch.Tensor) -> torch.Tensor:
@@ -201,11 +205,47 @@ def kld_forward(self, prototype_distances: torch.Tensor, target_labels: torch.Te
     ranges = tuple(tuple(int(v) for v in self.scale_num_prototypes[s]) for s in range(self.num_scales))
     ident = self.prototype_class_identity
     sig = (ranges, tuple(ident.shape), int(ident.data_ptr()), int(ident._version), str(prototype_distances.device))
-    hit: Optional[Tuple[tuple, KldTables]] = _TABLE_CACHE.get(id(self))
+    hit: Optional[Tuple[tuple, KldTables]] = _TABLE_CACHE.get(self)
     if hit is None or hit[0] != sig:
         hit = (sig, KldTables(ident, ranges, prototype_distances.device))
-        _TABLE_CACHE[id(self)] = hit
+        _TABLE_CACHE[self] = hit
     if isinstance(prototype_distances, DeferredDistances):     # fused-mode training: no (B,P,H,W) map exists
         d = prototype_distances
         return kld_loss_from_features(d.z, d.protos, target_labels, hit[1], d.cfg)
     return kld_loss(prototype_distances.float(), target_labels, hit[1])
+
+
+def kld_group_loss(list_group_activation, target_labels: torch.Tensor, tables: KldTables) -> torch.Tensor:
+    """Same value as KLDLossGroup(...)(list_group_activation, target_labels) of the reference (loss.py:467-545).
+
+    The loss is KLDLoss with the group activations in the role of the distances: per image and class, log-softmax over the
+    class's pixels of each of the class's `num_groups` group columns, symmetric KL of every column pair, mean of exp(-kld).
+    So the same kernels run on the (B, J*Kc, HW) view of the concatenated group activations, with tables built from
+    group_class_identity (one 'scale' owning every column: the groups of a class are its members, pairs j < k as :521-527).
+    list_group_activation: Kc tensors (N, J) in class-slot order (compute_group's output), N = B*H*W."""
+    acts = torch.cat(list(list_group_activation), dim=-1) if not torch.is_tensor(list_group_activation) else list_group_activation
+    B = target_labels.shape[0]
+    G = acts.shape[-1]
+    if G != tables.P:
+        raise RuntimeError(f"group activations have {G} columns, group_class_identity has {tables.P} rows")
+    hw = acts.shape[0] // max(B, 1)
+    # (N, G) -> (B, G, HW, 1): the kernels read a channel-major map; a 4-byte-per-element layout change done by torch
+    # (plumbing; autograd carries the gradient back through it)
+    as_map = acts.float().reshape(B, hw, G).permute(0, 2, 1).contiguous().view(B, G, hw, 1)
+    labels = labels_int16(target_labels.reshape(B, hw, 1), tables.K).to(acts.device)
+    return KldLossFn.apply(as_map, labels, tables)
+
+
+def kld_group_forward(self, list_group_activation, target_labels: torch.Tensor) -> torch.Tensor:
+    """Bound over KLDLossGroup.forward by install(): `self` is the reference's module (attributes prototype_class_identity,
+    group_class_identity, num_groups; loss.py:470-476)."""
+    first = list_group_activation[0]
+    if not first.is_cuda:
+        raise RuntimeError("scaleprotoseg_b200 KLD loss runs on CUDA only: there is no CPU path")
+    gident = self.group_class_identity
+    sig = (tuple(gident.shape), int(gident.data_ptr()), int(gident._version), str(first.device), int(self.num_groups))
+    hit: Optional[Tuple[tuple, KldTables]] = _TABLE_CACHE.get(self)
+    if hit is None or hit[0] != sig:
+        hit = (sig, KldTables(gident, [(0, int(gident.shape[0]))], first.device))
+        _TABLE_CACHE[self] = hit
+    return kld_group_loss(list_group_activation, target_labels, hit[1])

@@ -2,6 +2,7 @@
 conventions and autograd behaviour (stand-in classes with the reference's attribute names, see
 tests/standin_model.py), plus edge cases and full-size properties."""
 import copy
+import os
 
 import pytest
 import torch
@@ -257,3 +258,74 @@ def test_single_scale_list_push_forward_and_image_level_branch(patched_single):
     assert len(o_got) == 3
     for a, b in zip(o_got, o_ref):
         assert_rel(a, b, TOL, "image-level output")
+
+
+# ---- push drop-ins (install.make_push_functions): compute_distances / min_across_dataset / global_min ---------------------
+class _FakePushDataset:
+    """What the three functions read from a PatchClassificationDataset (push_multiscale_optimization.py:116-131)."""
+    convert_targets = None
+    image_margin_size = 0
+
+    def __init__(self, n, ann_dir):
+        self.img_ids = [f"img{i:03d}" for i in range(n)]
+        self.annotations_dir = ann_dir
+
+    def __len__(self):
+        return len(self.img_ids)
+
+
+def _push_fixture_env(golden_dir, name, tmp_path, patched_cls):
+    import types
+    import numpy as np
+    from test_gpu_parity import _load
+    g = _load(golden_dir, name)
+    n = g["x"].shape[0]
+    ds = _FakePushDataset(n, str(tmp_path))
+    for i, iid in enumerate(ds.img_ids):
+        np.save(os.path.join(str(tmp_path), iid + ".npy"), g["labels"][i].astype(np.int64))
+    maps = {iid: torch.from_numpy(g["x"][i]) for i, iid in enumerate(ds.img_ids)}
+    # the same stand-ins oracle/gen_golden.py::push_case used with the reference's own functions: a pass-through
+    # to_normalized_tensor (the "image" is the pre-sigmoid map) and a same-size label resize
+    pm = types.SimpleNamespace(to_normalized_tensor=lambda t: t,
+                               resize_label=lambda t, size: torch.from_numpy(np.asarray(t)).long())
+    P, K = g["protos"].shape[0], int(g["K"])
+    torch.manual_seed(0)
+    model = patched_cls(P, K).to(DEV)
+    model.prototype_vectors.data.copy_(torch.from_numpy(g["protos"]))
+    from scaleprotoseg_b200.install import make_push_functions
+    fns = make_push_functions(pm, load_image=lambda dataset, iid: maps[iid])
+    return g, ds, pm, model, fns
+
+
+@pytest.mark.parametrize("name", ["push_small", "push_city228"])
+def test_push_dropins_golden(patched_classes, golden_dir, tmp_path, name):
+    """The installed replacements of compute_distances / min_across_dataset / global_min
+    (segmentation/push_multiscale_optimization.py:35-190) driven the way push_prototypes_multiscale drives them (:286-293),
+    against the fixtures the reference's own functions produced: per-image indices and values, winning image per prototype
+    (first image wins a tie, void-only image, class absent from the dataset) and the projected prototypes."""
+    import numpy as np
+    sps.set_default_math(sps.PUSH_MATH)       # what install() runs the scan in
+    g, ds, pm, model, (compute_distances, min_across_dataset, global_min) = _push_fixture_env(golden_dir, name, tmp_path, patched_classes[0])
+    K = int(g["K"])
+    n = len(ds)
+    for i in range(n):
+        idx, val = compute_distances(model, ds, torch.from_numpy(g["x"][i]), g["labels"][i].astype(np.int64), num_classes=K,
+                                     void_class=0, device=DEV)
+        assert idx.shape == (1, g["idx"].shape[1]) and idx.dtype == torch.int64 and val.dtype == torch.float32
+        ref_val = torch.from_numpy(g["val"][i])
+        absent = ref_val >= 1e10
+        assert torch.equal(val.cpu()[0] >= 1e10, absent)
+        assert_rel(val.cpu()[0][~absent], ref_val[~absent], 1e-3, "compute_distances values")
+    proto_min_dist, list_idx = min_across_dataset(ds, model, K, void_class=0, device=DEV)
+    assert proto_min_dist.dtype == torch.int64 and len(list_idx) == n and list_idx[0].shape == (1, g["idx"].shape[1])
+    assert torch.equal(proto_min_dist.cpu(), torch.from_numpy(g["win"]))
+    got_idx = torch.cat(list_idx).cpu()
+    ref_idx = torch.from_numpy(g["idx"])
+    win = torch.from_numpy(g["win"])
+    cols = torch.arange(win.numel())
+    live = torch.from_numpy(g["val"])[win, cols] < 1e10
+    assert torch.equal(got_idx[win, cols][live], ref_idx[win, cols][live])      # the winning positions
+    patches = global_min(proto_min_dist, list_idx, ds, model, device=DEV)
+    assert len(patches) == win.numel() and patches[0].shape == (64, 1, 1) and patches[0].dtype == np.float32
+    new = np.reshape(patches, g["new_protos"].shape)
+    assert np.allclose(new[live.numpy()], g["new_protos"][live.numpy()], rtol=0, atol=1e-6)

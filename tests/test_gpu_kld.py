@@ -15,6 +15,7 @@ import torch.nn as nn
 import scaleprotoseg_b200 as sps
 from oracle import head_oracle as ho
 from scaleprotoseg_b200.kld import KldTables, kld_loss
+from test_gpu_parity import assert_grad
 
 pytestmark = pytest.mark.gpu
 DEV = "cuda:0"
@@ -281,3 +282,43 @@ def test_unchanged_trainer_step_in_fused_mode(built_lib):
         sps.set_deferred_distances(False)
         sps.set_default_math(old_math)
         sps.uninstall()
+
+
+# ---- KLDLossGroup (segmentation/model/loss.py:467-545): the stage-2 loss over the group activations -----------------------
+@pytest.mark.parametrize("name", ["kld_group_em", "kld_group_city_ragged"])
+def test_kld_group_golden(built_lib, golden_dir, name):
+    """Value and gradient against the fixtures the unmodified reference produced (class without prototypes, class absent
+    from the labels, void-only image), through the same kernels as KLDLoss with the group activations as rows."""
+    g = _load(golden_dir, name)
+    J = int(g["J"])
+    gident = torch.from_numpy(g["group_identity"])
+    tables = sps.KldTables(gident, [(0, gident.shape[0])], DEV)
+    acts = torch.from_numpy(g["acts"]).to(DEV).requires_grad_(True)
+    labels = torch.from_numpy(g["labels"]).to(DEV)
+    loss = sps.kld_group_loss(list(torch.split(acts, J, dim=-1)), labels, tables)
+    assert abs(float(loss) - float(g["loss"])) <= 1e-5 * max(float(g["loss"]), 1e-3)
+    (da,) = torch.autograd.grad(loss * float(g["upstream"]), acts)
+    assert_grad(da, g["dacts"], 1e-4, "kld group dacts")
+
+
+def test_kld_group_dropin_on_a_standin(built_lib, golden_dir):
+    """install_kld_group binds the fused loss over a class with the reference's three attributes (loss.py:470-476);
+    CPU inputs keep the class's own loop."""
+    g = _load(golden_dir, "kld_group_city_ragged")
+    J = int(g["J"])
+
+    class KLDLossGroupStandin(torch.nn.Module):
+        def __init__(self, prototype_class_identity, group_class_identity, num_groups):
+            super().__init__()
+            self.prototype_class_identity, self.group_class_identity, self.num_groups = prototype_class_identity, group_class_identity, num_groups
+
+        def forward(self, list_group_activation, target_labels):
+            return ho.kld_group_loss(torch.cat(list_group_activation, -1), target_labels, self.group_class_identity)
+
+    sps.install_kld_group(KLDLossGroupStandin)
+    mod = KLDLossGroupStandin(torch.from_numpy(g["proto_identity"]), torch.from_numpy(g["group_identity"]), J)
+    acts = torch.from_numpy(g["acts"])
+    cpu = mod(list(torch.split(acts, J, dim=-1)), torch.from_numpy(g["labels"]))
+    gpu = mod(list(torch.split(acts.to(DEV), J, dim=-1)), torch.from_numpy(g["labels"]).to(DEV))
+    assert gpu.is_cuda and abs(float(gpu) - float(cpu)) <= 1e-5 * max(float(cpu), 1e-3)
+    assert abs(float(gpu) - float(g["loss"])) <= 1e-5 * max(float(g["loss"]), 1e-3)

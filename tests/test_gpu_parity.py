@@ -498,3 +498,26 @@ def test_topk_nearest_vs_oracle(built_lib, math):
     a, b = spush.topk_keys(k0, k, 0), spush.topk_keys(k1, k, 5)
     mk, mp = spush.merge_topk([a[0], b[0]], [a[1], b[1]])
     assert torch.equal(mk.cpu(), top[0].cpu()) and torch.equal(mp.cpu(), top[1].cpu())
+
+
+def test_topk_nearest_golden(built_lib, golden_dir):
+    """k nearest images per prototype against the ranking the reference's own find_k_nearest_patches_to_prototypes
+    (find_nearest.py:71-352) produced on a small on-disk dataset (tests/golden/topk_small.npz): image order exact wherever
+    consecutive ranks are further apart than the distance tolerance; distances and positions against the oracle."""
+    g = _load(golden_dir, "topk_small")
+    ranges, k, K = _ranges(g), int(g["k"]), int(g["K"])
+    z = torch.sigmoid(torch.from_numpy(g["x"]))
+    protos = torch.from_numpy(g["protos"])
+    labels = torch.from_numpy(g["labels"].astype(np.int64))
+    maps = [ho.scale_l2_convolution(z[i:i + 1], protos, ranges) for i in range(z.shape[0])]
+    val, img, pix = ho.topk_nearest(maps, list(labels), k)
+    assert np.array_equal(img.numpy(), g["rank_img"])
+    for math in (sps.MATH_FP32, sps.MATH_F16X3):
+        cfg = sps.HeadConfig.from_ranges(ranges, K, math=math)
+        d, m, px = spush.topk_nearest(z.to(DEV), labels.to(torch.int16).to(DEV), protos.to(DEV), cfg, k)
+        tol = _tol(math)
+        assert_rel(d, val, tol, "top-k distances")
+        gap = (val[:, 1:] - val[:, :-1]) > 4 * tol * val[:, 1:].clamp_min(1.0)
+        clear = torch.cat([gap, torch.ones(val.shape[0], 1, dtype=torch.bool)], 1) & torch.cat([torch.ones(val.shape[0], 1, dtype=torch.bool), gap], 1)
+        assert torch.equal(m.cpu()[clear], torch.from_numpy(g["rank_img"])[clear]), "ranked images"
+        assert torch.equal(px.cpu()[clear], pix[clear]), "positions of the closest patches"

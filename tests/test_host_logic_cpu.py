@@ -105,6 +105,139 @@ def test_push_two_rank_exchange_gloo(tmp_path):
     assert open(out).read() == "ok"
 
 
+def _dropin_rank_main(rank, world, port, tmp, ann_dir):
+    """The INSTALLED push drop-ins (install.make_push_functions) on `world` gloo ranks.  The three CUDA entry points they
+    call are replaced by oracle-based CPU stand-ins (no GPU here): what is under test is the sharding of dataset.img_ids,
+    the batching of same-size maps, the min all-reduce of packed keys, the all-gather of the per-image index lists and
+    the sum all-reduce of the gathered winners - against the oracle's single-process push."""
+    import types
+    import torch.distributed as dist
+    os.environ["MASTER_ADDR"], os.environ["MASTER_PORT"] = "127.0.0.1", str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    from scaleprotoseg_b200 import push as sp
+    from scaleprotoseg_b200.install import make_push_functions
+    from standin_model import Stage1Standin
+    K, P, S, n = 4, 32, 4, 7
+    sizes = [(6, 5)] * 3 + [(4, 7)] * 2 + [(6, 5)] * 2            # a change of map size forces a batch flush
+    torch.manual_seed(3)
+    model = Stage1Standin(P, K)
+    xs = [torch.randn(256, h, w, generator=torch.Generator().manual_seed(50 + i)) for i, (h, w) in enumerate(sizes)]
+    xs[5] = xs[0].clone()          # cross-shard exact tie: the lower global index must win
+    labels = [ho.make_labels(i, h, w, K, absent_class=2) for i, (h, w) in enumerate(sizes)]
+    labels[5] = labels[0].clone()
+    ident, ranges = model.prototype_class_identity, model._ranges()
+
+    def scan_maps(z, lab, protos, pc, cfg, keys_out=None):
+        rows = []
+        for i in range(z.shape[0]):
+            d = ho.scale_l2_convolution(z[i:i + 1], protos, ranges)
+            idx, val = ho.push_image_min(d, lab[i].long(), ident, K, 0)
+            rows.append((val.view(torch.int32).to(torch.int64) << 32) | idx)
+        keys = torch.cat(rows)
+        if keys_out is not None:
+            keys_out.copy_(keys)
+        return keys
+
+    def reduce_keys(keys, map_base, best=None):
+        k = (keys & ~0xFFFFFFFF) | (torch.arange(keys.shape[0]).unsqueeze(1) + map_base)
+        return k.min(dim=0).values
+
+    def gather_winners(z, keys, best, map_base, proto_scale, cfg, out=None):
+        _, C, H, W = z.shape
+        for p in range(keys.shape[1]):
+            if int(best[p] & 0xFFFFFFFF) == map_base:
+                pix = int(keys[0, p] & 0xFFFFFFFF)
+                out[p] = z[0].view(S, C // S, H * W)[int(proto_scale[p]), :, pix]
+        return out
+
+    sp.scan_maps, sp.reduce_keys, sp.gather_winners = scan_maps, reduce_keys, gather_winners
+    ids = [f"i{i}" for i in range(n)]
+    ds = types.SimpleNamespace(img_ids=ids, annotations_dir=ann_dir, convert_targets=None, image_margin_size=0)
+    pm = types.SimpleNamespace(to_normalized_tensor=lambda t: t, resize_label=lambda t, size: torch.from_numpy(np.asarray(t)).long())
+    maps = dict(zip(ids, xs))
+    _, min_across_dataset, global_min = make_push_functions(pm, load_image=lambda d, iid: maps[iid])
+    win, list_idx = min_across_dataset(ds, model, K, void_class=0, device="cpu")
+    patches = global_min(win, list_idx, ds, model, device="cpu")
+    ref_win, ref_idx, _, ref_new = ho.push_full([torch.sigmoid(x).unsqueeze(0) for x in xs], labels, model.prototype_vectors.detach(),
+                                                ranges, ident, K)
+    ok = torch.equal(win, ref_win) and all(torch.equal(a, b) for a, b in zip(list_idx, ref_idx))
+    ok = ok and np.array_equal(np.reshape(patches, ref_new.shape), ref_new)
+    open(tmp + f".{rank}", "w").write("ok" if ok else "mismatch")
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_push_dropins_sharded_gloo(tmp_path, world):
+    """Row e' of the scope table: the reference's unchanged push_prototypes_multiscale calls min_across_dataset / global_min
+    as module globals (:286,:291); with torch.distributed initialised the installed versions shard the dataset."""
+    import torch.multiprocessing as mp
+    n = 7
+    sizes = [(6, 5)] * 3 + [(4, 7)] * 2 + [(6, 5)] * 2
+    for i, (h, w) in enumerate(sizes):
+        lab = ho.make_labels(i if i != 5 else 0, h, w, 4, absent_class=2)
+        np.save(str(tmp_path / f"i{i}.npy"), lab.numpy())
+    out = str(tmp_path / "result")
+    port = 29500 + ((os.getpid() + 17 * world) % 2000)
+    mp.spawn(_dropin_rank_main, args=(world, port, out, str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        assert open(out + f".{r}").read() == "ok", f"rank {r}"
+
+
+def test_shard_bounds_cover_the_dataset_contiguously():
+    from scaleprotoseg_b200.install import shard_bounds
+    for n in (0, 1, 7, 8, 3000):
+        for world in (1, 2, 3, 8):
+            cuts = [shard_bounds(n, r, world) for r in range(world)]
+            assert cuts[0][0] == 0 and cuts[-1][1] == n
+            assert all(a[1] == b[0] for a, b in zip(cuts, cuts[1:])) and all(lo <= hi for lo, hi in cuts)
+
+
+def test_install_on_the_real_reference_classes():
+    """install() on the UNMODIFIED reference (skipped where /root/reference is absent, i.e. on the GPU box): every patched
+    method and push global exists there, keeps its parameter names, and uninstall() puts the originals back."""
+    import inspect
+    import sys
+    ref = "/root/reference"
+    if not os.path.isdir(os.path.join(ref, "segmentation")):
+        pytest.skip("reference checkout not present")
+    for k in ["DATA_PATH_CITY", "DATA_PATH_PASCAL", "DATA_PATH_ADE", "DATA_PATH_EM", "DATA_PATH_COCO", "LOG_DIR"]:
+        os.environ.setdefault(k, "/tmp/sps_ref_env")
+    os.makedirs("/tmp/sps_ref_env", exist_ok=True)
+    for p in (ref, os.path.join(os.path.dirname(os.path.abspath(__file__)), "_stubs")):
+        if p not in sys.path:
+            sys.path.insert(0, p)
+    import scaleprotoseg_b200 as sps
+    from segmentation.model import loss as ml
+    from segmentation.model import model as m1
+    from segmentation.model import model_multiscale as mm
+    from segmentation.model import model_multiscale_group as mg
+    import segmentation.push_multiscale_optimization as pm
+    import segmentation.push_optimization as pm1
+    targets = [(mm.PPNetMultiScale, ["_scale_l2_convolution", "prototype_distances", "push_forward", "forward_from_conv_features"]),
+               (mg.PPNetMultiScale, ["_scale_l2_convolution", "push_forward", "compute_group", "run_last_layer", "forward_from_conv_features"]),
+               (m1.PPNet, ["_l2_convolution", "prototype_distances", "push_forward", "forward_from_conv_features"]),
+               (ml.KLDLoss, ["forward"]), (ml.KLDLossGroup, ["forward"]),
+               (pm, ["compute_distances", "min_across_dataset", "global_min"]),
+               (pm1, ["compute_distances", "min_across_dataset", "global_min"])]
+    before = {(id(o), n): getattr(o, n) for o, names in targets for n in names}
+    sig = {k: list(inspect.signature(v).parameters) for k, v in before.items()}
+    sps.install()
+    try:
+        for o, names in targets:
+            for n in names:
+                new = getattr(o, n)
+                assert new is not before[(id(o), n)], f"{o.__name__}.{n} was not replaced"
+                assert list(inspect.signature(new).parameters) == sig[(id(o), n)], f"{o.__name__}.{n}: parameter names differ"
+        # the push driver resolves its three helpers as module globals at call time
+        assert pm.push_prototypes_multiscale.__globals__["min_across_dataset"] is pm.min_across_dataset
+        assert pm1.push_prototypes.__globals__["global_min"] is pm1.global_min
+    finally:
+        sps.uninstall()
+    for o, names in targets:
+        for n in names:
+            assert getattr(o, n) is before[(id(o), n)], f"{o.__name__}.{n} was not restored"
+
+
 def test_kld_tables_follow_the_reference_pair_order():
     """Groups = (class, scale) in class-major order, members ascending, pairs (j, k > j) as loss.py:105-127."""
     from scaleprotoseg_b200.kld import KldTables, labels_int16

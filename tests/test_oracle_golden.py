@@ -94,6 +94,30 @@ def test_kld_loss_and_gradient(golden_dir, name):
     np.testing.assert_allclose(ddist.numpy(), g["ddist"], rtol=1e-4, atol=1e-7)
 
 
+@pytest.mark.parametrize("name", ["kld_group_em", "kld_group_city_ragged"])
+def test_kld_group_loss_and_gradient(golden_dir, name):
+    """KLDLossGroup.forward (segmentation/model/loss.py:467-545) run by the unmodified reference on random group
+    activations (class without prototypes, class absent from the labels, void-only image) vs the oracle's restatement."""
+    g = _load(golden_dir, name)
+    acts = torch.from_numpy(g["acts"]).requires_grad_(True)
+    loss = ho.kld_group_loss(acts, torch.from_numpy(g["labels"]), torch.from_numpy(g["group_identity"]))
+    np.testing.assert_allclose(loss.detach().numpy(), g["loss"], rtol=1e-5, atol=1e-7)
+    (da,) = torch.autograd.grad(loss * float(g["upstream"]), acts)
+    np.testing.assert_allclose(da.numpy(), g["dacts"], rtol=1e-4, atol=1e-7 * float(np.abs(g["dacts"]).max()))
+
+
+def test_topk_ranking_from_the_reference(golden_dir):
+    """find_k_nearest_patches_to_prototypes (find_nearest.py:71-352) run by the unmodified reference on a small on-disk
+    dataset: the ranked image list per prototype (ascending distance of the image's closest non-void patch)."""
+    g = _load(golden_dir, "topk_small")
+    ranges = _ranges(g)
+    protos = torch.from_numpy(g["protos"])
+    maps = [ho.scale_l2_convolution(torch.sigmoid(torch.from_numpy(x)).unsqueeze(0), protos, ranges) for x in g["x"]]
+    val, img, pix = ho.topk_nearest(maps, [torch.from_numpy(l.astype(np.int64)) for l in g["labels"]], int(g["k"]))
+    assert np.array_equal(img.numpy(), g["rank_img"])
+    assert (val[:, 1:] >= val[:, :-1]).all() and (val < 1e6).all()
+
+
 def test_kld_no_contribution_is_zero():
     """Void-only labels, or one pixel per class: no pair contributes and the loss is 0 (loss.py:142-146)."""
     ident, ranges = ho.make_identity(24, 2, 4), ho.uniform_ranges(24, 4)
