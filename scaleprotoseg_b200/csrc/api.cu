@@ -89,11 +89,16 @@ static bool use_zpack(const SpsHeadDesc* d) {
 static bool is_split(int math) { return math == SPS_MATH_F16X3 || math == SPS_MATH_BF16X3; }
 static size_t align1k(size_t v) { return (v + 1023) / 1024 * 1024; }
 
+static const int WIDE_K = 32;   // more classes than this: the one-pass wide backward (head_bwd_wide.cu); the forward may
+                                // need the re-lay route as well (3-term operands + a wide last layer do not fit the loader kernel)
+static int single_term(int math) { return (math == SPS_MATH_BF16 || math == SPS_MATH_BF16X3) ? SPS_MATH_BF16 : SPS_MATH_F16; }
+
 size_t sps_head_fwd_workspace_bytes(const SpsHeadDesc* desc) {
   if (validate_desc(desc) != SPS_OK || desc->math == SPS_MATH_FP32) return 0;
   const HeadShape s = make_shape(desc);
   size_t n = align1k(head_fwd_tc_workspace(s));
-  if (use_zpack(desc) && !(desc->flags & SPS_FLAG_ZRELAYED)) n += z_pack_bytes(s, desc->math);
+  if (desc->z_dtype == SPS_Z_F32 && !(desc->flags & SPS_FLAG_ZRELAYED) && desc->D == 64 && (use_zpack(desc) || s.K > WIDE_K))
+    n += z_pack_bytes(s, desc->math);
   return n;
 }
 
@@ -102,8 +107,16 @@ size_t sps_workspace_bytes(const SpsHeadDesc* desc) {
   HeadShape s = make_shape(desc);
   size_t a = desc->z_dtype == SPS_Z_F32 ? head_bwd_simt_workspace(s, desc->flags) : 0;
   size_t b = desc->math != SPS_MATH_FP32 ? head_bwd_tc_workspace(s) : 0;
-  size_t n = align1k(a > b ? a : b);
-  if (use_zpack(desc) && !(desc->flags & SPS_FLAG_ZRELAYED)) n += z_pack_bytes(s, desc->math);
+  size_t w = (desc->math != SPS_MATH_FP32 && s.K > WIDE_K && s.D == 64) ? head_bwd_wide_workspace(s) : 0;
+  size_t n = align1k(a > b ? (a > w ? a : w) : (b > w ? b : w));
+  if (desc->z_dtype == SPS_Z_F32 && !(desc->flags & SPS_FLAG_ZRELAYED)) {
+    size_t r = use_zpack(desc) ? z_pack_bytes(s, desc->math) : 0;
+    if (w > 0) {   // fp32 maps and a wide last layer: the map is re-laid (one 16-bit term) for the TMA-fed kernels
+      const size_t r1 = z_pack_bytes(s, single_term(desc->math));
+      r = r > r1 ? r : r1;
+    }
+    n += r;
+  }
   return n;
 }
 
@@ -144,7 +157,11 @@ int sps_head_fwd(const SpsHeadDesc* desc, const void* z, const float* protos, co
     return launch_head_fwd_tma(s, desc->math, z, nullptr, protos, last_w, logits, dist, act, workspace, workspace_bytes, st);
   }
   const float* zf = reinterpret_cast<const float*>(z);
-  if (use_zpack(desc) && head_fwd_tma_supported(s, desc->math, last_w != nullptr, act != nullptr, is_split(desc->math))) {
+  const bool tma_ok = desc->math != SPS_MATH_FP32 && head_fwd_tma_supported(s, desc->math, last_w != nullptr, act != nullptr, is_split(desc->math));
+  const bool ldg_ok = desc->math != SPS_MATH_FP32 && head_fwd_tc_supported(s, desc->math, last_w != nullptr, act != nullptr);
+  // re-lay route: asked for (SPS_FLAG_ZPACK / ZRELAYED), or the loader-fed kernel does not fit this shape (3-term operands
+  // with a wide last layer) while the TMA-fed one does
+  if (tma_ok && (use_zpack(desc) || (!ldg_ok && s.K > WIDE_K))) {
     const size_t img_bytes = align1k(head_fwd_tc_workspace(s));
     const void *hi, *lo;
     if (desc->flags & SPS_FLAG_ZRELAYED) {
@@ -188,6 +205,25 @@ int sps_head_bwd(const SpsHeadDesc* desc, const void* z, const float* protos, co
   // tcgen05 backward; a gradient through the activation map (dact), no dlogits, or SPS_MATH_FP32: exact-operand
   // CUDA-core kernels
   const bool tc_ok = head_bwd_tc_supported(s, desc->math, last_w, dlogits, ddist, dact);
+  if (s.K > WIDE_K && head_bwd_wide_supported(s, desc->math, last_w, dlogits, ddist, dact)) {
+    // more than 32 classes: one pass over the distances (tile-stationary dz kernel + chunk-stationary dp / dW kernel), TMA-fed
+    if (z16)
+      return launch_head_bwd_wide(s, desc->math, z, true, protos, last_w, dlogits, dz, dprotos, dlast_w, workspace, workspace_bytes, st);
+    const size_t base_bytes = align1k(head_bwd_wide_workspace(s));
+    const void *hi, *lo;
+    if (desc->flags & SPS_FLAG_ZRELAYED) {
+      z_pack_parts(s, desc->math, z, &hi, &lo);      // the hi part of any re-lay is the map rounded to one 16-bit term
+    } else {
+      const int m1 = single_term(desc->math);
+      SPS_REQUIRE(workspace != nullptr && workspace_bytes >= base_bytes + z_pack_bytes(s, m1), SPS_ERR_WORKSPACE,
+                  "head_bwd workspace: need %zu bytes, got %zu", base_bytes + z_pack_bytes(s, m1), workspace_bytes);
+      void* area = reinterpret_cast<unsigned char*>(workspace) + base_bytes;
+      rc = launch_z_pack(s, m1, reinterpret_cast<const float*>(z), area, st);
+      if (rc != SPS_OK) return rc;
+      z_pack_parts(s, m1, area, &hi, &lo);
+    }
+    return launch_head_bwd_wide(s, desc->math, hi, false, protos, last_w, dlogits, dz, dprotos, dlast_w, workspace, base_bytes, st);
+  }
   if (z16) {
     SPS_REQUIRE(tc_ok, SPS_ERR_UNSUPPORTED,
                 "16-bit channels-last backward needs last_w + dlogits (no gradient through the activation map) and K <= 256");

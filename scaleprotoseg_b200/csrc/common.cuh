@@ -118,6 +118,12 @@ size_t head_bwd_tc_workspace(const HeadShape& s);
 int launch_head_bwd_tc(const HeadShape& s, int math, int zmode, const void* z, const void* z_lo, const float* protos,
                        const float* last_w, const float* dlogits, const float* ddist, void* dz, float* dprotos,
                        float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st);
+// one-pass tcgen05 backward for more than 32 classes (tile-stationary dz kernel + chunk-stationary dp / dW kernel)
+bool head_bwd_wide_supported(const HeadShape& s, int math, const float* last_w, const float* dlogits, const float* ddist,
+                             const float* dact);
+size_t head_bwd_wide_workspace(const HeadShape& s);
+int launch_head_bwd_wide(const HeadShape& s, int math, const void* z16, bool dz16, const float* protos, const float* last_w,
+                         const float* dlogits, void* dz, float* dprotos, float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st);
 int launch_head_bwd_simt(const HeadShape& s, int flags, const float* z, const float* protos, const float* last_w,
                          const float* dlogits, const float* ddist, const float* dact, float* dz, float* dprotos,
                          float* dlast_w, void* ws, size_t ws_bytes, cudaStream_t st);

@@ -725,6 +725,17 @@ static int bwd_nsplit(const tcb::GroupTable& gt) {
   return m;
 }
 
+// plain launch of the fixed-order reduction of per-CTA partials (also used by head_bwd_wide.cu)
+int launch_bwd_reduce(const float* part_dp, long long c1, float* dprotos, const float* part_dw, long long c2, float* dlast_w, int nsplit,
+                      const float* part_cs, const float* protos, int D, int P, cudaStream_t st) {
+  if (c1 + c2 <= 0) return SPS_OK;
+  tcb::bwd_reduce_kernel<<<(unsigned)((c1 + c2 + 255) / 256), 256, 0, st>>>(part_dp, c1, dprotos, part_dw, c2, dlast_w, nsplit, part_cs,
+                                                                           protos, D, P, 0);
+  count_launch();
+  SPS_CUDA_TRY(cudaGetLastError());
+  return SPS_OK;
+}
+
 bool head_bwd_tc_supported(const HeadShape& s, int math, const float* last_w, const float* dlogits, const float* ddist,
                            const float* dact) {
   if (!(math != SPS_MATH_FP32 && last_w != nullptr && dlogits != nullptr && dact == nullptr && s.K <= 8 * tcb::KP_BWD &&
@@ -789,12 +800,14 @@ static int launch_bwd_slab(const HeadShape& s, int zmode, const void* z, const v
   bool any_multi = false;
   for (int g = 0; g < prm.gt.n_groups; ++g) any_multi |= prm.gt.multi[g] != 0;
   const bool dz_atomic = any_multi || several_slabs;
-  SPS_REQUIRE(!(zmode == tcb::ZM_TMA16 && dz_atomic && dz != nullptr), SPS_ERR_UNSUPPORTED,
+  SPS_REQUIRE(!(zmode == tc::ZM_TMA16 && dz_atomic && dz != nullptr), SPS_ERR_UNSUPPORTED,
               "16-bit channels-last backward: a scale with more than %d prototypes or more than %d classes needs dz accumulation, "
               "which the 16-bit dz layout does not support (P=%d, K=%d)", tcb::GROUP_CHUNKS * tc::CN, tcb::KP_BWD, s.P, s.K);
-  if (dz != nullptr && first_slab && dz_atomic)
-    SPS_CUDA_TRY(cudaMemsetAsync(dz, 0, sizeof(float) * (size_t)s.B * s.C * s.HW, st));
-  if (zmode != tcb::ZM_LDG) {
+  bool empty_scale = false;   // a scale without prototypes has no chunk group: its block of dz is zero
+  for (int sc = 0; sc < s.S; ++sc) empty_scale |= s.scale_lo[sc + 1] == s.scale_lo[sc];
+  if (dz != nullptr && first_slab && (dz_atomic || empty_scale))
+    SPS_CUDA_TRY(cudaMemsetAsync(dz, 0, (zmode == tc::ZM_TMA16 ? 2 : 4) * (size_t)s.B * s.C * s.HW, st));
+  if (zmode != tc::ZM_LDG) {
     const bool bf = std::is_same<X, __nv_bfloat16>::value;
     rc = make_tmap_2d_16bit(&prm.tm_hi, z, bf, s.N, s.C, tc::TILE_M, 64, 128);
     if (rc != SPS_OK) return rc;
@@ -830,13 +843,13 @@ static int launch_bwd_slab(const HeadShape& s, int zmode, const void* z, const v
     SPS_CUDA_TRY(launch_pdl(tcb::head_bwd_tc_kernel<X, NSPLIT, DD, ZM>, dim3(grid), dim3(tcb::NTHREADS), (size_t)SMEM, st, prm));      \
   } while (0)
   if (ddist != nullptr) {
-    if (zmode == tcb::ZM_LDG) SPS_BWD_LAUNCH(true, tcb::ZM_LDG);
-    else if (zmode == tcb::ZM_TMA16) SPS_BWD_LAUNCH(true, tcb::ZM_TMA16);
-    else SPS_BWD_LAUNCH(true, tcb::ZM_TMAHL);
+    if (zmode == tc::ZM_LDG) SPS_BWD_LAUNCH(true, tc::ZM_LDG);
+    else if (zmode == tc::ZM_TMA16) SPS_BWD_LAUNCH(true, tc::ZM_TMA16);
+    else SPS_BWD_LAUNCH(true, tc::ZM_TMAHL);
   } else {
-    if (zmode == tcb::ZM_LDG) SPS_BWD_LAUNCH(false, tcb::ZM_LDG);
-    else if (zmode == tcb::ZM_TMA16) SPS_BWD_LAUNCH(false, tcb::ZM_TMA16);
-    else SPS_BWD_LAUNCH(false, tcb::ZM_TMAHL);
+    if (zmode == tc::ZM_LDG) SPS_BWD_LAUNCH(false, tc::ZM_LDG);
+    else if (zmode == tc::ZM_TMA16) SPS_BWD_LAUNCH(false, tc::ZM_TMA16);
+    else SPS_BWD_LAUNCH(false, tc::ZM_TMAHL);
   }
 #undef SPS_BWD_LAUNCH
   count_launch();
@@ -871,12 +884,12 @@ static int launch_bwd_tc_t(const HeadShape& s, int zmode, const void* z, const v
   return SPS_OK;
 }
 
-// zmode: tcb::ZM_LDG (z = fp32 NCHW map), ZM_TMA16 (z = 16-bit channels-last map, dz likewise), ZM_TMAHL (z / z_lo = hi / lo
+// zmode: tc::ZM_LDG (z = fp32 NCHW map), ZM_TMA16 (z = 16-bit channels-last map, dz likewise), ZM_TMAHL (z / z_lo = hi / lo
 // re-lay of an fp32 map, dz fp32 NCHW)
 int launch_head_bwd_tc(const HeadShape& s, int math, int zmode, const void* z, const void* z_lo, const float* protos,
                        const float* last_w, const float* dlogits, const float* ddist, void* dz, float* dprotos, float* dlast_w,
                        void* ws, size_t ws_bytes, cudaStream_t st) {
-  SPS_REQUIRE(zmode == tcb::ZM_LDG || s.D == 64, SPS_ERR_UNSUPPORTED, "TMA-fed backward: D=%d, only 64 channels per scale", s.D);
+  SPS_REQUIRE(zmode == tc::ZM_LDG || s.D == 64, SPS_ERR_UNSUPPORTED, "TMA-fed backward: D=%d, only 64 channels per scale", s.D);
   // the split modes recompute the distances with the 3-term product (a' = da/dd is as sensitive to d as a is);
   // the gradient GEMMs themselves run single-term 16-bit operands with fp32 accumulation
   switch (math) {

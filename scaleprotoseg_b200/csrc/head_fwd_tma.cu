@@ -52,15 +52,17 @@ struct Plan {
   __host__ __device__ int b_off(int i) const { return b0 + i * b_stride; }
   __host__ __device__ int w_off(int i) const { return w0 + i * w_stride; }
 };
-template <int NSPLIT, bool ZLO, int NSETS> __host__ __device__ inline Plan make_plan(int kp, int scratch_warps) {
+// LSPLIT: terms of the activation / last-layer operands of the logits GEMM (3 = hi + lo as the distance products, 1 = one
+// 16-bit term: wide last layers, whose hi + lo tiles do not fit shared memory; logits then carry ~5e-4 of sum |a W|)
+template <int NSPLIT, bool ZLO, int NSETS, int LSPLIT> __host__ __device__ inline Plan make_plan(int kp, int scratch_warps) {
   Plan pl;
   pl.a_stride = a_stage_bytes<ZLO>();
   pl.na = a_stages<ZLO>();
   pl.p0 = pl.na * pl.a_stride;
-  pl.p_stride = (NSPLIT == 3 ? 2 : 1) * P_BYTES;
+  pl.p_stride = (LSPLIT == 3 ? 2 : 1) * P_BYTES;
   pl.b0 = pl.p0 + NSETS * pl.p_stride;
   pl.b_stride = ((NSPLIT == 3 ? 2 : 1) * CN * 128 + CN * 32 + 1023) / 1024 * 1024;
-  pl.w_stride = ((NSPLIT == 3 ? 2 : 1) * kp * 128 + 1023) / 1024 * 1024;
+  pl.w_stride = ((LSPLIT == 3 ? 2 : 1) * kp * 128 + 1023) / 1024 * 1024;
   const int w_total = kp > 0 ? NSTW * pl.w_stride : 0;
   const int scr_total = scratch_warps * ACT_SCRATCH;
   int nst = (227 * 1024 - 512 - 1024 - pl.b0 - w_total - scr_total) / pl.b_stride;
@@ -78,7 +80,7 @@ enum { BAR_TFULL = 0, BAR_AFULL = 4, BAR_AEMPTY = 8, BAR_BFULL = 12, BAR_BEMPTY 
 
 __host__ __device__ constexpr int n_threads(int nsets) { return (4 * nsets + 4) * 32; }
 
-template <typename X, int NSPLIT, bool ZLO, bool DENSE, int NSETS>
+template <typename X, int NSPLIT, bool ZLO, bool DENSE, int NSETS, int LSPLIT>
 __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const __grid_constant__ FwdTmaParams prm) {
   constexpr int NEPI = 4 * NSETS;
   constexpr int TMEM_L0 = NSETS * CN;
@@ -89,7 +91,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
   const ChunkTable& ct = prm.ct;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   unsigned char* gbase = smem_raw + (base - smem_u32(smem_raw));
-  const Plan pl = make_plan<NSPLIT, ZLO, NSETS>(ct.kp, prm.act != nullptr ? NEPI : 0);
+  const Plan pl = make_plan<NSPLIT, ZLO, NSETS, LSPLIT>(ct.kp, prm.act != nullptr ? NEPI : 0);
   const uint32_t bar0 = base + pl.bar_off;
   auto bar = [&](int i) { return bar0 + 8u * (uint32_t)i; };
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + pl.bar_off + 8 * BAR_COUNT);
@@ -192,7 +194,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
 #pragma unroll
           for (int k = 0; k < 4; ++k)
             mma_f16(d, desc_sw128(pa + 32 * k), desc_sw128(w2 + 32 * k), ID2, (c > 0 || k > 0) ? 1 : 0);
-          if (NSPLIT == 3) {
+          if (LSPLIT == 3) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pa + 32 * k), desc_sw128(w2 + KP * 128 + 32 * k), ID2, 1);
 #pragma unroll
@@ -210,7 +212,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
     // ================================ prototype-chunk producer ================================
     pdl_wait();  // the packed prototype images come from the pre-pass launched just before this kernel
     const int U = my_tiles * NC;
-    const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128, bytes_n = CN * 32, bytes_w = (NSPLIT == 3 ? 2 : 1) * KP * 128;
+    const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128, bytes_n = CN * 32, bytes_w = (LSPLIT == 3 ? 2 : 1) * KP * 128;
     auto fetch_b = [&](int i) {
       const int c = i % NC, st = i % NST;
       mbar_wait(bar(BAR_BEMPTY + st), ((i / NST) & 1) ^ 1);
@@ -398,14 +400,14 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
             for (int e = 0; e < 4; ++e) {
               const float x0 = av[g * 8 + 2 * e], x1 = av[g * 8 + 2 * e + 1];
               w[e] = Pack2<X>::pack(x0, x1);
-              if (NSPLIT == 3) {
+              if (LSPLIT == 3) {
                 const float2 h = Pack2<X>::unpack(w[e]);
                 wl[e] = Pack2<X>::pack(x0 - h.x, x1 - h.y);
               }
             }
             const uint32_t poff = (((uint32_t)(hf * 4 + g)) ^ ((uint32_t)m & 7u)) << 4;
             *reinterpret_cast<uint4*>(prow + poff) = make_uint4(w[0], w[1], w[2], w[3]);
-            if (NSPLIT == 3) *reinterpret_cast<uint4*>(prow + P_BYTES + poff) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
+            if (LSPLIT == 3) *reinterpret_cast<uint4*>(prow + P_BYTES + poff) = make_uint4(wl[0], wl[1], wl[2], wl[3]);
           }
         }
       }
@@ -571,10 +573,37 @@ int launch_z_pack(const HeadShape& s, int math, const float* z, void* out, cudaS
 }
 
 // three epilogue sets when the outputs are only the logits and the third distance accumulator / activation tile fit
-template <int NSPLIT, bool ZLO> static bool three_sets_fit(int kp, bool dense) {
+template <int NSPLIT, bool ZLO, int LSPLIT> static bool three_sets_fit(int kp, bool dense) {
   if (dense || 3 * tc::CN + 2 * kp > 512) return false;
-  const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 3>(kp, 0);
+  const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 3, LSPLIT>(kp, 0);
   return pl.nst >= 2 && pl.total <= 227 * 1024;
+}
+template <int NSPLIT, bool ZLO, int LSPLIT> static bool two_sets_fit(int kp, bool dense_act) {
+  const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 2, LSPLIT>(kp, dense_act ? 8 : 0);
+  return pl.nst >= 2 && pl.total <= 227 * 1024 && 2 * tc::CN + 2 * kp <= 512;
+}
+
+template <typename X, int NSPLIT, bool ZLO, int LSPLIT>
+static int launch_fwd_tma_l(const HeadShape& s, const tc::ChunkTable& ct, tf::FwdTmaParams& prm, bool dense, bool dense_act, cudaStream_t st) {
+  const int grid = prm.n_tiles < sm_count() ? prm.n_tiles : sm_count();
+  if (three_sets_fit<NSPLIT, ZLO, LSPLIT>(ct.kp, dense)) {
+    const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 3, LSPLIT>(ct.kp, 0);
+    SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 3, LSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+    SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 3, LSPLIT>, dim3(grid), dim3(tf::n_threads(3)), (size_t)pl.total, st, prm));
+  } else {
+    const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 2, LSPLIT>(ct.kp, dense_act ? 8 : 0);
+    SPS_REQUIRE(pl.nst >= 2 && pl.total <= 227 * 1024, SPS_ERR_UNSUPPORTED,
+                "TMA-fed head: %d bytes of shared memory needed (K=%d)", pl.total, s.K);
+    if (dense) {
+      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, true, 2, LSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+      SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, true, 2, LSPLIT>, dim3(grid), dim3(tf::n_threads(2)), (size_t)pl.total, st, prm));
+    } else {
+      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 2, LSPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+      SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 2, LSPLIT>, dim3(grid), dim3(tf::n_threads(2)), (size_t)pl.total, st, prm));
+    }
+  }
+  count_launch();
+  return SPS_OK;
 }
 
 template <typename X, int NSPLIT, bool ZLO>
@@ -597,25 +626,10 @@ static int launch_fwd_tma_t(const HeadShape& s, const tc::ChunkTable& ct, const 
   prm.act = act;
   prm.n_tiles = (int)((s.N + tc::TILE_M - 1) / tc::TILE_M);
   const bool dense = dist != nullptr || act != nullptr;
-  const int grid = prm.n_tiles < sm_count() ? prm.n_tiles : sm_count();
-  if (three_sets_fit<NSPLIT, ZLO>(ct.kp, dense)) {
-    const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 3>(ct.kp, 0);
-    SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 3>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
-    SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 3>, dim3(grid), dim3(tf::n_threads(3)), (size_t)pl.total, st, prm));
-  } else {
-    const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 2>(ct.kp, act != nullptr ? 8 : 0);
-    SPS_REQUIRE(pl.nst >= 2 && pl.total <= 227 * 1024, SPS_ERR_UNSUPPORTED,
-                "TMA-fed head: %d bytes of shared memory needed (K=%d)", pl.total, s.K);
-    if (dense) {
-      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, true, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
-      SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, true, 2>, dim3(grid), dim3(tf::n_threads(2)), (size_t)pl.total, st, prm));
-    } else {
-      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
-      SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 2>, dim3(grid), dim3(tf::n_threads(2)), (size_t)pl.total, st, prm));
-    }
-  }
-  count_launch();
-  return SPS_OK;
+  // a wide last layer whose hi + lo tiles do not fit keeps the 3-term distances and runs the logits GEMM on one term
+  if (NSPLIT == 3 && !two_sets_fit<NSPLIT, ZLO, NSPLIT>(ct.kp, act != nullptr))
+    return launch_fwd_tma_l<X, NSPLIT, ZLO, 1>(s, ct, prm, dense, act != nullptr, st);
+  return launch_fwd_tma_l<X, NSPLIT, ZLO, NSPLIT>(s, ct, prm, dense, act != nullptr, st);
 }
 
 // Shapes the TMA-fed forward covers.  zlo: the map has a lo part (fp32 source re-laid by z_pack_kernel in a split mode).
@@ -625,10 +639,9 @@ bool head_fwd_tma_supported(const HeadShape& s, int math, bool with_last_layer, 
   for (int sc = 0; sc < s.S; ++sc) nc += (s.scale_lo[sc + 1] - s.scale_lo[sc] + tc::CN - 1) / tc::CN;
   if (nc > tc::MAX_CHUNKS) return false;
   const int kp = with_last_layer ? (s.K + 15) / 16 * 16 : 0;
-  const int scr = dense_act ? 8 : 0;
-  const bool split = math_is_split(math);
-  const tf::Plan pl = split ? (zlo ? tf::make_plan<3, true, 2>(kp, scr) : tf::make_plan<3, false, 2>(kp, scr)) : tf::make_plan<1, false, 2>(kp, scr);
-  return pl.nst >= 2 && pl.total <= 227 * 1024;
+  if (!math_is_split(math)) return two_sets_fit<1, false, 1>(kp, dense_act);
+  if (zlo) return two_sets_fit<3, true, 3>(kp, dense_act) || two_sets_fit<3, true, 1>(kp, dense_act);
+  return two_sets_fit<3, false, 3>(kp, dense_act) || two_sets_fit<3, false, 1>(kp, dense_act);
 }
 
 // z_hi / z_lo: 16-bit [N][C] arrays (z_lo may be null: the map is exactly 16 bit).  img: 1 KB aligned workspace for the

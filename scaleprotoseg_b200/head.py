@@ -123,8 +123,9 @@ def wants_relay(z: torch.Tensor, cfg: HeadConfig) -> bool:
     """fp32 NCHW map + FLAG_ZPACK + tensor-core math + D = 64: the map is re-laid ONCE per step (sps_z_relay) as 16-bit
     channels-last hi / lo arrays and both the forward and the backward run their TMA-fed kernels on it."""
     S = len(cfg.scale_lo) - 1
-    return (z.dtype == torch.float32 and bool(cfg.flags & FLAG_ZPACK) and cfg.math != MATH_FP32 and z.shape[1] == 64 * S
-            and z.numel() > 0)
+    # asked for, or a wide last layer (more than 32 classes: forward and backward both run TMA-fed kernels)
+    asked = bool(cfg.flags & FLAG_ZPACK) or cfg.num_classes > 32
+    return (z.dtype == torch.float32 and asked and cfg.math != MATH_FP32 and z.shape[1] == 64 * S and z.numel() > 0)
 
 
 def z_relay(z: torch.Tensor, protos: torch.Tensor, cfg: HeadConfig) -> torch.Tensor:

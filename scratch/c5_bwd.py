@@ -1,0 +1,18 @@
+import sys, os
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import torch
+import scaleprotoseg_b200 as sps
+from oracle import head_oracle as ho
+dev = "cuda:0"
+B, H, W, P, K = 32, 65, 65, 6840, 171
+g = torch.Generator(device=dev).manual_seed(1)
+z = torch.sigmoid(torch.randn(B, 256, H, W, device=dev, generator=g)).half().contiguous(memory_format=torch.channels_last)
+protos = torch.rand(P, 64, device=dev, generator=g)
+W_ = ho.make_last_layer(ho.make_identity(P, K, 4)).contiguous().to(dev)
+dl = torch.randn(B * H * W, K, device=dev, generator=g) / (B * H * W)
+cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, 4), K, math=sps.MATH_F16)
+for _ in range(2):
+    sps.head_forward_raw(z, protos, W_, cfg, False, False)
+    sps.head_backward_raw(z, protos, W_, cfg, dl, None, None, True, True, True)
+torch.cuda.synchronize()
+print("ok")
