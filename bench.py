@@ -34,7 +34,8 @@ import torch  # noqa: E402
 SEED = 20220227
 C2 = dict(B=16, H=65, W=65, S=4, D=64, P=760, K=19)       # BASELINE.json configs[1]
 PUSH = dict(n_maps=3000, H=129, W=257, P=760, K=19)         # configs[3], the reference's full-res push map
-CPU_SAMPLE_B = 1                                            # maps per CPU step (bounded sample)
+PUSH_COCO = dict(n_maps=512, H=65, W=65, P=6840, K=171)     # configs[4]'s push: COCO-Stuff head on 65x65 maps (bounded sample)
+CPU_SAMPLE_B = 16                                           # maps per CPU step: the whole C2 batch (~0.3 s per step)
 
 
 def parse_args():
@@ -197,6 +198,90 @@ def run_ours(args):
                 value=value, launches=launches, t_fwd=t_fwd, t_bwd=t_bwd, sampler=sampler, barrier=barrier)
 
 
+def measure_nhwc16(ctx, args):
+    """Second feature-map source (SpsHeadDesc.z_dtype / z_layout): the same C2 step on 16-bit channels-last maps, fed to
+    the tensor cores by TMA (cp.async.bulk.tensor, no conversion work on the SM).  Algorithmic bytes halve (z read, dz
+    written in 16 bit), flops stay."""
+    sps, c, dev, pk = ctx["sps"], C2, ctx["dev"], peaks()
+    n = c["B"] * c["H"] * c["W"]
+    out = {"workload": "C2 shape, fp16 / bf16 channels-last feature maps (TMA-fed kernels), fused mode, dz returned in the same layout"}
+    for name, dt, math in (("fp16 maps, f16x3", torch.float16, MATH["f16x3"]), ("fp16 maps, f16", torch.float16, MATH["f16"]),
+                           ("bf16 maps, bf16", torch.bfloat16, MATH["bf16"])):
+        zs = [z.to(dt).contiguous(memory_format=torch.channels_last) for z in ctx["zs"]]
+        cfg = sps.HeadConfig.from_ranges(ctx["ho"].uniform_ranges(c["P"], c["S"]), c["K"], math=math)
+        fwd = lambda i: sps.head_forward_raw(zs[i % N_SETS], ctx["p2"], ctx["last_w"], cfg, False, False)           # noqa: E731
+        bwd = lambda i: sps.head_backward_raw(zs[i % N_SETS], ctx["p2"], ctx["last_w"], cfg, ctx["dls"][i % N_SETS], None, None, True, True, True)  # noqa: E731
+        for i in range(3):
+            fwd(i), bwd(i)
+        it = max(5, min(args.steps, 100))
+        tf, tb = event_ms(fwd, it), event_ms(bwd, it)
+        bytes_b = n * (2 * c["S"] * c["D"] * 2 + 4 * c["K"])
+        flops_b = ctx["units"] * (4 * c["D"] + 4 * c["K"])
+        out[name] = {"fwd_ms": tf, "bwd_ms": tb, "step_ms": tf + tb, "value": ctx["units"] / ((tf + tb) * 1e-3),
+                     "bwd_hbm_frac": bytes_b / (tb * 1e-3) / 1e9 / pk["hbm"], "bwd_tensor_frac": flops_b / (tb * 1e-3) / 1e12 / pk["tensor_sustained"],
+                     "step_tensor_frac": ctx["units"] * (6 * c["D"] + 6 * c["K"]) / ((tf + tb) * 1e-3) / 1e12 / pk["tensor_sustained"]}
+    return out
+
+
+def measure_h2d_probe(ctx, args):
+    """Copy-only probe behind the e2e number: the same bytes per step (z + dlogits from pinned host memory, no kernels).
+    At N = 8 every GPU of the box hangs off the same host memory / PCIe fabric, which is what flattens the e2e curve."""
+    dev, c = ctx["dev"], C2
+    zh, dh = ctx["zs"][0].cpu().pin_memory(), ctx["dls"][0].cpu().pin_memory()
+    zd, dd = torch.empty_like(ctx["zs"][0]), torch.empty_like(ctx["dls"][0])
+
+    def cp(i):
+        zd.copy_(zh, non_blocking=True)
+        dd.copy_(dh, non_blocking=True)
+
+    for i in range(3):
+        cp(i)
+    ctx["barrier"]()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    it = max(5, min(args.steps, 50))
+    for i in range(it):
+        cp(i)
+    e1.record()
+    ctx["barrier"]()
+    ms = torch.tensor([e0.elapsed_time(e1) / it], device=dev)
+    if ctx["world"] > 1:
+        ctx["dist"].all_reduce(ms, op=ctx["dist"].ReduceOp.MAX)
+    nbytes = zh.numel() * 4 + dh.numel() * 4
+    return {"ms_per_step": ms.item(), "h2d_gbs_per_gpu": nbytes / (ms.item() * 1e-3) / 1e9, "h2d_gbs_all_gpus": ctx["world"] * nbytes / (ms.item() * 1e-3) / 1e9,
+            "note": "pure pinned-host -> device copies of one step's inputs on every rank at once (max over ranks)"}
+
+
+def measure_c1(args):
+    """BASELINE.json configs[0] (C1): whole-model CPU forward on one 1x3x513x513 image, backbone vs prototype head.  The
+    reference's DeepLabv2-ResNet101 is not on the GPU box, so the backbone here is torchvision's deeplabv3_resnet101 body
+    (random init, output stride 8: the same ResNet-101 + ASPP cost class) and the head is the oracle port at 65x65;
+    profiles/r02_c1_reference_cpu.json holds the same split measured with the UNMODIFIED reference in the build container."""
+    from oracle import head_oracle as ho
+    import torchvision
+    torch.set_num_threads(os.cpu_count() or 1)
+    net = torchvision.models.segmentation.deeplabv3_resnet101(weights=None, weights_backbone=None, num_classes=256,
+                                                              aux_loss=None).eval()
+    x = torch.randn(1, 3, 513, 513)
+    c = C2
+    protos = torch.rand(c["P"], c["D"], 1, 1)
+    w = ho.make_last_layer(ho.make_identity(c["P"], c["K"], c["S"]))
+    ranges = ho.uniform_ranges(c["P"], c["S"])
+    with torch.no_grad():
+        net.classifier(net.backbone(x)["out"])          # warm-up (thread pool, allocator)
+        t0 = time.perf_counter()
+        f = net.classifier(net.backbone(x)["out"])
+        t1 = time.perf_counter()
+        z = torch.sigmoid(torch.nn.functional.interpolate(f, size=(c["H"], c["W"]), mode="bilinear", align_corners=False))
+        t2 = time.perf_counter()
+        ho.head_stage1(z, protos, ranges, w)
+        t3 = time.perf_counter()
+    return {"workload": "C1: whole-model CPU forward, 1x3x513x513, random init; backbone = torchvision deeplabv3_resnet101 stand-in, head = oracle port (P=760, K=19, 65x65)",
+            "cores": os.cpu_count(), "backbone_ms": (t1 - t0) * 1e3, "head_ms": (t3 - t2) * 1e3,
+            "head_share": (t3 - t2) / max((t1 - t0) + (t3 - t2), 1e-9), "single_run": True,
+            "reference_run": "profiles/r02_c1_reference_cpu.json (unmodified reference, build container)"}
+
+
 def measure_e2e(ctx, args):
     """fwd+bwd through the public autograd API with HOST buffers: every step uploads its batch (z, dlogits) from pinned
     host memory and downloads logits + parameter gradients.  The upload of step i+1 runs on a copy stream while step i
@@ -265,48 +350,82 @@ def measure_e2e(ctx, args):
             "note": "public autograd API, pinned host buffers; upload of batch i+1 overlaps compute of batch i"}
 
 
-def measure_push(ctx, args):
-    """Push scan (configs[3]): n_maps Cityscapes-shaped maps sharded over the ranks, one min all-reduce of packed keys."""
+def measure_push(ctx, args, shape=None, zdtype=None):
+    """Push projection (configs[3]): n_maps Cityscapes-shaped maps sharded over the ranks.  The timed region is the WHOLE
+    projection: scan of the shard, dataset arg-min, min all-reduce of the packed keys, gather of the winners on their owner
+    ranks and the sum all-reduce that hands the (P, D) block to everybody.  Per-phase device times from CUDA events."""
     sps, spush, ho, dev, world, rank = ctx["sps"], ctx["spush"], ctx["ho"], ctx["dev"], ctx["world"], ctx["rank"]
-    p = PUSH
-    per_rank = (args.push_maps + world - 1) // world
+    p = dict(PUSH if shape is None else shape)
+    n_maps = args.push_maps if shape is None else p["n_maps"]
+    per_rank = (n_maps + world - 1) // world
     lo = rank * per_rank
-    n_local = max(0, min(args.push_maps, lo + per_rank) - lo)
+    n_local = max(0, min(n_maps, lo + per_rank) - lo)
     pool = min(n_local, 64)            # distinct resident maps (64 x 34 MB = 2.2 GB >> L2), cycled to cover the shard
     g = torch.Generator(device=dev).manual_seed(SEED + 17 * rank)
     z = torch.sigmoid(torch.randn(pool, 256, p["H"], p["W"], device=dev, generator=g))
+    if zdtype is not None:
+        z = z.to(zdtype).contiguous(memory_format=torch.channels_last)
     labels = torch.stack([ho.make_labels(lo + i, p["H"], p["W"], p["K"], absent_class=3) for i in range(pool)]).to(torch.int16).to(dev)
-    cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(p["P"], 4), p["K"], math=ctx["cfg"].math if PUSH_TC(sps) else sps.MATH_FP32)
-    pc = spush.proto_class_of(ctx["ident"]).to(dev)
+    math = ctx["cfg"].math if PUSH_TC(sps) else sps.MATH_FP32
+    cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(p["P"], 4), p["K"], math=math)
+    ident = ho.make_identity(p["P"], p["K"], 4)
+    protos = torch.rand(p["P"], 64, device=dev, generator=g)
+    pc = spush.proto_class_of(ident).to(dev)
+    ps = spush.proto_scale_reference(p["P"], 4).to(dev)
     keys = torch.empty(n_local, p["P"], device=dev, dtype=torch.int64)
     batch = 16
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
 
-    def scan_all():
+    def project(timed):
+        if timed:
+            ev[0].record()
         for i in range(0, n_local, batch):
             b = min(batch, n_local - i)
             j = i % pool
             if j + b > pool:
                 j = 0
-            spush.scan_maps(z[j:j + b], labels[j:j + b], ctx["protos"], pc, cfg, keys_out=keys[i:i + b])
+            spush.scan_maps(z[j:j + b], labels[j:j + b], protos, pc, cfg, keys_out=keys[i:i + b])
+        if timed:
+            ev[1].record()
         best = spush.reduce_keys(keys, lo)
+        if timed:
+            ev[2].record()
         if world > 1:
             ctx["dist"].all_reduce(best, op=ctx["dist"].ReduceOp.MIN)
-        return best
+        if timed:
+            ev[3].record()
+        # winners' vectors from the rank that owns the winning map (the resident pool stands for the shard: map m sits in
+        # slot m % pool; which vector is copied is the tests' business, the cost of the gather is what is timed here)
+        out = torch.zeros(p["P"], 64, device=dev)
+        local = (best & 0xFFFFFFFF) - lo
+        mine = (local >= 0) & (local < n_local)
+        slot_best = torch.where(mine, (best & ~0xFFFFFFFF) | (local % max(pool, 1)), torch.full_like(best, 0xFFFFFFF))
+        if pool > 0:
+            spush.gather_winners(z, keys[:pool], slot_best, 0, ps, cfg, out=out)
+        if timed:
+            ev[4].record()
+        if world > 1:
+            ctx["dist"].all_reduce(out, op=ctx["dist"].ReduceOp.SUM)
+        if timed:
+            ev[5].record()
+        return best, out
 
-    scan_all()
+    project(False)
     ctx["barrier"]()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    e0.record()
-    scan_all()
-    e1.record()
+    project(True)
     ctx["barrier"]()
-    ms = torch.tensor([e0.elapsed_time(e1)], device=dev)
+    ph = [ev[i].elapsed_time(ev[i + 1]) for i in range(5)]
+    ms = torch.tensor([ev[0].elapsed_time(ev[5])] + ph, device=dev)
     if world > 1:
         ctx["dist"].all_reduce(ms, op=ctx["dist"].ReduceOp.MAX)
-    patches = args.push_maps * p["H"] * p["W"]
-    return {"value": patches / (ms.item() * 1e-3), "unit": "patches/s", "ms": ms.item(), "scaling": "strong",
-            "workload": f"{args.push_maps} maps 256x{p['H']}x{p['W']} fp32, P={p['P']}, sharded {world}-way, "
-                        f"{pool} distinct resident maps per rank cycled, one NCCL min all-reduce of {p['P']} packed keys",
+    ms = ms.tolist()
+    patches = n_maps * p["H"] * p["W"]
+    bytes_per_patch = 256 * (2 if zdtype is not None else 4) + 2
+    return {"value": patches / (ms[0] * 1e-3), "unit": "patches/s", "ms": ms[0], "scaling": "strong",
+            "phases_ms": {"scan": ms[1], "dataset_argmin": ms[2], "allreduce_min_keys": ms[3], "gather_winners": ms[4], "allreduce_sum_winners": ms[5]},
+            "scan_hbm_frac_per_gpu": (patches / world) * bytes_per_patch / (ms[1] * 1e-3) / 1e9 / peaks()["hbm"],
+            "workload": f"{n_maps} maps 256x{p['H']}x{p['W']} {'fp32 NCHW' if zdtype is None else str(zdtype).replace('torch.', '') + ' NHWC'}, "
+                        f"P={p['P']}, K={p['K']}, sharded {world}-way, {pool} resident maps per rank cycled; whole projection timed",
             "math": "fp32" if cfg.math == 0 else args.math}
 
 
@@ -468,40 +587,46 @@ def measure_eval_topk(ctx, args):
 
 
 def measure_c5(ctx, args):
-    """Secondary: the COCO-Stuff head shape of BASELINE.json configs[4] (K=171, P=6840, B=32, 65x65), fused forward
-    (the headline of this object, tensor-bound) and the backward (class slabs)."""
-    sps, ho, dev = ctx["sps"], ctx["ho"], ctx["dev"]
+    """Secondary: the COCO-Stuff head shape of BASELINE.json configs[4] (K=171, P=6840, B=32, 65x65) per GPU, fused
+    forward + backward in the package's default math (3-term distances; the wide last layer runs the logits GEMM on one
+    16-bit term and the one-pass wide backward, see head_bwd_wide.cu).  At N > 1 every rank runs a replica."""
+    sps, ho, dev, world = ctx["sps"], ctx["ho"], ctx["dev"], ctx["world"]
     B, H, W, P, K, S, D = 32, 65, 65, 6840, 171, 4, 64
-    g = torch.Generator(device=dev).manual_seed(SEED + 5)
+    g = torch.Generator(device=dev).manual_seed(SEED + 5 + ctx["rank"])
     z = torch.sigmoid(torch.randn(B, S * D, H, W, device=dev, generator=g))
     protos = torch.rand(P, D, device=dev, generator=g)
     last_w = ho.make_last_layer(ho.make_identity(P, K, S)).contiguous().to(dev)
-    # 3-term products need hi + lo last-layer tiles that do not fit shared memory at K=171 (the library would route to
-    # the fp32 kernels), so this shape is timed with single fp16 products: logits within 1e-3 of fp32 (tests)
-    math_name = {"f16x3": "f16", "bf16x3": "bf16"}.get(args.math, args.math)
-    cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, S), K, math=MATH[math_name])
-    iters = max(3, min(args.steps, 20))
-    ms = event_ms(lambda i: sps.head_forward_raw(z, protos, last_w, cfg, False, False), iters)   # 138 MB of z per pass > L2
+    dl = torch.randn(B * H * W, K, device=dev, generator=g) / (B * H * W)
+    cfg = sps.HeadConfig.from_ranges(ho.uniform_ranges(P, S), K, math=MATH[args.math])
+    r0 = int(ctx["lib"].sps_fp32_reroute_count())
+    fwd = lambda i: sps.head_forward_raw(z, protos, last_w, cfg, False, False)                       # noqa: E731  (138 MB of z per pass > L2)
+    bwd = lambda i: sps.head_backward_raw(z, protos, last_w, cfg, dl, None, None, True, True, True)  # noqa: E731
+    fwd(0), bwd(0)
+    iters = max(3, min(args.steps, 10))
+    ctx["barrier"]()
+    t = torch.tensor([event_ms(fwd, iters), event_ms(bwd, iters)], device=dev)
+    if world > 1:
+        ctx["dist"].all_reduce(t, op=ctx["dist"].ReduceOp.MAX)
+    ms, ms_b = t.tolist()
     units = B * H * W * P
-    flops = units * (2 * D + 2 * K)
     pk = peaks()
-    out = {"workload": f"COCO-Stuff head forward (configs[4] shape): B={B} maps 256x{H}x{W}, P={P}, K={K}, fused mode",
-           "ms": ms, "value": units / (ms * 1e-3), "unit": "positions*prototypes/s (forward only)",
-           "tflops_algorithmic": flops / (ms * 1e-3) / 1e12, "tensor_frac": flops / (ms * 1e-3) / 1e12 / pk["tensor_sustained"],
-           "math": math_name}
-    # the backward of this shape: K = 171 runs the tcgen05 backward as six slabs of <= 32 classes (gamma, dz, dprototypes are
-    # linear in dlogits), each recomputing the distances; reported so the cost is visible
-    try:
-        dl = torch.randn(B * H * W, K, device=dev, generator=g) / (B * H * W)
-        run_b = lambda i: sps.head_backward_raw(z, protos, last_w, cfg, dl, None, None, True, True, True)
-        run_b(0)
-        ms_b = event_ms(run_b, 3)
-        out["backward_ms"] = ms_b
-        out["backward_note"] = "tcgen05 backward in 6 class slabs of <= 32 classes (distances recomputed per slab), dz by atomics"
-        out["fwd_bwd_value"] = units / ((ms + ms_b) * 1e-3)
-    except RuntimeError as e:   # report, do not hide
-        out["backward_error"] = str(e)[:200]
-    return out
+    flops_f, flops_b = units * (2 * D + 2 * K), units * (4 * D + 4 * K)
+    z16 = z.half().contiguous(memory_format=torch.channels_last)
+    fwd16 = lambda i: sps.head_forward_raw(z16, protos, last_w, cfg, False, False)                       # noqa: E731
+    bwd16 = lambda i: sps.head_backward_raw(z16, protos, last_w, cfg, dl, None, None, True, True, True)  # noqa: E731
+    fwd16(0), bwd16(0)
+    t16 = [event_ms(fwd16, iters), event_ms(bwd16, iters)]
+    return {"workload": f"COCO-Stuff head (configs[4] shape) per GPU: B={B} maps 256x{H}x{W} fp32 NCHW, P={P}, K={K}, fused mode, {world} replica(s)",
+            "math": args.math, "forward_ms": ms, "backward_ms": ms_b, "value": world * units / ((ms + ms_b) * 1e-3),
+            "unit": "positions*prototypes/s (fwd+bwd, all replicas)",
+            "forward_tensor_frac": flops_f / (ms * 1e-3) / 1e12 / pk["tensor_sustained"],
+            "fwd_bwd_tflops_algorithmic_per_gpu": (flops_f + flops_b) / ((ms + ms_b) * 1e-3) / 1e12,
+            "fwd_bwd_tensor_frac": (flops_f + flops_b) / ((ms + ms_b) * 1e-3) / 1e12 / pk["tensor_sustained"],
+            "fp16_nhwc_maps": {"forward_ms": t16[0], "backward_ms": t16[1],
+                               "fwd_bwd_tensor_frac": (flops_f + flops_b) / ((t16[0] + t16[1]) * 1e-3) / 1e12 / pk["tensor_sustained"]},
+            "fp32_reroutes": int(ctx["lib"].sps_fp32_reroute_count()) - r0,
+            "backward_note": "one pass: tile-stationary dz kernel + chunk-stationary dp/dW kernel (no class slabs, no dz atomics); "
+                             "the fp32 map is re-laid once per call as a 16-bit channels-last array for the TMA-fed kernels"}
 
 
 def PUSH_TC(sps):
@@ -590,8 +715,8 @@ def main():
     if args.impl == "reference":
         if rank != 0:
             return
-        steps = max(1, min(args.steps, 10))
-        cpu = measure_cpu(steps, max(1, min(args.warmup, 2)))
+        steps = max(1, min(args.steps, 5))
+        cpu = measure_cpu(steps, 1)
         out = dict(base)
         out.update({"impl": "reference", "value": cpu["value"], "ms_per_step": cpu["ms_per_step"], "dtype": "f32",
                     "steps": steps, "cpu_baseline": cpu, "gpu_launches": 0,
@@ -602,13 +727,18 @@ def main():
     ctx = run_ours(args)
     e2e = measure_e2e(ctx, args)
     ctx["clocks"] = ctx["sampler"].stop() if rank == 0 else None
+    h2d = measure_h2d_probe(ctx, args)
     push = None if args.no_push else measure_push(ctx, args)
-    c5 = None if (args.no_c5 or ctx["world"] > 1) else measure_c5(ctx, args)
-    dense = None if (args.no_c5 or ctx["world"] > 1) else measure_dense(ctx, args)
-    stage2 = None if (args.no_c5 or ctx["world"] > 1) else measure_stage2(ctx, args)
-    torch_gpu = None if (args.no_c5 or ctx["world"] > 1) else measure_torch_gpu(ctx, args)
-    kld = None if (args.no_c5 or ctx["world"] > 1) else measure_kld(ctx, args)
-    extra = None if (args.no_c5 or ctx["world"] > 1) else measure_eval_topk(ctx, args)
+    push16 = None if args.no_push else measure_push(ctx, args, zdtype=torch.float16)
+    push_coco = None if (args.no_push or args.no_c5) else measure_push(ctx, args, shape=PUSH_COCO)
+    c5 = None if args.no_c5 else measure_c5(ctx, args)
+    single = not (args.no_c5 or ctx["world"] > 1)
+    nhwc16 = measure_nhwc16(ctx, args) if single else None
+    dense = measure_dense(ctx, args) if single else None
+    stage2 = measure_stage2(ctx, args) if single else None
+    torch_gpu = measure_torch_gpu(ctx, args) if single else None
+    kld = measure_kld(ctx, args) if single else None
+    extra = measure_eval_topk(ctx, args) if single else None
     if ctx["world"] > 1:
         ctx["barrier"]()
     if rank != 0:
@@ -635,31 +765,29 @@ def main():
         roof = {"bound": "hbm", "achieved": ph["bytes"] / t / 1e9, "peak": pk["hbm"], "unit": "GB/s", "frac": hbm_frac}
     traffic = None   # DRAM bytes per launch of the dominant kernel, from the committed ncu --set full capture
     try:
-        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r01_traffic.json")) as f:
+        with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "profiles", "r02_traffic.json")) as f:
             traffic = json.load(f).get("backward" if "backward" in name else "forward")
     except (OSError, ValueError):
         pass
     roof.update({"kernel": name, "ms_per_launch": ph["ms"], "peak_source": pk["source"] + " (sustained bf16 / copy)", "traffic": traffic,
                  "phases_ms": {k: v["ms"] for k, v in phases.items()}, "tensor_frac": tensor_frac, "hbm_frac": hbm_frac})
     out = dict(base)
-    out.update({"value": ctx["value"], "ms_per_step": ctx["ms_per_step"], "dtype": args.math + " operands, f32 accumulate",
-                "clocks": ctx["clocks"], "e2e": e2e, "gpu_launches": ctx["launches"], "roofline": roof})
-    if push is not None:
+    out.update({"value": ctx["value"], "ms_per_step": ctx["ms_per_step"], "dtype": args.math + " operands, f32 accumulate"})
+    if push is not None:     # early in the line: the driver keeps the head of a long stdout line
         out["push"] = push
-    if c5 is not None:
-        out["coco_forward"] = c5
-    if dense is not None:
-        out["dense_mode"] = dense
-    if stage2 is not None:
-        out["stage2"] = stage2
-    if kld is not None:
-        out["kld"] = kld
+    out.update({"clocks": ctx["clocks"], "e2e": e2e, "gpu_launches": ctx["launches"], "roofline": roof,
+                "fp32_reroutes": int(ctx["lib"].sps_fp32_reroute_count()), "h2d_probe": h2d})
+    for k, v in (("push_fp16_nhwc", push16), ("push_coco", push_coco), ("coco", c5), ("nhwc16", nhwc16), ("dense_mode", dense),
+                 ("stage2", stage2), ("kld", kld)):
+        if v is not None:
+            out[k] = v
     if extra is not None:
         out.update(extra)
     if torch_gpu is not None:
         out["torch_gpu_baseline"] = torch_gpu
     if not args.no_cpu and ctx["world"] == 1:
-        out["cpu_baseline"] = measure_cpu(8, 2)
+        out["cpu_baseline"] = measure_cpu(5, 1)
+        out["c1"] = measure_c1(args)
     if ctx["world"] > 1:
         ctx["dist"].destroy_process_group()
     print(json.dumps(out), file=json_out, flush=True)
