@@ -453,9 +453,11 @@ def measure_dense(ctx, args):
 
 
 def measure_stage2(ctx, args):
-    """Secondary: BASELINE.json configs[2], the stage-2 grouping finetune step on the same batch: head forward writing
-    the (N x P) activation map, group projection + exp + last_layer_group forward, backward to the projections and
-    the group last layer (prototypes and features frozen, as finetune_wandb_group trains)."""
+    """Secondary: BASELINE.json configs[2], the stage-2 grouping finetune step on the same batch AS THE TRAINER CALLS IT
+    (module_multiscale_group_train.py:224,242,260): the head forward returns BOTH dense maps (distances and activations),
+    the group projection + exp + last_layer_group produce logits and the group activations, and the backward receives
+    dlogits (cross-entropy) AND a gradient on the group activations (KLDLossGroup / entropy losses); prototypes and
+    features frozen, as finetune_wandb_group trains."""
     sps, ho, dev, c = ctx["sps"], ctx["ho"], ctx["dev"], C2
     from scaleprotoseg_b200 import head as sh
     tables = sh.build_group_tables(ctx["ident"], 3, dev)
@@ -463,22 +465,27 @@ def measure_stage2(ctx, args):
     Gp = torch.rand(3 * c["P"], device=dev, generator=g).requires_grad_(True)
     Wg = torch.randn(c["K"], 3 * tables.Kc, device=dev, generator=g).requires_grad_(True)
     zs, p2, dls, cfg = ctx["zs"], ctx["p2"], ctx["dls"], ctx["cfg"]
+    n = c["B"] * c["H"] * c["W"]
+    dgr = torch.randn(n, 3 * tables.Kc, device=dev, generator=g) / n
 
     def step(i):
-        act = sps.head_forward_raw(zs[i % N_SETS], p2, None, cfg, False, True)[2]
-        _, logits = sh.GroupHeadFn.apply(act, Gp, Wg, cfg, tables, (c["B"], c["H"], c["W"]))
+        _, dist, act = sps.head_forward_raw(zs[i % N_SETS], p2, None, cfg, True, True)
+        groups, logits = sh.GroupHeadFn.apply(act, Gp, Wg, cfg, tables, (c["B"], c["H"], c["W"]))
         Gp.grad = Wg.grad = None
-        logits.backward(dls[i % N_SETS])
+        torch.autograd.backward([logits, groups], [dls[i % N_SETS], dgr])
 
     iters = max(3, min(args.steps, 50))
     for i in range(3):
         step(i)
     ms = event_ms(step, iters)
-    n = c["B"] * c["H"] * c["W"]
-    bytes_alg = n * c["S"] * c["D"] * 4 + 4 * n * c["P"] * 4      # z read; activation map written once, read 3 times
-    return {"workload": "stage-2 grouping head (3 groups per class), fwd + bwd to group projections and last_layer_group, same batch",
+    gt = 3 * tables.Kc
+    # z read; distance + activation maps written (API outputs); activations read twice (projection, dG); groups / logits
+    bytes_alg = n * c["S"] * c["D"] * 4 + 4 * n * c["P"] * 4 + 4 * n * gt * 4
+    return {"workload": "stage-2 grouping head as the trainer calls it: dense distance + activation maps out, group projection (3 per class) + "
+                        "last_layer_group, backward from dlogits and dgroups to the projections and the group last layer, same batch",
             "ms_per_step": ms, "value": ctx["units"] / (ms * 1e-3), "unit": "positions*prototypes/s",
-            "hbm_frac": bytes_alg / (ms * 1e-3) / 1e9 / peaks()["hbm"]}
+            "hbm_frac": bytes_alg / (ms * 1e-3) / 1e9 / peaks()["hbm"],
+            "traffic_model": "z + 2 dense maps written + activation map read twice = 4.3 passes of 205 MB (was 5.3: the backward no longer re-reads it for the groups)"}
 
 
 def measure_kld(ctx, args):

@@ -173,8 +173,10 @@ int sps_group_fwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* a
 size_t sps_group_workspace_bytes(const SpsHeadDesc* desc, const SpsGroupDesc* g);
 
 /* Backward of sps_group_fwd.  dlogits [N,K] or NULL, dgroups [N,J*Kc] or NULL.
+ *   groups [N,J*Kc] or NULL: the group activations sps_group_fwd returned.  When given, the (N x P) activation map is read
+ *   exactly once in the whole backward (by the dG reduction); NULL recomputes them from act.
  *   dact [N,P] or NULL (overwritten), dG [J*P] or NULL, dWg [K x J*Kc] or NULL (overwritten). */
-int sps_group_bwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* act, const float* dlogits,
+int sps_group_bwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* act, const float* groups, const float* dlogits,
                   const float* dgroups, float* dact, float* dG, float* dWg, void* workspace,
                   size_t workspace_bytes, void* stream);
 

@@ -65,7 +65,7 @@ _SIGNATURES = {
     "sps_head_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "sps_group_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc), _P, _P, _P, _P]),
     "sps_group_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc)]),
-    "sps_group_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc), _P, _P, _P, _P, _P, _P, _P,
+    "sps_group_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc), _P, _P, _P, _P, _P, _P, _P, _P,
                                 C.c_size_t, _P]),
     "sps_kld_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc)]),
     "sps_kld_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsKldDesc), _P, _P, _P, C.c_size_t, _P, _P]),

@@ -279,7 +279,7 @@ size_t sps_group_workspace_bytes(const SpsHeadDesc* desc, const SpsGroupDesc* g)
   return sizeof(float) * 2 * (size_t)desc->B * desc->H * desc->W * (size_t)g->J * g->Kc;
 }
 
-int sps_group_bwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* act, const float* dlogits,
+int sps_group_bwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* act, const float* groups, const float* dlogits,
                   const float* dgroups, float* dact, float* dG, float* dWg, void* workspace, size_t workspace_bytes,
                   void* stream) {
   int rc = validate_desc(desc);
@@ -291,7 +291,7 @@ int sps_group_bwd(const SpsHeadDesc* desc, const SpsGroupDesc* g, const float* a
   SPS_REQUIRE(need == 0 || (workspace != nullptr && workspace_bytes >= need), SPS_ERR_WORKSPACE,
               "group_bwd workspace: need %zu bytes, got %zu", need, workspace_bytes);
   HeadShape s = make_shape(desc);
-  return launch_group_bwd(s, *g, act, dlogits, dgroups, dact, dG, dWg, reinterpret_cast<float*>(workspace),
+  return launch_group_bwd(s, *g, act, groups, dlogits, dgroups, dact, dG, dWg, reinterpret_cast<float*>(workspace),
                           reinterpret_cast<cudaStream_t>(stream));
 }
 

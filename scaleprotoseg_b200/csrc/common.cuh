@@ -130,7 +130,7 @@ int launch_head_bwd_simt(const HeadShape& s, int flags, const float* z, const fl
 size_t head_bwd_simt_workspace(const HeadShape& s, int flags);
 int launch_group_fwd(const HeadShape& s, const SpsGroupDesc& g, const float* act, float* groups, float* logits,
                      cudaStream_t st);
-int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act, const float* dlogits,
+int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act, const float* groups_in, const float* dlogits,
                      const float* dgroups, float* dact, float* dG, float* dWg, float* ws, cudaStream_t st);
 int launch_push_scan_simt(const HeadShape& s, const float* z, const float* protos, const int16_t* labels,
                           const int32_t* proto_class, unsigned long long* keys, cudaStream_t st);

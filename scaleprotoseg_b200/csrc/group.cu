@@ -198,8 +198,12 @@ int launch_group_fwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
 
 // Backward pass 1: recompute groups, dpre = (dlogits Wg + dgroups) * groups, dact; spill groups and
 // dpre to the workspace for the two reductions over n.
+// groups_in: the group activations the forward returned (saved by the caller).  With them this pass reads nothing of size
+// N x P: dpre and dact depend on the activations only through the groups, so the 205 MB activation map is not re-read
+// and the projections are not recomputed (the dG kernel is then the only reader of the map in the whole backward).
 template <bool STAGED>
 __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGroupDesc g, const float* __restrict__ act,
+                                                             const float* __restrict__ groups_in,
                                                              const float* __restrict__ dlogits,
                                                              const float* __restrict__ dgroups,
                                                              float* __restrict__ dact, float* __restrict__ ws_groups,
@@ -215,17 +219,23 @@ __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGrou
   float* dls = Ws + (ws_smem ? s.K * Gt : 0);              // dlogits rows of the tile [GTM][K]
   const float* Wp = ws_smem ? Ws : g.Wg;
   long long n0 = (long long)blockIdx.x * GTPB * GTM;
-  if (STAGED) stage_rows(s, act, n0, As);
+  const bool recompute = groups_in == nullptr;
+  if (STAGED && recompute) stage_rows(s, act, n0, As);
   if (dlogits != nullptr && ws_smem)
     for (int i = threadIdx.x; i < s.K * Gt; i += blockDim.x) Ws[i] = __ldg(g.Wg + i);
   stage_tables(s, g, Gs, Ms);
   for (int t = 0; t < GTPB && n0 < s.N; ++t, n0 += GTM) {
     if (dlogits != nullptr)
       for (int i = threadIdx.x; i < GTM * s.K; i += blockDim.x) dls[i] = n0 * s.K + i < s.N * s.K ? __ldg(dlogits + n0 * s.K + i) : 0.f;
-    if (STAGED && t > 0) stage_rows(s, act, n0, As);
-    __syncthreads();           // the dlogits tile
-    if (STAGED || t == 0) wait_rows();
-    group_tile<STAGED>(s, g, act, n0, gs, Gs, Ms, Gt, As);
+    if (recompute) {
+      if (STAGED && t > 0) stage_rows(s, act, n0, As);
+      __syncthreads();           // the dlogits tile
+      if (STAGED || t == 0) wait_rows();
+      group_tile<STAGED>(s, g, act, n0, gs, Gs, Ms, Gt, As);
+    } else {
+      if (t == 0) wait_rows();   // the tables (cp.async)
+      for (int idx = threadIdx.x; idx < GTM * Gt; idx += blockDim.x) gs[idx] = n0 * Gt + idx < s.N * Gt ? __ldg(groups_in + n0 * Gt + idx) : 0.f;
+    }
     __syncthreads();
     for (int idx = threadIdx.x; idx < GTM * Gt; idx += blockDim.x) {
       const int m = idx / Gt, gg = idx % Gt;
@@ -236,7 +246,7 @@ __global__ void __launch_bounds__(GNT) group_bwd_pos_kernel(HeadShape s, SpsGrou
         if (dlogits != nullptr)
           for (int k = 0; k < s.K; ++k) up = fmaf(dls[m * s.K + k], Wp[(long long)k * Gt + gg], up);
         v = up * gs[idx];
-        ws_groups[n * Gt + gg] = gs[idx];
+        if (recompute) ws_groups[n * Gt + gg] = gs[idx];
         ws_dpre[n * Gt + gg] = v;
       }
       dps[idx] = v;
@@ -366,7 +376,7 @@ __global__ void __launch_bounds__(GWT) group_bwd_dWg_kernel(HeadShape s, int Gt,
   }
 }
 
-int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act, const float* dlogits,
+int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act, const float* groups_in, const float* dlogits,
                      const float* dgroups, float* dact, float* dG, float* dWg, float* ws, cudaStream_t st) {
   const int Gt = g.J * g.Kc;
   if (dG != nullptr) SPS_CUDA_TRY(cudaMemsetAsync(dG, 0, sizeof(float) * (size_t)g.J * s.P, st));
@@ -382,15 +392,16 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
   SPS_REQUIRE(smem <= 200 * 1024, SPS_ERR_UNSUPPORTED, "group head: J*Kc=%d, J*P=%d need %zu bytes of shared memory", Gt, g.J * s.P, smem);
   float* ws_groups = ws;
   float* ws_dpre = ws + (size_t)s.N * Gt;
+  const float* groups_rd = groups_in != nullptr ? groups_in : ws_groups;   // what the dWg kernel reads
   long long tiles = (s.N + GTM - 1) / GTM;
   const size_t rows_bytes = sizeof(float) * (size_t)GTM * s.P;
-  if (smem + rows_bytes <= kGroupStagedMax) {
+  if (groups_in == nullptr && smem + rows_bytes <= kGroupStagedMax) {
     smem += rows_bytes;
     SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_pos_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    group_bwd_pos_kernel<true><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre, ws_smem);
+    group_bwd_pos_kernel<true><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, groups_in, dlogits, dgroups, dact, ws_groups, ws_dpre, ws_smem);
   } else {
     SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_pos_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    group_bwd_pos_kernel<false><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, dlogits, dgroups, dact, ws_groups, ws_dpre, ws_smem);
+    group_bwd_pos_kernel<false><<<(unsigned)((tiles + GTPB - 1) / GTPB), group_threads(g), smem, st>>>(s, g, act, groups_in, dlogits, dgroups, dact, ws_groups, ws_dpre, ws_smem);
   }
   count_launch();
   SPS_CUDA_TRY(cudaGetLastError());
@@ -416,7 +427,7 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
     int gwr = GWR;                                                           // fewer rows per step for wide heads (COCO-Stuff)
     while (gwr > 8 && gwr * row_bytes > 96 * 1024) gwr >>= 1;
     SPS_CUDA_TRY(cudaFuncSetAttribute(group_bwd_dWg_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(gwr * row_bytes)));
-    group_bwd_dWg_kernel<<<grid, GWT, gwr * row_bytes, st>>>(s, Gt, gwr, dlogits, ws_groups, dWg);
+    group_bwd_dWg_kernel<<<grid, GWT, gwr * row_bytes, st>>>(s, Gt, gwr, dlogits, groups_rd, dWg);
     count_launch();
     SPS_CUDA_TRY(cudaGetLastError());
   }

@@ -306,14 +306,14 @@ class GroupHeadFn(torch.autograd.Function):
             _lib.check(lib.sps_group_fwd(C.byref(desc), C.byref(gd), _ptr(act), _ptr(groups), _ptr(logits), _stream()),
                        "sps_group_fwd")
         ctx.cfg, ctx.tables, ctx.hw = cfg, tables, hw
-        ctx.save_for_backward(act, G, Wg)
+        ctx.save_for_backward(act, G, Wg, groups)     # groups: 1/13 of the activation map; saves its re-read in the backward
         ctx.set_materialize_grads(False)
         return groups, logits
 
     @staticmethod
     def backward(ctx, dgroups, dlogits):
         lib = _lib.load()
-        act, G, Wg = ctx.saved_tensors
+        act, G, Wg, groups = ctx.saved_tensors
         if dgroups is None and dlogits is None:
             return None, None, None, None, None, None
         cfg, tables, hw = ctx.cfg, ctx.tables, ctx.hw
@@ -333,7 +333,7 @@ class GroupHeadFn(torch.autograd.Function):
         nbytes = int(lib.sps_group_workspace_bytes(C.byref(desc), C.byref(gd)))
         ws = torch.empty(max(nbytes, 16), device=act.device, dtype=torch.uint8)
         with torch.cuda.device(act.device):
-            _lib.check(lib.sps_group_bwd(C.byref(desc), C.byref(gd), _ptr(act), _ptr(dlogits), _ptr(dgroups),
+            _lib.check(lib.sps_group_bwd(C.byref(desc), C.byref(gd), _ptr(act), _ptr(groups), _ptr(dlogits), _ptr(dgroups),
                                          _ptr(dact), _ptr(dG), _ptr(dWg), _ptr(ws), nbytes, _stream()),
                        "sps_group_bwd")
         if dWg is not None and dlogits is None:

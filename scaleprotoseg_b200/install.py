@@ -263,7 +263,9 @@ def install_kld(kld_cls):
 
     @functools.wraps(old)
     def forward(self, prototype_distances, target_labels):
-        if not prototype_distances.is_cuda:
+        if not prototype_distances.is_cuda or not _kld.kld_supported(self, prototype_distances.device):
+            if isinstance(prototype_distances, model_api.DeferredDistances):
+                prototype_distances = prototype_distances.materialize()
             return old(self, prototype_distances, target_labels)
         return _kld.kld_forward(self, prototype_distances, target_labels)
 

@@ -196,23 +196,35 @@ import weakref
 _TABLE_CACHE: "weakref.WeakKeyDictionary" = weakref.WeakKeyDictionary()
 
 
+def tables_for(self, device) -> KldTables:
+    """Tables of a KLDLoss module (attributes prototype_class_identity, num_scales, scale_num_prototypes; loss.py:56-64),
+    rebuilt only when what they were derived from changes."""
+    ranges = tuple(tuple(int(v) for v in self.scale_num_prototypes[s]) for s in range(self.num_scales))
+    ident = self.prototype_class_identity
+    sig = (ranges, tuple(ident.shape), int(ident.data_ptr()), int(ident._version), str(device))
+    hit: Optional[Tuple[tuple, KldTables]] = _TABLE_CACHE.get(self)
+    if hit is None or hit[0] != sig:
+        hit = (sig, KldTables(ident, ranges, device))
+        _TABLE_CACHE[self] = hit
+    return hit[1]
+
+
+def kld_supported(self, device) -> bool:
+    """The kernels hold one (class, scale) group of at most 32 prototypes per warp; a wider group keeps the reference's loop."""
+    return tables_for(self, device).mmax <= 32
+
+
 def kld_forward(self, prototype_distances: torch.Tensor, target_labels: torch.Tensor) -> torch.Tensor:
     """Bound over KLDLoss.forward by install(): `self` is the reference's KLDLoss module (attributes
     prototype_class_identity, num_scales, scale_num_prototypes; loss.py:56-64)."""
     from .model_api import DeferredDistances
     if not prototype_distances.is_cuda:
         raise RuntimeError("scaleprotoseg_b200 KLD loss runs on CUDA only: there is no CPU path")
-    ranges = tuple(tuple(int(v) for v in self.scale_num_prototypes[s]) for s in range(self.num_scales))
-    ident = self.prototype_class_identity
-    sig = (ranges, tuple(ident.shape), int(ident.data_ptr()), int(ident._version), str(prototype_distances.device))
-    hit: Optional[Tuple[tuple, KldTables]] = _TABLE_CACHE.get(self)
-    if hit is None or hit[0] != sig:
-        hit = (sig, KldTables(ident, ranges, prototype_distances.device))
-        _TABLE_CACHE[self] = hit
+    tables = tables_for(self, prototype_distances.device)
     if isinstance(prototype_distances, DeferredDistances):     # fused-mode training: no (B,P,H,W) map exists
         d = prototype_distances
-        return kld_loss_from_features(d.z, d.protos, target_labels, hit[1], d.cfg)
-    return kld_loss(prototype_distances.float(), target_labels, hit[1])
+        return kld_loss_from_features(d.z, d.protos, target_labels, tables, d.cfg)
+    return kld_loss(prototype_distances.float(), target_labels, tables)
 
 
 def kld_group_loss(list_group_activation, target_labels: torch.Tensor, tables: KldTables) -> torch.Tensor:

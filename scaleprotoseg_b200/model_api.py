@@ -25,12 +25,30 @@ def head_config(m, math=None) -> HeadConfig:
                                   default_math() if math is None else math)
 
 
+MAX_CLASSES, MAX_DEPTH, MAX_CHUNKS, MAX_GROUPS_PER_CLASS = 192, 64, 160, 8     # limits of csrc/ (api.cu, tc_common.cuh, group.cu)
+
+
 def is_supported(m) -> bool:
-    """Configurations the kernels cover; anything else keeps running the reference's own code."""
+    """Configurations the kernels cover; anything else keeps running the reference's own code (never an error in the middle
+    of training): activation kind, 1x1 prototypes, no scale head, and the kernels' shape limits - at most 192 classes, a
+    prototype depth that is a multiple of 8 up to 64, at most 160 chunks of 64 prototypes over the scales, and at most 8
+    groups per class for the stage-2 head."""
     act = m.prototype_activation_function
     shape = tuple(m.prototype_vectors.shape)
-    return (getattr(m, "scale_head", None) is None and isinstance(act, str) and act in ("log", "linear")
-            and len(shape) == 4 and shape[2] == 1 and shape[3] == 1)
+    if not (getattr(m, "scale_head", None) is None and isinstance(act, str) and act in ("log", "linear")
+            and len(shape) == 4 and shape[2] == 1 and shape[3] == 1):
+        return False
+    if shape[1] > MAX_DEPTH or shape[1] % 8 != 0 or int(m.num_classes) > MAX_CLASSES or int(m.num_classes) < 1:
+        return False
+    if hasattr(m, "scale_num_prototypes"):
+        ranges = [tuple(m.scale_num_prototypes[s]) for s in range(m.num_scales)]
+    else:
+        ranges = [(0, shape[0])]
+    if sum((int(b) - int(a) + 63) // 64 for a, b in ranges) > MAX_CHUNKS:
+        return False
+    if hasattr(m, "num_groups") and not (1 <= int(m.num_groups) <= MAX_GROUPS_PER_CLASS):
+        return False
+    return True
 
 
 _DEFER_DISTANCES = False
@@ -46,9 +64,12 @@ def set_deferred_distances(on: bool):
 
 class DeferredDistances:
     """Stands in for the dense distance map of one head call.  Carries what is needed to compute any part of it
-    (features, prototypes, head configuration).  The patched KLDLoss.forward consumes it without materialising it;
-    any other use (an attribute or method of a tensor) materialises the map through the head kernels and delegates,
-    so callers that really want the tensor still get it, with autograd intact."""
+    (features, prototypes, head configuration).  The patched KLDLoss.forward consumes it without materialising it.
+    Named attributes and methods of a tensor (`.shape`, `.mean()`, `.permute(...)`, ...), indexing, `len()` and
+    `torch.*(handle)` calls materialise the map through the head kernels and delegate, with autograd intact.  It is NOT a
+    Tensor subclass: `isinstance(handle, torch.Tensor)` is False and arithmetic operators are not forwarded - call
+    `.materialize()` first where a real tensor is required.  Opt-in (set_deferred_distances), for the reference trainer
+    whose only use of the map is KLDLoss."""
 
     def __init__(self, z: torch.Tensor, protos: torch.Tensor, cfg: HeadConfig):
         self.z, self.protos, self.cfg = z, protos, cfg
@@ -76,6 +97,17 @@ class DeferredDistances:
         if name.startswith("__"):
             raise AttributeError(name)
         return getattr(self.materialize(), name)
+
+    def __getitem__(self, idx):
+        return self.materialize()[idx]
+
+    def __len__(self):
+        return int(self.z.shape[0])
+
+    @classmethod
+    def __torch_function__(cls, func, types, args=(), kwargs=None):
+        unwrap = lambda a: a.materialize() if isinstance(a, DeferredDistances) else a      # noqa: E731
+        return func(*[unwrap(a) for a in args], **{k: unwrap(v) for k, v in (kwargs or {}).items()})
 
 
 def _require_cuda(x: torch.Tensor):
@@ -146,17 +178,31 @@ def forward_from_conv_features_stage1(self, conv_features: Union[torch.Tensor, L
 
 
 # ---- stage 2 ------------------------------------------------------------------------------------
+# module -> (key, weakref to the activation tensor, (groups, logits)).  The stage-2 trainer runs the group head TWICE per
+# step on the same activations: once inside forward_from_conv_features for the logits and once through compute_group for
+# the KLD / entropy losses (module_multiscale_group_train.py:224 -> :306, then :242).  The second call gets the first
+# call's outputs (one autograd node, one backward) instead of recomputing them.
+_apply_cache: "weakref.WeakKeyDictionary" = weakref.WeakKeyDictionary()
+
+
 def _group_apply(self, prototype_activations: torch.Tensor, hw=None):
     _require_cuda(prototype_activations)
     tables = group_tables(self, prototype_activations.device)
     if len(self.group_projection) != tables.Kc:
         raise RuntimeError("group_projection does not match prototype_class_identity "
                            f"({len(self.group_projection)} modules, {tables.Kc} classes with prototypes)")
+    key = (id(prototype_activations), prototype_activations._version, tuple(gp.weight._version for gp in self.group_projection),
+           tuple(gp.weight.data_ptr() for gp in self.group_projection), self.last_layer_group.weight._version,
+           self.last_layer_group.weight.data_ptr(), torch.is_grad_enabled())
+    ent = _apply_cache.get(self)
+    if ent is not None and ent[0] == key and ent[1]() is prototype_activations:
+        return ent[2], tables
     G = torch.cat([gp.weight.reshape(-1) for gp in self.group_projection])
     N = prototype_activations.shape[0]
     hw = hw if hw is not None else (1, 1, N)
-    return GroupHeadFn.apply(prototype_activations.float(), G, self.last_layer_group.weight, head_config(self),
-                             tables, hw), tables
+    res = GroupHeadFn.apply(prototype_activations.float(), G, self.last_layer_group.weight, head_config(self), tables, hw)
+    _apply_cache[self] = (key, weakref.ref(prototype_activations), res)
+    return res, tables
 
 
 def compute_group(self, prototype_activations: torch.Tensor) -> List[torch.Tensor]:

@@ -79,7 +79,7 @@ def test_stage1_golden(built_lib, golden_dir, name, math):
     assert_grad(dw, g["dlast_w"], gt, "dlast_w")
 
 
-@pytest.mark.parametrize("math", MATHS)
+@pytest.mark.parametrize("math", MATHS + [sps.MATH_F16X3])      # F16X3: what install() feeds the group head with by default
 @pytest.mark.parametrize("name", ["stage2_em", "stage2_city228_ragged"])
 def test_stage2_golden(built_lib, golden_dir, name, math):
     g = _load(golden_dir, name)
