@@ -2,7 +2,7 @@
 import json
 import sys
 import os
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch
 import scaleprotoseg_b200 as sps
 from scaleprotoseg_b200 import _lib, head as sh
