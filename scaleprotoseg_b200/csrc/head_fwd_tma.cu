@@ -22,6 +22,17 @@ namespace sps {
 namespace tf {
 using namespace sps::tc;
 
+#ifdef SPS_TIMELINE
+// Debug build only: clock stamps of CTA 0, row = role * 8 + event kind, column = unit / pair index (profiles/tools/timeline_tma.py)
+__device__ long long g_tl2[64 * 1024];
+#define TL2(row, idx)                                                                                   \
+  do {                                                                                                  \
+    if (blockIdx.x == 0 && (idx) >= 0 && (idx) < 1024) g_tl2[(row) * 1024 + (idx)] = clock64();          \
+  } while (0)
+#else
+#define TL2(row, idx) do { } while (0)
+#endif
+
 struct FwdTmaParams {
   CUtensorMap tm_hi;   // [N][C] 16-bit: the map itself, or the hi part of an fp32 map
   CUtensorMap tm_lo;   // lo part (ZLO only)
@@ -39,14 +50,14 @@ constexpr int A_TILE = TILE_M * 128;          // 16 KB: 128 positions x 64 chann
 constexpr int A_NORM = TILE_M * 32;           // 4 KB norm K step
 constexpr int P_BYTES = TILE_M * 128;
 constexpr int TMEM_S0 = 0;
-constexpr int NSTW = 2;
+constexpr int MAX_NSTW = 4;   // last-layer tile ring: as deep as it is cheap (small K), the chunk producer runs that far ahead
 constexpr int ACT_SCRATCH = 32 * 33 * 4;
 
 template <bool ZLO> __host__ __device__ constexpr int a_stage_bytes() { return (ZLO ? 2 : 1) * A_TILE + A_NORM; }
 template <bool ZLO> __host__ __device__ constexpr int a_stages() { return ZLO ? 2 : 3; }
 
 struct Plan {
-  int a_stride, na, p0, p_stride, b0, b_stride, nst, w0, w_stride, scr0, bar_off, total;
+  int a_stride, na, p0, p_stride, b0, b_stride, nst, nstw, w0, w_stride, scr0, bar_off, total;
   __host__ __device__ int a_off(int i) const { return i * a_stride; }
   __host__ __device__ int p_off(int i) const { return p0 + i * p_stride; }
   __host__ __device__ int b_off(int i) const { return b0 + i * b_stride; }
@@ -63,7 +74,8 @@ template <int NSPLIT, bool ZLO, int NSETS, int LSPLIT> __host__ __device__ inlin
   pl.b0 = pl.p0 + NSETS * pl.p_stride;
   pl.b_stride = ((NSPLIT == 3 ? 2 : 1) * CN * 128 + CN * 32 + 1023) / 1024 * 1024;
   pl.w_stride = ((LSPLIT == 3 ? 2 : 1) * kp * 128 + 1023) / 1024 * 1024;
-  const int w_total = kp > 0 ? NSTW * pl.w_stride : 0;
+  pl.nstw = pl.w_stride <= 8 * 1024 ? MAX_NSTW : 2;
+  const int w_total = kp > 0 ? pl.nstw * pl.w_stride : 0;
   const int scr_total = scratch_warps * ACT_SCRATCH;
   int nst = (227 * 1024 - 512 - 1024 - pl.b0 - w_total - scr_total) / pl.b_stride;
   pl.nst = nst > MAX_NST ? MAX_NST : nst;
@@ -76,15 +88,16 @@ template <int NSPLIT, bool ZLO, int NSETS, int LSPLIT> __host__ __device__ inlin
 
 enum { BAR_TFULL = 0, BAR_AFULL = 4, BAR_AEMPTY = 8, BAR_BFULL = 12, BAR_BEMPTY = 12 + MAX_NST, BAR_SFULL = 12 + 2 * MAX_NST,
        BAR_SEMPTY = 16 + 2 * MAX_NST, BAR_PFULL = 20 + 2 * MAX_NST, BAR_PEMPTY = 24 + 2 * MAX_NST, BAR_LFULL = 28 + 2 * MAX_NST,
-       BAR_LEMPTY = 30 + 2 * MAX_NST, BAR_WFULL = 32 + 2 * MAX_NST, BAR_WEMPTY = 34 + 2 * MAX_NST, BAR_COUNT = 36 + 2 * MAX_NST };
+       BAR_LEMPTY = 30 + 2 * MAX_NST, BAR_WFULL = 32 + 2 * MAX_NST, BAR_WEMPTY = 36 + 2 * MAX_NST, BAR_COUNT = 40 + 2 * MAX_NST };
 
-__host__ __device__ constexpr int n_threads(int nsets) { return (4 * nsets + 4) * 32; }
+constexpr int NZ = 4;   // feature-tile warps: one issues the TMA, all four compute the row norms (one row per thread)
+__host__ __device__ constexpr int n_threads(int nsets) { return (4 * nsets + NZ + 3) * 32; }
 
 template <typename X, int NSPLIT, bool ZLO, bool DENSE, int NSETS, int LSPLIT>
 __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const __grid_constant__ FwdTmaParams prm) {
   constexpr int NEPI = 4 * NSETS;
   constexpr int TMEM_L0 = NSETS * CN;
-  constexpr int WARP_Z = NEPI, WARP_PROD = NEPI + 1, WARP_MMA = NEPI + 2, WARP_MMA2 = NEPI + 3;
+  constexpr int WARP_Z = NEPI, WARP_PROD = NEPI + NZ, WARP_MMA = NEPI + NZ + 1, WARP_MMA2 = NEPI + NZ + 2;
   constexpr int NA = a_stages<ZLO>();
   extern __shared__ unsigned char smem_raw[];
   const HeadShape& s = prm.s;
@@ -97,7 +110,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + pl.bar_off + 8 * BAR_COUNT);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int NC = ct.n_chunks, KP = ct.kp, NST = pl.nst;
+  const int NC = ct.n_chunks, KP = ct.kp, NST = pl.nst, NSTW = pl.nstw;
   const bool has_w = KP > 0;
   uint32_t tmem_cols = 32;
   while ((int)tmem_cols < TMEM_L0 + 2 * KP) tmem_cols <<= 1;
@@ -105,7 +118,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
   if (threadIdx.x == 0) {
     for (int i = 0; i < NA; ++i) {
       mbar_init(bar(BAR_TFULL + i), 1);    // arrive.expect_tx by the producer lane + the TMA bytes
-      mbar_init(bar(BAR_AFULL + i), 1);    // norm K step written
+      mbar_init(bar(BAR_AFULL + i), NZ);   // norm K step written (one arrive per feature-tile warp)
       mbar_init(bar(BAR_AEMPTY + i), 1);   // tcgen05.commit
     }
     for (int i = 0; i < NSETS; ++i) {
@@ -117,6 +130,8 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(BAR_LFULL + i), 1);
       mbar_init(bar(BAR_LEMPTY + i), 4);
+    }
+    for (int i = 0; i < MAX_NSTW; ++i) {
       mbar_init(bar(BAR_WFULL + i), 1);
       mbar_init(bar(BAR_WEMPTY + i), 1);
     }
@@ -144,12 +159,16 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
       const bool first_of_scale = c == 0 || ct.scale[c] != ct.scale[c - 1];
       const bool last_of_scale = c == NC - 1 || ct.scale[c + 1] != ct.scale[c];
       const uint32_t ab = acount % NA, aph = (acount / NA) & 1, st = i % NST, sb = i % NSETS;
+      if (lane == 0) TL2(0, i);
       if (first_of_scale) {
         mbar_wait(bar(BAR_TFULL + ab), aph);
         mbar_wait(bar(BAR_AFULL + ab), aph);
       }
+      if (lane == 0) TL2(1, i);
       mbar_wait(bar(BAR_BFULL + st), (i / NST) & 1);
+      if (lane == 0) TL2(2, i);
       mbar_wait(bar(BAR_SEMPTY + sb), ((i / NSETS) & 1) ^ 1);
+      if (lane == 0) TL2(3, i);
       tc_fence_after();
       {
         const uint32_t a_hi = base + pl.a_off(ab), a_lo = a_hi + A_TILE;
@@ -171,6 +190,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
         mma_commit(bar(BAR_SFULL + sb));
         if (last_of_scale) mma_commit(bar(BAR_AEMPTY + ab));
         mma_commit(bar(BAR_BEMPTY + st));
+        if (lane == 0) TL2(4, i);
       }
       __syncwarp();
       if (last_of_scale) ++acount;
@@ -184,9 +204,12 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
       int c = 0, tl = 0;
       for (int u = 0; u < U; ++u) {
         const uint32_t pb = u % NSETS, sw = u % NSTW, lb = tl & 1;
+        if (lane == 0) TL2(8, u);
         if (c == 0) mbar_wait(bar(BAR_LEMPTY + lb), ((tl >> 1) & 1) ^ 1);
         mbar_wait(bar(BAR_WFULL + sw), (u / NSTW) & 1);
+        if (lane == 0) TL2(9, u);
         mbar_wait(bar(BAR_PFULL + pb), (u / NSETS) & 1);
+        if (lane == 0) TL2(10, u);
         tc_fence_after();
         {
           const uint32_t pa = base + pl.p_off(pb), w2 = base + pl.w_off(sw);
@@ -203,6 +226,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
           mma_commit(bar(BAR_PEMPTY + pb));
           mma_commit(bar(BAR_WEMPTY + sw));
           if (c == NC - 1) mma_commit(bar(BAR_LFULL + lb));
+          if (lane == 0) TL2(11, u);
         }
         __syncwarp();
         if (++c == NC) { c = 0; ++tl; }
@@ -215,7 +239,9 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
     const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128, bytes_n = CN * 32, bytes_w = (LSPLIT == 3 ? 2 : 1) * KP * 128;
     auto fetch_b = [&](int i) {
       const int c = i % NC, st = i % NST;
+      if (lane == 0) TL2(16, i);
       mbar_wait(bar(BAR_BEMPTY + st), ((i / NST) & 1) ^ 1);
+      if (lane == 0) TL2(17, i);
       if (lane == 0) {
         mbar_arrive_expect_tx(bar(BAR_BFULL + st), bytes_b + bytes_n);
         const unsigned char* src = prm.img + (size_t)c * ct.img_bytes;
@@ -227,7 +253,9 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
     };
     auto fetch_w = [&](int i) {
       const int c = i % NC, sw = i % NSTW;
+      if (lane == 0) TL2(18, i);
       mbar_wait(bar(BAR_WEMPTY + sw), ((i / NSTW) & 1) ^ 1);
+      if (lane == 0) TL2(19, i);
       if (lane == 0) {
         mbar_arrive_expect_tx(bar(BAR_WFULL + sw), bytes_w);
         bulk_g2s(base + pl.w_off(sw), prm.img + (size_t)c * ct.img_bytes + OFF_W2, bytes_w, bar(BAR_WFULL + sw));
@@ -239,10 +267,13 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
       if (i + 1 < U) fetch_b(i + 1);
       if (has_w) fetch_w(i);
     }
-  } else if (warp == WARP_Z) {
+  } else if (warp >= WARP_Z && warp < WARP_Z + NZ) {
     // ================================ feature-tile producer + row norms ================================
-    // Work list: (tile, scale) pairs in the order the distance-GEMM issuer consumes them.  The TMA of pair i + 1 goes
-    // out as soon as its stage is free (tried before the norms of pair i, waited for after them).
+    // Work list: (tile, scale) pairs in the order the distance-GEMM issuer consumes them.  The first warp keeps up to NA
+    // tiles in flight (a stage is re-armed as soon as a NON-blocking probe sees it free); every thread of the four warps
+    // then computes the squared norm of one row of the landed tile.  (One warp for all 128 rows took 2 200 clk per pair, and
+    // a try_wait used as a probe suspended it ~3 000 clk per pair: together 5 200 clk per pair, the period of the whole
+    // kernel - profiles/r02_timeline_fwd_tma_before.txt.)
     // (a 16-bit re-lay of an fp32 map was written by a kernel that completed before the prototype pre-pass started)
     auto advance = [&](int& ti, int& c) {
       const int sc = ct.scale[c];
@@ -250,6 +281,8 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
       if (c == NC) { c = 0; ++ti; }
     };
     constexpr uint32_t TX = (ZLO ? 2 : 1) * A_TILE;
+    const bool issuer = warp == WARP_Z;
+    const int m = (warp - WARP_Z) * 32 + lane;
     int iti = 0, ic = 0;        // next pair to issue
     uint32_t issued = 0;
     auto issue = [&](bool blocking) -> bool {
@@ -257,13 +290,14 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
       const uint32_t ab = issued % NA, aph = (issued / NA) & 1;
       if (blocking) {
         mbar_wait(bar(BAR_AEMPTY + ab), aph ^ 1);
-      } else {   // warp-uniform outcome: the lanes of a warp may see the phase flip at different polls
-        const bool ok = mbar_try_wait(bar(BAR_AEMPTY + ab), aph ^ 1);
+      } else {   // warp-uniform outcome of the probe
+        const bool ok = mbar_test(bar(BAR_AEMPTY + ab), aph ^ 1);
         if (!__all_sync(0xffffffffu, ok)) return false;
       }
       if (lane == 0) {
         const int row0 = (int)(((long long)blockIdx.x + (long long)iti * gridDim.x) * TILE_M);
         const int c0 = ct.scale[ic] * s.D;
+        TL2(27, issued);
         mbar_arrive_expect_tx(bar(BAR_TFULL + ab), TX);
         tma_load_2d(base + pl.a_off(ab), &prm.tm_hi, c0, row0, bar(BAR_TFULL + ab));
         if (ZLO) tma_load_2d(base + pl.a_off(ab) + A_TILE, &prm.tm_lo, c0, row0, bar(BAR_TFULL + ab));
@@ -275,26 +309,26 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
     };
     int ti = 0, c = 0;
     uint32_t acount = 0;
-    issue(true);
     while (ti < my_tiles) {
       const uint32_t ab = acount % NA, aph = (acount / NA) & 1;
-      while (issued < acount + NA && iti < my_tiles && issue(false)) {   // keep up to NA pairs in flight
+      if (issuer) {
+        if (issued <= acount) issue(true);                                   // the pair waited for next must be on its way
+        while (issued < acount + NA && iti < my_tiles && issue(false)) {     // keep up to NA pairs in flight
+        }
       }
+      if (issuer && lane == 0) TL2(24, acount);
       mbar_wait(bar(BAR_TFULL + ab), aph);
+      if (issuer && lane == 0) TL2(25, acount);
       unsigned char* a_hi = gbase + pl.a_off(ab);
       unsigned char* a_lo = a_hi + A_TILE;
       unsigned char* a_n = a_hi + (ZLO ? 2 : 1) * A_TILE;
-#pragma unroll
-      for (int rr = 0; rr < 4; ++rr) {
-        const int r = lane + 32 * rr;
-        ZStage<X, NSPLIT>::store_norm(r, a_n, tile_row_norm<X, ZLO>(a_hi, a_lo, r));
-      }
+      ZStage<X, NSPLIT>::store_norm(m, a_n, tile_row_norm<X, ZLO>(a_hi, a_lo, m));
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(BAR_AFULL + ab));
+      if (issuer && lane == 0) TL2(26, acount);
       ++acount;
       advance(ti, c);
-      if (issued <= acount && iti < my_tiles) issue(true);   // the pair waited for next must be on its way
     }
   } else {
     // ================================ epilogue ================================
@@ -333,7 +367,9 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
       const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
       float* drow = DENSE && prm.dist != nullptr ? prm.dist + b * (long long)s.P * s.HW + pix : nullptr;
       const uint32_t sb = set, pb = set, ph = (u / NSETS) & 1;
+      if (q == 0 && lane == 0) TL2(32, u);
       mbar_wait(bar(BAR_SFULL + sb), ph);
+      if (q == 0 && lane == 0) TL2(33, u);
       tc_fence_after();
       unsigned char* prow = gbase + pl.p_off(pb) + (uint32_t)m * 128u;
 #pragma unroll 1
@@ -341,6 +377,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
         uint32_t r[32];
         tmem_ld32(tmem + lane_base + TMEM_S0 + sb * CN + hf * 32, r);
         tmem_ld_wait();
+        if (q == 0 && lane == 0) TL2(34 + hf, u);
         if (hf == 1) {
           tc_fence_before();
           __syncwarp();
@@ -353,7 +390,11 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
 #pragma unroll
           for (int j = 0; j < 32; ++j) {
             const float d = fmaxf(__uint_as_float(r[j]), 0.0f);
+#ifdef SPS_DBG_NOEPI
+            av[j] = d * ome;   // debug build only: no MUFU, to see what the pipeline around the epilogue can sustain
+#else
             av[j] = lg2_approx(fmaf(ome, rcp_approx(d + eps), 1.0f));
+#endif
             if (DENSE) r[j] = __float_as_uint(d);
           }
         } else {
@@ -393,6 +434,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
         }
         if (has_w) {
           if (hf == 0) mbar_wait(bar(BAR_PEMPTY + pb), ph ^ 1);
+          if (q == 0 && lane == 0 && hf == 0) TL2(36, u);
 #pragma unroll
           for (int g = 0; g < 4; ++g) {
             uint32_t w[4], wl[4];
@@ -412,9 +454,11 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
         }
       }
       if (has_w) {
+        if (q == 0 && lane == 0) TL2(37, u);
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(BAR_PFULL + pb));
+        if (q == 0 && lane == 0) TL2(38, u);
       }
       if (has_w && set == 0) {
         while (next_store < ti - 1) store_logits(next_store++);
@@ -486,6 +530,12 @@ __global__ void __launch_bounds__(256) z_pack_kernel(const float* __restrict__ z
 }
 
 }  // namespace tf
+
+#ifdef SPS_TIMELINE
+extern "C" int sps_debug_timeline2(long long* host, int count) {
+  return (int)cudaMemcpyFromSymbol(host, tf::g_tl2, sizeof(long long) * (size_t)count);
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // Host side

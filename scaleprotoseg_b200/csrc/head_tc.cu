@@ -118,9 +118,9 @@ template <int NSPLIT> __host__ __device__ constexpr int a_buf_bytes() { return (
 // that a run-time buffer index never turns into a local-memory lookup.  The prototype operands (hi [lo] | norm) and the
 // last-layer tile of a chunk travel in SEPARATE rings: a B slot is free again as soon as the distance GEMM of its unit
 // has completed, a W slot only after the logits GEMM a unit later, so the B ring runs several units ahead.
-constexpr int NSTW = 2;
+constexpr int MAX_NSTW = 4;   // last-layer tile ring: as deep as it is cheap (small K), the chunk producer runs that far ahead
 struct SmemPlan {
-  int a_stride, p0, b0, b_stride, nst, w0, w_stride, scr0, bar_off, total;
+  int a_stride, p0, b0, b_stride, nst, nstw, w0, w_stride, scr0, bar_off, total;
   __host__ __device__ int a_off(int i) const { return i * a_stride; }
   int p_stride;
   __host__ __device__ int p_off(int i) const { return p0 + i * p_stride; }
@@ -136,7 +136,8 @@ template <int NSPLIT> __host__ __device__ inline SmemPlan smem_plan(int kp, bool
   pl.b0 = pl.p0 + 2 * pl.p_stride;
   pl.b_stride = ((NSPLIT == 3 ? 2 : 1) * CN * 128 + CN * 32 + 1023) / 1024 * 1024;
   pl.w_stride = ((NSPLIT == 3 ? 2 : 1) * kp * 128 + 1023) / 1024 * 1024;
-  const int w_total = kp > 0 ? NSTW * pl.w_stride : 0;
+  pl.nstw = pl.w_stride <= 8 * 1024 ? MAX_NSTW : 2;
+  const int w_total = kp > 0 ? pl.nstw * pl.w_stride : 0;
   const int scr_total = dense_act ? 8 * ACT_SCRATCH : 0;
   int nst = (227 * 1024 - 512 - 1024 - pl.b0 - w_total - scr_total) / pl.b_stride;
   pl.nst = nst > MAX_NST ? MAX_NST : nst;
@@ -150,7 +151,7 @@ template <int NSPLIT> __host__ __device__ inline SmemPlan smem_plan(int kp, bool
 // barrier indices
 enum { BAR_AFULL = 0, BAR_AEMPTY = 2, BAR_BFULL = 4, BAR_BEMPTY = 4 + MAX_NST, BAR_SFULL = 4 + 2 * MAX_NST,
        BAR_SEMPTY = 6 + 2 * MAX_NST, BAR_PFULL = 8 + 2 * MAX_NST, BAR_PEMPTY = 10 + 2 * MAX_NST, BAR_LFULL = 12 + 2 * MAX_NST,
-       BAR_LEMPTY = 14 + 2 * MAX_NST, BAR_WFULL = 16 + 2 * MAX_NST, BAR_WEMPTY = 18 + 2 * MAX_NST, BAR_COUNT = 20 + 2 * MAX_NST };
+       BAR_LEMPTY = 14 + 2 * MAX_NST, BAR_WFULL = 16 + 2 * MAX_NST, BAR_WEMPTY = 20 + 2 * MAX_NST, BAR_COUNT = 24 + 2 * MAX_NST };
 
 // DENSE: the distance and / or activation maps leave the SM as well.  A compile-time switch: as a run-time test the
 // compiler merged both paths and the fused epilogue carried the (predicated-off) address arithmetic of the dense stores.
@@ -167,7 +168,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + pl.bar_off + 8 * BAR_COUNT);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int NC = ct.n_chunks, KP = ct.kp, NST = pl.nst;
+  const int NC = ct.n_chunks, KP = ct.kp, NST = pl.nst, NSTW = pl.nstw;
   const bool has_w = KP > 0;
   uint32_t tmem_cols = 32;
   while ((int)tmem_cols < TMEM_L0 + 2 * KP) tmem_cols <<= 1;
@@ -183,6 +184,8 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       mbar_init(bar(BAR_PEMPTY + i), 1);
       mbar_init(bar(BAR_LFULL + i), 1);
       mbar_init(bar(BAR_LEMPTY + i), 4);   // epilogue warps 0..3 read the logits
+    }
+    for (int i = 0; i < MAX_NSTW; ++i) {
       mbar_init(bar(BAR_WFULL + i), 1);
       mbar_init(bar(BAR_WEMPTY + i), 1);
     }
