@@ -64,3 +64,6 @@ print("pairs: tma issue / z wait start / landed / norm done | mma1 first unit st
 for p_ in range(10):
     u0 = 3 * p_
     print(p_, int(t[27, p_] - t0), int(t[24, p_] - t0), int(t[25, p_] - t0), int(t[26, p_] - t0), "|", int(t[0, u0] - t0), int(t[1, u0] - t0), int(t[4, u0 + 2] - t0))
+print("unit: B(i) bulk issued / mma1 starts waiting for B(i) / B(i) seen ready / W(i) issued / mma2 W ready")
+for u in range(8, 26):
+    print(u, int(t[17, u] - t0), int(t[1, u] - t0), int(t[2, u] - t0), int(t[19, u] - t0), int(t[9, u] - t0))

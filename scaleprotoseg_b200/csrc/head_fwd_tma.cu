@@ -91,13 +91,13 @@ enum { BAR_TFULL = 0, BAR_AFULL = 4, BAR_AEMPTY = 8, BAR_BFULL = 12, BAR_BEMPTY 
        BAR_LEMPTY = 30 + 2 * MAX_NST, BAR_WFULL = 32 + 2 * MAX_NST, BAR_WEMPTY = 36 + 2 * MAX_NST, BAR_COUNT = 40 + 2 * MAX_NST };
 
 constexpr int NZ = 4;   // feature-tile warps: one issues the TMA, all four compute the row norms (one row per thread)
-__host__ __device__ constexpr int n_threads(int nsets) { return (4 * nsets + NZ + 3) * 32; }
+__host__ __device__ constexpr int n_threads(int nsets) { return (4 * nsets + NZ + 4) * 32; }
 
 template <typename X, int NSPLIT, bool ZLO, bool DENSE, int NSETS, int LSPLIT>
 __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const __grid_constant__ FwdTmaParams prm) {
   constexpr int NEPI = 4 * NSETS;
   constexpr int TMEM_L0 = NSETS * CN;
-  constexpr int WARP_Z = NEPI, WARP_PROD = NEPI + NZ, WARP_MMA = NEPI + NZ + 1, WARP_MMA2 = NEPI + NZ + 2;
+  constexpr int WARP_Z = NEPI, WARP_PROD = NEPI + NZ, WARP_MMA = NEPI + NZ + 1, WARP_MMA2 = NEPI + NZ + 2, WARP_PRODW = NEPI + NZ + 3;
   constexpr int NA = a_stages<ZLO>();
   extern __shared__ unsigned char smem_raw[];
   const HeadShape& s = prm.s;
@@ -153,28 +153,27 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
     // ================================ distance-GEMM issuer ================================
     constexpr uint32_t ID1 = idesc_f16(Fmt<X>::id, TILE_M, CN);
     const int U = my_tiles * NC;
-    uint32_t acount = 0;
+    uint32_t acount = 0, ab = 0, aph = 0, st = 0, bph = 0, sb = 0, sph = 0;
     int c = 0;
     for (int i = 0; i < U; ++i) {
       const bool first_of_scale = c == 0 || ct.scale[c] != ct.scale[c - 1];
       const bool last_of_scale = c == NC - 1 || ct.scale[c + 1] != ct.scale[c];
-      const uint32_t ab = acount % NA, aph = (acount / NA) & 1, st = i % NST, sb = i % NSETS;
       if (lane == 0) TL2(0, i);
       if (first_of_scale) {
         mbar_wait(bar(BAR_TFULL + ab), aph);
         mbar_wait(bar(BAR_AFULL + ab), aph);
       }
       if (lane == 0) TL2(1, i);
-      mbar_wait(bar(BAR_BFULL + st), (i / NST) & 1);
+      mbar_wait(bar(BAR_BFULL + st), bph);
       if (lane == 0) TL2(2, i);
-      mbar_wait(bar(BAR_SEMPTY + sb), ((i / NSETS) & 1) ^ 1);
+      mbar_wait(bar(BAR_SEMPTY + sb), sph ^ 1);
       if (lane == 0) TL2(3, i);
       tc_fence_after();
       {
         const uint32_t a_hi = base + pl.a_off(ab), a_lo = a_hi + A_TILE;
         const uint32_t a_n = a_hi + (ZLO ? 2 : 1) * A_TILE;
         const uint32_t b_hi = base + pl.b_off(st) + OFF_BHI, b_lo = base + pl.b_off(st) + OFF_BLO;
-        const uint32_t b_n = base + pl.b_off(st) + (NSPLIT == 3 ? 2 : 1) * CN * 128;
+        const uint32_t b_n = base + pl.b_off(st) + OFF_BN;
         const uint32_t d = tmem + TMEM_S0 + sb * CN;
         mma_f16(d, desc_noswz(a_n, NORM_LBO, NORM_SBO), desc_noswz(b_n, NORM_LBO, NORM_SBO), ID1, 0);
 #pragma unroll
@@ -193,7 +192,12 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
         if (lane == 0) TL2(4, i);
       }
       __syncwarp();
-      if (last_of_scale) ++acount;
+      if (last_of_scale) {
+        ++acount;
+        if (++ab == NA) { ab = 0; aph ^= 1; }
+      }
+      if (++st == (uint32_t)NST) { st = 0; bph ^= 1; }
+      if (++sb == NSETS) { sb = 0; sph ^= 1; }
       if (++c == NC) c = 0;
     }
   } else if (warp == WARP_MMA2) {
@@ -202,13 +206,14 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
       const uint32_t ID2 = idesc_f16(Fmt<X>::id, TILE_M, KP);
       const int U = my_tiles * NC;
       int c = 0, tl = 0;
+      uint32_t pb = 0, pph = 0, sw = 0, wph = 0;
       for (int u = 0; u < U; ++u) {
-        const uint32_t pb = u % NSETS, sw = u % NSTW, lb = tl & 1;
+        const uint32_t lb = tl & 1;
         if (lane == 0) TL2(8, u);
         if (c == 0) mbar_wait(bar(BAR_LEMPTY + lb), ((tl >> 1) & 1) ^ 1);
-        mbar_wait(bar(BAR_WFULL + sw), (u / NSTW) & 1);
+        mbar_wait(bar(BAR_WFULL + sw), wph);
         if (lane == 0) TL2(9, u);
-        mbar_wait(bar(BAR_PFULL + pb), (u / NSETS) & 1);
+        mbar_wait(bar(BAR_PFULL + pb), pph);
         if (lane == 0) TL2(10, u);
         tc_fence_after();
         {
@@ -229,43 +234,62 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
           if (lane == 0) TL2(11, u);
         }
         __syncwarp();
+        if (++pb == NSETS) { pb = 0; pph ^= 1; }
+        if (++sw == (uint32_t)NSTW) { sw = 0; wph ^= 1; }
         if (++c == NC) { c = 0; ++tl; }
       }
     }
   } else if (warp == WARP_PROD) {
     // ================================ prototype-chunk producer ================================
+    // One bulk copy per unit (hi | norm [| lo] are contiguous in the packed image), running counters instead of
+    // divisions, and the last-layer tiles have a producer warp of their own: one warp doing both with `i % NC`,
+    // `i / NST` arithmetic took ~750 clk per copy and delivered every chunk just in time (MMA issuer waiting ~500 clk per
+    // unit for it, profiles/r02_timeline_fwd_tma_*.txt).
     pdl_wait();  // the packed prototype images come from the pre-pass launched just before this kernel
     const int U = my_tiles * NC;
-    const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128, bytes_n = CN * 32, bytes_w = (LSPLIT == 3 ? 2 : 1) * KP * 128;
-    auto fetch_b = [&](int i) {
-      const int c = i % NC, st = i % NST;
-      if (lane == 0) TL2(16, i);
-      mbar_wait(bar(BAR_BEMPTY + st), ((i / NST) & 1) ^ 1);
-      if (lane == 0) TL2(17, i);
-      if (lane == 0) {
-        mbar_arrive_expect_tx(bar(BAR_BFULL + st), bytes_b + bytes_n);
-        const unsigned char* src = prm.img + (size_t)c * ct.img_bytes;
-        const uint32_t dst = base + pl.b_off(st);
-        bulk_g2s(dst + OFF_BHI, src + OFF_BHI, bytes_b, bar(BAR_BFULL + st));
-        bulk_g2s(dst + (NSPLIT == 3 ? 2 : 1) * CN * 128, src + OFF_BN, bytes_n, bar(BAR_BFULL + st));
-      }
-      __syncwarp();
-    };
-    auto fetch_w = [&](int i) {
-      const int c = i % NC, sw = i % NSTW;
-      if (lane == 0) TL2(18, i);
-      mbar_wait(bar(BAR_WEMPTY + sw), ((i / NSTW) & 1) ^ 1);
-      if (lane == 0) TL2(19, i);
-      if (lane == 0) {
-        mbar_arrive_expect_tx(bar(BAR_WFULL + sw), bytes_w);
-        bulk_g2s(base + pl.w_off(sw), prm.img + (size_t)c * ct.img_bytes + OFF_W2, bytes_w, bar(BAR_WFULL + sw));
-      }
-      __syncwarp();
-    };
-    if (U > 0) fetch_b(0);
+    const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128 + CN * 32;
+    const unsigned char* img = prm.img;
+    const int img_bytes = ct.img_bytes;
+    int c = 0, st = 0;
+    uint32_t ph = 1;
+    const unsigned char* src = img;
     for (int i = 0; i < U; ++i) {
-      if (i + 1 < U) fetch_b(i + 1);
-      if (has_w) fetch_w(i);
+      if (lane == 0) TL2(16, i);
+      mbar_wait(bar(BAR_BEMPTY + st), ph);
+      if (lane == 0) {
+        TL2(17, i);
+        mbar_arrive_expect_tx(bar(BAR_BFULL + st), bytes_b);
+        bulk_g2s(base + pl.b_off(st), src, bytes_b, bar(BAR_BFULL + st));
+      }
+      __syncwarp();
+      src += img_bytes;
+      if (++c == NC) { c = 0; src = img; }
+      if (++st == NST) { st = 0; ph ^= 1; }
+    }
+  } else if (warp == WARP_PRODW) {
+    // ================================ last-layer tile producer ================================
+    if (has_w) {
+      pdl_wait();
+      const int U = my_tiles * NC;
+      const uint32_t bytes_w = (LSPLIT == 3 ? 2 : 1) * KP * 128;
+      const unsigned char* img = prm.img + OFF_W2;
+      const int img_bytes = ct.img_bytes;
+      int c = 0, sw = 0;
+      uint32_t ph = 1;
+      const unsigned char* src = img;
+      for (int i = 0; i < U; ++i) {
+        if (lane == 0) TL2(18, i);
+        mbar_wait(bar(BAR_WEMPTY + sw), ph);
+        if (lane == 0) {
+          TL2(19, i);
+          mbar_arrive_expect_tx(bar(BAR_WFULL + sw), bytes_w);
+          bulk_g2s(base + pl.w_off(sw), src, bytes_w, bar(BAR_WFULL + sw));
+        }
+        __syncwarp();
+        src += img_bytes;
+        if (++c == NC) { c = 0; src = img; }
+        if (++sw == NSTW) { sw = 0; ph ^= 1; }
+      }
     }
   } else if (warp >= WARP_Z && warp < WARP_Z + NZ) {
     // ================================ feature-tile producer + row norms ================================

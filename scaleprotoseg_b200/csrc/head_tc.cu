@@ -104,8 +104,8 @@ struct FwdParams {
   int n_tiles;
 };
 
-constexpr int NTHREADS = 480;
-constexpr int WARP_EPI0 = 0, WARP_LOAD0 = 8, WARP_PROD = 12, WARP_MMA = 13, WARP_MMA2 = 14;
+constexpr int NTHREADS = 512;
+constexpr int WARP_EPI0 = 0, WARP_LOAD0 = 8, WARP_PROD = 12, WARP_MMA = 13, WARP_MMA2 = 14, WARP_PRODW = 15;
 constexpr int MAX_NST = 8;                   // prototype-chunk ring depth is chosen at launch (2..MAX_NST)
 constexpr int A_HI = TILE_M * 128;           // 16384
 constexpr int A_NORM = TILE_M * 32;          // 4096
@@ -210,16 +210,16 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
     // epilogue of unit i-1, and the epilogue starved (timeline in profiles/).
     constexpr uint32_t ID1 = idesc_f16(Fmt<X>::id, TILE_M, CN);
     const int U = my_tiles * NC;
-    uint32_t acount = 0;
+    uint32_t acount = 0, st = 0, bph = 0;
     int c = 0;
     for (int i = 0; i < U; ++i) {
       const bool first_of_scale = c == 0 || ct.scale[c] != ct.scale[c - 1];
       const bool last_of_scale = c == NC - 1 || ct.scale[c + 1] != ct.scale[c];
-      const uint32_t ab = acount & 1, st = i % NST, sb = i & 1;
+      const uint32_t ab = acount & 1, sb = i & 1;
       if (lane == 0) TL(5, i);
       if (first_of_scale) mbar_wait(bar(BAR_AFULL + ab), (acount >> 1) & 1);
       if (lane == 0) TL(6, i);
-      mbar_wait(bar(BAR_BFULL + st), (i / NST) & 1);
+      mbar_wait(bar(BAR_BFULL + st), bph);
       if (lane == 0) TL(4, i);
       mbar_wait(bar(BAR_SEMPTY + sb), ((i >> 1) & 1) ^ 1);
       if (lane == 0) TL(7, i);
@@ -228,7 +228,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
         const uint32_t a_hi = base + pl.a_off(ab), a_lo = a_hi + A_HI;
         const uint32_t a_n = a_hi + (NSPLIT == 3 ? 2 : 1) * A_HI;
         const uint32_t b_hi = base + pl.b_off(st) + OFF_BHI, b_lo = base + pl.b_off(st) + OFF_BLO;
-        const uint32_t b_n = base + pl.b_off(st) + (NSPLIT == 3 ? 2 : 1) * CN * 128;
+        const uint32_t b_n = base + pl.b_off(st) + OFF_BN;
         const uint32_t d = tmem + TMEM_S0 + sb * CN;
         mma_f16(d, desc_noswz(a_n, NORM_LBO, NORM_SBO), desc_noswz(b_n, NORM_LBO, NORM_SBO), ID1, 0);
 #pragma unroll
@@ -246,6 +246,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       }
       __syncwarp();
       if (last_of_scale) ++acount;
+      if (++st == (uint32_t)NST) { st = 0; bph ^= 1; }
       if (++c == NC) c = 0;
     }
   } else if (warp == WARP_MMA2) {
@@ -254,10 +255,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
       const uint32_t ID2 = idesc_f16(Fmt<X>::id, TILE_M, KP);
       const int U = my_tiles * NC;
       int c = 0, tl = 0;
+      uint32_t sw = 0, wph = 0;
       for (int u = 0; u < U; ++u) {
-        const uint32_t pb = u & 1, sw = u % NSTW, lb = tl & 1;
+        const uint32_t pb = u & 1, lb = tl & 1;
         if (c == 0) mbar_wait(bar(BAR_LEMPTY + lb), ((tl >> 1) & 1) ^ 1);
-        mbar_wait(bar(BAR_WFULL + sw), (u / NSTW) & 1);
+        mbar_wait(bar(BAR_WFULL + sw), wph);
         mbar_wait(bar(BAR_PFULL + pb), (u >> 1) & 1);
         tc_fence_after();
         {
@@ -279,42 +281,56 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_fwd_tc_kernel(const __grid_c
           if (lane == 0) TL(2, u);
         }
         __syncwarp();
+        if (++sw == (uint32_t)NSTW) { sw = 0; wph ^= 1; }
         if (++c == NC) { c = 0; ++tl; }
       }
     }
   } else if (warp == WARP_PROD) {
     // ================================ prototype-chunk producer ================================
+    // One bulk copy per unit (hi | norm [| lo] are contiguous in the packed image) and running counters; the last-layer
+    // tiles have a producer warp of their own (see head_fwd_tma.cu: one warp doing both delivered every chunk just in time).
     {
       pdl_wait();  // the packed images come from the pre-pass launched just before this kernel
       const int U = my_tiles * NC;
-      const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128, bytes_n = CN * 32, bytes_w = (NSPLIT == 3 ? 2 : 1) * KP * 128;
-      // W(i) is fetched together with B(i + 1): the W slot frees a unit later than the B slot, and a producer that
-      // waited for it first would hold the B ring back
-      auto fetch_b = [&](int i) {
-        const int c = i % NC, st = i % NST;
-        mbar_wait(bar(BAR_BEMPTY + st), ((i / NST) & 1) ^ 1);
+      const uint32_t bytes_b = (NSPLIT == 3 ? 2 : 1) * CN * 128 + CN * 32;
+      const unsigned char* img = prm.img;
+      const int img_bytes = ct.img_bytes;
+      int c = 0, st = 0;
+      uint32_t ph = 1;
+      const unsigned char* src = img;
+      for (int i = 0; i < U; ++i) {
+        mbar_wait(bar(BAR_BEMPTY + st), ph);
         if (lane == 0) {
-          mbar_arrive_expect_tx(bar(BAR_BFULL + st), bytes_b + bytes_n);
-          const unsigned char* src = prm.img + (size_t)c * ct.img_bytes;
-          const uint32_t dst = base + pl.b_off(st);
-          bulk_g2s(dst + OFF_BHI, src + OFF_BHI, bytes_b, bar(BAR_BFULL + st));
-          bulk_g2s(dst + (NSPLIT == 3 ? 2 : 1) * CN * 128, src + OFF_BN, bytes_n, bar(BAR_BFULL + st));
+          mbar_arrive_expect_tx(bar(BAR_BFULL + st), bytes_b);
+          bulk_g2s(base + pl.b_off(st), src, bytes_b, bar(BAR_BFULL + st));
         }
         __syncwarp();
-      };
-      auto fetch_w = [&](int i) {
-        const int c = i % NC, sw = i % NSTW;
-        mbar_wait(bar(BAR_WEMPTY + sw), ((i / NSTW) & 1) ^ 1);
+        src += img_bytes;
+        if (++c == NC) { c = 0; src = img; }
+        if (++st == NST) { st = 0; ph ^= 1; }
+      }
+    }
+  } else if (warp == WARP_PRODW) {
+    // ================================ last-layer tile producer ================================
+    if (has_w) {
+      pdl_wait();
+      const int U = my_tiles * NC;
+      const uint32_t bytes_w = (NSPLIT == 3 ? 2 : 1) * KP * 128;
+      const unsigned char* img = prm.img + OFF_W2;
+      const int img_bytes = ct.img_bytes;
+      int c = 0, sw = 0;
+      uint32_t ph = 1;
+      const unsigned char* src = img;
+      for (int i = 0; i < U; ++i) {
+        mbar_wait(bar(BAR_WEMPTY + sw), ph);
         if (lane == 0) {
           mbar_arrive_expect_tx(bar(BAR_WFULL + sw), bytes_w);
-          bulk_g2s(base + pl.w_off(sw), prm.img + (size_t)c * ct.img_bytes + OFF_W2, bytes_w, bar(BAR_WFULL + sw));
+          bulk_g2s(base + pl.w_off(sw), src, bytes_w, bar(BAR_WFULL + sw));
         }
         __syncwarp();
-      };
-      if (U > 0) fetch_b(0);
-      for (int i = 0; i < U; ++i) {
-        if (i + 1 < U) fetch_b(i + 1);
-        if (has_w) fetch_w(i);
+        src += img_bytes;
+        if (++c == NC) { c = 0; src = img; }
+        if (++sw == NSTW) { sw = 0; ph ^= 1; }
       }
     }
   } else if (warp >= WARP_LOAD0 && warp < WARP_PROD) {

@@ -400,8 +400,9 @@ __device__ __forceinline__ void store_proto_norm(unsigned char* t_n, int t, floa
 // Prototype chunks.  The prototypes of every scale are cut into chunks of <= CN rows; the pre-pass writes
 // one packed image per chunk that the main kernels bulk-copy straight into shared memory:
 //   [Bhi  CN x 128 B  SW128]  rows j: -2 * p_(p0+j)            (hi part)
-//   [Blo  CN x 128 B  SW128]  lo part (zeros in the single-term modes)
 //   [Bn   CN x  32 B  noswz]  k=0..2: |p|^2 split in three; k=3..5: 1; rest 0
+//   [Blo  CN x 128 B  SW128]  lo part (zeros in the single-term modes)
+//   (hi | norm | lo in this order: what a kernel needs per chunk is ONE contiguous bulk copy, 10 KB single-term, 18 KB split)
 //   [W2   KP x 128 B  SW128]  rows k: ln2 * W[k, p0+j]  ('log'; W itself for 'linear'); only with a last layer
 //   [W2lo KP x 128 B  SW128]  lo part of W2 (used by the split modes)
 // ---------------------------------------------------------------------------------------------
@@ -419,7 +420,7 @@ struct ChunkTable {
 };
 
 __host__ __device__ inline int chunk_img_bytes(int kp) { return 2 * CN * 128 + CN * 32 + 2 * kp * 128; }
-constexpr int OFF_BHI = 0, OFF_BLO = CN * 128, OFF_BN = 2 * CN * 128, OFF_W2 = 2 * CN * 128 + CN * 32;
+constexpr int OFF_BHI = 0, OFF_BN = CN * 128, OFF_BLO = CN * 128 + CN * 32, OFF_W2 = 2 * CN * 128 + CN * 32;
 
 }  // namespace tc
 }  // namespace sps
