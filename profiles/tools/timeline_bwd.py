@@ -1,13 +1,14 @@
 import sys, os, ctypes, torch
-os.environ["SCALEPROTO_B200_LIB"] = "/root/repo/build/libsps_tl.so"
-sys.path.insert(0, "/root/repo")
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))   # SCALEPROTO_B200_LIB -> a -DSPS_TIMELINE build
 import scaleprotoseg_b200 as sps
 from scaleprotoseg_b200 import _lib
 from oracle import head_oracle as ho
 dev = "cuda:0"
 math = int(sys.argv[1]) if len(sys.argv) > 1 else sps.MATH_F16X3
+nhwc = len(sys.argv) > 2 and sys.argv[2] == "nhwc16"
 B, H, W, P, K = 16, 65, 65, 760, 19
 z = torch.sigmoid(torch.randn(B, 256, H, W, device=dev)); protos = torch.rand(P, 64, device=dev)
+if nhwc: z = z.half().contiguous(memory_format=torch.channels_last)
 W_ = ho.make_last_layer(ho.make_identity(P, K, 4)).contiguous().to(dev)
 N = B * H * W
 dl = torch.randn(N, K, device=dev) / N

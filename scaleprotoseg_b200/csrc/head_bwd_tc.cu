@@ -66,7 +66,8 @@ struct BwdParams {
   HeadShape s;
   ChunkTable ct;
   GroupTable gt;
-  const float* z;
+  const float* z;               // the map (ZM_LDG: fp32 NCHW; TMA modes: the 16-bit [N][C] array / hi part)
+  const void* z_lo;             // ZM_TMAHL in a split mode: lo part
   const float* protos;
   const float* dlogits;
   const float* ddist;           // [B, P, H, W] gradient arriving through the distance map (KLD loss), or nullptr
@@ -167,13 +168,13 @@ template <int NSPLIT> struct Lay {
   static constexpr int SM_RES = 0;
   static constexpr int SM_A = (GROUP_CHUNKS * RES + 1023) / 1024 * 1024;
   static constexpr int SM_G = SM_A + 2 * A_BUF;
-  static constexpr int SM_SG = SM_G + 2 * G_BUF;                   // sgbuf[2 parity][2 half][128] floats
-  static constexpr int SM_BAR = SM_SG + 2 * 2 * 128 * 4;
+  static constexpr int SM_SG = SM_G + 2 * G_BUF;                   // sgbuf[4 tiles in flight][2 half / set][128] floats
+  static constexpr int SM_BAR = SM_SG + 4 * 2 * 128 * 4;
   static constexpr int SM_TOTAL = SM_BAR + 256 + 1024;
 };
 constexpr int T_S = 0, T_DA = 128, T_DZ = 256, T_ACC = 320;
 enum { B_AFULL = 0, B_AEMPTY = 2, B_SFULL = 4, B_SEMPTY = 6, B_GFULL = 8, B_GEMPTY = 10, B_DZFULL = 12, B_DZEMPTY = 13,
-       B_RES = 14, B_ACC = 15, B_TFULL = 16, B_COUNT = 18 };
+       B_RES = 14, B_ACC = 15, B_TFULL = 16, B_SGFULL = 18, B_COUNT = 22 };
 
 // HAS_DD: a gradient also arrives through the dense distance map (prm.ddist; the KLD loss of stage-1 training).
 template <typename X, int NSPLIT, bool HAS_DD, int ZMODE>
@@ -181,6 +182,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
   using L = Lay<NSPLIT>;
   // the feature tile has a lo part: fp32 source in a split mode (a 16-bit map is exact in one term)
   constexpr bool ZLO = NSPLIT == 3 && ZMODE != ZM_TMA16;
+  constexpr bool RD_BY_TILE_WARPS = ZMODE != ZM_LDG;
   constexpr int A_BUF = L::A_BUF, RES = L::RES, SM_RES = L::SM_RES, SM_A = L::SM_A, SM_G = L::SM_G, SM_SG = L::SM_SG,
                 SM_BAR = L::SM_BAR;
   extern __shared__ unsigned char smem_raw[];
@@ -204,18 +206,25 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
 
   if (threadIdx.x == 0) {
     TLB_CTA(5);
+    // TMA modes: the dz read-out (TMEM -> + 2 z sum(gamma) -> HBM) runs on the four tile warps, which have little else to
+    // do once the tile arrives by TMA; on the epilogue warps it was 2 350 of the 9 000 clk tile period
+    // (profiles/r02_timeline_bwd_tma16_before.txt).  The loader-fed mode keeps it on the epilogue warps: its tile warps
+    // hold the next tile's 64 prefetched values in registers.
     for (int i = 0; i < 2; ++i) {
       mbar_init(bar(B_AFULL + i), 4);
-      mbar_init(bar(B_AEMPTY + i), 9);   // 8 epilogue warps (dz read z from smem) + 1 commit (dp GEMM read it)
+      mbar_init(bar(B_AEMPTY + i), RD_BY_TILE_WARPS ? 1 : 9);   // commit of the tile's last GEMMs (+ the 8 epilogue warps whose read-out reads the z tile)
+      mbar_init(bar(B_SGFULL + i), 8);   // row sums of gamma of a tile written by the 8 epilogue warps
+      mbar_init(bar(B_SGFULL + 2 + i), 8);
       mbar_init(bar(B_SFULL + i), 1);
-      mbar_init(bar(B_SEMPTY + i), 8);
-      mbar_init(bar(B_GFULL + i), 8);
+      // TMA modes: the two epilogue sets take ALTERNATE units (4 warps per unit); loader-fed mode: column halves of one unit
+      mbar_init(bar(B_SEMPTY + i), RD_BY_TILE_WARPS ? 4 : 8);
+      mbar_init(bar(B_GFULL + i), RD_BY_TILE_WARPS ? 4 : 8);
       mbar_init(bar(B_GEMPTY + i), 1);
     }
     mbar_init(bar(B_TFULL), 1);      // TMA modes: arrive.expect_tx + the tile bytes
     mbar_init(bar(B_TFULL + 1), 1);
     mbar_init(bar(B_DZFULL), 1);
-    mbar_init(bar(B_DZEMPTY), 8);
+    mbar_init(bar(B_DZEMPTY), RD_BY_TILE_WARPS ? 4 : 8);
     mbar_init(bar(B_RES), 1);
     mbar_init(bar(B_ACC), 1);
     mbar_fence_init();
@@ -330,6 +339,77 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
 #pragma unroll
       for (int k = 0; k < KP_BWD; ++k) dl[k] = k < kl ? __ldg(src + k) : 0.0f;
     };
+    float G_loader = 1.0f;
+    // dz of (tile tj, this scale) by the tile warps (TMA modes): acc + 2 z sum_p gamma, row m of the tile per thread.
+    // Two steps with the NEXT tile's load between them: readout_begin empties the TMEM accumulator (the issuer may start
+    // the next tile's dz GEMMs), readout_finish does the arithmetic and the stores.  z comes back from global memory (the
+    // row is one 128-byte line, L2-resident: the tile was loaded from it a few microseconds earlier), so the shared-memory
+    // stage is free as soon as the tile's GEMMs have completed and the next load never waits for a read-out.
+    uint32_t r0[32], r1[32];
+    auto readout_begin = [&](int tj) {
+      const uint32_t lane_base = ((uint32_t)((warp & 3) * 32)) << 16;
+      mbar_wait(bar(B_DZFULL), tj & 1);
+      tc_fence_after();
+      tmem_ld32(tmem + lane_base + T_DZ, r0);
+      tmem_ld32(tmem + lane_base + T_DZ + 32, r1);
+      tmem_ld_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(B_DZEMPTY));
+    };
+    auto readout_finish = [&](int tj) {
+      const long long n = row_of(tj);
+      if (prm.dz == nullptr || n >= s.N) return;
+      const float invG_ = 1.0f / G_loader;
+      mbar_wait(bar(B_SGFULL + (tj & 3)), (tj >> 2) & 1);
+      const float* sgb = reinterpret_cast<const float*>(gbase + SM_SG) + (tj & 3) * 256;
+      const float tot2 = 2.0f * (sgb[m] + sgb[128 + m]);
+      const uint4* zg = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(prm.z) + ((size_t)n * s.C + (size_t)sc * s.D) * 2);
+      const uint4* zgl = reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(prm.z_lo) + ((size_t)n * s.C + (size_t)sc * s.D) * 2);
+      const uint32_t bimg = (uint32_t)n / hw, pix = (uint32_t)n % hw;
+#pragma unroll
+      for (int h = 0; h < 2; ++h) {
+        uint4 zq[4], zl[4];
+#pragma unroll
+        for (int gq = 0; gq < 4; ++gq) {
+          zq[gq] = __ldg(zg + 4 * h + gq);
+          if (ZLO) zl[gq] = __ldg(zgl + 4 * h + gq);
+        }
+        float dv[32];
+#pragma unroll
+        for (int gq = 0; gq < 4; ++gq) {
+          const uint32_t zw[4] = {zq[gq].x, zq[gq].y, zq[gq].z, zq[gq].w};
+          const uint32_t zlw[4] = {ZLO ? zl[gq].x : 0u, ZLO ? zl[gq].y : 0u, ZLO ? zl[gq].z : 0u, ZLO ? zl[gq].w : 0u};
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float2 zf = Pack2<X>::unpack(zw[e]);
+            if (ZLO) {
+              const float2 zl2 = Pack2<X>::unpack(zlw[e]);
+              zf.x += zl2.x;
+              zf.y += zl2.y;
+            }
+            const int k = gq * 8 + 2 * e;
+            dv[k] = fmaf(zf.x, tot2, __uint_as_float(h == 0 ? r0[k] : r1[k])) * invG_;
+            dv[k + 1] = fmaf(zf.y, tot2, __uint_as_float(h == 0 ? r0[k + 1] : r1[k + 1])) * invG_;
+          }
+        }
+        if (ZMODE == ZM_TMA16) {
+          uint4* dst = reinterpret_cast<uint4*>(reinterpret_cast<unsigned char*>(prm.dz) + ((size_t)n * s.C + (size_t)sc * s.D + 32 * h) * 2);
+#pragma unroll
+          for (int gq = 0; gq < 4; ++gq)
+            dst[gq] = make_uint4(Pack2<X>::pack(dv[gq * 8], dv[gq * 8 + 1]), Pack2<X>::pack(dv[gq * 8 + 2], dv[gq * 8 + 3]),
+                                 Pack2<X>::pack(dv[gq * 8 + 4], dv[gq * 8 + 5]), Pack2<X>::pack(dv[gq * 8 + 6], dv[gq * 8 + 7]));
+        } else {
+          float* dzp = prm.dz + ((size_t)bimg * s.C + (size_t)sc * s.D + 32 * h) * s.HW + pix;
+          const size_t pitch = (size_t)s.HW;
+#pragma unroll
+          for (int k = 0; k < 32; ++k) {
+            if (multi) atomicAdd(dzp, dv[k]); else *dzp = dv[k];
+            dzp += pitch;
+          }
+        }
+      }
+    };
     ZStage<X, NSPLIT> zst;
     float dl[KP_BWD];
     if (my_tiles > 0) {
@@ -339,12 +419,14 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
         zst.issue_half(0, p0, hw, s.D);
         zst.issue_half(1, p0, hw, s.D);
       }
-      load_dl(n0, dl);
+      if (ZMODE == ZM_LDG) load_dl(n0, dl);
     }
     pdl_wait();  // max |dlogits| comes from the pre-pass launched just before this kernel (the loads above are in flight)
     const float G = grad_scale(*reinterpret_cast<const volatile unsigned int*>(prm.amax_bits));
-    for (int ti = 0; ti < my_tiles; ++ti) {
+    G_loader = G;
+    auto load_tile = [&](int ti) {
       const uint32_t ab = ti & 1;
+      if (ZMODE != ZM_LDG) load_dl(row_of(ti), dl);   // TMA modes: the tile warps run two tiles ahead of the read-outs, no prefetch across tiles
       if (m == 0) TLB(2, 4 * ti);
       mbar_wait(bar(B_AEMPTY + ab), ((ti >> 1) & 1) ^ 1);
       if (m == 0) TLB(2, 4 * ti + 1);
@@ -382,14 +464,28 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       if (lane == 0) mbar_arrive(bar(B_AFULL + ab));
       if (m == 0) TLB(2, 4 * ti + 2);
       // the next tile's loads go out AFTER the arrive: mbarrier.arrive has release semantics and would wait for them
-      if (ti + 1 < my_tiles) {
+      if (ZMODE == ZM_LDG && ti + 1 < my_tiles) {
         const long long nn = row_of(ti + 1);
-        if (ZMODE == ZM_LDG) {
-          const float* pn = row_ptr(nn);
-          zst.issue_half(0, pn, hw, s.D);
-          zst.issue_half(1, pn, hw, s.D);
-        }
+        const float* pn = row_ptr(nn);
+        zst.issue_half(0, pn, hw, s.D);
+        zst.issue_half(1, pn, hw, s.D);
         load_dl(nn, dl);
+      }
+    };
+    if (!RD_BY_TILE_WARPS) {
+      for (int ti = 0; ti < my_tiles; ++ti) load_tile(ti);
+    } else {
+      // Loads run two tiles ahead of the read-outs: a stage is free again when the GEMMs of its tile have completed (the
+      // read-out takes z from L2, not from the stage), which is also when that tile's dz accumulator is complete.
+      //   begin(t): wait for the accumulator, move it to registers, release it to the issuer
+      //   load(t+2): into the stage tile t has just left
+      //   finish(t): 2 z sum(gamma) + acc, stores
+      if (my_tiles > 0) load_tile(0);
+      if (my_tiles > 1) load_tile(1);
+      for (int t = 0; t < my_tiles; ++t) {
+        readout_begin(t);
+        if (t + 2 < my_tiles) load_tile(t + 2);
+        readout_finish(t);
       }
     }
   }
@@ -487,6 +583,103 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       }
       if (threadIdx.x == 0) TLB(4, 4 * tj + 2);
     };
+    if (RD_BY_TILE_WARPS) {
+      // ---- TMA modes.  The two warp sets take ALTERNATE units, each walking both 32-column halves of its unit: the two
+      // warps of an SM sub-partition are then out of phase (one computes while the other waits for its accumulators or
+      // stores its tiles) instead of stalling together.  dz is read out by the tile warps; a set publishes its row sums
+      // of gamma for a tile as soon as it has finished its last unit of that tile.
+      const int set = half;
+      int ti = set / nch, j = set % nch;
+      float sg = 0.f;
+      auto publish = [&](int t_from, int t_to, float v) {   // tiles [t_from, t_to): the first gets v, the rest (no unit of this set) 0
+        for (int t = t_from; t < t_to; ++t) {
+          sgbuf[(t & 3) * 256 + set * 128 + m] = t == t_from ? v : 0.f;
+          __syncwarp();
+          if (lane == 0) mbar_arrive(bar(B_SGFULL + (t & 3)));
+        }
+      };
+      if (U <= set) publish(0, my_tiles, 0.f);      // no unit at all for this set
+      else if (set == 1) publish(0, ti, 0.f);      // (one chunk per tile: the second set has no unit in tile 0)
+      for (int u = set; u < U; u += 2) {
+        const uint32_t sb = u & 1, gb = u & 1, ph = (u >> 1) & 1;
+        const long long n_row = ((long long)cta_local + (long long)ti * ncta) * TILE_M + m;
+        const bool row_valid = n_row < s.N;
+        const uint32_t row_b = row_valid ? (uint32_t)n_row / (uint32_t)s.HW : 0u, row_pix = row_valid ? (uint32_t)n_row % (uint32_t)s.HW : 0u;
+        unsigned char* grow = gbase + SM_G + gb * G_BUF + (uint32_t)m * 128u;
+#pragma unroll 1
+        for (int hf = 0; hf < 2; ++hf) {
+          uint32_t rs[32], ra[32];
+          float dd[HAS_DD ? 32 : 1];
+          if (HAS_DD) {
+            const int c = c0 + j, nlive = row_valid ? ct.n[c] - hf * 32 : 0;
+            const float* src = prm.ddist + ((size_t)row_b * s.P + ct.p0[c] + hf * 32) * s.HW + row_pix;
+#pragma unroll
+            for (int k = 0; k < 32; ++k) dd[k] = k < nlive ? __ldg(src + (size_t)k * s.HW) : 0.0f;
+          }
+          if (hf == 0) {
+            mbar_wait(bar(B_SFULL + sb), ph);
+            tc_fence_after();
+          }
+          tmem_ld32(tmem + lane_base + T_S + sb * CN + hf * 32, rs);
+          tmem_ld32(tmem + lane_base + T_DA + sb * CN + hf * 32, ra);
+          tmem_ld_wait();
+          if (hf == 1) {
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(B_SEMPTY + sb));
+          }
+          uint32_t gw[16], aw[16];
+          auto gamma_act = [&](auto log_t) {
+            constexpr bool LOG = decltype(log_t)::value;
+#pragma unroll
+            for (int e = 0; e < 16; ++e) {
+              float gm[2], a2[2];
+#pragma unroll
+              for (int h = 0; h < 2; ++h) {
+                const float sv = __uint_as_float(rs[2 * e + h]), dav = __uint_as_float(ra[2 * e + h]);
+                const float d = fmaxf(sv, 0.0f);
+                float ap, av;
+                if (LOG) {
+                  const float s1 = d + 1.0f, ru = rcp_approx(s1 * (d + eps));
+                  ap = -ome * ru;
+                  av = lg2_approx(s1 * s1 * ru);
+                } else {
+                  ap = -1.0f;
+                  av = -d;
+                }
+                gm[h] = sv > 0.0f ? (HAS_DD ? fmaf(dav, ap, dd[2 * e + h] * G) : dav * ap) : 0.0f;
+                a2[h] = av;
+                sg += gm[h];
+              }
+              gw[e] = Pack2<X>::pack(gm[0], gm[1]);
+              aw[e] = Pack2<X>::pack(a2[0], a2[1]);
+            }
+          };
+          if (is_log) gamma_act(std::true_type{}); else gamma_act(std::false_type{});
+          if (hf == 0) mbar_wait(bar(B_GEMPTY + gb), ph ^ 1);
+#pragma unroll
+          for (int gq = 0; gq < 4; ++gq) {
+            const uint32_t off = (((uint32_t)(hf * 4 + gq)) ^ ((uint32_t)m & 7u)) << 4;
+            *reinterpret_cast<uint4*>(grow + off) = make_uint4(gw[4 * gq], gw[4 * gq + 1], gw[4 * gq + 2], gw[4 * gq + 3]);
+            *reinterpret_cast<uint4*>(grow + TILE_M * 128 + off) = make_uint4(aw[4 * gq], aw[4 * gq + 1], aw[4 * gq + 2], aw[4 * gq + 3]);
+          }
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(B_GFULL + gb));
+        // next unit of this set; leaving the tile publishes its row sums
+        int nti = ti, nj = j + 2;
+        while (nj >= nch) { nj -= nch; ++nti; }
+        const bool more = u + 2 < U;
+        if (!more) nti = my_tiles;
+        if (nti != ti) {
+          publish(ti, nti, sg);
+          sg = 0.f;
+        }
+        ti = nti;
+        j = nj;
+      }
+    } else {
     int u = 0;
     for (int ti = 0; ti < my_tiles; ++ti) {
       float sg = 0.f;
@@ -563,6 +756,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) head_bwd_tc_kernel(const __grid_c
       sgbuf[(ti & 1) * 256 + half * 128 + m] = sg;   // row sums of gamma of this tile (read after the named barrier in dz_readout)
     }
     if (my_tiles > 0) dz_readout(my_tiles - 1);
+    }
     if (threadIdx.x == 0) TLB_CTA(6);
     pdl_launch_dependents();   // the reduce kernel may be scheduled as the CTAs drain (it waits for the whole grid)
     // ---- partial dp / dW of this CTA ----
@@ -824,6 +1018,7 @@ static int launch_bwd_slab(const HeadShape& s, int zmode, const void* z, const v
   SPS_CUDA_TRY(cudaGetLastError());
   prm.s = s;
   prm.z = reinterpret_cast<const float*>(z);
+  prm.z_lo = z_lo != nullptr ? z_lo : z;
   prm.protos = protos;
   prm.dlogits = dlogits;
   prm.dl_stride = dl_stride;
