@@ -709,15 +709,17 @@ int launch_bwd_reduce(const float* part_dp, long long c1, float* dprotos, const 
                       const float* part_cs, const float* protos, int D, int P, cudaStream_t st);
 
 static int wide_nsplit(int n_chunks, int n_tiles) {
-  // tile ranges per chunk: the grid (n_chunks * ranges CTAs, one per SM at a time) should fill whole waves; at least two
-  // waves so that the tail of one range overlaps the start of another, never more ranges than tiles
+  // tile ranges per chunk: the grid (n_chunks * ranges CTAs, one per SM at a time) should fill whole waves, with at least two
+  // waves (the tail of one range overlaps the start of another) but few of them: every CTA pays a prologue (resident
+  // operands, first tile) and a 61 KB partial flush, and every range adds a partial buffer to the reduction
   const int sms = sm_count();
   int best = 1;
-  double best_eff = 0.0;
-  for (int ns = 1; ns <= 16 && ns <= n_tiles; ++ns) {
+  double best_score = -1.0;
+  for (int ns = 1; ns <= 8 && ns <= n_tiles; ++ns) {
     const int ctas = n_chunks * ns, waves = (ctas + sms - 1) / sms;
-    const double eff = (double)ctas / ((double)waves * sms) - (waves < 2 ? 0.25 : 0.0);
-    if (eff > best_eff + 1e-9) best_eff = eff, best = ns;
+    const double eff = (double)ctas / ((double)waves * sms);
+    const double score = eff - (waves < 2 ? 0.25 : 0.0) - 0.01 * waves;
+    if (score > best_score + 1e-9) best_score = score, best = ns;
   }
   return best;
 }
