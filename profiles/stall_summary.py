@@ -1,16 +1,28 @@
 #!/usr/bin/env python
 """Summarise `ncu -i X.ncu-rep --page source --csv` (one kernel): stall-reason totals and the hottest SASS lines.
-usage: python profiles/stall_summary.py source_page.csv [top_n] [kernel_index]"""
+usage: python profiles/stall_summary.py source_page.csv [top_n] [kernel_index | all out_prefix]
+With `all`, one summary per captured launch is written to <out_prefix><index>_<kernel>.txt."""
+import contextlib
 import csv
+import re
 import sys
 
 
 def main():
     rows = list(csv.reader(open(sys.argv[1])))
     topn = int(sys.argv[2]) if len(sys.argv) > 2 else 40
-    which = int(sys.argv[3]) if len(sys.argv) > 3 else 0
     starts = [i for i, r in enumerate(rows) if r and r[0] == "Kernel Name"]
-    rows = rows[starts[which]:]
+    if len(sys.argv) > 3 and sys.argv[3] == "all":
+        for which, st in enumerate(starts):
+            name = re.sub(r"[^A-Za-z0-9_]+", "_", re.sub(r"[<(].*", "", rows[st][1].replace("void ", "")))[:40]
+            with open(f"{sys.argv[4]}{which:02d}_{name}.txt", "w") as f, contextlib.redirect_stdout(f):
+                summarize(rows[st:], topn)
+        return
+    which = int(sys.argv[3]) if len(sys.argv) > 3 else 0
+    summarize(rows[starts[which]:], topn)
+
+
+def summarize(rows, topn):
     h = next(i for i, r in enumerate(rows) if r and r[0] == "Address")
     hdr = rows[h]
     ix = {n: i for i, n in enumerate(hdr)}
