@@ -150,14 +150,33 @@ size_t sps_head_fwd_workspace_bytes(const SpsHeadDesc* desc);
 int sps_head_fwd(const SpsHeadDesc* desc, const void* z, const float* protos, const float* last_w,
                  float* logits, float* dist, float* act, void* workspace, size_t workspace_bytes, void* stream);
 
+/* Prototype head forward that allocates nothing and takes no workspace: for callers that cannot call cudaMalloc (code
+ * under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * NO COUNTERPART IN THE REFERENCE.
+ * Same arguments, outputs, routing and error codes as sps_head_fwd; the scratch the forward needs (the packed prototype /
+ * last-layer images, sps_head_fwd_workspace_bytes(desc)) lives in a static device array of SPS_STATIC_SCRATCH_BYTES
+ * inside the library (held by every GPU that loads the library until exit). The call itself uses no cudaMalloc /
+ * cudaFree / allocating library routine.
+ *   - shapes whose scratch exceeds SPS_STATIC_SCRATCH_BYTES are rejected with SPS_ERR_WORKSPACE and a message naming
+ *     both sizes (Cityscapes shape: 0.3 MB; COCO-Stuff shape with 16-bit maps: 6.5 MB; an fp32 map that needs the 16-bit
+ *     re-lay, e.g. K > 32 with fp32 maps, does not fit: use sps_head_fwd);
+ *   - every call on a device shares the one array: calls that overlap on the GPU (two streams, two threads, two graphs
+ *     replayed concurrently) RACE; serialise them on one stream. Contents left by a call are never read by the next
+ *     (the pre-pass rewrites all of it), so nothing needs clearing between calls;
+ *   - the first call on each device asks the runtime for the array's address (cudaGetSymbolAddress, with that device
+ *     current): make it once outside graph capture. */
+#define SPS_STATIC_SCRATCH_BYTES (8u << 20)
+int sps_head_fwd_static(const SpsHeadDesc* desc, const void* z, const float* protos, const float* last_w,
+                        float* logits, float* dist, float* act, void* stream);
+
 /* Prototype head backward (what autograd derives from the lines above; driven by manual_backward,
  * segmentation/model/module_multiscale.py:292).  d and a are recomputed from z and protos.
  *   dlogits [N,K] or NULL, ddist [B,P,H,W] or NULL (KLD loss back-props straight into distances,
  *   module_multiscale.py:242), dact [N,P] or NULL.
  *   dz (same element type and layout as z) or NULL, dprotos [P,D] or NULL, dlast_w [K,P] or NULL: OVERWRITTEN.
  *   workspace: >= sps_workspace_bytes(desc) bytes, contents undefined on entry and exit.
- * Routing: a tensor-core math mode with last_w, dlogits (and optionally ddist) runs the tcgen05 backward (K <= 256; more
- * than 32 classes run as slabs of 32, the gradients being linear in dlogits); a gradient through act, a call without
+ * Routing: a tensor-core math mode with last_w, dlogits (and optionally ddist) runs the tcgen05 backward (more
+ * than 32 classes: the one-pass wide backward, K <= 192, D == 64, no ddist; with ddist they run as slabs of 32); a gradient through act, a call without
  * last_w/dlogits, K > 256, or SPS_MATH_FP32 runs the exact-operand CUDA-core kernels. */
 int sps_head_bwd(const SpsHeadDesc* desc, const void* z, const float* protos, const float* last_w,
                  const float* dlogits, const float* ddist, const float* dact, void* dz, float* dprotos,

@@ -52,6 +52,8 @@ class SpsKldDesc(C.Structure):
 
 
 _P = C.c_void_p
+STATIC_SCRATCH_BYTES = 8 << 20   # SPS_STATIC_SCRATCH_BYTES
+
 _SIGNATURES = {
     "sps_version": (C.c_int, []),
     "sps_last_error": (C.c_char_p, []),
@@ -62,6 +64,7 @@ _SIGNATURES = {
     "sps_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc)]),
     "sps_head_fwd_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc)]),
     "sps_head_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
+    "sps_head_fwd_static": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, _P]),
     "sps_head_bwd": (C.c_int, [C.POINTER(SpsHeadDesc), _P, _P, _P, _P, _P, _P, _P, _P, _P, _P, C.c_size_t, _P]),
     "sps_group_fwd": (C.c_int, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc), _P, _P, _P, _P]),
     "sps_group_workspace_bytes": (C.c_size_t, [C.POINTER(SpsHeadDesc), C.POINTER(SpsGroupDesc)]),

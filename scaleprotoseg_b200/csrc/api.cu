@@ -3,6 +3,7 @@
 #include <string.h>
 
 #include <atomic>
+#include <mutex>
 
 #include "common.cuh"
 
@@ -182,6 +183,52 @@ int sps_head_fwd(const SpsHeadDesc* desc, const void* z, const float* protos, co
     return launch_head_fwd_simt(s, zf, protos, last_w, logits, dist, act, st);
   }
   return launch_head_fwd_tc(s, desc->math, zf, protos, last_w, logits, dist, act, workspace, workspace_bytes, st);
+}
+
+// ---- allocation-free forward (no counterpart in the reference; see the header) ---------------------------------------
+// The scratch of the forward (the packed prototype / last-layer chunk images the pre-pass writes and the main kernel
+// reads) lives in this file-scope device array instead of a caller workspace: every GPU that loads the library holds
+// SPS_STATIC_SCRATCH_BYTES of it until exit. In host code `g_fwd_scratch` is only a handle for the runtime, not a device
+// address: the address is asked for once per device, with that device current, and cached.
+static __device__ __align__(256) unsigned char g_fwd_scratch[SPS_STATIC_SCRATCH_BYTES];
+
+static const int MAX_DEVICES = 64;
+static void* g_fwd_scratch_addr[MAX_DEVICES] = {};
+static std::mutex g_fwd_scratch_mutex;
+
+static int fwd_scratch_address(void** out) {
+  int dev = -1;
+  SPS_CUDA_TRY(cudaGetDevice(&dev));
+  SPS_REQUIRE(dev >= 0 && dev < MAX_DEVICES, SPS_ERR_UNSUPPORTED, "device ordinal %d outside [0,%d)", dev, MAX_DEVICES);
+  std::lock_guard<std::mutex> lock(g_fwd_scratch_mutex);
+  if (g_fwd_scratch_addr[dev] == nullptr) {
+    void* p = nullptr;
+    SPS_CUDA_TRY(cudaGetSymbolAddress(&p, g_fwd_scratch));   // the copy of the array on the CURRENT device
+    SPS_REQUIRE(p != nullptr, SPS_ERR_CUDA, "cudaGetSymbolAddress returned NULL for the static scratch on device %d", dev);
+    g_fwd_scratch_addr[dev] = p;
+  }
+  *out = g_fwd_scratch_addr[dev];
+  return SPS_OK;
+}
+
+int sps_head_fwd_static(const SpsHeadDesc* desc, const void* z, const float* protos, const float* last_w, float* logits,
+                        float* dist, float* act, void* stream) {
+  int rc = validate_desc(desc);
+  if (rc != SPS_OK) return rc;
+  const size_t need = sps_head_fwd_workspace_bytes(desc);
+  SPS_REQUIRE(need <= (size_t)SPS_STATIC_SCRATCH_BYTES, SPS_ERR_WORKSPACE,
+              "head_fwd_static: this shape needs %zu bytes of scratch, the static array holds %zu (B=%d P=%d K=%d%s); "
+              "use sps_head_fwd with a caller workspace",
+              need, (size_t)SPS_STATIC_SCRATCH_BYTES, desc->B, desc->P, desc->K,
+              (desc->z_dtype == SPS_Z_F32 && need > (size_t)(1u << 20)) ? ", includes the 16-bit re-lay of the fp32 map" : "");
+  void* scratch = nullptr;
+  if (need > 0) {
+    rc = fwd_scratch_address(&scratch);
+    if (rc != SPS_OK) return rc;
+  }
+  // nothing in the scratch has to start at zero: the pre-pass rewrites every byte the main kernel reads, so what the
+  // previous call left behind is never seen
+  return sps_head_fwd(desc, z, protos, last_w, logits, dist, act, scratch, need > 0 ? (size_t)SPS_STATIC_SCRATCH_BYTES : 0, stream);
 }
 
 int sps_head_bwd(const SpsHeadDesc* desc, const void* z, const float* protos, const float* last_w,
