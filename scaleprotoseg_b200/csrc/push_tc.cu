@@ -18,6 +18,17 @@ namespace sps {
 namespace tcp {
 using namespace sps::tc;
 
+#ifdef SPS_PUSH_TIMELINE
+// Debug build only: clock stamps of CTA 0, row = event kind, column = tile index (profiles/tools/timeline_push.py)
+__device__ long long g_tlp[16 * 1024];
+#define TLP(row, idx)                                                                                  \
+  do {                                                                                                 \
+    if (blockIdx.x == 0 && (idx) >= 0 && (idx) < 1024) g_tlp[(row) * 1024 + (idx)] = clock64();          \
+  } while (0)
+#else
+#define TLP(row, idx) do { } while (0)
+#endif
+
 constexpr int PGROUP_CHUNKS = 4;   // 256 prototype rows per CTA
 constexpr int MAX_PGROUPS = 64;
 constexpr int NTHREADS = 576;      // 8 epilogue warps, 8 loader warps, 1 MMA warp, 1 resident-operand warp
@@ -48,21 +59,49 @@ struct PushParams {
 
 // ZLO: the streamed feature tile has a lo part (fp32 source in a split mode; a 16-bit map is exact in one term)
 template <int NSPLIT, bool ZLO> struct PLay {
-  static constexpr int RES_T = (NSPLIT == 3 ? 2 : 1) * TILE_M * 128 + TILE_M * 32;        // one 128-row prototype tile
-  static constexpr int ROFF_LO = TILE_M * 128, ROFF_N = (NSPLIT == 3 ? 2 : 1) * TILE_M * 128;
+  static constexpr int RES_N = TILE_M * 32;                                               // norm K step of one 128-row prototype tile
   static constexpr int STAGE = (ZLO ? 2 : 1) * TILE_M * 128 + TILE_M * 32;                // z hi [lo] | norm
   static constexpr int SOFF_LO = TILE_M * 128, SOFF_N = (ZLO ? 2 : 1) * TILE_M * 128;
   static constexpr int SM_RES = 0;
-  static constexpr int SM_Z = 2 * RES_T;
+  static constexpr int SM_Z = 2 * RES_N;
   static constexpr int NSTAGE = (227 * 1024 - 2048 - 4096 - SM_Z) / STAGE >= 6 ? 6 : (227 * 1024 - 2048 - 4096 - SM_Z) / STAGE;
   // labels of the tile in flight: a ring of LAB_RING >= NSTAGE + 2 slots needs no barrier of its own (the loader of
-  // tile i has waited for the MMA of tile i-NSTAGE, which waited for the epilogue of tile i-NSTAGE-2)
+  // tile i has waited for the MMA of tile i-NSTAGE, which waited for the epilogue of tile i-NSTAGE-1)
   static constexpr int LAB_RING = 8;
   static constexpr int SM_LAB = SM_Z + NSTAGE * STAGE;
   static constexpr int SM_BAR = SM_LAB + LAB_RING * TILE_M * 4;
-  static constexpr int SM_TOTAL = SM_BAR + 256 + 1024;
+  static constexpr int SM_TOTAL = SM_BAR + 512 + 1024;
 };
-enum { PB_ZFULL = 0, PB_ZEMPTY = 8, PB_DFULL = 16, PB_DEMPTY = 18, PB_RES = 20, PB_RES2 = 21, PB_TFULL = 22, PB_COUNT = 30 };
+// TMEM columns: a ring of three 128-column accumulators (unit u = tile * n_mt + prototype tile, slot u % 3) and the
+// resident prototype operand (-2p, hi | lo part: 32 columns each = 64 channels as 16-bit pairs) of prototype tile t at
+// TM_A + t*64.  With the A operand in TMEM an M128 x N128 x K16 MMA reads 4 KB of shared memory instead of 8 (measured,
+// profiles/tools/mma_ts_probe.cu: same 65 clk), which leaves half of the shared-memory bandwidth to the feature loaders.
+// Each slot is used by the two epilogue sets in turn; no wait can alias because a set reaches unit u only after it has
+// seen the commit of unit u-2, and commits are ordered (so unit u-3, the slot's previous user, has committed too).
+constexpr int D_SLOTS = 3;
+constexpr uint32_t TM_A = 384;
+enum { PB_ZFULL = 0, PB_ZEMPTY = 8, PB_DFULL = 16, PB_DEMPTY = 20, PB_RES = 24, PB_RES2 = 25, PB_ATMEM = 26, PB_TFULL = 27, PB_COUNT = 36 };
+
+__device__ __forceinline__ void mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p, q;\n\t"
+      "elect.sync _|q, 0xffffffff;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "@q tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+      ::"r"(tmem_d), "r"(tmem_a), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_st32(uint32_t taddr, const uint32_t (&r)[32]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0],"
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16,"
+      " %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+      ::"r"(taddr), "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]),
+        "r"(r[9]), "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15]), "r"(r[16]), "r"(r[17]),
+        "r"(r[18]), "r"(r[19]), "r"(r[20]), "r"(r[21]), "r"(r[22]), "r"(r[23]), "r"(r[24]), "r"(r[25]), "r"(r[26]),
+        "r"(r[27]), "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
+      : "memory");
+}
 
 __device__ __forceinline__ unsigned long long absent_key64() { return ((unsigned long long)0x501502F9u) << 32; }  // 1e10f
 
@@ -82,6 +121,10 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + L::SM_BAR + 8 * PB_COUNT);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
+#ifdef SPS_PUSH_TIMELINE
+  long long cta_t0;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(cta_t0));
+#endif
   int g = 0;
   while (g + 1 < gt.n_groups && (int)blockIdx.x >= gt.cta0[g + 1]) ++g;
   const int cta_local = (int)blockIdx.x - gt.cta0[g], ncta = gt.ncta[g];
@@ -91,19 +134,20 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
   const int my_tiles = (int)(t_hi - t_lo);
 
   // zero the resident operand area (rows of missing chunks must read as zeros), then barrier init
-  for (int i = threadIdx.x; i < 2 * L::RES_T / 16; i += NTHREADS) reinterpret_cast<uint4*>(gbase + L::SM_RES)[i] = make_uint4(0, 0, 0, 0);
+  for (int i = threadIdx.x; i < 2 * L::RES_N / 16; i += NTHREADS) reinterpret_cast<uint4*>(gbase + L::SM_RES)[i] = make_uint4(0, 0, 0, 0);
   if (threadIdx.x == 0) {
     for (int i = 0; i < L::NSTAGE; ++i) {
       mbar_init(bar(PB_ZFULL + i), 4);     // the 4 warps of one loader group
       mbar_init(bar(PB_ZEMPTY + i), 1);    // tcgen05.commit
       mbar_init(bar(PB_TFULL + i), 1);     // TMA mode: arrive.expect_tx + the tile bytes
     }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(bar(PB_DFULL + i), 1);
-      mbar_init(bar(PB_DEMPTY + i), 8);
+    for (int i = 0; i < D_SLOTS; ++i) {
+      mbar_init(bar(PB_DFULL + i), 1);     // tcgen05.commit
+      mbar_init(bar(PB_DEMPTY + i), 4);    // the 4 epilogue warps of the prototype tile that used the slot
     }
     mbar_init(bar(PB_RES), 1);
     mbar_init(bar(PB_RES2), 1);
+    mbar_init(bar(PB_ATMEM), 8);           // the 8 epilogue warps have written the prototype operand into TMEM
     mbar_fence_init();
   }
   fence_proxy_async();
@@ -115,14 +159,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
 
   if (warp == WARP_RES) {
     if (lane == 0) {
-      const uint32_t per = (NSPLIT == 3 ? 2 : 1) * CN * 128 + CN * 32;
-      mbar_arrive_expect_tx(bar(PB_RES), (uint32_t)nch * per);
+      // the norm K step of the prototype tiles stays in shared memory (it also carries the class mask); -2p goes to TMEM
+      mbar_arrive_expect_tx(bar(PB_RES), (uint32_t)nch * CN * 32);
       for (int j = 0; j < nch; ++j) {
         const unsigned char* src = prm.img + (size_t)(c0 + j) * ct.img_bytes;
-        const uint32_t dst = base + L::SM_RES + (j >> 1) * L::RES_T, half = (uint32_t)(j & 1);
-        bulk_g2s(dst + half * CN * 128, src + OFF_BHI, CN * 128, bar(PB_RES));
-        if (NSPLIT == 3) bulk_g2s(dst + L::ROFF_LO + half * CN * 128, src + OFF_BLO, CN * 128, bar(PB_RES));
-        bulk_g2s(dst + L::ROFF_N + half * CN * 32, src + OFF_BN, CN * 32, bar(PB_RES));
+        bulk_g2s(base + L::SM_RES + (j >> 1) * L::RES_N + (uint32_t)(j & 1) * CN * 32, src + OFF_BN, CN * 32, bar(PB_RES));
       }
     }
     if (MASKED) {
@@ -132,42 +173,61 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
         const int jr = r >> 6, jj = r & 63;
         if (jr < nch && jj < ct.n[c0 + jr]) {
           const int cls1 = __ldg(prm.proto_class + ct.p0[c0 + jr] + jj) + 1;
-          ZStage<X, NSPLIT>::write_proto_mask(gbase + L::SM_RES + (r >> 7) * L::RES_T + L::ROFF_N, r & 127, cls1);
+          ZStage<X, NSPLIT>::write_proto_mask(gbase + L::SM_RES + (r >> 7) * L::RES_N, r & 127, cls1);
         }
       }
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(PB_RES2));
     }
+    if (ZMODE != ZM_LDG && lane == 0) {
+      // 16-bit channels-last maps: this warp is the TMA producer. Each tile is ONE box {64 channels of this scale, 128
+      // positions} landing in the MMA's own layout; it runs as far ahead as the stage ring allows (its waits block nobody:
+      // when the loader groups issued their own look-ahead, the wait for a future stage sat in front of the tile at hand)
+      for (int i = 0; i < my_tiles; ++i) {
+        const int st = i % L::NSTAGE;
+        mbar_wait(bar(PB_ZEMPTY + st), ((i / L::NSTAGE) & 1) ^ 1);
+        const long long t = t_lo + i;
+        const long long row0 = (t / prm.tiles_per_map) * s.HW + (t % prm.tiles_per_map) * TILE_M;
+        TLP(4, i);
+        mbar_arrive_expect_tx(bar(PB_TFULL + st), TILE_M * 128u);
+        tma_load_2d(base + L::SM_Z + st * L::STAGE, &prm.tm_z, sc * s.D, (int)row0, bar(PB_TFULL + st));
+      }
+    }
   } else if (warp == WARP_MMA) {
     // ================================ MMA issuer ================================
     constexpr uint32_t ID = idesc_f16(Fmt<X>::id, TILE_M, TILE_M);
     mbar_wait(bar(PB_RES), 0);
     if (MASKED) mbar_wait(bar(PB_RES2), 0);
+    mbar_wait(bar(PB_ATMEM), 0);
+    tc_fence_after();
     for (int i = 0; i < my_tiles; ++i) {
-      const int st = i % L::NSTAGE, db = i & 1;
+      const int st = i % L::NSTAGE;
+      if (lane == 0) TLP(0, i);
       mbar_wait(bar(PB_ZFULL + st), (i / L::NSTAGE) & 1);
-      mbar_wait(bar(PB_DEMPTY + db), ((i >> 1) & 1) ^ 1);
+      if (lane == 0) TLP(1, i);
       tc_fence_after();
-      {
-        const uint32_t zt = base + L::SM_Z + st * L::STAGE;
-        for (int t = 0; t < n_mt; ++t) {
-          const uint32_t pt = base + L::SM_RES + t * L::RES_T, d = tmem + db * 256 + t * 128;
-          mma_f16(d, desc_noswz(pt + L::ROFF_N, NORM_LBO, NORM_SBO), desc_noswz(zt + L::SOFF_N, NORM_LBO, NORM_SBO), ID, 0);
+      const uint32_t zt = base + L::SM_Z + st * L::STAGE;
+      for (int t = 0; t < n_mt; ++t) {
+        const int u = i * n_mt + t, slot = u % D_SLOTS;
+        mbar_wait(bar(PB_DEMPTY + slot), ((u / D_SLOTS) & 1) ^ 1);
+        tc_fence_after();
+        const uint32_t d = tmem + slot * 128, ah = tmem + TM_A + t * 64, al = ah + 32;
+        mma_f16(d, desc_noswz(base + L::SM_RES + t * L::RES_N, NORM_LBO, NORM_SBO), desc_noswz(zt + L::SOFF_N, NORM_LBO, NORM_SBO), ID, 0);
 #pragma unroll
-          for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pt + 32 * k), desc_sw128(zt + 32 * k), ID, 1);
-          if (NSPLIT == 3) {
-            if (ZLO) {
+        for (int k = 0; k < 4; ++k) mma_f16_ts(d, ah + 8 * k, desc_sw128(zt + 32 * k), ID, 1);
+        if (NSPLIT == 3) {
+          if (ZLO) {
 #pragma unroll
-              for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pt + 32 * k), desc_sw128(zt + L::SOFF_LO + 32 * k), ID, 1);
-            }
-#pragma unroll
-            for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(pt + L::ROFF_LO + 32 * k), desc_sw128(zt + 32 * k), ID, 1);
+            for (int k = 0; k < 4; ++k) mma_f16_ts(d, ah + 8 * k, desc_sw128(zt + L::SOFF_LO + 32 * k), ID, 1);
           }
+#pragma unroll
+          for (int k = 0; k < 4; ++k) mma_f16_ts(d, al + 8 * k, desc_sw128(zt + 32 * k), ID, 1);
         }
-        mma_commit(bar(PB_DFULL + db));
-        mma_commit(bar(PB_ZEMPTY + st));
+        mma_commit(bar(PB_DFULL + slot));
       }
+      mma_commit(bar(PB_ZEMPTY + st));
+      if (lane == 0) TLP(3, i);
       __syncwarp();
     }
   } else if (warp >= WARP_LOAD0 && warp < WARP_MMA) {
@@ -198,7 +258,9 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       const float* nxt = have_next ? row_ptr(i + 2, nb, npix) : cur;
       const int lab = pix < s.HW ? (int)__ldg(prm.labels + b * s.HW + pix) : 0;
       const int st = i % L::NSTAGE;
+      if (m == 0) TLP(5, i);
       mbar_wait(bar(PB_ZEMPTY + st), ((i / L::NSTAGE) & 1) ^ 1);
+      if (m == 0) TLP(6, i);
       unsigned char* a0 = gbase + L::SM_Z + st * L::STAGE;
       float zn = 0.f;
       zst.convert_half(0, m, a0, a0 + L::SOFF_LO, zn);
@@ -212,6 +274,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(PB_ZFULL + st));
+      if (m == 0) TLP(7, i);
       // the next tile's loads go out AFTER the arrive: mbarrier.arrive has release semantics and would wait for them
       if (have_next) {
         zst.issue_half(0, nxt, hw, s.D);
@@ -222,31 +285,17 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       pix = npix;
     }
     } else {
-      // 16-bit channels-last maps: each tile is ONE TMA box {64 channels of this scale, 128 positions} landing in the
-      // MMA's own layout; every loader group keeps three tiles in flight.  The thread's job per row: label, squared norm
-      // (read back from the landed tile) and the norm / class-mask K step.
-      int next_issue = grp;
-      auto issue_upto = [&](int upto) {
-        if (m != 0) return;
-        while (next_issue <= upto && next_issue < my_tiles) {
-          const int st = next_issue % L::NSTAGE;
-          mbar_wait(bar(PB_ZEMPTY + st), ((next_issue / L::NSTAGE) & 1) ^ 1);
-          const long long t = t_lo + next_issue;
-          const long long row0 = (t / prm.tiles_per_map) * s.HW + (t % prm.tiles_per_map) * TILE_M;
-          mbar_arrive_expect_tx(bar(PB_TFULL + st), TILE_M * 128u);
-          tma_load_2d(base + L::SM_Z + st * L::STAGE, &prm.tm_z, sc * s.D, (int)row0, bar(PB_TFULL + st));
-          next_issue += 2;
-        }
-      };
-      issue_upto(grp + 2);
+      // 16-bit channels-last maps (tiles brought by the producer warp): the thread's job per row is the label, the squared
+      // norm (read back from the landed tile) and the norm / class-mask K step.
       for (int i = grp; i < my_tiles; i += 2) {
-        issue_upto(i + 4);
         const long long t = t_lo + i;
         const long long b = t / prm.tiles_per_map;
         const int pix = (int)(t % prm.tiles_per_map) * TILE_M + m;
         const int lab = pix < s.HW ? (int)__ldg(prm.labels + b * s.HW + pix) : 0;
         const int st = i % L::NSTAGE;
+        if (m == 0) TLP(5, i);
         mbar_wait(bar(PB_TFULL + st), (i / L::NSTAGE) & 1);
+        if (m == 0) TLP(6, i);
         unsigned char* a0 = gbase + L::SM_Z + st * L::STAGE;
         const float zn = tile_row_norm<X, false>(a0, a0, m);
         if (MASKED) {
@@ -258,6 +307,7 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
         fence_proxy_async();
         __syncwarp();
         if (lane == 0) mbar_arrive(bar(PB_ZFULL + st));
+        if (m == 0) TLP(7, i);
       }
     }
   }
@@ -272,6 +322,31 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       cls = __ldg(prm.proto_class + p) + 1;              // labels: 0 = void, c + 1 = class c
     }
     const bool live_warp = mt < n_mt;
+    // the resident operand: row r of -2p (hi, lo) from the pre-pass image (K-major, 128-byte swizzle) into TMEM, lane =
+    // row, 32-bit column j = channels 2j, 2j+1 (rows of missing chunks: zeros)
+    {
+      const int j = r >> 6, jr = r & 63;
+#pragma unroll 1
+      for (int part = 0; part < (NSPLIT == 3 ? 2 : 1); ++part) {
+        uint32_t v[32];
+        if (j < nch) {
+          const uint4* src = reinterpret_cast<const uint4*>(prm.img + (size_t)(c0 + j) * ct.img_bytes + (part ? OFF_BLO : OFF_BHI) + jr * 128);
+#pragma unroll
+          for (int c = 0; c < 8; ++c) {
+            const uint4 w = __ldg(src + (c ^ (jr & 7)));
+            v[4 * c] = w.x; v[4 * c + 1] = w.y; v[4 * c + 2] = w.z; v[4 * c + 3] = w.w;
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) v[c] = 0u;
+        }
+        tmem_st32(tmem + lane_base + TM_A + mt * 64 + part * 32, v);
+      }
+      asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(PB_ATMEM));
+    }
     float best = 3.0e38f;
     unsigned bidx = 0;
     long long cur_map = -1;
@@ -280,44 +355,57 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       if (p >= 0 && cur_map >= 0 && best < (MASKED ? 0.5f * MASK_BIG : 1.0e38f))
         atomicMin(prm.keys + cur_map * s.P + p, ((unsigned long long)__float_as_uint(best) << 32) | bidx);
     };
-    for (int i = 0; i < my_tiles; ++i) {
+    for (int i = 0; live_warp && i < my_tiles; ++i) {
       const long long t = t_lo + i;
       const long long b = t / prm.tiles_per_map;
       const unsigned pix0 = (unsigned)(t % prm.tiles_per_map) * TILE_M;
-      const int db = i & 1;
       if (b != cur_map) {
         flush();
         cur_map = b;
         best = 3.0e38f;
         bidx = 0;
       }
-      mbar_wait(bar(PB_DFULL + db), (i >> 1) & 1);
+      const int u = i * n_mt + mt, slot = u % D_SLOTS;
+      if (threadIdx.x == 0) TLP(8, i);
+      mbar_wait(bar(PB_DFULL + slot), (u / D_SLOTS) & 1);
+      if (threadIdx.x == 0) TLP(9, i);
       tc_fence_after();
-      if (live_warp && MASKED) {
-#pragma unroll 1
-        for (int cb = 0; cb < 4; ++cb) {
-          uint32_t acc[32];
-          tmem_ld32(tmem + lane_base + db * 256 + mt * 128 + cb * 32, acc);
-          tmem_ld_wait();
-          float mn = __uint_as_float(acc[0]);
+      const uint32_t tsrc = tmem + lane_base + slot * 128;
+#ifdef SPS_PUSH_DBG_NOEPI
+      if (true) {
+      } else
+#endif
+      if (MASKED) {
+        // the load of block cb+1 flies while block cb is reduced (two register buffers); four partial minima per block
+        // instead of one 16-deep chain
+        uint32_t acc[2][32];
+        tmem_ld32(tsrc, acc[0]);
 #pragma unroll
-          for (int j = 1; j < 32; ++j) mn = fminf(mn, __uint_as_float(acc[j]));
-          mn = fmaxf(mn, 0.0f);                            // relu commutes with the minimum
-          if (mn < best) {                                 // strict <: an earlier batch keeps a tie
+        for (int cb = 0; cb < 4; ++cb) {
+          tmem_ld_wait();
+          if (cb < 3) tmem_ld32(tsrc + (cb + 1) * 32, acc[(cb + 1) & 1]);
+          const uint32_t* a = acc[cb & 1];
+          float m4[4];
+#pragma unroll
+          for (int k = 0; k < 4; ++k) m4[k] = __uint_as_float(a[k]);
+#pragma unroll
+          for (int jj = 4; jj < 32; ++jj) m4[jj & 3] = fminf(m4[jj & 3], __uint_as_float(a[jj]));
+          const float mn = fmaxf(fminf(fminf(m4[0], m4[1]), fminf(m4[2], m4[3])), 0.0f);   // relu commutes with the minimum
+          if (mn < best) {                                 // strict <: an earlier block keeps a tie
             best = mn;
             int jf = 31;                                   // first column whose clamped value is the minimum
 #pragma unroll
-            for (int j = 30; j >= 0; --j)
-              if (__uint_as_float(acc[j]) <= mn) jf = j;
+            for (int jj = 30; jj >= 0; --jj)
+              if (__uint_as_float(a[jj]) <= mn) jf = jj;
             bidx = pix0 + (unsigned)(cb * 32 + jf);
           }
         }
-      } else if (live_warp) {
+      } else {
         const int4* labs = reinterpret_cast<const int4*>(gbase + L::SM_LAB + (i % L::LAB_RING) * TILE_M * 4);
 #pragma unroll 1
         for (int cb = 0; cb < 4; ++cb) {
           uint32_t acc[32];
-          tmem_ld32(tmem + lane_base + db * 256 + mt * 128 + cb * 32, acc);
+          tmem_ld32(tsrc + cb * 32, acc);
           tmem_ld_wait();
 #pragma unroll
           for (int j4 = 0; j4 < 8; ++j4) {
@@ -336,13 +424,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       }
       tc_fence_before();
       __syncwarp();
-      if (lane == 0) mbar_arrive(bar(PB_DEMPTY + db));
+      if (lane == 0) mbar_arrive(bar(PB_DEMPTY + slot));
+      if (threadIdx.x == 0) TLP(10, i);
     }
     flush();
   }
 
   tc_fence_before();
   __syncthreads();
+#ifdef SPS_PUSH_TIMELINE
+  if (threadIdx.x == 0 && blockIdx.x < 512) {   // rows 12/13: start / end of every CTA on the global timer (ns)
+    unsigned long long gt;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(gt));
+    g_tlp[13 * 1024 + blockIdx.x] = (long long)gt;
+    g_tlp[12 * 1024 + blockIdx.x] = cta_t0;
+  }
+#endif
   if (warp == WARP_MMA) {
     tc_fence_after();
     tmem_dealloc(tmem, 512);
@@ -350,6 +447,12 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
 }
 
 }  // namespace tcp
+
+#ifdef SPS_PUSH_TIMELINE
+extern "C" int sps_debug_push_timeline(long long* host, int count) {
+  return (int)cudaMemcpyFromSymbol(host, tcp::g_tlp, sizeof(long long) * (size_t)count);
+}
+#endif
 
 // ---------------------------------------------------------------------------------------------
 // Host side
