@@ -572,8 +572,7 @@ typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t,
                                   const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
                                   CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
 
-int make_tmap_2d_16bit(CUtensorMap* out, const void* base, bool bf16, long long rows, long long cols, int box_rows, int box_cols,
-                       int swizzle_bytes) {
+static int encode_tiled_fn(EncodeTiledFn* out) {
   static EncodeTiledFn fn = nullptr;
   if (fn == nullptr) {
     void* p = nullptr;
@@ -582,6 +581,38 @@ int make_tmap_2d_16bit(CUtensorMap* out, const void* base, bool bf16, long long 
     SPS_REQUIRE(p != nullptr && qres == cudaDriverEntryPointSuccess, SPS_ERR_CUDA, "cuTensorMapEncodeTiled not available in this driver");
     fn = reinterpret_cast<EncodeTiledFn>(p);
   }
+  *out = fn;
+  return SPS_OK;
+}
+
+int make_tmap_nchw_f32(TmapNchwF32* out, const float* z, long long B, long long C, long long HW, int px, int box_rows) {
+  const int box_px = px + 4;
+  EncodeTiledFn fn = nullptr;
+  const int rc = encode_tiled_fn(&fn);
+  if (rc != SPS_OK) return rc;
+  SPS_REQUIRE(C % 4 == 0 && (reinterpret_cast<uintptr_t>(z) & 3) == 0 && (box_px * 4) % 16 == 0, SPS_ERR_UNSUPPORTED,
+              "fp32 NCHW tensor maps: C=%lld must be a multiple of 4 and the map 4-byte aligned", C);
+  for (int r = 0; r < 4; ++r) {
+    const uintptr_t row = reinterpret_cast<uintptr_t>(z) + (uintptr_t)r * (uintptr_t)HW * 4u, base = row & ~(uintptr_t)15;
+    out->shift[r] = (int)((row - base) / 4);
+    const cuuint64_t gdim[3] = {(cuuint64_t)(HW + out->shift[r]), (cuuint64_t)(C / 4), (cuuint64_t)(B > 0 ? B : 1)};
+    const cuuint64_t gstride[2] = {(cuuint64_t)HW * 16u, (cuuint64_t)C * (cuuint64_t)HW * 4u};
+    const cuuint32_t box[3] = {(cuuint32_t)box_px, (cuuint32_t)box_rows, 1u};
+    const cuuint32_t estr[3] = {1, 1, 1};
+    const CUresult res = fn(&out->map[r], CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 3, reinterpret_cast<void*>(base), gdim, gstride, box, estr,
+                            CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                            CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    SPS_REQUIRE(res == CUDA_SUCCESS, SPS_ERR_CUDA, "cuTensorMapEncodeTiled failed (%d) for an fp32 NCHW map [%lld x %lld x %lld], residue %d",
+                (int)res, B, C, HW, r);
+  }
+  return SPS_OK;
+}
+
+int make_tmap_2d_16bit(CUtensorMap* out, const void* base, bool bf16, long long rows, long long cols, int box_rows, int box_cols,
+                       int swizzle_bytes) {
+  EncodeTiledFn fn = nullptr;
+  const int rc0 = encode_tiled_fn(&fn);
+  if (rc0 != SPS_OK) return rc0;
   SPS_REQUIRE((reinterpret_cast<uintptr_t>(base) & 15) == 0, SPS_ERR_BAD_ARG, "16-bit channels-last map: base address must be 16-byte aligned");
   SPS_REQUIRE((cols * 2) % 16 == 0, SPS_ERR_UNSUPPORTED, "16-bit channels-last map: %lld channels give a row pitch that is not a multiple of 16 bytes", cols);
   const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)(rows > 0 ? rows : 1)};

@@ -45,6 +45,7 @@ struct PGroupTable {
 
 struct PushParams {
   CUtensorMap tm_z;                // ZM_TMA16: the 16-bit channels-last maps as one [B*HW][C] array
+  TmapNchwF32 tm_f32;              // ZM_LDG (fp32 NCHW maps): four tensor maps, one per channel residue mod 4 (tma.cuh)
   HeadShape s;
   ChunkTable ct;
   PGroupTable gt;
@@ -58,17 +59,27 @@ struct PushParams {
 };
 
 // ZLO: the streamed feature tile has a lo part (fp32 source in a split mode; a 16-bit map is exact in one term)
-template <int NSPLIT, bool ZLO> struct PLay {
+template <int NSPLIT, bool ZLO, bool STAGED> struct PLay {
   static constexpr int RES_N = TILE_M * 32;                                               // norm K step of one 128-row prototype tile
   static constexpr int STAGE = (ZLO ? 2 : 1) * TILE_M * 128 + TILE_M * 32;                // z hi [lo] | norm
   static constexpr int SOFF_LO = TILE_M * 128, SOFF_N = (ZLO ? 2 : 1) * TILE_M * 128;
   static constexpr int SM_RES = 0;
   static constexpr int SM_Z = 2 * RES_N;
-  static constexpr int NSTAGE = (227 * 1024 - 2048 - 4096 - SM_Z) / STAGE >= 6 ? 6 : (227 * 1024 - 2048 - 4096 - SM_Z) / STAGE;
+  // fp32 NCHW source (STAGED): a tile arrives as four TMA boxes {128 + 4 positions, D/4 channels} (channels r, r+4, ... of the
+  // scale, one box per residue r, tma.cuh) in one of NSTG staging buffers; the loader warps convert from there.  Nothing
+  // goes through L1 or registers on the way in, so the bytes in flight are bounded by the staging buffers (4 x 32 KB), not
+  // by the load queue of the loader warps (LDG-fed, the scan stayed at 2.6 TB/s).  Loader group g owns buffers 2g and 2g+1
+  // (tile i: buffer (i&1)*2 + ((i>>1)&1), use number i>>2), so every barrier has ONE waiting group going through its
+  // phases in order (boxes of different tiles may land out of order: with a shared ring a parity wait could take phase k
+  // for phase k+2)
+  static constexpr int STG_PX = TILE_M + 4, STG_BYTES = 64 * STG_PX * 4, NSTG = STAGED ? 4 : 0;   // box rows of 132 floats (tma.cuh)
+  static constexpr int SM_FREE = 227 * 1024 - 2048 - 4096 - SM_Z - NSTG * STG_BYTES;
+  static constexpr int NSTAGE = SM_FREE / STAGE >= 6 ? 6 : SM_FREE / STAGE;
   // labels of the tile in flight: a ring of LAB_RING >= NSTAGE + 2 slots needs no barrier of its own (the loader of
   // tile i has waited for the MMA of tile i-NSTAGE, which waited for the epilogue of tile i-NSTAGE-1)
   static constexpr int LAB_RING = 8;
-  static constexpr int SM_LAB = SM_Z + NSTAGE * STAGE;
+  static constexpr int SM_STG = SM_Z + NSTAGE * STAGE;
+  static constexpr int SM_LAB = SM_STG + NSTG * STG_BYTES;
   static constexpr int SM_BAR = SM_LAB + LAB_RING * TILE_M * 4;
   static constexpr int SM_TOTAL = SM_BAR + 512 + 1024;
 };
@@ -80,7 +91,7 @@ template <int NSPLIT, bool ZLO> struct PLay {
 // seen the commit of unit u-2, and commits are ordered (so unit u-3, the slot's previous user, has committed too).
 constexpr int D_SLOTS = 3;
 constexpr uint32_t TM_A = 384;
-enum { PB_ZFULL = 0, PB_ZEMPTY = 8, PB_DFULL = 16, PB_DEMPTY = 20, PB_RES = 24, PB_RES2 = 25, PB_ATMEM = 26, PB_TFULL = 27, PB_COUNT = 36 };
+enum { PB_ZFULL = 0, PB_ZEMPTY = 8, PB_DFULL = 16, PB_DEMPTY = 20, PB_RES = 24, PB_RES2 = 25, PB_ATMEM = 26, PB_TFULL = 27, PB_SFULL = 36, PB_SEMPTY = 40, PB_COUNT = 44 };
 
 __device__ __forceinline__ void mma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
   asm volatile(
@@ -110,7 +121,7 @@ __device__ __forceinline__ unsigned long long absent_key64() { return ((unsigned
 template <typename X, int NSPLIT, bool MASKED, int ZMODE>
 __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_constant__ PushParams prm) {
   constexpr bool ZLO = NSPLIT == 3 && ZMODE == ZM_LDG;
-  using L = PLay<NSPLIT, ZLO>;
+  using L = PLay<NSPLIT, ZLO, ZMODE == ZM_LDG>;
   extern __shared__ unsigned char smem_raw[];
   const HeadShape& s = prm.s;
   const ChunkTable& ct = prm.ct;
@@ -147,7 +158,11 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
     }
     mbar_init(bar(PB_RES), 1);
     mbar_init(bar(PB_RES2), 1);
-    mbar_init(bar(PB_ATMEM), 8);           // the 8 epilogue warps have written the prototype operand into TMEM
+    mbar_init(bar(PB_ATMEM), 8);
+    for (int i = 0; i < 4; ++i) {
+      mbar_init(bar(PB_SFULL + i), 1);     // staging buffer: arrive.expect_tx + the bytes of its 64 bulk copies
+      mbar_init(bar(PB_SEMPTY + i), 4);    // the 4 warps of the loader group that converted it
+    }           // the 8 epilogue warps have written the prototype operand into TMEM
     mbar_fence_init();
   }
   fence_proxy_async();
@@ -179,6 +194,22 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
       fence_proxy_async();
       __syncwarp();
       if (lane == 0) mbar_arrive(bar(PB_RES2));
+    }
+    if (ZMODE == ZM_LDG && lane == 0) {
+      // fp32 NCHW maps: this warp is the TMA producer, four boxes per tile
+      const int rows = s.D / 4;
+      for (int i = 0; i < my_tiles; ++i) {
+        const int slot = (i & 1) * 2 + ((i >> 1) & 1);
+        mbar_wait(bar(PB_SEMPTY + slot), ((i >> 2) & 1) ^ 1);
+        const long long t = t_lo + i;
+        const int b = (int)(t / prm.tiles_per_map), pix0 = (int)(t % prm.tiles_per_map) * TILE_M;
+        TLP(4, i);
+        mbar_arrive_expect_tx(bar(PB_SFULL + slot), (uint32_t)(4 * rows * L::STG_PX * 4));
+#pragma unroll
+        for (int r = 0; r < 4; ++r)
+          tma_load_3d(base + L::SM_STG + slot * L::STG_BYTES + (uint32_t)(r * rows) * (L::STG_PX * 4), &prm.tm_f32.map[r], pix0, sc * rows, b,
+                      bar(PB_SFULL + slot));
+      }
     }
     if (ZMODE != ZM_LDG && lane == 0) {
       // 16-bit channels-last maps: this warp is the TMA producer. Each tile is ONE box {64 channels of this scale, 128
@@ -235,55 +266,49 @@ __global__ void __launch_bounds__(NTHREADS, 1) push_scan_tc_kernel(const __grid_
     // Software pipeline per group: the feature loads of the group's next tile are issued right after the current one
     // has been handed over and fly during the wait for its stage.
     const int lt = threadIdx.x - WARP_LOAD0 * 32, grp = lt >> 7, m = lt & 127;
-    const uint32_t hw = (uint32_t)s.HW;
-    auto row_ptr = [&](int i, long long& b, int& pix) -> const float* {
-      const long long t = t_lo + i;
-      b = t / prm.tiles_per_map;
-      pix = (int)(t % prm.tiles_per_map) * TILE_M + m;
-      const int px = pix < s.HW ? pix : s.HW - 1;  // rows past the end of the map read a valid row; their label is void
-      return prm.z + (b * s.C + (long long)sc * s.D) * s.HW + px;
-    };
     if (ZMODE == ZM_LDG) {
-    ZStage<X, NSPLIT> zst;
-    long long b = 0, nb = 0;
-    int pix = 0, npix = 0;
-    const float* cur = nullptr;
-    if (grp < my_tiles) {
-      cur = row_ptr(grp, b, pix);
-      zst.issue_half(0, cur, hw, s.D);
-      zst.issue_half(1, cur, hw, s.D);
-    }
-    for (int i = grp; i < my_tiles; i += 2) {
-      const bool have_next = i + 2 < my_tiles;
-      const float* nxt = have_next ? row_ptr(i + 2, nb, npix) : cur;
-      const int lab = pix < s.HW ? (int)__ldg(prm.labels + b * s.HW + pix) : 0;
-      const int st = i % L::NSTAGE;
-      if (m == 0) TLP(5, i);
-      mbar_wait(bar(PB_ZEMPTY + st), ((i / L::NSTAGE) & 1) ^ 1);
-      if (m == 0) TLP(6, i);
-      unsigned char* a0 = gbase + L::SM_Z + st * L::STAGE;
-      float zn = 0.f;
-      zst.convert_half(0, m, a0, a0 + L::SOFF_LO, zn);
-      zst.convert_half(1, m, a0, a0 + L::SOFF_LO, zn);
-      if (MASKED) {
-        ZStage<X, NSPLIT>::store_norm_mask(m, a0 + L::SOFF_N, zn, lab);
-      } else {
-        ZStage<X, NSPLIT>::store_norm(m, a0 + L::SOFF_N, zn);
-        reinterpret_cast<int*>(gbase + L::SM_LAB)[(i % L::LAB_RING) * TILE_M + m] = lab;
+      ZStage<X, NSPLIT> zst;
+      const int rows = s.D / 4;
+      for (int i = grp; i < my_tiles; i += 2) {
+        const long long t = t_lo + i;
+        const long long b = t / prm.tiles_per_map;
+        const int pix = (int)(t % prm.tiles_per_map) * TILE_M + m;
+        const int lab = pix < s.HW ? (int)__ldg(prm.labels + b * s.HW + pix) : 0;
+        const int slot = (i & 1) * 2 + ((i >> 1) & 1), st = i % L::NSTAGE;
+        if (m == 0) TLP(5, i);
+        mbar_wait(bar(PB_SFULL + slot), (i >> 2) & 1);
+        if (m == 0) TLP(6, i);
+        // channel c = 4j + r of this thread's position: box r, row j, element m + shift_r
+        const float* stg = reinterpret_cast<const float*>(gbase + L::SM_STG + slot * L::STG_BYTES) + m;
+        const int sh0 = prm.tm_f32.shift[0], sh1 = prm.tm_f32.shift[1], sh2 = prm.tm_f32.shift[2], sh3 = prm.tm_f32.shift[3];
+        mbar_wait(bar(PB_ZEMPTY + st), ((i / L::NSTAGE) & 1) ^ 1);
+        unsigned char* a0 = gbase + L::SM_Z + st * L::STAGE;
+        float zn = 0.f;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+#pragma unroll
+          for (int k = 0; k < 32; ++k) {
+            const int c = h * 32 + k;
+            const int sh = (c & 3) == 0 ? sh0 : (c & 3) == 1 ? sh1 : (c & 3) == 2 ? sh2 : sh3;
+            zst.v[c] = c < s.D ? stg[((c & 3) * rows + (c >> 2)) * L::STG_PX + sh] : 0.0f;
+          }
+          if (h == 1) {                                   // every value of the tile is in registers: the buffer can be refilled
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar(PB_SEMPTY + slot));
+          }
+          zst.convert_half(h, m, a0, a0 + L::SOFF_LO, zn);
+        }
+        if (MASKED) {
+          ZStage<X, NSPLIT>::store_norm_mask(m, a0 + L::SOFF_N, zn, lab);
+        } else {
+          ZStage<X, NSPLIT>::store_norm(m, a0 + L::SOFF_N, zn);
+          reinterpret_cast<int*>(gbase + L::SM_LAB)[(i % L::LAB_RING) * TILE_M + m] = lab;
+        }
+        fence_proxy_async();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(PB_ZFULL + st));
+        if (m == 0) TLP(7, i);
       }
-      fence_proxy_async();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(bar(PB_ZFULL + st));
-      if (m == 0) TLP(7, i);
-      // the next tile's loads go out AFTER the arrive: mbarrier.arrive has release semantics and would wait for them
-      if (have_next) {
-        zst.issue_half(0, nxt, hw, s.D);
-        zst.issue_half(1, nxt, hw, s.D);
-      }
-      cur = nxt;
-      b = nb;
-      pix = npix;
-    }
     } else {
       // 16-bit channels-last maps (tiles brought by the producer warp): the thread's job per row is the label, the squared
       // norm (read back from the landed tile) and the norm / class-mask K step.
@@ -498,6 +523,10 @@ static int launch_push_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const 
   const int grid = build_pgroups(ct, prm.n_tiles, sm_count(), &prm.gt);
   if (grid <= 0) return SPS_ERR_UNSUPPORTED;
   prm.z = reinterpret_cast<const float*>(z);
+  if (ZMODE == tc::ZM_LDG) {
+    const int rc = make_tmap_nchw_f32(&prm.tm_f32, prm.z, s.B, s.C, s.HW, tc::TILE_M, s.D / 4);
+    if (rc != SPS_OK) return rc;
+  }
   if (ZMODE != tc::ZM_LDG) {
     const int rc = make_tmap_2d_16bit(&prm.tm_z, z, std::is_same<X, __nv_bfloat16>::value, s.N, s.C, tc::TILE_M, 64, 128);
     if (rc != SPS_OK) return rc;
@@ -506,8 +535,9 @@ static int launch_push_tc_t(const HeadShape& s, const tc::ChunkTable& ct, const 
   prm.labels = labels;
   prm.proto_class = proto_class;
   prm.keys = keys;
-  using L = tcp::PLay<NSPLIT, NSPLIT == 3 && ZMODE == tc::ZM_LDG>;
+  using L = tcp::PLay<NSPLIT, NSPLIT == 3 && ZMODE == tc::ZM_LDG, ZMODE == tc::ZM_LDG>;
   constexpr int SMEM = L::SM_TOTAL;
+  static_assert(sizeof(tcp::PushParams) <= 4096, "kernel parameter block");
   static_assert(SMEM <= 227 * 1024 && L::NSTAGE >= 2 && L::NSTAGE + 2 <= L::LAB_RING, "push kernel shared memory plan");
   SPS_CUDA_TRY(cudaFuncSetAttribute(tcp::push_scan_tc_kernel<X, NSPLIT, MASKED, ZMODE>, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM));
   tcp::push_scan_tc_kernel<X, NSPLIT, MASKED, ZMODE><<<grid, tcp::NTHREADS, SMEM, st>>>(prm);

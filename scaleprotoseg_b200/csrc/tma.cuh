@@ -20,6 +20,13 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst_smem, const CUtensorMap
       "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
       : "memory");
 }
+// 3-D box global -> shared (UTMALDG), completion on an mbarrier
+__device__ __forceinline__ void tma_load_3d(uint32_t dst_smem, const CUtensorMap* map, int c0, int c1, int c2, uint32_t bar) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];" ::"r"(dst_smem),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
 // 2-D tile shared -> global (UTMASTG), bulk-group completion.  Elements outside the tensor are not written.
 __device__ __forceinline__ void tma_store_2d(const CUtensorMap* map, int c0, int c1, uint32_t src_smem) {
   asm volatile("cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];" ::"l"(reinterpret_cast<uint64_t>(map)),
@@ -83,5 +90,20 @@ __device__ __forceinline__ float tile_row_norm(const unsigned char* a_hi, const 
 // swizzle_bytes: 128 (box_cols * 2 == 128), 64 (box_cols * 2 == 64) or 0.  Returns an SpsStatus.
 int make_tmap_2d_16bit(CUtensorMap* out, const void* base, bool bf16, long long rows, long long cols, int box_rows,
                        int box_cols, int swizzle_bytes);
+
+// fp32 NCHW maps by TMA.  A channel row of H*W floats starts at any multiple of 4 bytes when H*W is odd, and a tensor map
+// wants 16-byte strides - but every FOURTH channel row is 16*H*W bytes further on.  So the map is described four times,
+// once per channel residue r = c mod 4: base = the address of channel r rounded DOWN to 16 bytes, dimensions
+// {H*W + shift_r, C/4, B} with strides {16*H*W, 4*C*H*W} bytes, where shift_r = the floats between the rounded base and
+// the real start of the row.  The start of a box must be 16-byte aligned as well (an x coordinate that is not a multiple
+// of 4 floats faults: profiles/tools/tma_nchw_probe2.cu), so a box is taken at x = pixel (a multiple of 4) with 4 extra
+// floats: {px + 4, rows, 1}; pixel p of channel r + 4j is then element p + shift_r of box row j, zeros past the end of
+// the row.  Needs C % 4 == 0 and a 4-byte aligned map.
+struct TmapNchwF32 {
+  CUtensorMap map[4];
+  int shift[4];
+};
+int make_tmap_nchw_f32(TmapNchwF32* out, const float* z, long long B, long long C, long long HW, int px, int box_rows);
+
 
 }  // namespace sps
