@@ -373,7 +373,7 @@ def measure_push(ctx, args, shape=None, zdtype=None):
     pc = spush.proto_class_of(ident).to(dev)
     ps = spush.proto_scale_reference(p["P"], 4).to(dev)
     keys = torch.empty(n_local, p["P"], device=dev, dtype=torch.int64)
-    batch = 16
+    batch = 64                         # maps per scan launch (the whole resident pool)
     ev = [torch.cuda.Event(enable_timing=True) for _ in range(6)]
 
     def project(timed):
@@ -420,10 +420,16 @@ def measure_push(ctx, args, shape=None, zdtype=None):
         ctx["dist"].all_reduce(ms, op=ctx["dist"].ReduceOp.MAX)
     ms = ms.tolist()
     patches = n_maps * p["H"] * p["W"]
+    split = cfg.math in (sps.MATH_F16X3, sps.MATH_BF16X3)
+    terms = 0 if cfg.math == sps.MATH_FP32 else (1 if not split else (3 if zdtype is None else 2))
     bytes_per_patch = 256 * (2 if zdtype is not None else 4) + 2
     return {"value": patches / (ms[0] * 1e-3), "unit": "patches/s", "ms": ms[0], "scaling": "strong",
             "phases_ms": {"scan": ms[1], "dataset_argmin": ms[2], "allreduce_min_keys": ms[3], "gather_winners": ms[4], "allreduce_sum_winners": ms[5]},
             "scan_hbm_frac_per_gpu": (patches / world) * bytes_per_patch / (ms[1] * 1e-3) / 1e9 / peaks()["hbm"],
+            # distance GEMM as issued: 2*D*P flops per patch and product term (3 terms for fp32 maps in a 3-term mode, 2 for
+            # 16-bit maps, 1 in the single-term modes) against the sustained bf16 tensor peak
+            "scan_tensor_frac_per_gpu": (patches / world) * 2 * 64 * p["P"] * terms / (ms[1] * 1e-3) / 1e12 / peaks()["tensor_sustained"],
+            "product_terms": terms,
             "workload": f"{n_maps} maps 256x{p['H']}x{p['W']} {'fp32 NCHW' if zdtype is None else str(zdtype).replace('torch.', '') + ' NHWC'}, "
                         f"P={p['P']}, K={p['K']}, sharded {world}-way, {pool} resident maps per rank cycled; whole projection timed",
             "math": "fp32" if cfg.math == 0 else args.math}
