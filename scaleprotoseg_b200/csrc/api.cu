@@ -1,5 +1,6 @@
 // extern "C" surface of libscaleproto_sm100.so: argument checks, math-mode routing, error text.
 #include <stdarg.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <atomic>
@@ -84,6 +85,15 @@ uint64_t sps_launch_count(void) { return g_launches.load(std::memory_order_relax
 
 uint64_t sps_fp32_reroute_count(void) { return g_reroutes.load(std::memory_order_relaxed); }
 
+// SPS_NO_F32TMA=1 in the environment keeps fp32 maps on the loader-fed forward kernel (A/B measurements only)
+static bool getenv_no_f32tma() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("SPS_NO_F32TMA");
+    v = (e != nullptr && e[0] == '1') ? 1 : 0;
+  }
+  return v == 1;
+}
 static bool use_zpack(const SpsHeadDesc* d) {
   return d->z_dtype == SPS_Z_F32 && d->math != SPS_MATH_FP32 && (d->flags & (SPS_FLAG_ZPACK | SPS_FLAG_ZRELAYED)) != 0 && d->D == 64;
 }
@@ -178,6 +188,9 @@ int sps_head_fwd(const SpsHeadDesc* desc, const void* z, const float* protos, co
     return launch_head_fwd_tma(s, desc->math, hi, lo, protos, last_w, logits, dist, act, workspace, img_bytes, st);
   }
   SPS_REQUIRE(!(desc->flags & SPS_FLAG_ZRELAYED), SPS_ERR_UNSUPPORTED, "SPS_FLAG_ZRELAYED: this shape has no TMA-fed forward");
+  // fp32 NCHW maps by TMA (four residue tensor maps), converted on the SM into a TMEM operand: the default where it fits
+  if (desc->math != SPS_MATH_FP32 && !getenv_no_f32tma() && head_fwd_f32tma_supported(s, desc->math, last_w != nullptr, act != nullptr))
+    return launch_head_fwd_f32tma(s, desc->math, zf, protos, last_w, logits, dist, act, workspace, workspace_bytes, st);
   if (desc->math == SPS_MATH_FP32 || !head_fwd_tc_supported(s, desc->math, last_w != nullptr, act != nullptr)) {
     if (desc->math != SPS_MATH_FP32) note_fp32_reroute();
     return launch_head_fwd_simt(s, zf, protos, last_w, logits, dist, act, st);

@@ -135,6 +135,9 @@ int launch_group_bwd(const HeadShape& s, const SpsGroupDesc& g, const float* act
 int launch_push_scan_simt(const HeadShape& s, const float* z, const float* protos, const int16_t* labels,
                           const int32_t* proto_class, unsigned long long* keys, cudaStream_t st);
 int launch_push_fill(unsigned long long* keys, long long count, cudaStream_t st);
+bool head_fwd_f32tma_supported(const HeadShape& s, int math, bool with_last_layer, bool dense_act);
+int launch_head_fwd_f32tma(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w, float* logits,
+                           float* dist, float* act, void* ws, size_t ws_bytes, cudaStream_t st);
 int launch_push_scan_tc(const HeadShape& s, int math, const void* z, bool z16, const float* protos, const int16_t* labels,
                         const int32_t* proto_class, unsigned long long* keys, void* ws, size_t ws_bytes, cudaStream_t st);
 int launch_push_reduce(const unsigned long long* keys, int n_maps, int P, uint32_t map_base,

@@ -36,6 +36,8 @@ __device__ long long g_tl2[64 * 1024];
 struct FwdTmaParams {
   CUtensorMap tm_hi;   // [N][C] 16-bit: the map itself, or the hi part of an fp32 map
   CUtensorMap tm_lo;   // lo part (ZLO only)
+  TmapNchwF32 tm_f32;  // F32 mode: the fp32 NCHW map itself, four tensor maps (tma.cuh)
+  int tiles_per_map;   // F32 mode: position tiles do not cross maps (a TMA box belongs to one map)
   HeadShape s;
   ChunkTable ct;
   const unsigned char* img;
@@ -53,8 +55,13 @@ constexpr int TMEM_S0 = 0;
 constexpr int MAX_NSTW = 4;   // last-layer tile ring: as deep as it is cheap (small K), the chunk producer runs that far ahead
 constexpr int ACT_SCRATCH = 32 * 33 * 4;
 
-template <bool ZLO> __host__ __device__ constexpr int a_stage_bytes() { return (ZLO ? 2 : 1) * A_TILE + A_NORM; }
-template <bool ZLO> __host__ __device__ constexpr int a_stages() { return ZLO ? 2 : 3; }
+// F32 mode (fp32 NCHW source): the "A stage" in shared memory is ONE staging buffer for the four fp32 boxes of a (tile,
+// scale) pair (64 channel rows of 132 floats, tma.cuh); the operand itself lives in TMEM (two buffers), written by the
+// tile warps with tcgen05.st after the fp32 -> hi / lo conversion.
+constexpr int STG_PX = TILE_M + 4, STG_BYTES = 64 * STG_PX * 4;   // 33 KB
+template <bool ZLO, bool F32> __host__ __device__ constexpr int a_stage_bytes() { return F32 ? STG_BYTES : (ZLO ? 2 : 1) * A_TILE + A_NORM; }
+template <bool ZLO, bool F32> __host__ __device__ constexpr int a_stages() { return F32 ? 1 : (ZLO ? 2 : 3); }
+template <int NSPLIT> __host__ __device__ constexpr int a_tmem_cols() { return NSPLIT == 3 ? 72 : 40; }   // hi 32 [+ lo 32] + norm 8
 
 struct Plan {
   int a_stride, na, p0, p_stride, b0, b_stride, nst, nstw, w0, w_stride, scr0, bar_off, total;
@@ -65,10 +72,10 @@ struct Plan {
 };
 // LSPLIT: terms of the activation / last-layer operands of the logits GEMM (3 = hi + lo as the distance products, 1 = one
 // 16-bit term: wide last layers, whose hi + lo tiles do not fit shared memory; logits then carry ~5e-4 of sum |a W|)
-template <int NSPLIT, bool ZLO, int NSETS, int LSPLIT> __host__ __device__ inline Plan make_plan(int kp, int scratch_warps) {
+template <int NSPLIT, bool ZLO, int NSETS, int LSPLIT, bool F32 = false> __host__ __device__ inline Plan make_plan(int kp, int scratch_warps) {
   Plan pl;
-  pl.a_stride = a_stage_bytes<ZLO>();
-  pl.na = a_stages<ZLO>();
+  pl.a_stride = a_stage_bytes<ZLO, F32>();
+  pl.na = a_stages<ZLO, F32>();
   pl.p0 = pl.na * pl.a_stride;
   pl.p_stride = (LSPLIT == 3 ? 2 : 1) * P_BYTES;
   pl.b0 = pl.p0 + NSETS * pl.p_stride;
@@ -93,18 +100,21 @@ enum { BAR_TFULL = 0, BAR_AFULL = 4, BAR_AEMPTY = 8, BAR_BFULL = 12, BAR_BEMPTY 
 constexpr int NZ = 4;   // feature-tile warps: one issues the TMA, all four compute the row norms (one row per thread)
 __host__ __device__ constexpr int n_threads(int nsets) { return (4 * nsets + NZ + 4) * 32; }
 
-template <typename X, int NSPLIT, bool ZLO, bool DENSE, int NSETS, int LSPLIT>
+template <typename X, int NSPLIT, bool ZLO, bool DENSE, int NSETS, int LSPLIT, bool F32 = false>
 __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const __grid_constant__ FwdTmaParams prm) {
+  static_assert(!F32 || ZLO == (NSPLIT == 3), "an fp32 source has a lo part exactly in the split modes");
   constexpr int NEPI = 4 * NSETS;
   constexpr int TMEM_L0 = NSETS * CN;
   constexpr int WARP_Z = NEPI, WARP_PROD = NEPI + NZ, WARP_MMA = NEPI + NZ + 1, WARP_MMA2 = NEPI + NZ + 2, WARP_PRODW = NEPI + NZ + 3;
-  constexpr int NA = a_stages<ZLO>();
+  constexpr int NA = F32 ? 2 : a_stages<ZLO, false>();     // F32: operand buffers in TMEM
+  constexpr int A_COLS = a_tmem_cols<NSPLIT>();
+  static_assert(WARP_Z % 4 == 0, "tile warp w writes TMEM lanes 32 (w % 4) ..");
   extern __shared__ unsigned char smem_raw[];
   const HeadShape& s = prm.s;
   const ChunkTable& ct = prm.ct;
   const uint32_t base = (smem_u32(smem_raw) + 1023u) & ~1023u;
   unsigned char* gbase = smem_raw + (base - smem_u32(smem_raw));
-  const Plan pl = make_plan<NSPLIT, ZLO, NSETS, LSPLIT>(ct.kp, prm.act != nullptr ? NEPI : 0);
+  const Plan pl = make_plan<NSPLIT, ZLO, NSETS, LSPLIT, F32>(ct.kp, prm.act != nullptr ? NEPI : 0);
   const uint32_t bar0 = base + pl.bar_off;
   auto bar = [&](int i) { return bar0 + 8u * (uint32_t)i; };
   volatile uint32_t* tmem_slot = reinterpret_cast<volatile uint32_t*>(gbase + pl.bar_off + 8 * BAR_COUNT);
@@ -113,7 +123,8 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
   const int NC = ct.n_chunks, KP = ct.kp, NST = pl.nst, NSTW = pl.nstw;
   const bool has_w = KP > 0;
   uint32_t tmem_cols = 32;
-  while ((int)tmem_cols < TMEM_L0 + 2 * KP) tmem_cols <<= 1;
+  const uint32_t TMEM_A0 = TMEM_L0 + 2 * KP;   // F32: two operand buffers of A_COLS columns
+  while ((int)tmem_cols < TMEM_L0 + 2 * KP + (F32 ? 2 * A_COLS : 0)) tmem_cols <<= 1;
 
   if (threadIdx.x == 0) {
     for (int i = 0; i < NA; ++i) {
@@ -121,6 +132,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
       mbar_init(bar(BAR_AFULL + i), NZ);   // norm K step written (one arrive per feature-tile warp)
       mbar_init(bar(BAR_AEMPTY + i), 1);   // tcgen05.commit
     }
+    if (F32) mbar_init(bar(BAR_TFULL + 2), NZ);   // F32: BAR_TFULL+0 = staging buffer landed, +2 = read out by the four tile warps
     for (int i = 0; i < NSETS; ++i) {
       mbar_init(bar(BAR_SFULL + i), 1);
       mbar_init(bar(BAR_SEMPTY + i), 4);   // the four warps of the set that owns the buffer
@@ -148,6 +160,18 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
   const uint32_t tmem = *tmem_slot;
 
   const int my_tiles = prm.n_tiles > (int)blockIdx.x ? (prm.n_tiles - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
+  // tile tj of this CTA: global position of its row 0 and the number of its rows that exist
+  auto tile_rows = [&](int tj, long long& n0) -> int {
+    const long long T = (long long)blockIdx.x + (long long)tj * gridDim.x;
+    if (F32) {
+      const long long b = T / prm.tiles_per_map;
+      const int pix0 = (int)(T - b * prm.tiles_per_map) * TILE_M;
+      n0 = b * s.HW + pix0;
+      return s.HW - pix0 < TILE_M ? s.HW - pix0 : TILE_M;
+    }
+    n0 = T * TILE_M;
+    return s.N - n0 < TILE_M ? (int)(s.N - n0) : TILE_M;
+  };
 
   if (warp == WARP_MMA) {
     // ================================ distance-GEMM issuer ================================
@@ -160,7 +184,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
       const bool last_of_scale = c == NC - 1 || ct.scale[c + 1] != ct.scale[c];
       if (lane == 0) TL2(0, i);
       if (first_of_scale) {
-        mbar_wait(bar(BAR_TFULL + ab), aph);
+        if (!F32) mbar_wait(bar(BAR_TFULL + ab), aph);
         mbar_wait(bar(BAR_AFULL + ab), aph);
       }
       if (lane == 0) TL2(1, i);
@@ -175,6 +199,18 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
         const uint32_t b_hi = base + pl.b_off(st) + OFF_BHI, b_lo = base + pl.b_off(st) + OFF_BLO;
         const uint32_t b_n = base + pl.b_off(st) + OFF_BN;
         const uint32_t d = tmem + TMEM_S0 + sb * CN;
+        if (F32) {
+          const uint32_t th = tmem + TMEM_A0 + ab * A_COLS, tl = th + 32, tn = th + (NSPLIT == 3 ? 64 : 32);
+          mma_f16_ts(d, tn, desc_noswz(b_n, NORM_LBO, NORM_SBO), ID1, 0);
+#pragma unroll
+          for (int k = 0; k < 4; ++k) mma_f16_ts(d, th + 8 * k, desc_sw128(b_hi + 32 * k), ID1, 1);
+          if (NSPLIT == 3) {
+#pragma unroll
+            for (int k = 0; k < 4; ++k) mma_f16_ts(d, th + 8 * k, desc_sw128(b_lo + 32 * k), ID1, 1);
+#pragma unroll
+            for (int k = 0; k < 4; ++k) mma_f16_ts(d, tl + 8 * k, desc_sw128(b_hi + 32 * k), ID1, 1);
+          }
+        } else {
         mma_f16(d, desc_noswz(a_n, NORM_LBO, NORM_SBO), desc_noswz(b_n, NORM_LBO, NORM_SBO), ID1, 0);
 #pragma unroll
         for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_hi + 32 * k), desc_sw128(b_hi + 32 * k), ID1, 1);
@@ -185,6 +221,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
 #pragma unroll
             for (int k = 0; k < 4; ++k) mma_f16(d, desc_sw128(a_lo + 32 * k), desc_sw128(b_hi + 32 * k), ID1, 1);
           }
+        }
         }
         mma_commit(bar(BAR_SFULL + sb));
         if (last_of_scale) mma_commit(bar(BAR_AEMPTY + ab));
@@ -307,6 +344,91 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
     constexpr uint32_t TX = (ZLO ? 2 : 1) * A_TILE;
     const bool issuer = warp == WARP_Z;
     const int m = (warp - WARP_Z) * 32 + lane;
+    if (F32) {
+      // fp32 NCHW source.  Per (tile, scale) pair: four TMA boxes {132 px, 16 channels} (channel residues mod 4) into the
+      // staging buffer; every thread then reads the 64 channels of ITS position (row m), releases the buffer (the next
+      // pair's boxes start right away), converts to hi / lo 16-bit pairs and writes them with the squared norm into the
+      // TMEM operand buffer of the pair: lane = position, column j = channels 2j, 2j+1.
+      const int sh0 = prm.tm_f32.shift[0], sh1 = prm.tm_f32.shift[1], sh2 = prm.tm_f32.shift[2], sh3 = prm.tm_f32.shift[3];
+      const uint32_t lane_base = ((uint32_t)((warp - WARP_Z) * 32)) << 16;
+      int iti = 0, ic = 0;
+      uint32_t issued = 0;
+      auto issue = [&]() {
+        if (iti >= my_tiles) return;
+        mbar_wait(bar(BAR_TFULL + 2), (issued & 1) ^ 1);   // all four warps have read the previous pair out
+        if (lane == 0) {
+          const long long T = (long long)blockIdx.x + (long long)iti * gridDim.x;
+          const int b = (int)(T / prm.tiles_per_map), pix0 = (int)(T - (long long)b * prm.tiles_per_map) * TILE_M;
+          const int row0 = ct.scale[ic] * 16;
+          TL2(27, issued);
+          mbar_arrive_expect_tx(bar(BAR_TFULL), (uint32_t)STG_BYTES);
+#pragma unroll
+          for (int r = 0; r < 4; ++r)
+            tma_load_3d(base + pl.a_off(0) + (uint32_t)(r * 16) * (STG_PX * 4), &prm.tm_f32.map[r], pix0, row0, b, bar(BAR_TFULL));
+        }
+        __syncwarp();
+        ++issued;
+        advance(iti, ic);
+      };
+      if (issuer) issue();
+      int ti = 0, c = 0;
+      uint32_t acount = 0;
+      const float* stg = reinterpret_cast<const float*>(gbase + pl.a_off(0)) + m;
+      while (ti < my_tiles) {
+        const uint32_t ab = acount & 1, aph = (acount >> 1) & 1;
+        if (issuer && lane == 0) TL2(24, acount);
+        mbar_wait(bar(BAR_TFULL), acount & 1);
+        if (issuer && lane == 0) TL2(25, acount);
+        float v[64];
+#pragma unroll
+        for (int cc = 0; cc < 64; ++cc) {
+          const int sh = (cc & 3) == 0 ? sh0 : (cc & 3) == 1 ? sh1 : (cc & 3) == 2 ? sh2 : sh3;
+          v[cc] = stg[((cc & 3) * 16 + (cc >> 2)) * STG_PX + sh];
+        }
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(BAR_TFULL + 2));
+        if (issuer) issue();
+        mbar_wait(bar(BAR_AEMPTY + ab), aph ^ 1);          // the MMAs that read this operand buffer two pairs ago are done
+        tc_fence_after();
+        const uint32_t ta = tmem + lane_base + TMEM_A0 + ab * A_COLS;
+        float zn = 0.f;
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t hw_[16], lw_[16];
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const float v0 = v[h * 32 + 2 * j], v1 = v[h * 32 + 2 * j + 1];
+            hw_[j] = Pack2<X>::pack(v0, v1);
+            float2 e = Pack2<X>::unpack(hw_[j]);
+            if (NSPLIT == 3) {
+              lw_[j] = Pack2<X>::pack(v0 - e.x, v1 - e.y);
+              const float2 el = Pack2<X>::unpack(lw_[j]);
+              e.x += el.x;
+              e.y += el.y;
+            }
+            zn = fmaf(e.x, e.x, zn);
+            zn = fmaf(e.y, e.y, zn);
+          }
+          tmem_st16(ta + h * 16, hw_);
+          if (NSPLIT == 3) tmem_st16(ta + 32 + h * 16, lw_);
+        }
+        {
+          X nh, nm, nl;
+          split3<X>(zn, nh, nm, nl);
+          const uint32_t one = bits16(Fmt<X>::from(1.0f));
+          const uint32_t nw[8] = {one | (one << 16), one | ((uint32_t)bits16(nh) << 16), (uint32_t)bits16(nm) | ((uint32_t)bits16(nl) << 16),
+                                  0u, 0u, 0u, 0u, 0u};
+          tmem_st8(ta + (NSPLIT == 3 ? 64 : 32), nw);
+        }
+        tmem_st_wait();
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive(bar(BAR_AFULL + ab));
+        if (issuer && lane == 0) TL2(26, acount);
+        ++acount;
+        advance(ti, c);
+      }
+    } else {
     int iti = 0, ic = 0;        // next pair to issue
     uint32_t issued = 0;
     auto issue = [&](bool blocking) -> bool {
@@ -354,6 +476,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
       ++acount;
       advance(ti, c);
     }
+    }
   } else {
     // ================================ epilogue ================================
     const int q = warp & 3, set = warp >> 2;
@@ -362,7 +485,9 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
     const float eps = s.eps, ome = 1.0f - s.eps;
     const bool is_log = s.act_kind == SPS_ACT_LOG;
     auto store_logits = [&](int tj) {
-      const long long nn = ((long long)blockIdx.x + (long long)tj * gridDim.x) * TILE_M + m;
+      long long nn0;
+      const int lim = tile_rows(tj, nn0);
+      const long long nn = nn0 + m;
       const uint32_t lb = tj & 1;
       mbar_wait(bar(BAR_LFULL + lb), (tj >> 1) & 1);
       tc_fence_after();
@@ -370,7 +495,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
         uint32_t lr[16];
         tmem_ld16(tmem + lane_base + TMEM_L0 + lb * KP + k0, lr);
         tmem_ld_wait();
-        if (nn < s.N) {
+        if (m < lim) {
 #pragma unroll
           for (int k = 0; k < 16; ++k)
             if (k0 + k < s.K) prm.logits[nn * s.K + k0 + k] = __uint_as_float(lr[k]);
@@ -384,10 +509,16 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
     int next_store = 0;   // set 0: next tile whose logits go to HBM
     const int U = my_tiles * NC;
     int ti = 0, c = set;
-    long long n = (long long)blockIdx.x * TILE_M + m;
-    while (c >= NC && NC > 0) { c -= NC; ++ti; n += (long long)gridDim.x * TILE_M; }
+    while (c >= NC && NC > 0) { c -= NC; ++ti; }
+    int cur_ti = -1, lim = 0;
+    long long n0 = 0;
     for (int u = set; u < U; u += NSETS) {
-      const bool valid = n < s.N;
+      if (ti != cur_ti) {
+        lim = tile_rows(ti, n0);
+        cur_ti = ti;
+      }
+      const long long n = n0 + m;
+      const bool valid = m < lim;
       const long long b = valid ? n / s.HW : 0, pix = valid ? n % s.HW : 0;
       float* drow = DENSE && prm.dist != nullptr ? prm.dist + b * (long long)s.P * s.HW + pix : nullptr;
       const uint32_t sb = set, pb = set, ph = (u / NSETS) & 1;
@@ -448,7 +579,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
             __syncwarp();
             const long long n_first = n - lane;
             float* abase = prm.act + n_first * (long long)s.P + p0 + lane;
-            const int rows = s.N - n_first < 32 ? (int)(s.N - n_first) : 32;
+            const int rows = lim - q * 32 < 32 ? lim - q * 32 : 32;
             if (lane < ncols) {
 #pragma unroll 8
               for (int rr = 0; rr < 32; ++rr)
@@ -489,7 +620,7 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
         if (next_store == ti - 1 && c >= defer_c) store_logits(next_store++);
       }
       c += NSETS;
-      while (c >= NC) { c -= NC; ++ti; n += (long long)gridDim.x * TILE_M; }
+      while (c >= NC) { c -= NC; ++ti; }
     }
     if (has_w && set == 0)
       while (next_store < my_tiles) store_logits(next_store++);
@@ -735,6 +866,82 @@ static int launch_fwd_tma_t(const HeadShape& s, const tc::ChunkTable& ct, const 
   if (NSPLIT == 3 && !two_sets_fit<NSPLIT, ZLO, NSPLIT>(ct.kp, act != nullptr))
     return launch_fwd_tma_l<X, NSPLIT, ZLO, 1>(s, ct, prm, dense, act != nullptr, st);
   return launch_fwd_tma_l<X, NSPLIT, ZLO, NSPLIT>(s, ct, prm, dense, act != nullptr, st);
+}
+
+// ---- fp32 NCHW maps: TMA staging + operand in TMEM (F32 mode of the kernel) ----
+template <int NSPLIT> static bool f32_sets_fit(int nsets, int kp, bool dense_act) {
+  if (nsets * tc::CN + 2 * kp + 2 * tf::a_tmem_cols<NSPLIT>() > 512) return false;
+  const tf::Plan pl = nsets == 3 ? tf::make_plan<NSPLIT, NSPLIT == 3, 3, NSPLIT, true>(kp, 0)
+                                 : tf::make_plan<NSPLIT, NSPLIT == 3, 2, NSPLIT, true>(kp, dense_act ? 8 : 0);
+  return pl.nst >= 2 && pl.total <= 227 * 1024;
+}
+
+bool head_fwd_f32tma_supported(const HeadShape& s, int math, bool with_last_layer, bool dense_act) {
+  if (math == SPS_MATH_FP32 || s.D != 64 || s.C % 4 != 0 || s.K > 192 || s.N >= (1ll << 31) || s.HW >= (1 << 30)) return false;
+  int nc = 0;
+  for (int sc = 0; sc < s.S; ++sc) nc += (s.scale_lo[sc + 1] - s.scale_lo[sc] + tc::CN - 1) / tc::CN;
+  if (nc > tc::MAX_CHUNKS) return false;
+  const int kp = with_last_layer ? (s.K + 15) / 16 * 16 : 0;
+  return math_is_split(math) ? f32_sets_fit<3>(2, kp, dense_act) : f32_sets_fit<1>(2, kp, dense_act);
+}
+
+template <typename X, int NSPLIT>
+static int launch_fwd_f32_t(const HeadShape& s, const tc::ChunkTable& ct, const float* z, const float* protos, const float* last_w,
+                            float* logits, float* dist, float* act, unsigned char* img, int math, cudaStream_t st) {
+  constexpr bool ZLO = NSPLIT == 3;
+  int rc = launch_proto_prep(s, math, ct, protos, last_w, img, st);
+  if (rc != SPS_OK) return rc;
+  tf::FwdTmaParams prm;
+  memset(&prm.tm_hi, 0, sizeof(prm.tm_hi));
+  memset(&prm.tm_lo, 0, sizeof(prm.tm_lo));
+  rc = make_tmap_nchw_f32(&prm.tm_f32, z, s.B, s.C, s.HW, tc::TILE_M, 16);
+  if (rc != SPS_OK) return rc;
+  prm.s = s;
+  prm.ct = ct;
+  prm.img = img;
+  prm.logits = logits;
+  prm.dist = dist;
+  prm.act = act;
+  prm.tiles_per_map = (s.HW + tc::TILE_M - 1) / tc::TILE_M;
+  prm.n_tiles = s.B * prm.tiles_per_map;
+  const bool dense = dist != nullptr || act != nullptr;
+  const int grid = prm.n_tiles < sm_count() ? prm.n_tiles : sm_count();
+  if (!dense && f32_sets_fit<NSPLIT>(3, ct.kp, false)) {
+    const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 3, NSPLIT, true>(ct.kp, 0);
+    SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 3, NSPLIT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+    SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 3, NSPLIT, true>, dim3(grid), dim3(tf::n_threads(3)), (size_t)pl.total, st, prm));
+  } else {
+    const tf::Plan pl = tf::make_plan<NSPLIT, ZLO, 2, NSPLIT, true>(ct.kp, act != nullptr ? 8 : 0);
+    SPS_REQUIRE(pl.nst >= 2 && pl.total <= 227 * 1024, SPS_ERR_UNSUPPORTED, "fp32 TMA-fed head: %d bytes of shared memory needed (K=%d)", pl.total, s.K);
+    if (dense) {
+      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, true, 2, NSPLIT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+      SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, true, 2, NSPLIT, true>, dim3(grid), dim3(tf::n_threads(2)), (size_t)pl.total, st, prm));
+    } else {
+      SPS_CUDA_TRY(cudaFuncSetAttribute(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 2, NSPLIT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, pl.total));
+      SPS_CUDA_TRY(launch_pdl(tf::head_fwd_tma_kernel<X, NSPLIT, ZLO, false, 2, NSPLIT, true>, dim3(grid), dim3(tf::n_threads(2)), (size_t)pl.total, st, prm));
+    }
+  }
+  count_launch();
+  return SPS_OK;
+}
+
+// z: fp32 NCHW.  img: workspace for the packed prototype images (head_fwd_tc_workspace bytes).
+int launch_head_fwd_f32tma(const HeadShape& s, int math, const float* z, const float* protos, const float* last_w, float* logits,
+                           float* dist, float* act, void* ws, size_t ws_bytes, cudaStream_t st) {
+  if (s.N == 0 || s.P == 0) return SPS_OK;
+  tc::ChunkTable ct;
+  int rc = build_chunk_table(s, last_w != nullptr, &ct);
+  if (rc != SPS_OK) return rc;
+  const size_t need = (size_t)ct.n_chunks * ct.img_bytes + 1024;
+  SPS_REQUIRE(ws != nullptr && ws_bytes >= need, SPS_ERR_WORKSPACE, "head_fwd workspace: need %zu bytes, got %zu", need, ws_bytes);
+  unsigned char* img = reinterpret_cast<unsigned char*>(((uintptr_t)ws + 1023) & ~(uintptr_t)1023);
+  switch (math) {
+    case SPS_MATH_F16: return launch_fwd_f32_t<__half, 1>(s, ct, z, protos, last_w, logits, dist, act, img, math, st);
+    case SPS_MATH_F16X3: return launch_fwd_f32_t<__half, 3>(s, ct, z, protos, last_w, logits, dist, act, img, math, st);
+    case SPS_MATH_BF16: return launch_fwd_f32_t<__nv_bfloat16, 1>(s, ct, z, protos, last_w, logits, dist, act, img, math, st);
+    case SPS_MATH_BF16X3: return launch_fwd_f32_t<__nv_bfloat16, 3>(s, ct, z, protos, last_w, logits, dist, act, img, math, st);
+  }
+  SPS_REQUIRE(false, SPS_ERR_BAD_ARG, "math=%d is not a tensor-core mode", math);
 }
 
 // Shapes the TMA-fed forward covers.  zlo: the map has a lo part (fp32 source re-laid by z_pack_kernel in a split mode).
