@@ -762,7 +762,7 @@ def main():
     n = c["B"] * c["H"] * c["W"]
     # dominant phase and its roofline (algorithmic counts: SURVEY 8(d), restated in DESIGN.md)
     phases = {
-        "forward (head_fwd_tc_kernel)": dict(ms=ctx["t_fwd"], flops=ctx["units"] * (2 * c["D"] + 2 * c["K"]),
+        "forward (head_fwd kernels)": dict(ms=ctx["t_fwd"], flops=ctx["units"] * (2 * c["D"] + 2 * c["K"]),
                                              bytes=n * (c["S"] * c["D"] * 4 + 4 * c["K"])),
         "backward (head_bwd kernels)": dict(ms=ctx["t_bwd"], flops=ctx["units"] * (4 * c["D"] + 4 * c["K"]),
                                             bytes=n * (2 * c["S"] * c["D"] * 4 + 4 * c["K"])),
