@@ -184,3 +184,53 @@ def test_push_scan_nhwc16_vs_oracle(built_lib, math, shape):
     assert same.float().mean() > 0.95
     got = out.cpu()[same]
     assert torch.equal(got, torch.from_numpy(newp).view(P, 64)[same]), "winning vectors (exact copies of the fp16 map values)"
+
+
+# ---- fp32 NCHW maps by TMA (four residue tensor maps; forward operand in TMEM, push staging) ------------------------------
+@pytest.mark.parametrize("math", [sps.MATH_F16X3, sps.MATH_F16, sps.MATH_BF16X3])
+@pytest.mark.parametrize("shape", [(2, 9, 7, 228, 19, 0), (3, 13, 11, 228, 19, 1), (1, 16, 16, 228, 19, 3), (2, 23, 17, 760, 19, 2),
+                                   (1, 12, 11, 24, 2, 1)])
+def test_fp32_maps_by_tma_any_alignment(built_lib, math, shape):
+    """The fp32 forward reads the map through tensor maps whose base is the channel row rounded DOWN to 16 bytes: every
+    residue of (H*W mod 4) and every 4-byte alignment of the map pointer (a view that starts 1..3 floats into a buffer) has
+    to give the oracle's distances, activations and logits; H*W below, equal to and above one 128-position tile; dense and
+    fused outputs; the push scan on the same views."""
+    B, H, W, P, K, off = shape
+    z, protos, ranges, w, dl = _case(B, H, W, P, K, seed=71 + off)
+    lo, do, ao, *_ = _oracle(z, protos, ranges, w, dl)
+    buf = torch.zeros(z.numel() + 8, device=DEV)
+    zv = buf[off:off + z.numel()].view(z.shape)
+    zv.copy_(z.to(DEV))
+    assert zv.data_ptr() % 16 == (4 * off) % 16 and zv.is_contiguous()
+    cfg = sps.HeadConfig.from_ranges(ranges, K, math=math)
+    pd, wd = protos.to(DEV), w.contiguous().to(DEV)
+    before = _lib.load().sps_fp32_reroute_count()
+    logits, dist, act = sps.head_forward_raw(zv, pd, wd, cfg, True, True)
+    tol = TOL[math]
+    assert_rel(dist.cpu(), do, tol, "distances")
+    assert_rel(act.cpu().view(B, H, W, P), ao.view(B, H, W, P), tol, "activations")
+    assert_rel(logits.cpu().view(B, H, W, K), lo, tol, "logits")
+    fused, dnone, anone = sps.head_forward_raw(zv, pd, wd, cfg, False, False)
+    assert dnone is None and anone is None
+    assert_rel(fused.cpu().view(B, H, W, K), lo, tol, "logits (fused)")
+    assert _lib.load().sps_fp32_reroute_count() == before
+    # push scan on the same view: winners must be positions of the right class at the oracle's distance
+    ident = ho.make_identity(P, K, 4)
+    labels = torch.stack([ho.make_labels(i, H, W, K, absent_class=1 if K > 2 else None) for i in range(B)]).to(torch.int16)
+    keys = spush.scan_maps(zv, labels.to(DEV), pd, spush.proto_class_of(ident).to(DEV), cfg).cpu()
+    dmin = (keys >> 32).to(torch.int32).view(torch.float32)     # float bits of the minimum distance (1e10 = absent)
+    pix = keys & 0xFFFFFFFF
+    pc = spush.proto_class_of(ident)
+    for b in range(B):
+        lab = labels[b].view(-1).to(torch.int64)
+        dmap = do[b].detach().view(P, -1)
+        for p in range(P):
+            m = lab == (int(pc[p]) + 1)
+            if not bool(m.any()):
+                assert float(dmin[b, p]) >= 1e9
+                continue
+            best = float(dmap[p][m].min())
+            scale = max(float(dmap[p].abs().max()), 1.0)
+            assert abs(float(dmin[b, p]) - best) <= 2 * tol * scale, (b, p)
+            assert bool(m[int(pix[b, p])]), (b, p)
+            assert abs(float(dmap[p, int(pix[b, p])]) - best) <= 2 * tol * scale, (b, p)
