@@ -6,14 +6,19 @@
 // [N positions][C channels] array (the user's fp16 / bf16 channels-last tensor, or the hi / lo re-lay of an fp32 NCHW map
 // written by z_pack_kernel), and a {64 channels x 128 positions} box with the 128-byte swizzle is exactly the K-major
 // SWIZZLE_128B operand tile of the distance GEMM: one cp.async.bulk.tensor per tile, no conversion work on the SM.
-// What is left of the loader's job is the row norm |z_s(n)|^2 (one warp, four rows per lane, read back from the landed
+// What is left of the loader's job is the row norm |z_s(n)|^2 (four warps, one row per thread, read back from the landed
 // tile), written into the 16-wide norm K step as before.  The four loader warps of head_tc.cu are gone, so a third set
 // of epilogue warps fits in the register file: three warps per SM sub-partition take units round-robin (the epilogue -
 // two MUFU per element - is what bounds this kernel).
 //
+// F32 mode: the same kernel on the reference's own fp32 NCHW maps.  The pair's tile arrives as four TMA boxes (channel
+// residues mod 4, tma.cuh) in one staging buffer; the four tile warps convert their position's channels to hi / lo 16-bit
+// pairs and write them, with the squared norm, into a TMEM operand buffer (tcgen05.st: lane = position), and the distance
+// MMAs take their A operand from TMEM.  Position tiles do not cross maps in this mode.  
+//
 // Warp roles (NSETS = 3 fused, 2 dense): warps [0, 4*NSETS) epilogue (warp % 4 = TMEM lane quarter, warp / 4 = set; set s
-// takes units u = s mod NSETS), then one feature-tile producer + row-norm warp, one prototype-chunk producer, the
-// distance-GEMM issuer and the logits-GEMM issuer.  Every set owns ITS distance accumulator (TMEM) and activation tile
+// takes units u = s mod NSETS), then four feature-tile warps (TMA issue + row norms / conversion), the prototype-chunk producer, the
+// distance-GEMM issuer, the logits-GEMM issuer and the last-layer tile producer.  Every set owns ITS distance accumulator (TMEM) and activation tile
 // (shared memory): a barrier is then only ever waited on by one set, one phase after the other (a parity wait cannot
 // tell phase k from phase k + 2, so a set must never skip a phase of a barrier it shares).
 #include "tma.cuh"

@@ -2,15 +2,17 @@
 // prototype's class.  Replaces compute_distances lines 68-91 of segmentation/push_multiscale_optimization.py
 // (one-hot, void column dropped, 1e10 mask, min / argmin over the flattened map).
 //
-// The distance GEMM is the forward's, TRANSPOSED: prototypes are the M rows (A operand, resident in shared
-// memory for the whole kernel), positions are the N columns (B operand, streamed), so every epilogue thread owns
-// one prototype and keeps its running (distance, index) minimum in registers — no cross-thread reduction.
+// The distance GEMM is the forward's, TRANSPOSED: prototypes are the M rows (A operand, resident for the whole kernel: -2p
+// in TMEM, the norm / class-mask K step in shared memory), positions are the N columns (B operand, streamed), so every
+// epilogue thread owns one prototype and keeps its running (distance, index) minimum in registers - no cross-thread
+// reduction.
 //   acc[p, n] = (-2 p_p).z_s(n) + |p_p|^2 + |z_s(n)|^2       (norms in the extra K step, as in head_tc.cu)
 //   key[p]    = min over n with label[n] == class(p)+1 of (bits(max(acc,0)) << 32 | n)   (first occurrence wins)
 // One CTA owns ONE scale and up to 256 of its prototypes (two M=128 accumulator tiles) and a contiguous range of
 // position tiles (128 positions of one map), so each feature value is read from HBM exactly once per 256
-// prototypes of its scale (once in total for the shipped configs).  The scan is HBM-bound: the feature loaders
-// (8 warps, two tiles in flight) are the critical resource; MMA and the compare/select epilogue hide under them.
+// prototypes of its scale (once in total for the shipped configs).  Feature tiles arrive by TMA in both map formats
+// (fp32 NCHW: four residue tensor maps into a staging buffer, converted by the loader warps; 16-bit channels-last:
+// straight into the operand layout).  In the 3-term modes the tensor pipe is what bounds the scan.
 // Results are merged into keys[map][p] with one 64-bit atomicMin per (CTA, map, prototype).
 #include "tma.cuh"
 
