@@ -146,7 +146,8 @@ struct DzParams {
   int n_tiles;
 };
 
-constexpr int DZ_THREADS = 384;    // 8 epilogue warps (2 sets), feature / dlogits producer + norms, chunk producer, 2 issuers
+constexpr int DZ_THREADS = 512;    // 8 epilogue warps (2 sets), feature / dlogits producer + norms, chunk producer, 2 issuers,
+                                   // 4 warps that move the dlogits tile into TMEM (warps 12..15: lane quarters 0..3)
 // The chunk operands travel in TWO rings.  The -2p tile (8 KB) is read by the distance GEMM and, an epilogue later, by the dz
 // GEMM: a long life, so a deep ring of small slots.  The norm K step + W3 tile (26 KB) are read by issuer 1 only and free
 // as soon as the dA GEMM has completed.  (One ring of whole 34 KB images held every slot for the full chain: 2 960 clk per unit.)
@@ -158,8 +159,12 @@ constexpr int DZ_SM_DL = 0, DZ_SM_A = DL_TILE, DZ_SM_G = DZ_SM_A + 2 * DZ_A, DZ_
               DZ_SM_TOTAL = DZ_SM_BAR + 512 + 1024;
 static_assert(DZ_SM_TOTAL <= 227 * 1024 && DZ_WSLOT % 1024 == 0, "dz kernel shared memory");
 enum { Z_TFULL = 0, Z_AFULL = 2, Z_AEMPTY = 4, Z_DLFULL = 6, Z_DLEMPTY = 7, Z_HFULL = 8, Z_HEMPTY = 16, Z_WFULL = 24, Z_WEMPTY = 26,
-       Z_SFULL = 28, Z_SEMPTY = 30, Z_GFULL = 32, Z_GEMPTY = 34, Z_DZFULL = 36, Z_DZEMPTY = 38, Z_COUNT = 40 };
-constexpr int ZT_S = 0, ZT_DA = 128, ZT_DZ = 256;
+       Z_SFULL = 28, Z_SEMPTY = 30, Z_GFULL = 32, Z_GEMPTY = 34, Z_DZFULL = 36, Z_DZEMPTY = 38, Z_DLTFULL = 40, Z_DLTEMPTY = 41, Z_COUNT = 42 };
+// The dlogits tile (128 positions x 192 classes) is the A operand of the dA GEMM of EVERY unit of its tile (12 of the 21 MMAs
+// of a unit): it is copied once per tile from its TMA landing buffer into 96 TMEM columns (lane = position, column j =
+// classes 2j, 2j+1), and those MMAs take A from TMEM: 32.8 clk instead of 48.9 for an M128 x N64 x K16 step
+// (profiles/r02_probe_mma_ts.txt) - the kernel is bound by the time its MMAs occupy the tensor pipe.
+constexpr int ZT_S = 0, ZT_DA = 128, ZT_DZ = 256, ZT_DL = 384;
 
 // DZ16: dz is written in the 16-bit channels-last layout of the feature map; otherwise fp32 NCHW
 template <typename X, bool DZ16>
@@ -188,7 +193,9 @@ __global__ void __launch_bounds__(DZ_THREADS, 1) wide_dz_kernel(const __grid_con
       mbar_init(bar(Z_DZEMPTY + i), 8);
     }
     mbar_init(bar(Z_DLFULL), 1);
-    mbar_init(bar(Z_DLEMPTY), 1);
+    mbar_init(bar(Z_DLEMPTY), 4);          // the landing buffer is free once the four copy warps have read it
+    mbar_init(bar(Z_DLTFULL), 4);          // TMEM copy of the dlogits tile written
+    mbar_init(bar(Z_DLTEMPTY), 1);         // commit after the last dA GEMM of the tile
     for (int i = 0; i < DZ_NSH; ++i) {
       mbar_init(bar(Z_HFULL + i), 1);
       mbar_init(bar(Z_HEMPTY + i), 2);     // both issuers read the -2p tile (distance GEMM, dz GEMM)
@@ -272,30 +279,54 @@ __global__ void __launch_bounds__(DZ_THREADS, 1) wide_dz_kernel(const __grid_con
         ++pair;
         mbar_wait(bar(Z_AFULL + (pair & 1)), (pair >> 1) & 1);
       }
-      if (c == 0) mbar_wait(bar(Z_DLFULL), ti & 1);
+      if (c == 0) mbar_wait(bar(Z_DLTFULL), ti & 1);
       mbar_wait(bar(Z_HFULL + sh), (u / DZ_NSH) & 1);
       mbar_wait(bar(Z_WFULL + sw), (u / DZ_NSW) & 1);
       mbar_wait(bar(Z_SEMPTY + sb), ((u >> 1) & 1) ^ 1);
       tc_fence_after();
       {
-        const uint32_t a0 = base + DZ_SM_A + (pair & 1) * DZ_A, bh = base + DZ_SM_H + sh * (CN * 128), bw = base + DZ_SM_W + sw * DZ_WSLOT,
-                       dl = base + DZ_SM_DL;
-        const uint32_t dS = tmem + ZT_S + sb * CN, dA = tmem + ZT_DA + sb * CN;
+        const uint32_t a0 = base + DZ_SM_A + (pair & 1) * DZ_A, bh = base + DZ_SM_H + sh * (CN * 128), bw = base + DZ_SM_W + sw * DZ_WSLOT;
+        const uint32_t dS = tmem + ZT_S + sb * CN, dA = tmem + ZT_DA + sb * CN, tdl = tmem + ZT_DL;
         mma_f16(dS, desc_noswz(a0 + TILE_M * 128, NORM_LBO, NORM_SBO), desc_noswz(bw, NORM_LBO, NORM_SBO), ID, 0);
 #pragma unroll
         for (int k = 0; k < 4; ++k) mma_f16(dS, desc_sw128(a0 + 32 * k), desc_sw128(bh + 32 * k), ID, 1);
 #pragma unroll
         for (int k = 0; k < KPW / 16; ++k)
-          mma_f16(dA, desc_sw128(dl + (k >> 2) * (TILE_M * 128) + 32 * (k & 3)), desc_sw128(bw + 2048 + (k >> 2) * (CN * 128) + 32 * (k & 3)),
-                  ID, k);
+          mma_f16_ts(dA, tdl + 8 * k, desc_sw128(bw + 2048 + (k >> 2) * (CN * 128) + 32 * (k & 3)), ID, k);
         mma_commit(bar(Z_SFULL + sb));
         mma_commit(bar(Z_HEMPTY + sh));
         mma_commit(bar(Z_WEMPTY + sw));
         if (last_of_scale(c)) mma_commit(bar(Z_AEMPTY + (pair & 1)));
-        if (c == NC - 1) mma_commit(bar(Z_DLEMPTY));
+        if (c == NC - 1) mma_commit(bar(Z_DLTEMPTY));
       }
       __syncwarp();
       if (++c == NC) { c = 0; ++ti; }
+    }
+  } else if (warp >= 12) {
+    // ================= dlogits tile: landing buffer -> TMEM (one row per thread) =================
+    const int q = warp - 12, m = q * 32 + lane;
+    const uint32_t lane_base = ((uint32_t)(q * 32)) << 16;
+    for (int ti = 0; ti < my_tiles; ++ti) {
+      mbar_wait(bar(Z_DLFULL), ti & 1);
+      mbar_wait(bar(Z_DLTEMPTY), (ti & 1) ^ 1);                   // the dA GEMMs of the previous tile have read the TMEM copy
+      tc_fence_after();
+#pragma unroll 1
+      for (int t = 0; t < 3; ++t) {
+        uint32_t v[32];
+        const uint4* row = reinterpret_cast<const uint4*>(gbase + DZ_SM_DL + t * (TILE_M * 128) + m * 128);
+#pragma unroll
+        for (int cc = 0; cc < 8; ++cc) {
+          const uint4 w = row[cc ^ (m & 7)];
+          v[4 * cc] = w.x; v[4 * cc + 1] = w.y; v[4 * cc + 2] = w.z; v[4 * cc + 3] = w.w;
+        }
+        tmem_st32(tmem + lane_base + ZT_DL + 32 * t, v);
+      }
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(Z_DLEMPTY));                // the next tile's dlogits may land (a whole tile ahead of their use)
+      tmem_st_wait();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(bar(Z_DLTFULL));
     }
   } else if (warp == 11) {
     // ================= issuer 2: dz_s += gamma . (-2 p) =================
