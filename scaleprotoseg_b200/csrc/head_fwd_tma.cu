@@ -586,9 +586,17 @@ __global__ void __launch_bounds__(n_threads(NSETS), 1) head_fwd_tma_kernel(const
             float* abase = prm.act + n_first * (long long)s.P + p0 + lane;
             const int rows = lim - q * 32 < 32 ? lim - q * 32 : 32;
             if (lane < ncols) {
-#pragma unroll 8
-              for (int rr = 0; rr < 32; ++rr)
-                if (rr < rows) abase[(long long)rr * s.P] = scr[rr * 33 + lane];
+              if (rows == 32) {   // the common case without a test per row (it compiled to a branch + reconvergence point each)
+                const size_t pitch = (size_t)s.P;
+                float* ap = abase;
+#pragma unroll
+                for (int rr = 0; rr < 32; ++rr) {
+                  *ap = scr[rr * 33 + lane];
+                  ap += pitch;
+                }
+              } else {
+                for (int rr = 0; rr < rows; ++rr) abase[(long long)rr * s.P] = scr[rr * 33 + lane];
+              }
             }
           }
         }
