@@ -112,7 +112,16 @@ __global__ void __launch_bounds__(256) bwd_prep_kernel(const __grid_constant__ C
     scan(ddist, dd_count);
 #pragma unroll
     for (int o = 16; o >= 1; o >>= 1) m = fmaxf(m, __shfl_xor_sync(0xffffffffu, m, o));
-    if ((threadIdx.x & 31) == 0 && m > 0.f) atomicMax(amax_out, __float_as_uint(m));
+    // one atomic per BLOCK: the main kernel's prologue waits for this pre-pass, so it runs on many small blocks (a block
+    // scans a few KB in one or two rounds of loads), and their atomics all hit one address
+    __shared__ float wmax[8];
+    if ((threadIdx.x & 31) == 0) wmax[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+      for (int w = 1; w < 8; ++w) m = fmaxf(m, wmax[w]);
+      if (m > 0.f) atomicMax(amax_out, __float_as_uint(m));
+    }
     return;
   }
   const int c = blockIdx.x, t = threadIdx.x;
@@ -1010,7 +1019,7 @@ static int launch_bwd_slab(const HeadShape& s, int zmode, const void* z, const v
   }
   // one launch: chunk images (n_chunks blocks) + max |dlogits| (the remaining blocks)
   // (the amax blocks also scan the dense ddist map when there is one: enough of them to stream it at HBM rate)
-  const int amax_blocks = sm_count() * (ddist != nullptr ? 16 : 1);
+  const int amax_blocks = sm_count() * (ddist != nullptr ? 16 : 4);
   tcb::bwd_prep_kernel<X, NSPLIT><<<prm.ct.n_chunks + amax_blocks, 256, 0, st>>>(prm.ct, s.D, s.P, s.K, protos, last_w, img, dl_all,
                                                                                 dl_all_count, ddist,
                                                                                 (long long)s.N * s.P, amax);
